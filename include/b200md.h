@@ -1,0 +1,224 @@
+/* b200md.h — C ABI of libb200md.so, the B200-native (sm_100a) short-range MD hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.  A LAMMPS
+ * suffix style (`lj/cut/b200`, `eam/b200`, `eam/alloy/b200`, `nve/b200`, `verlet/b200`; see
+ * INTEGRATION.md) binds these exactly as the reference's GPU package binds its
+ * `ljl_gpu_init / ljl_gpu_compute_n / ljl_gpu_clear` layer
+ * (/root/reference/src/GPU/pair_lj_cut_gpu.cpp:36-54).
+ *
+ * Conventions
+ *   - every call returns 0 on success, non-zero on failure; b200md_last_error() holds the
+ *     message (the reference's Error::all/one text where one exists, src/error.cpp).
+ *   - host pointers are borrowed for the duration of the call only; the context owns all
+ *     device memory and its stream.
+ *   - per-type tables are 1-based and contiguous, `(ntypes+1)*(ntypes+1)` doubles, like the
+ *     reference's `memory->create(cutsq,n+1,n+1)` blocks (src/memory.h:144-160).
+ *   - atom arrays on the host side are the reference's AoS `double x[n][3]`, `int type[n]`,
+ *     `tagint tag[n]` (32-bit, LAMMPS_SMALLBIG, src/lmptype.h:90-92), `imageint image[n]`.
+ *   - there is no CPU fallback: every compute entry point fails with
+ *     "b200md: no CUDA device" when no sm_100 device is usable.
+ */
+#ifndef B200MD_H
+#define B200MD_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200md_ctx b200md_ctx;
+
+#define B200MD_OK 0
+#define B200MD_ERR 1
+
+/* neighbor list kinds (reference: NeighRequest half/full, src/neigh_request.h:21-135) */
+#define B200MD_LIST_FULL 0        /* NPairFullBinAtomonly, src/npair_full_bin_atomonly.cpp:32-92 */
+#define B200MD_LIST_HALF_NEWTON 1 /* NPairHalfBinAtomonlyNewton, src/npair_half_bin_atomonly_newton.cpp:33-113 */
+
+/* pair styles */
+#define B200MD_PAIR_NONE 0
+#define B200MD_PAIR_LJ_CUT 1 /* src/pair_lj_cut.cpp */
+#define B200MD_PAIR_EAM 2    /* src/MANYBODY/pair_eam.cpp, pair_eam_alloy.cpp (same compute) */
+
+const char *b200md_last_error(void);
+const char *b200md_version(void);
+
+/* ---- host-only helpers (no GPU needed) ------------------------------------------------ */
+
+/* ProcMap::onelevel_grid + best_factors (src/procmap.cpp:46-132, 853-895): factor nranks
+ * into px*py*pz minimising sub-domain surface for box lengths prd[3]. */
+int b200md_procgrid(int nranks, const double prd[3], int procgrid[3]);
+/* rank -> grid location, row-major like MPI_Cart_create without reorder (x slowest). */
+int b200md_rank2loc(int rank, const int procgrid[3], int myloc[3]);
+/* Domain::set_local_box (src/domain.cpp:335-357), uniform splits. */
+int b200md_local_box(const double boxlo[3], const double boxhi[3], const int procgrid[3],
+                     const int myloc[3], double sublo[3], double subhi[3]);
+
+/* CommBrick::setup swap schedule (src/comm_brick.cpp:191-483), SINGLE mode, orthogonal box.
+ * Arrays have room for B200MD_MAXSWAP entries. */
+#define B200MD_MAXSWAP 64
+typedef struct b200md_swap_schedule {
+  int nswap;
+  int maxneed[3];
+  int dim[B200MD_MAXSWAP];       /* 0,1,2 */
+  int ineed[B200MD_MAXSWAP];     /* index within the dim (even: send to -dim side) */
+  int sendflag[B200MD_MAXSWAP];  /* ineed/2 < sendneed[dim][ineed%2] */
+  int sendproc[B200MD_MAXSWAP];
+  int recvproc[B200MD_MAXSWAP];
+  int pbc[B200MD_MAXSWAP][3];    /* periodic shift multiples applied by pack_border/pack_comm */
+  double slablo[B200MD_MAXSWAP];
+  double slabhi[B200MD_MAXSWAP];
+} b200md_swap_schedule;
+int b200md_comm_schedule(const double boxlo[3], const double boxhi[3], const int periodic[3],
+                         const int procgrid[3], const int myloc[3], double cutghost,
+                         b200md_swap_schedule *out);
+
+/* NBinStandard::setup_bins (src/nbin_standard.cpp:82-214) + NStencil::create_setup
+ * (src/nstencil.cpp:213-247): the reference's bin geometry for a sub-box. */
+typedef struct b200md_bin_geometry {
+  int nbinx, nbiny, nbinz;       /* global bins */
+  int mbinx, mbiny, mbinz;       /* local bins incl. ghost layers */
+  int mbinxlo, mbinylo, mbinzlo;
+  int sx, sy, sz;                /* stencil half-extent */
+  double binsizex, binsizey, binsizez;
+  double bininvx, bininvy, bininvz;
+} b200md_bin_geometry;
+int b200md_bin_setup(const double boxlo[3], const double boxhi[3], const double sublo[3],
+                     const double subhi[3], double cutghost, double cutneighmax,
+                     b200md_bin_geometry *out);
+
+/* fcc lattice + `velocity all create T seed loop geom` (src/create_atoms.cpp:1301-1370,
+ * src/lattice.cpp:469-486, src/velocity.cpp:160-372, src/random_park.cpp:86-124) restricted
+ * to what bench/in.lj and bench/in.eam use: `lattice fcc`, `region box block 0 nx 0 ny 0 nz`,
+ * one type, dist uniform, mom yes, rot no.  `scale` is the lattice constant in box units
+ * (lj: (4/rho*)^(1/3); metal: a).  Generates only the atoms inside [sublo,subhi).
+ * Pass x=NULL to count.  Velocities are the un-scaled, un-zeroed draws; use
+ * b200md_velocity_finalize after set_atoms (momentum zeroing and rescaling are global). */
+int b200md_lattice_fcc(double scale, int nx, int ny, int nz, const double sublo[3],
+                       const double subhi[3], int seed, double mass, int *natoms_out,
+                       double *x_aos, double *v_aos, int *tag);
+
+/* ---- context ------------------------------------------------------------------------- */
+
+int b200md_create(int device, int rank, int nranks, b200md_ctx **out);
+int b200md_destroy(b200md_ctx *ctx);
+
+/* 128-byte NCCL unique id: rank 0 obtains it, the launcher broadcasts it (torch.distributed /
+ * MPI), every rank then calls b200md_comm_init.  nranks==1 needs neither. */
+int b200md_comm_unique_id(void *id128);
+int b200md_comm_init(b200md_ctx *ctx, const void *id128);
+
+/* unit constants (src/update.cpp:145-200): boltz, mvv2e, ftm2v, nktv2p */
+int b200md_set_units(b200md_ctx *ctx, double boltz, double mvv2e, double ftm2v, double nktv2p);
+
+/* Domain + Comm::set_procs: global box, periodicity, process grid (b200md_procgrid).  Computes
+ * myloc / sub-box like the reference. */
+int b200md_set_box(b200md_ctx *ctx, const double boxlo[3], const double boxhi[3],
+                   const int periodic[3], const int procgrid[3]);
+int b200md_get_subbox(b200md_ctx *ctx, double sublo[3], double subhi[3]);
+
+/* Upload owned atoms (AtomVecAtomic fields, src/atom_vec_atomic.cpp).  mass is 1-based
+ * [ntypes+1].  image may be NULL (all zero = (512,512,512) packed like Domain). */
+int b200md_set_atoms(b200md_ctx *ctx, int nlocal, const double *x_aos, const double *v_aos,
+                     const int *type, const int *tag, const int *image, int ntypes,
+                     const double *mass);
+/* Download owned atoms in current local order.  Any pointer may be NULL. */
+int b200md_get_nlocal(b200md_ctx *ctx, int *nlocal, int *nghost);
+int b200md_get_atoms(b200md_ctx *ctx, double *x_aos, double *v_aos, double *f_aos, int *type,
+                     int *tag, int *image);
+/* ghost atoms (x with periodic shift applied, tag, type) in local order nlocal..nall-1 */
+int b200md_get_ghosts(b200md_ctx *ctx, double *x_aos, int *type, int *tag);
+
+/* Velocity::zero_momentum + Velocity::rescale (src/velocity.cpp:358-368, 663-700 region):
+ * global over all ranks. */
+int b200md_velocity_finalize(b200md_ctx *ctx, double t_desired, int zero_momentum);
+
+/* ---- neighbor ------------------------------------------------------------------------ */
+
+/* Neighbor::init cutoffs (src/neighbor.cpp:348-388) + neigh_modify every/delay/check
+ * (src/neighbor.cpp:2622-…).  cutneighsq is (ntypes+1)^2.  list_kind = B200MD_LIST_*. */
+int b200md_neigh_config(b200md_ctx *ctx, int ntypes, const double *cutneighsq,
+                        double cutneighmax, double skin, int every, int delay, int check,
+                        int list_kind);
+/* Neighbor::decide (src/neighbor.cpp:2309-2324) incl. check_distance (:2338-2390). */
+int b200md_neigh_decide(b200md_ctx *ctx, int *rebuild);
+/* The reneighbor branch of Verlet::run (src/verlet.cpp:289-307): Domain::pbc, Comm::exchange,
+ * spatial sort, Comm::borders, Neighbor::build (bin_atoms + NPair::build). */
+int b200md_neigh_build(b200md_ctx *ctx);
+/* non-reneighbor branch: Comm::forward_comm (src/comm_brick.cpp:538-591). */
+int b200md_forward_comm(b200md_ctx *ctx);
+/* Export the list for parity checks.  numneigh[nlocal]; neigh_flat receives, atom after
+ * atom, the neighbors as local indices (by_tag=0) or as tags (by_tag=1), unsorted.
+ * Pass neigh_flat=NULL to obtain only numneigh and *total. */
+int b200md_neigh_export(b200md_ctx *ctx, int by_tag, int *numneigh, int *neigh_flat,
+                        long long *total);
+int b200md_neigh_stats(b200md_ctx *ctx, long long *nbuilds, long long *ndanger,
+                       long long *total_neighbors, int *maxneigh_pitch);
+
+/* ---- pair ---------------------------------------------------------------------------- */
+
+/* PairLJCut::init_one products (src/pair_lj_cut.cpp:501-556): all (ntypes+1)^2, 1-based. */
+int b200md_pair_lj_cut_config(b200md_ctx *ctx, int ntypes, const double *cutsq,
+                              const double *lj1, const double *lj2, const double *lj3,
+                              const double *lj4, const double *offset);
+/* PairEAM::array2spline products (src/MANYBODY/pair_eam.cpp:744-797).  Splines are the
+ * reference's `[ntable][n+1][7]` blocks (row 0 unused, 1-based rows); type2* are 1-based
+ * `[ntypes+1]` / `[(ntypes+1)^2]` maps. */
+int b200md_pair_eam_config(b200md_ctx *ctx, int ntypes, int nrho, int nr, double rdr,
+                           double rdrho, double rhomax, double cutforcesq, int nfrho,
+                           const double *frho_spline, int nrhor, const double *rhor_spline,
+                           int nz2r, const double *z2r_spline, const int *type2frho,
+                           const int *type2rhor, const int *type2z2r, const double *scale);
+/* Pair::compute(eflag,vflag) (src/pair_lj_cut.cpp:69-137, src/MANYBODY/pair_eam.cpp:142-328);
+ * includes Verlet::force_clear (fused) and, for EAM, the fp forward_comm
+ * (pair_eam.cpp:251).  eng_vdwl / virial[6] (xx,yy,zz,xy,xz,yz) are this rank's
+ * contributions, written only when the corresponding flag is set. */
+int b200md_pair_compute(b200md_ctx *ctx, int eflag, int vflag, double *eng_vdwl,
+                        double virial[6]);
+/* Comm::reverse_comm of forces (src/comm_brick.cpp:598-639); no-op for full lists. */
+int b200md_reverse_comm(b200md_ctx *ctx);
+
+/* ---- fix nve + thermo ---------------------------------------------------------------- */
+
+/* FixNVE::initial_integrate / final_integrate (src/fix_nve.cpp:64-141). dtf = 0.5*dt*ftm2v. */
+int b200md_nve_initial(b200md_ctx *ctx, double dtv, double dtf);
+int b200md_nve_final(b200md_ctx *ctx, double dtf);
+/* ComputeTemp / ComputePE / ComputePressure scalars (src/compute_temp.cpp:72-99,
+ * src/compute_pe.cpp:84-112, src/compute_pressure.cpp:228-262), summed over ranks.
+ * Requires that the last pair_compute ran with eflag=vflag=1. */
+typedef struct b200md_thermo {
+  long long step;
+  double natoms;
+  double temp, pe, ke, press; /* pe, ke extensive (not divided by N) */
+  double virial[6];
+} b200md_thermo;
+int b200md_thermo_compute(b200md_ctx *ctx, b200md_thermo *out);
+
+/* ---- whole loop ---------------------------------------------------------------------- */
+
+/* Verlet::setup (src/verlet.cpp:93-162): initial build + force evaluation with energy/virial. */
+int b200md_setup(b200md_ctx *ctx);
+/* Verlet::run(nsteps) (src/verlet.cpp:229-360) with fix nve, thermo every `thermo_every`
+ * steps (0: only last step).  thermo_out (may be NULL) receives up to max_thermo records
+ * (the step-0 record is produced by b200md_setup + b200md_thermo_compute). */
+int b200md_run(b200md_ctx *ctx, int nsteps, double dt, int thermo_every,
+               b200md_thermo *thermo_out, int max_thermo, int *n_thermo);
+
+/* timing / counters of the last b200md_run (device time by CUDA events on the context's
+ * stream, ms): total, pair, neigh(build incl. sort/borders), comm, modify(nve); kernel
+ * launches issued. */
+typedef struct b200md_timing {
+  double total_ms, pair_ms, neigh_ms, comm_ms, modify_ms;
+  long long launches;
+  long long pair_launches;
+  int nbuilds;
+} b200md_timing;
+int b200md_get_timing(b200md_ctx *ctx, b200md_timing *out);
+/* tuning knob: lanes cooperating on one atom in the pair/neighbor kernels (4,8,16,32). */
+int b200md_set_lanes_per_atom(b200md_ctx *ctx, int lanes);
+/* cudaStream_t of the context (as void*), for callers that time with their own events. */
+int b200md_get_stream(b200md_ctx *ctx, void **stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

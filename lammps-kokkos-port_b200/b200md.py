@@ -1,0 +1,362 @@
+"""ctypes binding of libb200md.so (include/b200md.h) plus a thin host-side driver that mirrors
+the reference's input-script vocabulary for the hot path (units / lattice / region /
+create_atoms / mass / velocity / pair_style / pair_coeff / neighbor / neigh_modify / fix nve /
+run), i.e. what `bench/in.lj` and `bench/in.eam` (/root/reference/bench) set up.
+
+PyTorch is not needed here; torch.distributed is used by callers only to ship the NCCL
+unique id between ranks.  There is no CPU fallback: every compute call goes to the CUDA
+library and raises B200MDError (with the library's message) when it fails.
+"""
+import ctypes as C
+import math
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200md.so")
+
+LIST_FULL, LIST_HALF_NEWTON = 0, 1
+MAXSWAP = 64
+
+
+class B200MDError(RuntimeError):
+    pass
+
+
+class SwapSchedule(C.Structure):
+    _fields_ = [("nswap", C.c_int), ("maxneed", C.c_int * 3), ("dim", C.c_int * MAXSWAP),
+                ("ineed", C.c_int * MAXSWAP), ("sendflag", C.c_int * MAXSWAP),
+                ("sendproc", C.c_int * MAXSWAP), ("recvproc", C.c_int * MAXSWAP),
+                ("pbc", (C.c_int * 3) * MAXSWAP), ("slablo", C.c_double * MAXSWAP),
+                ("slabhi", C.c_double * MAXSWAP)]
+
+
+class BinGeometry(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("nbinx", "nbiny", "nbinz", "mbinx", "mbiny", "mbinz", "mbinxlo",
+                                        "mbinylo", "mbinzlo", "sx", "sy", "sz")] + \
+               [(n, C.c_double) for n in ("binsizex", "binsizey", "binsizez", "bininvx", "bininvy", "bininvz")]
+
+
+class Thermo(C.Structure):
+    _fields_ = [("step", C.c_longlong), ("natoms", C.c_double), ("temp", C.c_double), ("pe", C.c_double),
+                ("ke", C.c_double), ("press", C.c_double), ("virial", C.c_double * 6)]
+
+    def as_dict(self):
+        return dict(step=self.step, natoms=self.natoms, temp=self.temp, pe=self.pe, ke=self.ke,
+                    press=self.press, virial=list(self.virial))
+
+
+class Timing(C.Structure):
+    _fields_ = [("total_ms", C.c_double), ("pair_ms", C.c_double), ("neigh_ms", C.c_double),
+                ("comm_ms", C.c_double), ("modify_ms", C.c_double), ("launches", C.c_longlong),
+                ("pair_launches", C.c_longlong), ("nbuilds", C.c_int)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libb200md.so (built in-tree by __graft_entry__.build()); fail loudly if absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise B200MDError("libb200md.so is not built (%s); run __graft_entry__.build()" % LIB_PATH)
+        _lib = C.CDLL(LIB_PATH)
+        _lib.b200md_last_error.restype = C.c_char_p
+        _lib.b200md_version.restype = C.c_char_p
+    return _lib
+
+
+def _chk(rc):
+    if rc != 0:
+        raise B200MDError(lib().b200md_last_error().decode())
+
+
+def _d(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _d3(v):
+    return (C.c_double * 3)(*[float(x) for x in v])
+
+
+def _i3(v):
+    return (C.c_int * 3)(*[int(x) for x in v])
+
+
+# ---- host-only helpers -------------------------------------------------------------------
+def procgrid(nranks, prd):
+    out = (C.c_int * 3)()
+    _chk(lib().b200md_procgrid(int(nranks), _d3(prd), out))
+    return list(out)
+
+
+def rank2loc(rank, grid):
+    out = (C.c_int * 3)()
+    _chk(lib().b200md_rank2loc(int(rank), _i3(grid), out))
+    return list(out)
+
+
+def local_box(boxlo, boxhi, grid, myloc):
+    lo, hi = (C.c_double * 3)(), (C.c_double * 3)()
+    _chk(lib().b200md_local_box(_d3(boxlo), _d3(boxhi), _i3(grid), _i3(myloc), lo, hi))
+    return list(lo), list(hi)
+
+
+def comm_schedule(boxlo, boxhi, periodic, grid, myloc, cutghost):
+    s = SwapSchedule()
+    _chk(lib().b200md_comm_schedule(_d3(boxlo), _d3(boxhi), _i3(periodic), _i3(grid), _i3(myloc),
+                                    C.c_double(cutghost), C.byref(s)))
+    return s
+
+
+def bin_setup(boxlo, boxhi, sublo, subhi, cutghost, cutneighmax):
+    g = BinGeometry()
+    _chk(lib().b200md_bin_setup(_d3(boxlo), _d3(boxhi), _d3(sublo), _d3(subhi), C.c_double(cutghost),
+                                C.c_double(cutneighmax), C.byref(g)))
+    return g
+
+
+def lattice_fcc(scale, nx, ny, nz, sublo, subhi, seed, mass):
+    """Atoms of `lattice fcc` + `create_atoms 1 box` inside [sublo,subhi) with the raw
+    `velocity ... loop geom` draws (host.cpp)."""
+    n = C.c_int(0)
+    L = lib()
+    _chk(L.b200md_lattice_fcc(C.c_double(scale), nx, ny, nz, _d3(sublo), _d3(subhi), int(seed), C.c_double(mass),
+                              C.byref(n), None, None, None))
+    x = np.empty((n.value, 3)); v = np.empty((n.value, 3)); tag = np.empty(n.value, dtype=np.int32)
+    _chk(L.b200md_lattice_fcc(C.c_double(scale), nx, ny, nz, _d3(sublo), _d3(subhi), int(seed), C.c_double(mass),
+                              C.byref(n), _p(x), _p(v), _p(tag)))
+    return x, v, tag
+
+
+# ---- unit systems (src/update.cpp:145-200) ---------------------------------------------------
+UNITS = {
+    "lj": dict(boltz=1.0, mvv2e=1.0, ftm2v=1.0, nktv2p=1.0, dt=0.005, skin=0.3),
+    "metal": dict(boltz=8.617343e-5, mvv2e=1.0364269e-4, ftm2v=1.0 / 1.0364269e-4, nktv2p=1.6021765e6,
+                  dt=0.001, skin=2.0),
+}
+
+
+class Context:
+    """One b200md_ctx (one GPU, one rank)."""
+
+    def __init__(self, device=0, rank=0, nranks=1):
+        self.L = lib()
+        self.h = C.c_void_p()
+        _chk(self.L.b200md_create(int(device), int(rank), int(nranks), C.byref(self.h)))
+        self.rank, self.nranks = rank, nranks
+        self.ntypes = 0
+
+    def close(self):
+        if self.h:
+            self.L.b200md_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # comm
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(128)
+        _chk(lib().b200md_comm_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, id128):
+        _chk(self.L.b200md_comm_init(self.h, C.c_char_p(id128)))
+
+    def set_units(self, name):
+        u = UNITS[name]
+        _chk(self.L.b200md_set_units(self.h, C.c_double(u["boltz"]), C.c_double(u["mvv2e"]), C.c_double(u["ftm2v"]),
+                                     C.c_double(u["nktv2p"])))
+        self.units = u
+
+    def set_box(self, boxlo, boxhi, periodic=(1, 1, 1), grid=(1, 1, 1)):
+        _chk(self.L.b200md_set_box(self.h, _d3(boxlo), _d3(boxhi), _i3(periodic), _i3(grid)))
+
+    def subbox(self):
+        lo, hi = (C.c_double * 3)(), (C.c_double * 3)()
+        _chk(self.L.b200md_get_subbox(self.h, lo, hi))
+        return list(lo), list(hi)
+
+    def set_atoms(self, x, v, type_, tag, mass, image=None):
+        x = _d(x); n = x.shape[0]
+        v = _d(v) if v is not None else None
+        type_ = _i(type_); tag = _i(tag)
+        mass = _d(mass)
+        self.ntypes = mass.shape[0] - 1
+        image = _i(image) if image is not None else None
+        _chk(self.L.b200md_set_atoms(self.h, n, _p(x), _p(v), _p(type_), _p(tag), _p(image), self.ntypes, _p(mass)))
+
+    def nlocal(self):
+        a, b = C.c_int(), C.c_int()
+        _chk(self.L.b200md_get_nlocal(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def get_atoms(self, fields=("x", "v", "f", "type", "tag", "image")):
+        n, _ = self.nlocal()
+        out = {}
+        arr = dict(x=np.empty((n, 3)), v=np.empty((n, 3)), f=np.empty((n, 3)), type=np.empty(n, np.int32),
+                   tag=np.empty(n, np.int32), image=np.empty(n, np.int32))
+        g = lambda k: _p(arr[k]) if k in fields else None
+        _chk(self.L.b200md_get_atoms(self.h, g("x"), g("v"), g("f"), g("type"), g("tag"), g("image")))
+        for k in fields:
+            out[k] = arr[k]
+        return out
+
+    def get_ghosts(self):
+        _, n = self.nlocal()
+        x = np.empty((n, 3)); t = np.empty(n, np.int32); tag = np.empty(n, np.int32)
+        _chk(self.L.b200md_get_ghosts(self.h, _p(x), _p(t), _p(tag)))
+        return dict(x=x, type=t, tag=tag)
+
+    def velocity_finalize(self, t_desired, zero_momentum=True):
+        _chk(self.L.b200md_velocity_finalize(self.h, C.c_double(t_desired), int(zero_momentum)))
+
+    # neighbor
+    def neigh_config(self, cutneighsq, cutneighmax, skin, every=1, delay=0, check=1, list_kind=LIST_FULL):
+        cn = _d(cutneighsq)
+        _chk(self.L.b200md_neigh_config(self.h, self.ntypes, _p(cn), C.c_double(cutneighmax), C.c_double(skin),
+                                        int(every), int(delay), int(check), int(list_kind)))
+
+    def neigh_decide(self):
+        r = C.c_int()
+        _chk(self.L.b200md_neigh_decide(self.h, C.byref(r)))
+        return r.value
+
+    def neigh_build(self):
+        _chk(self.L.b200md_neigh_build(self.h))
+
+    def forward_comm(self):
+        _chk(self.L.b200md_forward_comm(self.h))
+
+    def reverse_comm(self):
+        _chk(self.L.b200md_reverse_comm(self.h))
+
+    def neigh_export(self, by_tag=True):
+        n, _ = self.nlocal()
+        nn = np.empty(n, np.int32)
+        tot = C.c_longlong()
+        _chk(self.L.b200md_neigh_export(self.h, int(by_tag), _p(nn), None, C.byref(tot)))
+        flat = np.empty(tot.value, np.int32)
+        _chk(self.L.b200md_neigh_export(self.h, int(by_tag), _p(nn), _p(flat), C.byref(tot)))
+        return nn, flat
+
+    def neigh_stats(self):
+        a, b, t, p = C.c_longlong(), C.c_longlong(), C.c_longlong(), C.c_int()
+        _chk(self.L.b200md_neigh_stats(self.h, C.byref(a), C.byref(b), C.byref(t), C.byref(p)))
+        return dict(nbuilds=a.value, ndanger=b.value, total=t.value, pitch=p.value)
+
+    def set_lanes_per_atom(self, n):
+        _chk(self.L.b200md_set_lanes_per_atom(self.h, int(n)))
+
+    # pair
+    def pair_lj_cut_config(self, cutsq, lj1, lj2, lj3, lj4, offset):
+        a = [_d(t) for t in (cutsq, lj1, lj2, lj3, lj4, offset)]
+        _chk(self.L.b200md_pair_lj_cut_config(self.h, self.ntypes, *[_p(t) for t in a]))
+
+    def pair_eam_config(self, tb):
+        """tb: dict with the PairEAM spline tables (see eam_host.py)."""
+        fr, rr, zr = _d(tb["frho_spline"]), _d(tb["rhor_spline"]), _d(tb["z2r_spline"])
+        t2f, t2r, t2z = _i(tb["type2frho"]), _i(tb["type2rhor"]), _i(tb["type2z2r"])
+        sc = _d(tb["scale"])
+        _chk(self.L.b200md_pair_eam_config(self.h, self.ntypes, int(tb["nrho"]), int(tb["nr"]), C.c_double(tb["rdr"]),
+                                           C.c_double(tb["rdrho"]), C.c_double(tb["rhomax"]),
+                                           C.c_double(tb["cutforcesq"]), fr.shape[0], _p(fr), rr.shape[0], _p(rr),
+                                           zr.shape[0], _p(zr), _p(t2f), _p(t2r), _p(t2z), _p(sc)))
+
+    def pair_compute(self, eflag=1, vflag=1):
+        e = C.c_double(); vir = (C.c_double * 6)()
+        _chk(self.L.b200md_pair_compute(self.h, int(eflag), int(vflag), C.byref(e), vir))
+        return e.value, list(vir)
+
+    # fix nve / thermo / loop
+    def nve_initial(self, dtv, dtf):
+        _chk(self.L.b200md_nve_initial(self.h, C.c_double(dtv), C.c_double(dtf)))
+
+    def nve_final(self, dtf):
+        _chk(self.L.b200md_nve_final(self.h, C.c_double(dtf)))
+
+    def thermo(self):
+        t = Thermo()
+        _chk(self.L.b200md_thermo_compute(self.h, C.byref(t)))
+        return t.as_dict()
+
+    def setup(self):
+        _chk(self.L.b200md_setup(self.h))
+
+    def run(self, nsteps, dt, thermo_every=0):
+        cap = (nsteps // thermo_every + 2) if thermo_every > 0 else 2
+        arr = (Thermo * cap)()
+        n = C.c_int()
+        _chk(self.L.b200md_run(self.h, int(nsteps), C.c_double(dt), int(thermo_every), arr, cap, C.byref(n)))
+        return [arr[k].as_dict() for k in range(n.value)]
+
+    def timing(self):
+        t = Timing()
+        _chk(self.L.b200md_get_timing(self.h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in Timing._fields_}
+
+    def stream(self):
+        s = C.c_void_p()
+        _chk(self.L.b200md_get_stream(self.h, C.byref(s)))
+        return s.value
+
+
+# ---- PairLJCut host side (src/pair_lj_cut.cpp:442-556, src/pair.cpp:705-733) -------------------
+def lj_cut_tables(ntypes, coeffs, cut_global, mix="geometric", shift=False):
+    """coeffs: {(i,j): (epsilon, sigma[, cut])} for i<=j as given by pair_coeff; missing i<j pairs
+    are mixed like Pair::mix_energy / mix_distance.  Returns 1-based (ntypes+1)^2 tables."""
+    n1 = ntypes + 1
+    eps = np.zeros((n1, n1)); sig = np.zeros((n1, n1)); cut = np.zeros((n1, n1)); setf = np.zeros((n1, n1), bool)
+    for (i, j), c in coeffs.items():
+        eps[i, j], sig[i, j] = c[0], c[1]
+        cut[i, j] = c[2] if len(c) > 2 else cut_global
+        setf[i, j] = True
+    T = {k: np.zeros((n1, n1)) for k in ("cutsq", "lj1", "lj2", "lj3", "lj4", "offset")}
+    for i in range(1, n1):
+        for j in range(i, n1):
+            if not setf[i, j]:
+                if not (setf[i, i] and setf[j, j]):
+                    raise B200MDError("All pair coeffs are not set")
+                if mix == "geometric":
+                    eps[i, j] = math.sqrt(eps[i, i] * eps[j, j]); sig[i, j] = math.sqrt(sig[i, i] * sig[j, j])
+                elif mix == "arithmetic":
+                    eps[i, j] = math.sqrt(eps[i, i] * eps[j, j]); sig[i, j] = 0.5 * (sig[i, i] + sig[j, j])
+                else:
+                    raise B200MDError("unsupported pair_modify mix " + mix)
+                cut[i, j] = max(cut[i, i], cut[j, j])
+            e, s, c = eps[i, j], sig[i, j], cut[i, j]
+            v = dict(cutsq=c * c, lj1=48.0 * e * s ** 12, lj2=24.0 * e * s ** 6, lj3=4.0 * e * s ** 12,
+                     lj4=4.0 * e * s ** 6, offset=0.0)
+            if shift and c > 0.0:
+                ratio = s / c
+                v["offset"] = 4.0 * e * (ratio ** 12 - ratio ** 6)
+            for k in T:
+                T[k][i, j] = T[k][j, i] = v[k]
+    return T
+
+
+def cutneighsq_table(ntypes, cutsq, skin):
+    """Neighbor::init (src/neighbor.cpp:348-388): cutneighsq = (sqrt(cutsq)+skin)^2."""
+    n1 = ntypes + 1
+    out = np.zeros((n1, n1)); cmax = 0.0
+    for i in range(1, n1):
+        for j in range(1, n1):
+            c = math.sqrt(cutsq[i, j]) + skin
+            out[i, j] = c * c
+            cmax = max(cmax, c)
+    return out, cmax

@@ -1,0 +1,546 @@
+// api.cu — the extern "C" entry points of include/b200md.h (context, atoms, neighbor
+// schedule, thermo, whole-loop driver).  Kernels live in neigh.cu / comm.cu / pair_*.cu /
+// nve.cu; host-only geometry in host.cpp.
+//
+// Step order follows Verlet::setup (/root/reference/src/verlet.cpp:93-162) and Verlet::run
+// (:229-360); the rebuild decision follows Neighbor::decide/check_distance
+// (src/neighbor.cpp:2309-2390).
+#include <math.h>
+#include <string.h>
+#include "ctx.h"
+
+int vel_adjust(b200md_ctx *c, double sx, double sy, double sz, double factor);  // nve.cu
+int pair_eam_config_impl(b200md_ctx *c, int ntypes, int nrho, int nr, double rdr, double rdrho, double rhomax,
+                         double cutforcesq, int nfrho, const double *frho_spline, int nrhor,
+                         const double *rhor_spline, int nz2r, const double *z2r_spline, const int *type2frho,
+                         const int *type2rhor, const int *type2z2r, const double *scale);  // pair_eam.cu
+void pair_eam_free(b200md_ctx *c);
+
+static thread_local std::string g_error;
+void b200md_set_error(const std::string &msg) { g_error = msg; }
+extern "C" const char *b200md_last_error(void) { return g_error.c_str(); }
+extern "C" const char *b200md_version(void) { return "b200md 0.1 (sm_100a)"; }
+
+#define NEED(cond, msg) do { if (!(cond)) { b200md_set_error(msg); return B200MD_ERR; } } while (0)
+
+extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out) {
+  NEED(out, "b200md: null output pointer");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    b200md_set_error("b200md: no CUDA device (this library has no CPU fallback)");
+    return B200MD_ERR;
+  }
+  NEED(device >= 0 && device < ndev, "b200md: device index out of range");
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    b200md_set_error(std::string("b200md: device ") + prop.name + " is not sm_100 (B200); kernels are built for sm_100a only");
+    return B200MD_ERR;
+  }
+  CUDA_TRY(cudaSetDevice(device));
+  b200md_ctx *c = new b200md_ctx();
+  c->device = device; c->rank = rank; c->nranks = nranks;
+  memset(&c->timing, 0, sizeof(c->timing));
+  memset(&c->bin, 0, sizeof(c->bin));
+  memset(&c->sched, 0, sizeof(c->sched));
+  CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CUDA_TRY(cudaMalloc(&c->d_result, 16 * sizeof(double)));
+  CUDA_TRY(cudaMallocHost(&c->h_result, 16 * sizeof(double)));
+  CUDA_TRY(cudaMalloc(&c->d_flags, 8 * sizeof(int)));
+  CUDA_TRY(cudaMemset(c->d_flags, 0, 8 * sizeof(int)));
+  CUDA_TRY(cudaMallocHost(&c->h_flags, 8 * sizeof(int)));
+  memset(c->h_flags, 0, 8 * sizeof(int));
+  *out = c;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_destroy(b200md_ctx *c) {
+  if (!c) return B200MD_OK;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  comm_free(c);
+  pair_eam_free(c);
+  void *ptrs[] = {c->xq, c->xq_tmp, c->cell_xq, c->v, c->v_tmp, c->f, c->xhold, c->tag, c->tag_tmp, c->image,
+                  c->image_tmp, c->mass, c->cutneighsq, c->atom_bin, c->cell_count, c->cell_start, c->cell_fill,
+                  c->cell_atoms, c->perm, c->scan_block, c->row_off, c->row_sx, c->row_flag, c->neigh, c->numneigh,
+                  c->ghost_src, c->ghost_pbc, c->sendbuf, c->recvbuf, c->ljtab, c->rho, c->fp, c->partials,
+                  c->d_result, c->d_flags};
+  for (void *p : ptrs) if (p) cudaFree(p);
+  if (c->h_result) cudaFreeHost(c->h_result);
+  if (c->h_flags) cudaFreeHost(c->h_flags);
+  for (auto e : c->ev_pool) cudaEventDestroy(e);
+  cudaStreamDestroy(c->stream);
+  delete c;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_set_units(b200md_ctx *c, double boltz, double mvv2e, double ftm2v, double nktv2p) {
+  NEED(c, "b200md: null context");
+  c->boltz = boltz; c->mvv2e = mvv2e; c->ftm2v = ftm2v; c->nktv2p = nktv2p;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_set_box(b200md_ctx *c, const double boxlo[3], const double boxhi[3], const int periodic[3],
+                              const int procgrid[3]) {
+  NEED(c, "b200md: null context");
+  NEED(procgrid[0] * procgrid[1] * procgrid[2] == c->nranks, "Bad grid of processors");
+  for (int d = 0; d < 3; d++) {
+    NEED(boxhi[d] > boxlo[d], "Box bounds are invalid or missing");
+    c->boxlo[d] = boxlo[d]; c->boxhi[d] = boxhi[d]; c->prd[d] = boxhi[d] - boxlo[d];
+    c->periodic[d] = periodic[d]; c->procgrid[d] = procgrid[d];
+  }
+  TRY(b200md_rank2loc(c->rank, c->procgrid, c->myloc));
+  TRY(b200md_local_box(c->boxlo, c->boxhi, c->procgrid, c->myloc, c->sublo, c->subhi));
+  for (int d = 0; d < 3; d++) {
+    int loc[3] = {c->myloc[0], c->myloc[1], c->myloc[2]};
+    int left = c->myloc[d] - 1; if (left < 0) left = c->procgrid[d] - 1;
+    int right = c->myloc[d] + 1; if (right == c->procgrid[d]) right = 0;
+    loc[d] = left; c->procneigh[d][0] = (loc[0] * c->procgrid[1] + loc[1]) * c->procgrid[2] + loc[2];
+    loc[d] = right; c->procneigh[d][1] = (loc[0] * c->procgrid[1] + loc[1]) * c->procgrid[2] + loc[2];
+  }
+  c->box_set = true;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_get_subbox(b200md_ctx *c, double sublo[3], double subhi[3]) {
+  NEED(c && c->box_set, "b200md: box not set");
+  for (int d = 0; d < 3; d++) { sublo[d] = c->sublo[d]; subhi[d] = c->subhi[d]; }
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// atoms
+// ---------------------------------------------------------------------------------------
+__global__ void k_upload_atoms(int n, int nmax, const double *__restrict__ x, const double *__restrict__ v,
+                               const int *__restrict__ type, double4 *__restrict__ xq, double *__restrict__ vo,
+                               double *__restrict__ f) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  xq[i] = make_double4(x[3 * i], x[3 * i + 1], x[3 * i + 2], __longlong_as_double((long long)type[i]));
+  const size_t s = (size_t)nmax;
+  vo[i] = v ? v[3 * i] : 0.0; vo[i + s] = v ? v[3 * i + 1] : 0.0; vo[i + 2 * s] = v ? v[3 * i + 2] : 0.0;
+  f[i] = 0; f[i + s] = 0; f[i + 2 * s] = 0;
+}
+__global__ void k_download_atoms(int n, int first, int nmax, const double4 *__restrict__ xq, const double *__restrict__ v,
+                                 const double *__restrict__ f, double *__restrict__ x, double *__restrict__ vo,
+                                 double *__restrict__ fo, int *__restrict__ type) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int i = first + k;
+  const double4 q = xq[i];
+  const size_t s = (size_t)nmax;
+  if (x) { x[3 * k] = q.x; x[3 * k + 1] = q.y; x[3 * k + 2] = q.z; }
+  if (type) type[k] = (int)(__double_as_longlong(q.w) & 0xffffffffll);
+  if (vo) { vo[3 * k] = v[i]; vo[3 * k + 1] = v[i + s]; vo[3 * k + 2] = v[i + 2 * s]; }
+  if (fo) { fo[3 * k] = f[i]; fo[3 * k + 1] = f[i + s]; fo[3 * k + 2] = f[i + 2 * s]; }
+}
+
+extern "C" int b200md_set_atoms(b200md_ctx *c, int nlocal, const double *x, const double *v, const int *type,
+                                const int *tag, const int *image, int ntypes, const double *mass) {
+  NEED(c && c->box_set, "b200md: box not set");
+  NEED(nlocal >= 0 && ntypes >= 1 && x && type && tag && mass, "b200md: bad set_atoms arguments");
+  CUDA_TRY(cudaSetDevice(c->device));
+  c->nlocal = 0; c->nghost = 0;
+  TRY(neigh_grow_atoms(c, nlocal + nlocal / 2 + 4096));
+  c->ntypes = ntypes;
+  c->h_mass.assign(mass, mass + ntypes + 1);
+  for (int t = 1; t <= ntypes; t++) NEED(mass[t] > 0.0, "Not all per-type masses are set");
+  if (c->mass) CUDA_TRY(cudaFree(c->mass));
+  CUDA_TRY(cudaMalloc(&c->mass, sizeof(double) * (ntypes + 1)));
+  CUDA_TRY(cudaMemcpy(c->mass, mass, sizeof(double) * (ntypes + 1), cudaMemcpyHostToDevice));
+  if (nlocal) {
+    double *dx = nullptr, *dv = nullptr; int *dt = nullptr;
+    CUDA_TRY(cudaMalloc(&dx, sizeof(double) * 3 * nlocal));
+    CUDA_TRY(cudaMalloc(&dt, sizeof(int) * nlocal));
+    CUDA_TRY(cudaMemcpy(dx, x, sizeof(double) * 3 * nlocal, cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(dt, type, sizeof(int) * nlocal, cudaMemcpyHostToDevice));
+    if (v) {
+      CUDA_TRY(cudaMalloc(&dv, sizeof(double) * 3 * nlocal));
+      CUDA_TRY(cudaMemcpy(dv, v, sizeof(double) * 3 * nlocal, cudaMemcpyHostToDevice));
+    }
+    k_upload_atoms<<<(nlocal + 255) / 256, 256, 0, c->stream>>>(nlocal, c->nmax, dx, dv, dt, c->xq, c->v, c->f);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(c->tag, tag, sizeof(int) * nlocal, cudaMemcpyHostToDevice, c->stream));
+    if (image) CUDA_TRY(cudaMemcpyAsync(c->image, image, sizeof(int) * nlocal, cudaMemcpyHostToDevice, c->stream));
+    else {
+      std::vector<int> img(nlocal, (512 << 20) | (512 << 10) | 512);
+      CUDA_TRY(cudaMemcpyAsync(c->image, img.data(), sizeof(int) * nlocal, cudaMemcpyHostToDevice, c->stream));
+      CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    cudaFree(dx); cudaFree(dt); if (dv) cudaFree(dv);
+  }
+  c->nlocal = nlocal;
+  double nat = nlocal;
+  TRY(comm_allreduce_sum(c, &nat, 1));
+  c->natoms_global = nat;
+  c->ago = 0; c->step = 0; c->ev_valid = false;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_get_nlocal(b200md_ctx *c, int *nlocal, int *nghost) {
+  NEED(c, "b200md: null context");
+  if (nlocal) *nlocal = c->nlocal;
+  if (nghost) *nghost = c->nghost;
+  return B200MD_OK;
+}
+
+static int download(b200md_ctx *c, int first, int n, double *x, double *v, double *f, int *type, int *tag, int *image) {
+  if (n == 0) return B200MD_OK;
+  CUDA_TRY(cudaSetDevice(c->device));
+  double *dx = nullptr, *dv = nullptr, *df = nullptr; int *dt = nullptr;
+  if (x) CUDA_TRY(cudaMalloc(&dx, sizeof(double) * 3 * n));
+  if (v) CUDA_TRY(cudaMalloc(&dv, sizeof(double) * 3 * n));
+  if (f) CUDA_TRY(cudaMalloc(&df, sizeof(double) * 3 * n));
+  if (type) CUDA_TRY(cudaMalloc(&dt, sizeof(int) * n));
+  k_download_atoms<<<(n + 255) / 256, 256, 0, c->stream>>>(n, first, c->nmax, c->xq, c->v, c->f, dx, dv, df, dt);
+  CUDA_TRY(cudaGetLastError());
+  if (x) CUDA_TRY(cudaMemcpyAsync(x, dx, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, c->stream));
+  if (v) CUDA_TRY(cudaMemcpyAsync(v, dv, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, c->stream));
+  if (f) CUDA_TRY(cudaMemcpyAsync(f, df, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, c->stream));
+  if (type) CUDA_TRY(cudaMemcpyAsync(type, dt, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
+  if (tag) CUDA_TRY(cudaMemcpyAsync(tag, c->tag + first, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
+  if (image) CUDA_TRY(cudaMemcpyAsync(image, c->image + first, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  if (dx) cudaFree(dx); if (dv) cudaFree(dv); if (df) cudaFree(df); if (dt) cudaFree(dt);
+  return B200MD_OK;
+}
+
+extern "C" int b200md_get_atoms(b200md_ctx *c, double *x, double *v, double *f, int *type, int *tag, int *image) {
+  NEED(c, "b200md: null context");
+  return download(c, 0, c->nlocal, x, v, f, type, tag, image);
+}
+extern "C" int b200md_get_ghosts(b200md_ctx *c, double *x, int *type, int *tag) {
+  NEED(c, "b200md: null context");
+  return download(c, c->nlocal, c->nghost, x, nullptr, nullptr, type, tag, nullptr);
+}
+
+extern "C" int b200md_velocity_finalize(b200md_ctx *c, double t_desired, int zero_momentum) {
+  NEED(c, "b200md: null context");
+  CUDA_TRY(cudaSetDevice(c->device));
+  double s[5];
+  double sx = 0, sy = 0, sz = 0;
+  if (zero_momentum) {
+    // Velocity::zero_momentum: subtract the centre-of-mass velocity (src/velocity.cpp, group->vcm)
+    TRY(thermo_ke(c, s));
+    TRY(comm_allreduce_sum(c, s, 5));
+    if (s[4] > 0) { sx = s[1] / s[4]; sy = s[2] / s[4]; sz = s[3] / s[4]; }
+    TRY(vel_adjust(c, sx, sy, sz, 1.0));
+  }
+  // Velocity::rescale: factor = sqrt(t_new/t_old) with ComputeTemp (dof = 3N-3)
+  TRY(thermo_ke(c, s));
+  TRY(comm_allreduce_sum(c, s, 5));
+  const double dof = 3.0 * c->natoms_global - 3.0;
+  const double tfactor = dof > 0 ? c->mvv2e / (dof * c->boltz) : 0.0;
+  const double t_old = s[0] * tfactor;
+  NEED(t_old != 0.0, "Attempting to rescale a 0.0 temperature");
+  TRY(vel_adjust(c, 0, 0, 0, sqrt(t_desired / t_old)));
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// neighbor
+// ---------------------------------------------------------------------------------------
+extern "C" int b200md_neigh_config(b200md_ctx *c, int ntypes, const double *cutneighsq, double cutneighmax,
+                                   double skin, int every, int delay, int check, int list_kind) {
+  NEED(c && c->box_set, "b200md: box not set");
+  NEED(ntypes >= 1 && cutneighsq && cutneighmax > 0, "b200md: bad neigh_config arguments");
+  NEED(every >= 1 && delay >= 0, "Illegal neigh_modify command");
+  NEED(list_kind == B200MD_LIST_FULL || list_kind == B200MD_LIST_HALF_NEWTON, "b200md: unknown list kind");
+  CUDA_TRY(cudaSetDevice(c->device));
+  const size_t nt = (size_t)(ntypes + 1) * (ntypes + 1);
+  c->h_cutneighsq.assign(cutneighsq, cutneighsq + nt);
+  if (c->cutneighsq) CUDA_TRY(cudaFree(c->cutneighsq));
+  CUDA_TRY(cudaMalloc(&c->cutneighsq, sizeof(double) * nt));
+  CUDA_TRY(cudaMemcpy(c->cutneighsq, cutneighsq, sizeof(double) * nt, cudaMemcpyHostToDevice));
+  c->cutneighmax = cutneighmax;
+  c->cutghost = cutneighmax;  // Comm::get_comm_cutoff: max(cutneighmax, user cutoff=0) (src/comm.cpp:681-730)
+  c->skin = skin;
+  c->triggersq = 0.25 * skin * skin;  // src/neighbor.cpp:348
+  c->every = every; c->delay = delay; c->check = check;
+  c->list_kind = list_kind;
+  c->pitch = 0;
+  TRY(comm_setup(c));
+  TRY(neigh_setup_bins(c));
+  c->neigh_configured = true;
+  return B200MD_OK;
+}
+
+static bool decide_will_check(const b200md_ctx *c) {
+  const int ago = c->ago + 1;
+  return ago >= c->delay && ago % c->every == 0 && c->check;
+}
+
+extern "C" int b200md_neigh_decide(b200md_ctx *c, int *rebuild) {
+  NEED(c && c->neigh_configured, "b200md: neighbor not configured");
+  c->ago++;
+  *rebuild = 0;
+  if (c->ago >= c->delay && c->ago % c->every == 0) {
+    if (!c->check) { *rebuild = 1; return B200MD_OK; }
+    // check_distance: the flag was raised by the fused initial-integrate kernel
+    CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    int flag = c->h_flags[0];
+    TRY(comm_allreduce_max_int(c, &flag));
+    if (flag && c->ago == (c->every > c->delay ? c->every : c->delay)) c->ndanger++;
+    *rebuild = flag;
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_neigh_build(b200md_ctx *c) {
+  NEED(c && c->neigh_configured, "b200md: neighbor not configured");
+  CUDA_TRY(cudaSetDevice(c->device));
+  TRY(neigh_pbc(c));
+  TRY(comm_exchange(c));
+  TRY(neigh_sort_owned(c));
+  TRY(comm_borders(c));
+  TRY(neigh_bin_all(c));
+  TRY(neigh_build_list(c));
+  TRY(neigh_save_xhold(c));
+  CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, sizeof(int), c->stream));
+  c->ago = 0;
+  c->nbuilds++;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_forward_comm(b200md_ctx *c) {
+  NEED(c && c->neigh_configured, "b200md: neighbor not configured");
+  return comm_forward(c);
+}
+extern "C" int b200md_reverse_comm(b200md_ctx *c) {
+  NEED(c && c->neigh_configured, "b200md: neighbor not configured");
+  return comm_reverse_force(c);
+}
+
+__global__ void k_export_list(int nlocal, int tpa, int pitch, const int *__restrict__ neigh, const int *__restrict__ numneigh,
+                              const long long *__restrict__ offs, const int *__restrict__ tag, int by_tag, int *__restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const int A = 32 / tpa;
+  const int tile = i / A, sub = i % A;
+  const int *nb = neigh + (size_t)tile * pitch * A + sub * tpa;
+  const int n = numneigh[i];
+  int *o = out + offs[i];
+  for (int k = 0; k < n; k++) {
+    const int j = nb[(k / tpa) * 32 + (k % tpa)];
+    o[k] = by_tag ? tag[j] : j;
+  }
+}
+
+extern "C" int b200md_neigh_export(b200md_ctx *c, int by_tag, int *numneigh, int *neigh_flat, long long *total) {
+  NEED(c && c->neigh && c->nbuilds > 0, "b200md: no neighbor list built");
+  CUDA_TRY(cudaSetDevice(c->device));
+  const int n = c->nlocal;
+  std::vector<int> nn(n);
+  CUDA_TRY(cudaMemcpyAsync(nn.data(), c->numneigh, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  std::vector<long long> offs(n + 1);
+  long long t = 0;
+  for (int i = 0; i < n; i++) { offs[i] = t; t += nn[i]; }
+  offs[n] = t;
+  if (numneigh) memcpy(numneigh, nn.data(), sizeof(int) * n);
+  if (total) *total = t;
+  if (neigh_flat && t > 0) {
+    long long *d_offs = nullptr; int *d_out = nullptr;
+    CUDA_TRY(cudaMalloc(&d_offs, sizeof(long long) * (n + 1)));
+    CUDA_TRY(cudaMalloc(&d_out, sizeof(int) * t));
+    CUDA_TRY(cudaMemcpy(d_offs, offs.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice));
+    k_export_list<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->tpa, c->pitch, c->neigh, c->numneigh, d_offs, c->tag, by_tag, d_out);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(neigh_flat, d_out, sizeof(int) * t, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    cudaFree(d_offs); cudaFree(d_out);
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_neigh_stats(b200md_ctx *c, long long *nbuilds, long long *ndanger, long long *total_neighbors,
+                                  int *maxneigh_pitch) {
+  NEED(c, "b200md: null context");
+  if (nbuilds) *nbuilds = c->nbuilds;
+  if (ndanger) *ndanger = c->ndanger;
+  if (maxneigh_pitch) *maxneigh_pitch = c->pitch;
+  if (total_neighbors) {
+    *total_neighbors = 0;
+    if (c->nbuilds > 0) TRY(b200md_neigh_export(c, 0, nullptr, nullptr, total_neighbors));
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_set_lanes_per_atom(b200md_ctx *c, int lanes) {
+  NEED(c, "b200md: null context");
+  NEED(lanes == 4 || lanes == 8 || lanes == 16 || lanes == 32, "b200md: lanes per atom must be 4, 8, 16 or 32");
+  c->tpa = lanes;
+  return B200MD_OK;
+}
+extern "C" int b200md_get_stream(b200md_ctx *c, void **stream) {
+  NEED(c && stream, "b200md: null argument");
+  *stream = (void *)c->stream;
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// pair
+// ---------------------------------------------------------------------------------------
+extern "C" int b200md_pair_lj_cut_config(b200md_ctx *c, int ntypes, const double *cutsq, const double *lj1,
+                                         const double *lj2, const double *lj3, const double *lj4, const double *offset) {
+  NEED(c, "b200md: null context");
+  NEED(ntypes >= 1 && cutsq && lj1 && lj2 && lj3 && lj4 && offset, "All pair coeffs are not set");
+  NEED(c->ntypes == 0 || c->ntypes == ntypes, "b200md: ntypes differs from set_atoms");
+  CUDA_TRY(cudaSetDevice(c->device));
+  const size_t nt = (size_t)(ntypes + 1) * (ntypes + 1);
+  c->h_ljtab.assign(nt * 8, 0.0);
+  double cmax = 0;
+  for (size_t k = 0; k < nt; k++) {
+    double *t = &c->h_ljtab[k * 8];
+    t[0] = cutsq[k]; t[1] = lj1[k]; t[2] = lj2[k]; t[3] = lj3[k]; t[4] = lj4[k]; t[5] = offset[k];
+    if (cutsq[k] > cmax) cmax = cutsq[k];
+  }
+  c->cutforcemax = sqrt(cmax);
+  if (c->ljtab) CUDA_TRY(cudaFree(c->ljtab));
+  CUDA_TRY(cudaMalloc(&c->ljtab, sizeof(double) * nt * 8));
+  CUDA_TRY(cudaMemcpy(c->ljtab, c->h_ljtab.data(), sizeof(double) * nt * 8, cudaMemcpyHostToDevice));
+  c->pair_style = B200MD_PAIR_LJ_CUT;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_pair_eam_config(b200md_ctx *c, int ntypes, int nrho, int nr, double rdr, double rdrho,
+                                      double rhomax, double cutforcesq, int nfrho, const double *frho_spline,
+                                      int nrhor, const double *rhor_spline, int nz2r, const double *z2r_spline,
+                                      const int *type2frho, const int *type2rhor, const int *type2z2r,
+                                      const double *scale) {
+  NEED(c, "b200md: null context");
+  NEED(ntypes >= 1 && frho_spline && rhor_spline && z2r_spline && type2frho && type2rhor && type2z2r,
+       "All pair coeffs are not set");
+  CUDA_TRY(cudaSetDevice(c->device));
+  TRY(pair_eam_config_impl(c, ntypes, nrho, nr, rdr, rdrho, rhomax, cutforcesq, nfrho, frho_spline, nrhor,
+                           rhor_spline, nz2r, z2r_spline, type2frho, type2rhor, type2z2r, scale));
+  c->cutforcemax = sqrt(cutforcesq);
+  c->pair_style = B200MD_PAIR_EAM;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_pair_compute(b200md_ctx *c, int eflag, int vflag, double *eng_vdwl, double virial[6]) {
+  NEED(c && c->nbuilds > 0, "b200md: pair_compute before the first neighbor build");
+  CUDA_TRY(cudaSetDevice(c->device));
+  if (c->pair_style == B200MD_PAIR_LJ_CUT) TRY(pair_lj_compute(c, eflag, vflag));
+  else if (c->pair_style == B200MD_PAIR_EAM) TRY(pair_eam_compute(c, eflag, vflag));
+  else { b200md_set_error("b200md: no pair style configured"); return B200MD_ERR; }
+  if (eflag && eng_vdwl) *eng_vdwl = c->eng_vdwl;
+  if (vflag && virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// fix nve, thermo
+// ---------------------------------------------------------------------------------------
+extern "C" int b200md_nve_initial(b200md_ctx *c, double dtv, double dtf) {
+  NEED(c && c->neigh_configured, "b200md: neighbor not configured");
+  CUDA_TRY(cudaSetDevice(c->device));
+  return nve_initial(c, dtv, dtf, decide_will_check(c) && c->nbuilds > 0);
+}
+extern "C" int b200md_nve_final(b200md_ctx *c, double dtf) {
+  NEED(c, "b200md: null context");
+  CUDA_TRY(cudaSetDevice(c->device));
+  return nve_final(c, dtf);
+}
+
+extern "C" int b200md_thermo_compute(b200md_ctx *c, b200md_thermo *out) {
+  NEED(c && out, "b200md: null argument");
+  NEED(c->ev_valid, "Energy was not tallied on needed timestep");
+  CUDA_TRY(cudaSetDevice(c->device));
+  double s[5];
+  TRY(thermo_ke(c, s));
+  double red[8] = {s[0], c->eng_vdwl, c->virial[0], c->virial[1], c->virial[2], c->virial[3], c->virial[4], c->virial[5]};
+  TRY(comm_allreduce_sum(c, red, 8));
+  const double dof = 3.0 * c->natoms_global - 3.0;  // ComputeTemp::dof_compute, extra_dof = 3
+  const double tfactor = dof > 0 ? c->mvv2e / (dof * c->boltz) : 0.0;
+  const double t = red[0] * tfactor;
+  const double vol = c->prd[0] * c->prd[1] * c->prd[2];
+  out->step = c->step;
+  out->natoms = c->natoms_global;
+  out->temp = t;
+  out->pe = red[1];
+  out->ke = t * 0.5 * dof * c->boltz;  // Thermo::compute_ke
+  for (int k = 0; k < 6; k++) out->virial[k] = red[2 + k];
+  out->press = (dof * c->boltz * t + red[2] + red[3] + red[4]) / 3.0 * (1.0 / vol) * c->nktv2p;
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// whole loop
+// ---------------------------------------------------------------------------------------
+extern "C" int b200md_setup(b200md_ctx *c) {
+  NEED(c && c->neigh_configured, "b200md: neighbor not configured");
+  NEED(c->pair_style != B200MD_PAIR_NONE, "b200md: no pair style configured");
+  TRY(b200md_neigh_build(c));
+  TRY(b200md_pair_compute(c, 1, 1, nullptr, nullptr));
+  TRY(b200md_reverse_comm(c));
+  return B200MD_OK;
+}
+
+struct PhaseTimer {
+  b200md_ctx *c; bool on; size_t *used; std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> spans;
+  cudaEvent_t get() {
+    if (*used == c->ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); c->ev_pool.push_back(e); }
+    return c->ev_pool[(*used)++];
+  }
+  void begin(int cat) { if (!on) return; cudaEvent_t a = get(), b = get(); cudaEventRecord(a, c->stream); spans.push_back({cat, {a, b}}); }
+  void end() { if (!on) return; cudaEventRecord(spans.back().second.second, c->stream); }
+};
+
+extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every, b200md_thermo *thermo_out,
+                          int max_thermo, int *n_thermo) {
+  NEED(c && c->neigh_configured && c->nbuilds > 0, "b200md: run before setup");
+  CUDA_TRY(cudaSetDevice(c->device));
+  const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;  // FixNVE::init (src/fix_nve.cpp:51-58)
+  const long long first = c->step, last = c->step + nsteps;
+  int nth = 0;
+  const char *pt = getenv("B200MD_PHASE_TIMING");
+  size_t ev_used = 0;
+  PhaseTimer T{c, pt && pt[0] == '1', &ev_used};
+  const long long launches0 = c->launches, pl0 = c->pair_launches, nb0 = c->nbuilds;
+  PhaseTimer TT{c, true, &ev_used};
+  TT.begin(0);
+  for (int i = 0; i < nsteps; i++) {
+    c->step++;
+    // Integrate::ev_set: energy/virial only on thermo output steps
+    const bool out_step = (thermo_every > 0 && (c->step - first) % thermo_every == 0) || c->step == last;
+    const int ev = out_step ? 1 : 0;
+    T.begin(4); TRY(b200md_nve_initial(c, dtv, dtf)); T.end();
+    int nflag = 0;
+    TRY(b200md_neigh_decide(c, &nflag));
+    if (!nflag) { T.begin(3); TRY(comm_forward(c)); T.end(); }
+    else { T.begin(2); TRY(b200md_neigh_build(c)); T.end(); }
+    T.begin(1); TRY(b200md_pair_compute(c, ev, ev, nullptr, nullptr)); T.end();
+    T.begin(3); TRY(comm_reverse_force(c)); T.end();
+    T.begin(4); TRY(nve_final(c, dtf)); T.end();
+    if (out_step && thermo_out && nth < max_thermo) { TRY(b200md_thermo_compute(c, &thermo_out[nth])); nth++; }
+  }
+  TT.end();
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  if (n_thermo) *n_thermo = nth;
+  float ms = 0;
+  cudaEventElapsedTime(&ms, TT.spans[0].second.first, TT.spans[0].second.second);
+  c->timing.total_ms = ms;
+  c->timing.pair_ms = c->timing.neigh_ms = c->timing.comm_ms = c->timing.modify_ms = 0;
+  for (auto &s : T.spans) {
+    float m = 0;
+    cudaEventElapsedTime(&m, s.second.first, s.second.second);
+    if (s.first == 1) c->timing.pair_ms += m; else if (s.first == 2) c->timing.neigh_ms += m;
+    else if (s.first == 3) c->timing.comm_ms += m; else c->timing.modify_ms += m;
+  }
+  c->timing.launches = c->launches - launches0;
+  c->timing.pair_launches = c->pair_launches - pl0;
+  c->timing.nbuilds = (int)(c->nbuilds - nb0);
+  return B200MD_OK;
+}
+
+extern "C" int b200md_get_timing(b200md_ctx *c, b200md_timing *out) {
+  NEED(c && out, "b200md: null argument");
+  *out = c->timing;
+  return B200MD_OK;
+}

@@ -1,0 +1,575 @@
+// comm.cu — ghost-atom halo exchange and atom migration on packed device buffers.
+//
+// Reference behaviour followed (/root/reference/src):
+//   CommBrick::setup          comm_brick.cpp:191-483   -> comm_setup (schedule from host.cpp)
+//   CommBrick::borders        comm_brick.cpp:771-979   -> comm_borders
+//   AtomVec::pack_border      atom_vec.cpp:794-830     -> k_pack_border / k_self_border (x + pbc*prd)
+//   CommBrick::forward_comm   comm_brick.cpp:538-591   -> comm_forward
+//   CommBrick::exchange       comm_brick.cpp:652-759   -> comm_exchange
+//   CommBrick::forward_comm(Pair*) :986-1016           -> comm_forward_scalar (EAM fp)
+//   CommBrick::reverse_comm   :598-639, (Pair*) :1023-1053 -> comm_reverse_force / _scalar
+//   MPI_Allreduce sites (neighbor.cpp:2387, compute_*.cpp)  -> comm_allreduce_*
+// Transport: a swap whose partner is this rank is a device gather kernel; remote swaps are
+// grouped ncclSend/ncclRecv of packed double4 records over NVLink, received in place into
+// the ghost slots (ghosts of one swap are contiguous), both directions of a dimension in
+// one NCCL group.  One process per GPU; the unique id is distributed by the launcher.
+#include <nccl.h>
+#include <algorithm>
+#include "ctx.h"
+#include "util.cuh"
+
+struct NcclState {
+  ncclComm_t comm = nullptr;
+  int *d_counts = nullptr;  // [4] scratch for count exchange
+  int *h_counts = nullptr;  // pinned [4]
+  double *d_red = nullptr;  // [16] allreduce scratch
+};
+
+#define NCCL_TRY(call)                                                                    \
+  do {                                                                                    \
+    ncclResult_t _r = (call);                                                             \
+    if (_r != ncclSuccess) {                                                              \
+      b200md_set_error(std::string("b200md: NCCL error: ") + ncclGetErrorString(_r) +     \
+                       " at " + __FILE__ + ":" + std::to_string(__LINE__));               \
+      return B200MD_ERR;                                                                  \
+    }                                                                                     \
+  } while (0)
+
+extern "C" int b200md_comm_unique_id(void *id128) {
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+  ncclUniqueId id;
+  NCCL_TRY(ncclGetUniqueId(&id));
+  memcpy(id128, &id, 128);
+  return B200MD_OK;
+}
+
+extern "C" int b200md_comm_init(b200md_ctx *c, const void *id128) {
+  if (c->nranks == 1) return B200MD_OK;
+  CUDA_TRY(cudaSetDevice(c->device));
+  ncclUniqueId id;
+  memcpy(&id, id128, 128);
+  c->nccl = new NcclState();
+  NCCL_TRY(ncclCommInitRank(&c->nccl->comm, c->nranks, id, c->rank));
+  CUDA_TRY(cudaMalloc(&c->nccl->d_counts, 8 * sizeof(int)));
+  CUDA_TRY(cudaMallocHost(&c->nccl->h_counts, 8 * sizeof(int)));
+  CUDA_TRY(cudaMalloc(&c->nccl->d_red, 32 * sizeof(double)));
+  return B200MD_OK;
+}
+
+void comm_free(b200md_ctx *c) {
+  for (auto &s : c->swaps) if (s.sendlist) cudaFree(s.sendlist);
+  c->swaps.clear();
+  if (c->nccl) {
+    if (c->nccl->comm) ncclCommDestroy(c->nccl->comm);
+    if (c->nccl->d_counts) cudaFree(c->nccl->d_counts);
+    if (c->nccl->h_counts) cudaFreeHost(c->nccl->h_counts);
+    if (c->nccl->d_red) cudaFree(c->nccl->d_red);
+    delete c->nccl;
+    c->nccl = nullptr;
+  }
+}
+
+int comm_allreduce_sum(b200md_ctx *c, double *v, int n) {
+  if (c->nranks == 1) return B200MD_OK;
+  if (!c->nccl) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
+  CUDA_TRY(cudaMemcpyAsync(c->nccl->d_red, v, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  NCCL_TRY(ncclAllReduce(c->nccl->d_red, c->nccl->d_red, n, ncclDouble, ncclSum, c->nccl->comm, c->stream));
+  CUDA_TRY(cudaMemcpyAsync(v, c->nccl->d_red, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return B200MD_OK;
+}
+
+int comm_allreduce_max_int(b200md_ctx *c, int *v) {
+  if (c->nranks == 1) return B200MD_OK;
+  if (!c->nccl) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
+  CUDA_TRY(cudaMemcpyAsync(c->nccl->d_counts, v, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  NCCL_TRY(ncclAllReduce(c->nccl->d_counts, c->nccl->d_counts, 1, ncclInt, ncclMax, c->nccl->comm, c->stream));
+  CUDA_TRY(cudaMemcpyAsync(v, c->nccl->d_counts, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  return B200MD_OK;
+}
+
+int comm_setup(b200md_ctx *c) {
+  TRY(b200md_comm_schedule(c->boxlo, c->boxhi, c->periodic, c->procgrid, c->myloc, c->cutghost, &c->sched));
+  for (auto &s : c->swaps) if (s.sendlist) cudaFree(s.sendlist);
+  c->swaps.assign(c->sched.nswap, Swap());
+  for (int i = 0; i < c->sched.nswap; i++) {
+    Swap &s = c->swaps[i];
+    s.dim = c->sched.dim[i]; s.ineed = c->sched.ineed[i]; s.sendflag = c->sched.sendflag[i];
+    s.sendproc = c->sched.sendproc[i]; s.recvproc = c->sched.recvproc[i];
+    for (int d = 0; d < 3; d++) s.pbc[d] = c->sched.pbc[i][d];
+    s.slablo = c->sched.slablo[i]; s.slabhi = c->sched.slabhi[i];
+  }
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// kernels
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ double comp(const double4 &q, int d) { return d == 0 ? q.x : (d == 1 ? q.y : q.z); }
+
+__global__ void k_slab_flag(const double4 *__restrict__ xq, int nfirst, int n, int dim, double lo, double hi,
+                            int *__restrict__ flag) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > n) return;
+  if (k == n) { flag[k] = 0; return; }
+  const double x = comp(xq[nfirst + k], dim);
+  flag[k] = (x >= lo && x <= hi) ? 1 : 0;  // comm_brick.cpp:838
+}
+__global__ void k_compact(const int *__restrict__ flag, const int *__restrict__ pos, int nfirst, int n,
+                          int *__restrict__ list) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  if (flag[k]) list[pos[k]] = nfirst + k;
+}
+
+__device__ __forceinline__ int pbc_code_add(int code, int px, int py, int pz) {
+  int cx = (code & 15) + px, cy = ((code >> 4) & 15) + py, cz = ((code >> 8) & 15) + pz;
+  return cx | (cy << 4) | (cz << 8);
+}
+#define PBC_ZERO (8 | (8 << 4) | (8 << 8))
+
+__device__ __forceinline__ double shift_n(double x, int n, double prd) {
+  // x + pbc*prd once per swap like AtomVec::pack_comm/pack_border (atom_vec.cpp:349-378, 794-830)
+  for (; n > 0; n--) x = __dadd_rn(x, prd);
+  for (; n < 0; n++) x = __dsub_rn(x, prd);
+  return x;
+}
+
+// self swap of borders: append ghosts, record flattened source
+__global__ void k_self_border(int n, const int *__restrict__ list, int first, int nlocal, double4 *__restrict__ xq,
+                              int *__restrict__ tag, int *__restrict__ ghost_src, int *__restrict__ ghost_pbc,
+                              int px, int py, int pz, double prdx, double prdy, double prdz) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int j = list[k];
+  double4 q = xq[j];
+  q.x = shift_n(q.x, px, prdx); q.y = shift_n(q.y, py, prdy); q.z = shift_n(q.z, pz, prdz);
+  xq[first + k] = q;
+  tag[first + k] = tag[j];
+  int src = j, code = PBC_ZERO;
+  if (j >= nlocal) { src = ghost_src[j]; code = ghost_pbc[j]; }
+  ghost_src[first + k] = src;
+  ghost_pbc[first + k] = pbc_code_add(code, px, py, pz);
+}
+// remote swap: packed records (positions with shift) + tags
+__global__ void k_pack_border(int n, const int *__restrict__ list, const double4 *__restrict__ xq,
+                              const int *__restrict__ tag, double4 *__restrict__ buf, int *__restrict__ tagbuf,
+                              int px, int py, int pz, double prdx, double prdy, double prdz) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int j = list[k];
+  double4 q = xq[j];
+  q.x = shift_n(q.x, px, prdx); q.y = shift_n(q.y, py, prdy); q.z = shift_n(q.z, pz, prdz);
+  buf[k] = q;
+  if (tagbuf) tagbuf[k] = tag[j];
+}
+__global__ void k_self_forward(int n, const int *__restrict__ list, int first, double4 *__restrict__ xq,
+                               int px, int py, int pz, double prdx, double prdy, double prdz) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  double4 q = xq[list[k]];
+  q.x = shift_n(q.x, px, prdx); q.y = shift_n(q.y, py, prdy); q.z = shift_n(q.z, pz, prdz);
+  xq[first + k] = q;
+}
+// all swaps are self: one gather from the owning atom
+__global__ void k_forward_flat(int nghost, int nlocal, double4 *__restrict__ xq, const int *__restrict__ ghost_src,
+                               const int *__restrict__ ghost_pbc, double prdx, double prdy, double prdz) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= nghost) return;
+  const int code = ghost_pbc[nlocal + g];
+  double4 q = xq[ghost_src[nlocal + g]];
+  q.x = shift_n(q.x, (code & 15) - 8, prdx);
+  q.y = shift_n(q.y, ((code >> 4) & 15) - 8, prdy);
+  q.z = shift_n(q.z, ((code >> 8) & 15) - 8, prdz);
+  xq[nlocal + g] = q;
+}
+__global__ void k_scalar_flat(int nghost, int nlocal, double *__restrict__ a, const int *__restrict__ ghost_src) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= nghost) return;
+  a[nlocal + g] = a[ghost_src[nlocal + g]];
+}
+__global__ void k_scalar_self(int n, const int *__restrict__ list, int first, double *__restrict__ a) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  a[first + k] = a[list[k]];
+}
+__global__ void k_scalar_pack(int n, const int *__restrict__ list, const double *__restrict__ a, double *__restrict__ buf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  buf[k] = a[list[k]];
+}
+
+static int ensure_buf(double *&p, size_t &cap, size_t need_doubles) {
+  if (need_doubles <= cap) return B200MD_OK;
+  if (p) CUDA_TRY(cudaFree(p));
+  cap = need_doubles + need_doubles / 4 + 1024;
+  CUDA_TRY(cudaMalloc(&p, cap * sizeof(double)));
+  return B200MD_OK;
+}
+
+static inline int nblk(int n) { return (n + 255) / 256; }
+
+// ---------------------------------------------------------------------------------------
+// borders
+// ---------------------------------------------------------------------------------------
+int comm_borders(b200md_ctx *c) {
+  cudaStream_t st = c->stream;
+  c->nghost = 0;
+  c->all_self = true;
+  for (auto &s : c->swaps) if (s.sendproc != c->rank || s.recvproc != c->rank) c->all_self = false;
+  int iswap = 0;
+  for (int dim = 0; dim < 3; dim++) {
+    int nlast = 0, nfirst = 0;
+    const int twoneed = 2 * c->sched.maxneed[dim];
+    for (int ineed = 0; ineed < twoneed; ineed++, iswap++) {
+      Swap &s = c->swaps[iswap];
+      if (ineed % 2 == 0) { nfirst = nlast; nlast = c->nlocal + c->nghost; }
+      int nsend = 0;
+      const int n = nlast - nfirst;
+      if (s.sendflag && n > 0) {
+        if (n + 1 > c->nmax) TRY(neigh_grow_atoms(c, n + 1));
+        // flag + scan + compact: deterministic ascending send list (comm_brick.cpp:836-842)
+        int *flag = c->perm, *pos = c->atom_bin;
+        k_slab_flag<<<nblk(n + 1), 256, 0, st>>>(c->xq, nfirst, n, s.dim, s.slablo, s.slabhi, flag);
+        TRY(dev_exclusive_scan(c, flag, pos, n + 1));
+        CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4, pos + n, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        nsend = c->h_flags[4];
+        if (nsend > s.sendcap) {
+          if (s.sendlist) CUDA_TRY(cudaFree(s.sendlist));
+          s.sendcap = nsend + nsend / 4 + 256;
+          CUDA_TRY(cudaMalloc(&s.sendlist, sizeof(int) * s.sendcap));
+        }
+        if (nsend) k_compact<<<nblk(n), 256, 0, st>>>(flag, pos, nfirst, n, s.sendlist);
+        c->launches += 2;
+      }
+      s.sendnum = nsend;
+      int nrecv = nsend;
+      const bool self = (s.sendproc == c->rank);
+      if (!self) {
+        // counts (comm_brick.cpp:917-918)
+        NcclState *nc = c->nccl;
+        if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
+        nc->h_counts[0] = nsend;
+        CUDA_TRY(cudaMemcpyAsync(nc->d_counts, nc->h_counts, sizeof(int), cudaMemcpyHostToDevice, st));
+        NCCL_TRY(ncclGroupStart());
+        NCCL_TRY(ncclSend(nc->d_counts, 1, ncclInt, s.sendproc, nc->comm, st));
+        NCCL_TRY(ncclRecv(nc->d_counts + 1, 1, ncclInt, s.recvproc, nc->comm, st));
+        NCCL_TRY(ncclGroupEnd());
+        CUDA_TRY(cudaMemcpyAsync(nc->h_counts + 1, nc->d_counts + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        nrecv = nc->h_counts[1];
+      }
+      const int first = c->nlocal + c->nghost;
+      if (first + nrecv > c->nmax) TRY(neigh_grow_atoms(c, first + nrecv));
+      if (self) {
+        if (nsend)
+          k_self_border<<<nblk(nsend), 256, 0, st>>>(nsend, s.sendlist, first, c->nlocal, c->xq, c->tag, c->ghost_src,
+                                                    c->ghost_pbc, s.pbc[0], s.pbc[1], s.pbc[2], c->prd[0],
+                                                    c->prd[1], c->prd[2]);
+        c->launches++;
+      } else {
+        NcclState *nc = c->nccl;
+        TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)nsend * 5 + 8));
+        double4 *buf = reinterpret_cast<double4 *>(c->sendbuf);
+        int *tagbuf = reinterpret_cast<int *>(c->sendbuf + (size_t)nsend * 4);
+        if (nsend)
+          k_pack_border<<<nblk(nsend), 256, 0, st>>>(nsend, s.sendlist, c->xq, c->tag, buf, tagbuf, s.pbc[0], s.pbc[1],
+                                                    s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
+        c->launches++;
+        NCCL_TRY(ncclGroupStart());
+        if (nsend) {
+          NCCL_TRY(ncclSend(buf, (size_t)nsend * 4, ncclDouble, s.sendproc, nc->comm, st));
+          NCCL_TRY(ncclSend(tagbuf, nsend, ncclInt, s.sendproc, nc->comm, st));
+        }
+        if (nrecv) {
+          NCCL_TRY(ncclRecv(c->xq + first, (size_t)nrecv * 4, ncclDouble, s.recvproc, nc->comm, st));
+          NCCL_TRY(ncclRecv(c->tag + first, nrecv, ncclInt, s.recvproc, nc->comm, st));
+        }
+        NCCL_TRY(ncclGroupEnd());
+      }
+      s.recvnum = nrecv;
+      s.firstrecv = first;
+      c->nghost += nrecv;
+    }
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// forward comm of positions (every non-rebuild step) and of a per-atom scalar (EAM fp)
+// ---------------------------------------------------------------------------------------
+template <bool SCALAR>
+static int forward_staged(b200md_ctx *c, double *arr) {
+  cudaStream_t st = c->stream;
+  NcclState *nc = c->nccl;
+  const int rec = SCALAR ? 1 : 4;
+  size_t off[2] = {0, 0};
+  int iswap = 0;
+  for (int dim = 0; dim < 3; dim++) {
+    const int twoneed = 2 * c->sched.maxneed[dim];
+    for (int pair = 0; pair < twoneed; pair += 2) {
+      // both directions of the pair read only atoms older than this pair's ghosts
+      size_t need = 0;
+      for (int k = 0; k < 2; k++) { off[k] = need; need += (size_t)c->swaps[iswap + k].sendnum * rec; }
+      TRY(ensure_buf(c->sendbuf, c->sendcap, need + 8));
+      bool any_remote = false;
+      for (int k = 0; k < 2; k++) {
+        Swap &s = c->swaps[iswap + k];
+        if (s.sendproc == c->rank) continue;
+        any_remote = true;
+        if (!s.sendnum) continue;
+        if (SCALAR) k_scalar_pack<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, arr, c->sendbuf + off[k]);
+        else k_pack_border<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, c->xq, nullptr,
+                                                            reinterpret_cast<double4 *>(c->sendbuf + off[k]), nullptr,
+                                                            s.pbc[0], s.pbc[1], s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
+        c->launches++;
+      }
+      if (any_remote) {
+        if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
+        NCCL_TRY(ncclGroupStart());
+        for (int k = 0; k < 2; k++) {
+          Swap &s = c->swaps[iswap + k];
+          if (s.sendproc == c->rank) continue;
+          if (s.sendnum) NCCL_TRY(ncclSend(c->sendbuf + off[k], (size_t)s.sendnum * rec, ncclDouble, s.sendproc, nc->comm, st));
+          if (s.recvnum) {
+            void *dst = SCALAR ? (void *)(arr + s.firstrecv) : (void *)(c->xq + s.firstrecv);
+            NCCL_TRY(ncclRecv(dst, (size_t)s.recvnum * rec, ncclDouble, s.recvproc, nc->comm, st));
+          }
+        }
+        NCCL_TRY(ncclGroupEnd());
+      }
+      for (int k = 0; k < 2; k++) {
+        Swap &s = c->swaps[iswap + k];
+        if (s.sendproc != c->rank || !s.sendnum) continue;
+        if (SCALAR) k_scalar_self<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, arr);
+        else k_self_forward<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, c->xq, s.pbc[0], s.pbc[1],
+                                                             s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
+        c->launches++;
+      }
+      iswap += 2;
+    }
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
+int comm_forward(b200md_ctx *c) {
+  if (c->nghost == 0 && c->all_self) return B200MD_OK;
+  if (c->all_self) {
+    k_forward_flat<<<nblk(c->nghost), 256, 0, c->stream>>>(c->nghost, c->nlocal, c->xq, c->ghost_src, c->ghost_pbc,
+                                                          c->prd[0], c->prd[1], c->prd[2]);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return B200MD_OK;
+  }
+  return forward_staged<false>(c, nullptr);
+}
+
+int comm_forward_scalar(b200md_ctx *c, double *arr) {
+  if (c->nghost == 0 && c->all_self) return B200MD_OK;
+  if (c->all_self) {
+    k_scalar_flat<<<nblk(c->nghost), 256, 0, c->stream>>>(c->nghost, c->nlocal, arr, c->ghost_src);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return B200MD_OK;
+  }
+  return forward_staged<true>(c, arr);
+}
+
+// ---------------------------------------------------------------------------------------
+// exchange: atom migration between neighbouring sub-boxes (comm_brick.cpp:652-759)
+// record = 8 doubles {x,y,z,type-bits, vx,vy,vz, (tag | image<<32)}
+// ---------------------------------------------------------------------------------------
+__global__ void k_exch_flag(const double4 *__restrict__ xq, int n, int dim, double lo, double hi, int *__restrict__ flag) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > n) return;
+  if (k == n) { flag[k] = 0; return; }
+  const double x = comp(xq[k], dim);
+  flag[k] = (x < lo || x >= hi) ? 1 : 0;  // comm_brick.cpp:706
+}
+__global__ void k_exch_split(int n, int nmax, const int *__restrict__ flag, const int *__restrict__ pos,
+                             const double4 *__restrict__ xq, const double *__restrict__ v, const int *__restrict__ tag,
+                             const int *__restrict__ image, double4 *__restrict__ xq_o, double *__restrict__ v_o,
+                             int *__restrict__ tag_o, int *__restrict__ image_o, double *__restrict__ buf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const double4 q = xq[k];
+  const double vx = v[k], vy = v[k + nmax], vz = v[k + 2 * (size_t)nmax];
+  if (flag[k]) {
+    double *r = buf + (size_t)pos[k] * 8;
+    r[0] = q.x; r[1] = q.y; r[2] = q.z; r[3] = q.w; r[4] = vx; r[5] = vy; r[6] = vz;
+    r[7] = __longlong_as_double(((long long)(unsigned)tag[k]) | ((long long)image[k] << 32));
+  } else {
+    const int d = k - pos[k];
+    xq_o[d] = q; v_o[d] = vx; v_o[d + nmax] = vy; v_o[d + 2 * (size_t)nmax] = vz;
+    tag_o[d] = tag[k]; image_o[d] = image[k];
+  }
+}
+__global__ void k_exch_recv_flag(const double *__restrict__ buf, int n, int dim, double lo, double hi, int *__restrict__ flag) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > n) return;
+  if (k == n) { flag[k] = 0; return; }
+  const double x = buf[(size_t)k * 8 + dim];
+  flag[k] = (x >= lo && x < hi) ? 1 : 0;  // comm_brick.cpp:745-752
+}
+__global__ void k_exch_unpack(const double *__restrict__ buf, int n, const int *__restrict__ flag, const int *__restrict__ pos,
+                              int first, int nmax, double4 *__restrict__ xq, double *__restrict__ v, int *__restrict__ tag,
+                              int *__restrict__ image) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n || !flag[k]) return;
+  const double *r = buf + (size_t)k * 8;
+  const int d = first + pos[k];
+  xq[d] = make_double4(r[0], r[1], r[2], r[3]);
+  v[d] = r[4]; v[d + nmax] = r[5]; v[d + 2 * (size_t)nmax] = r[6];
+  const long long ti = __double_as_longlong(r[7]);
+  tag[d] = (int)(ti & 0xffffffffll);
+  image[d] = (int)(ti >> 32);
+}
+
+int comm_exchange(b200md_ctx *c) {
+  c->nghost = 0;  // ghosts are discarded (comm_brick.cpp:672-676)
+  if (c->nranks == 1) return B200MD_OK;
+  cudaStream_t st = c->stream;
+  NcclState *nc = c->nccl;
+  if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
+  for (int dim = 0; dim < 3; dim++) {
+    if (c->procgrid[dim] == 1) continue;
+    const int n = c->nlocal;
+    if (n + 1 > c->nmax) TRY(neigh_grow_atoms(c, n + 1));
+    int *flag = c->perm, *pos = c->atom_bin;
+    k_exch_flag<<<nblk(n + 1), 256, 0, st>>>(c->xq, n, dim, c->sublo[dim], c->subhi[dim], flag);
+    TRY(dev_exclusive_scan(c, flag, pos, n + 1));
+    CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4, pos + n, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const int nsend = c->h_flags[4];
+    TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)nsend * 8 + 8));
+    if (n) {
+      k_exch_split<<<nblk(n), 256, 0, st>>>(n, c->nmax, flag, pos, c->xq, c->v, c->tag, c->image, c->xq_tmp, c->v_tmp,
+                                           c->tag_tmp, c->image_tmp, c->sendbuf);
+      std::swap(c->xq, c->xq_tmp); std::swap(c->v, c->v_tmp);
+      std::swap(c->tag, c->tag_tmp); std::swap(c->image, c->image_tmp);
+    }
+    c->launches += 2;
+    c->nlocal = n - nsend;
+    // counts: to the left neighbour always, to the right one when procgrid > 2
+    const int left = c->procneigh[dim][0], right = c->procneigh[dim][1];
+    const bool both = c->procgrid[dim] > 2;
+    nc->h_counts[0] = nsend;
+    CUDA_TRY(cudaMemcpyAsync(nc->d_counts, nc->h_counts, sizeof(int), cudaMemcpyHostToDevice, st));
+    NCCL_TRY(ncclGroupStart());
+    NCCL_TRY(ncclSend(nc->d_counts, 1, ncclInt, left, nc->comm, st));
+    NCCL_TRY(ncclRecv(nc->d_counts + 1, 1, ncclInt, right, nc->comm, st));
+    if (both) {
+      NCCL_TRY(ncclSend(nc->d_counts, 1, ncclInt, right, nc->comm, st));
+      NCCL_TRY(ncclRecv(nc->d_counts + 2, 1, ncclInt, left, nc->comm, st));
+    }
+    NCCL_TRY(ncclGroupEnd());
+    CUDA_TRY(cudaMemcpyAsync(nc->h_counts + 1, nc->d_counts + 1, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const int nrecv1 = nc->h_counts[1], nrecv2 = both ? nc->h_counts[2] : 0;
+    const int nrecv = nrecv1 + nrecv2;
+    TRY(ensure_buf(c->recvbuf, c->recvcap, (size_t)nrecv * 8 + 8));
+    NCCL_TRY(ncclGroupStart());
+    if (nsend) NCCL_TRY(ncclSend(c->sendbuf, (size_t)nsend * 8, ncclDouble, left, nc->comm, st));
+    if (nrecv1) NCCL_TRY(ncclRecv(c->recvbuf, (size_t)nrecv1 * 8, ncclDouble, right, nc->comm, st));
+    if (both) {
+      if (nsend) NCCL_TRY(ncclSend(c->sendbuf, (size_t)nsend * 8, ncclDouble, right, nc->comm, st));
+      if (nrecv2) NCCL_TRY(ncclRecv(c->recvbuf + (size_t)nrecv1 * 8, (size_t)nrecv2 * 8, ncclDouble, left, nc->comm, st));
+    }
+    NCCL_TRY(ncclGroupEnd());
+    if (nrecv) {
+      if (c->nlocal + nrecv + 1 > c->nmax) TRY(neigh_grow_atoms(c, c->nlocal + nrecv + 1));
+      flag = c->perm; pos = c->atom_bin;
+      k_exch_recv_flag<<<nblk(nrecv + 1), 256, 0, st>>>(c->recvbuf, nrecv, dim, c->sublo[dim], c->subhi[dim], flag);
+      TRY(dev_exclusive_scan(c, flag, pos, nrecv + 1));
+      k_exch_unpack<<<nblk(nrecv), 256, 0, st>>>(c->recvbuf, nrecv, flag, pos, c->nlocal, c->nmax, c->xq, c->v, c->tag, c->image);
+      CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4, pos + nrecv, sizeof(int), cudaMemcpyDeviceToHost, st));
+      CUDA_TRY(cudaStreamSynchronize(st));
+      c->nlocal += c->h_flags[4];
+      c->launches += 2;
+    }
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// reverse comm (half lists with newton on): ghost contributions summed back to owners
+// ---------------------------------------------------------------------------------------
+__global__ void k_rev_self3(int n, const int *__restrict__ list, int first, int nmax, double *__restrict__ f) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int j = list[k];
+#pragma unroll
+  for (int d = 0; d < 3; d++) f[j + d * (size_t)nmax] += f[first + k + d * (size_t)nmax];
+}
+__global__ void k_rev_self1(int n, const int *__restrict__ list, int first, double *__restrict__ a) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  a[list[k]] += a[first + k];
+}
+__global__ void k_rev_pack3(int n, int first, int nmax, const double *__restrict__ f, double *__restrict__ buf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+#pragma unroll
+  for (int d = 0; d < 3; d++) buf[(size_t)k * 3 + d] = f[first + k + d * (size_t)nmax];
+}
+__global__ void k_rev_unpack3(int n, const int *__restrict__ list, int nmax, double *__restrict__ f, const double *__restrict__ buf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int j = list[k];
+#pragma unroll
+  for (int d = 0; d < 3; d++) f[j + d * (size_t)nmax] += buf[(size_t)k * 3 + d];
+}
+__global__ void k_rev_unpack1(int n, const int *__restrict__ list, double *__restrict__ a, const double *__restrict__ buf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  a[list[k]] += buf[k];
+}
+
+// swaps in reverse order, one at a time: a send list may name the same atom only once per
+// swap, so the += of one swap is race-free; later (earlier-numbered) swaps see its result
+// exactly like comm_brick.cpp:610-638.
+template <int NV>
+static int reverse_staged(b200md_ctx *c, double *arr) {
+  cudaStream_t st = c->stream;
+  NcclState *nc = c->nccl;
+  for (int iswap = (int)c->swaps.size() - 1; iswap >= 0; iswap--) {
+    Swap &s = c->swaps[iswap];
+    if (s.sendproc == c->rank) {
+      if (!s.sendnum) continue;
+      if (NV == 3) k_rev_self3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, c->nmax, arr);
+      else k_rev_self1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, arr);
+      c->launches++;
+      continue;
+    }
+    if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
+    TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)s.recvnum * NV + 8));
+    TRY(ensure_buf(c->recvbuf, c->recvcap, (size_t)s.sendnum * NV + 8));
+    const double *src = arr + s.firstrecv;
+    if (NV == 3 && s.recvnum) { k_rev_pack3<<<nblk(s.recvnum), 256, 0, st>>>(s.recvnum, s.firstrecv, c->nmax, arr, c->sendbuf); src = c->sendbuf; c->launches++; }
+    NCCL_TRY(ncclGroupStart());
+    if (s.recvnum) NCCL_TRY(ncclSend(src, (size_t)s.recvnum * NV, ncclDouble, s.recvproc, nc->comm, st));
+    if (s.sendnum) NCCL_TRY(ncclRecv(c->recvbuf, (size_t)s.sendnum * NV, ncclDouble, s.sendproc, nc->comm, st));
+    NCCL_TRY(ncclGroupEnd());
+    if (s.sendnum) {
+      if (NV == 3) k_rev_unpack3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, c->nmax, arr, c->recvbuf);
+      else k_rev_unpack1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, arr, c->recvbuf);
+      c->launches++;
+    }
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
+int comm_reverse_force(b200md_ctx *c) {
+  if (c->list_kind == B200MD_LIST_FULL) return B200MD_OK;  // newton off: nothing on ghosts
+  return reverse_staged<3>(c, c->f);
+}
+int comm_reverse_scalar(b200md_ctx *c, double *arr) {
+  if (c->list_kind == B200MD_LIST_FULL) return B200MD_OK;
+  return reverse_staged<1>(c, arr);
+}

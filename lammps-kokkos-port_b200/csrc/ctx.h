@@ -1,0 +1,181 @@
+// ctx.h — internal device state of libb200md (not part of the ABI).
+//
+// Data layout in HBM (all FP64, int32 indices):
+//   xq[nmax]      double4 {x,y,z,type-bits}: one 32-byte sector per atom, so a neighbor
+//                 gather costs exactly one sector (the reference's AoS `double x[n][3]` +
+//                 `int type[n]`, src/atom.h, straddles sectors; lib/gpu's numtyp4 has the same
+//                 idea in FP32, lib/gpu/lal_lj.cu:16-25)
+//   v[3][nmax], f[3][nmax], xhold[3][nmax]   SoA doubles (streamed only)
+//   tag[nmax], image[nmax]                   int32
+//   owned atoms 0..nlocal-1 are kept in neighbor-bin order (re-sorted at every rebuild),
+//   ghosts nlocal..nall-1 in swap order like CommBrick::borders.
+//   neighbor list: warp-tile transposed.  TPA lanes cooperate on one atom, A=32/TPA atoms
+//   share a warp; tile t = atoms [t*A,(t+1)*A); slot k of atom i lives at
+//       neigh[(size_t)t*pitch*A + (k/TPA)*32 + (i%A)*TPA + (k%TPA)]
+//   so iteration `it` of a warp reads 128 contiguous bytes.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/b200md.h"
+
+struct NcclState;  // comm.cu
+
+struct EamTables {
+  int ntypes = 0, nrho = 0, nr = 0, nfrho = 0, nrhor = 0, nz2r = 0;
+  double rdr = 0, rdrho = 0, rhomax = 0, cutforcesq = 0;
+  // repacked tables, rows 0..n (row m as in the reference, 1-based)
+  double *frho = nullptr;   // [nfrho][nrho+1][8]  c0..c6,pad
+  double *rhoA = nullptr;   // [nrhor][nr+1][4]    value coeffs c3..c6 (density pass)
+  double *pairC = nullptr;  // [nz2r or nrhor combos] see pair_eam.cu
+  double *rhoD = nullptr;   // [nrhor][nr+1][4]    derivative coeffs c0..c2,pad
+  double *z2r = nullptr;    // [nz2r][nr+1][8]     c0..c6,pad
+  int *type2frho = nullptr; // [ntypes+1]
+  int *type2rhor = nullptr; // [(ntypes+1)^2]
+  int *type2z2r = nullptr;  // [(ntypes+1)^2]
+  double *scale = nullptr;  // [(ntypes+1)^2]
+};
+
+struct Swap {
+  int dim, ineed, sendflag, sendproc, recvproc;
+  int pbc[3];
+  double slablo, slabhi;
+  int sendnum = 0, recvnum = 0, firstrecv = 0;
+  int *sendlist = nullptr;  // device
+  int sendcap = 0;
+};
+
+struct b200md_ctx {
+  int device = 0, rank = 0, nranks = 1;
+  cudaStream_t stream = nullptr;
+  // units
+  double boltz = 1, mvv2e = 1, ftm2v = 1, nktv2p = 1;
+  // box
+  double boxlo[3], boxhi[3], prd[3], sublo[3], subhi[3];
+  int periodic[3] = {1, 1, 1}, procgrid[3] = {1, 1, 1}, myloc[3] = {0, 0, 0};
+  int procneigh[3][2];
+  bool box_set = false;
+  // atoms
+  int nlocal = 0, nghost = 0, nmax = 0, ntypes = 0;
+  double natoms_global = 0;
+  double4 *xq = nullptr, *xq_tmp = nullptr;
+  double *v = nullptr, *v_tmp = nullptr;  // 3*nmax each, SoA with stride nmax
+  double *f = nullptr;
+  double *xhold = nullptr;
+  int *tag = nullptr, *tag_tmp = nullptr, *image = nullptr, *image_tmp = nullptr;
+  double *mass = nullptr;  // device [ntypes+1]
+  std::vector<double> h_mass;
+  // neighbor config
+  int list_kind = B200MD_LIST_FULL;
+  double *cutneighsq = nullptr;  // device (ntypes+1)^2
+  std::vector<double> h_cutneighsq;
+  double cutneighmax = 0, skin = 0, triggersq = 0, cutghost = 0;
+  int every = 1, delay = 0, check = 1;
+  int ago = 0;
+  long long nbuilds = 0, ndanger = 0;
+  bool neigh_configured = false;
+  b200md_bin_geometry bin;
+  int mbins = 0;
+  // binning scratch
+  int *atom_bin = nullptr;    // [nmax]
+  int *cell_count = nullptr;  // [mbins+1]
+  int *cell_start = nullptr;  // [mbins+1]
+  int *cell_fill = nullptr;   // [mbins]
+  int *cell_atoms = nullptr;  // [nmax]  atom indices in cell order
+  double4 *cell_xq = nullptr; // [nmax]  positions in cell order
+  int *perm = nullptr;        // [nmax]
+  int cell_cap = 0;
+  int *scan_block = nullptr;  // scan partials
+  int scan_cap = 0;
+  // stencil rows: (dy,dz) rows with x half-extent
+  int nrows = 0;
+  int *row_off = nullptr;  // device [nrows] flattened (dz*mbiny+dy)*mbinx
+  int *row_sx = nullptr;   // device [nrows]
+  int *row_flag = nullptr; // device [nrows] half-stencil role (0 skip,1 full row,2 own row)
+  // neighbor list
+  int tpa = 8;
+  int pitch = 0;  // max neighbors per atom (multiple of tpa)
+  int *neigh = nullptr;
+  size_t neigh_cap = 0;
+  int *numneigh = nullptr;  // [nmax]
+  // comm
+  b200md_swap_schedule sched;
+  std::vector<Swap> swaps;
+  NcclState *nccl = nullptr;
+  int *ghost_src = nullptr;       // single-rank fast path: flattened owner index per ghost
+  int *ghost_pbc = nullptr;       // packed periodic-shift multiples (px+8)|(py+8)<<4|(pz+8)<<8
+  bool all_self = true;           // every swap partner is this rank -> flattened forward path
+  double *sendbuf = nullptr, *recvbuf = nullptr;
+  size_t sendcap = 0, recvcap = 0;
+  // pair
+  int pair_style = B200MD_PAIR_NONE;
+  double *ljtab = nullptr;  // device (ntypes+1)^2 * 8: cutsq,lj1,lj2,lj3,lj4,offset,pad,pad
+  std::vector<double> h_ljtab;
+  double cutforcemax = 0;
+  EamTables eam;
+  double *rho = nullptr, *fp = nullptr;  // [nmax]
+  // reductions
+  double *partials = nullptr;  // device [npartial_blocks*8]
+  int partial_cap = 0;
+  double *d_result = nullptr;  // device [16]
+  double *h_result = nullptr;  // pinned [16]
+  int *d_flags = nullptr;      // device [8]: 0 rebuild flag, 1 overflow, 2 nonfinite, 3 counter
+  int *h_flags = nullptr;      // pinned [8]
+  // last energies
+  double eng_vdwl = 0, virial[6] = {0, 0, 0, 0, 0, 0};
+  bool ev_valid = false;
+  long long step = 0;
+  // timing
+  b200md_timing timing;
+  long long launches = 0, pair_launches = 0;
+  std::vector<cudaEvent_t> ev_pool;
+};
+
+// ---- error helpers (api.cu) ----
+void b200md_set_error(const std::string &msg);
+#define CUDA_TRY(call)                                                                   \
+  do {                                                                                   \
+    cudaError_t _e = (call);                                                             \
+    if (_e != cudaSuccess) {                                                             \
+      b200md_set_error(std::string("b200md: CUDA error: ") + cudaGetErrorString(_e) +    \
+                       " at " + __FILE__ + ":" + std::to_string(__LINE__));              \
+      return B200MD_ERR;                                                                 \
+    }                                                                                    \
+  } while (0)
+#define TRY(call)                      \
+  do {                                 \
+    int _r = (call);                   \
+    if (_r != B200MD_OK) return _r;    \
+  } while (0)
+
+// ---- kernels' host launchers ----
+// neigh.cu
+int neigh_grow_atoms(b200md_ctx *c, int need);   // grow per-atom arrays to >= need
+int neigh_setup_bins(b200md_ctx *c);             // geometry + stencil rows
+int neigh_pbc(b200md_ctx *c);                    // Domain::pbc on owned atoms
+int neigh_sort_owned(b200md_ctx *c);             // bin-order sort of owned atoms
+int neigh_bin_all(b200md_ctx *c);                // cell lists over owned+ghost
+int neigh_build_list(b200md_ctx *c);             // NPair build
+int neigh_save_xhold(b200md_ctx *c);
+int dev_exclusive_scan(b200md_ctx *c, const int *in, int *out, int n);
+// comm.cu
+int comm_setup(b200md_ctx *c);
+int comm_exchange(b200md_ctx *c);
+int comm_borders(b200md_ctx *c);
+int comm_forward(b200md_ctx *c);
+int comm_forward_scalar(b200md_ctx *c, double *arr);  // EAM fp
+int comm_reverse_force(b200md_ctx *c);
+int comm_reverse_scalar(b200md_ctx *c, double *arr);  // EAM rho (half lists)
+int comm_allreduce_sum(b200md_ctx *c, double *hostvals, int n);
+int comm_allreduce_max_int(b200md_ctx *c, int *hostval);
+void comm_free(b200md_ctx *c);
+// pair_lj.cu / pair_eam.cu
+int pair_lj_compute(b200md_ctx *c, int eflag, int vflag);
+int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);
+// nve.cu
+int nve_initial(b200md_ctx *c, double dtv, double dtf, bool check_dist);
+int nve_final(b200md_ctx *c, double dtf);
+int thermo_ke(b200md_ctx *c, double *sum_mv2);
+int reduce_partials(b200md_ctx *c, int nblocks, int nvals, double *host_out);
+int ensure_partials(b200md_ctx *c, int nblocks);

@@ -1,0 +1,309 @@
+// pair_eam.cu — pair_style eam / eam/alloy force evaluation (same compute for both; the
+// file formats differ only in how the spline tables are produced on the host side).
+//
+// Reference: PairEAM::compute (/root/reference/src/MANYBODY/pair_eam.cpp:142-328)
+//   pass 1 (:187-220)  rho_i += rhor_spline[type2rhor[jtype][itype]][m] value cubic at p
+//   embed  (:231-247)  fp_i = F'(rho_i); phi = F(rho_i) (+ linear extrapolation past rhomax)
+//   comm   (:251)      forward_comm(fp)
+//   pass 3 (:257-325)  psip = fp_i*rhojp + fp_j*rhoip + phip; fpair = -scale*psip/r
+// B200 design: full list / newton off, so pass 1 needs no reverse_comm of rho and pass 1 and
+// the embedding are one kernel (what the reference's Kokkos port calls KernelAB,
+// src/KOKKOS/pair_eam_kokkos.cpp:839-921): TPA lanes gather, shuffle-reduce rho_i, lane 0
+// evaluates F and F'.  Tables are repacked so that each lookup is whole 32-byte sectors:
+//   rhoA[t][m] = {c3,c4,c5,c6}   density value           (pass 1: 1 sector / pair)
+//   rhoD[t][m] = {c0,c1,c2,0}    density derivative      (pass 3: 1 sector per distinct table)
+//   z2r [t][m] = {c0..c6,0}      pair term               (pass 3: 2 sectors)
+// and are staged into shared memory when one table set fits (Cu_u3: nr=500 -> 16+16+32 KB),
+// otherwise read through L1/L2 (Cu_mishin1: nr=10001 -> 1.3 MB, L2-resident).
+#include "ctx.h"
+#include "util.cuh"
+
+#define EAM_THREADS 256
+
+void pair_eam_free(b200md_ctx *c) {
+  EamTables &e = c->eam;
+  void *p[] = {e.frho, e.rhoA, e.rhoD, e.z2r, e.type2frho, e.type2rhor, e.type2z2r, e.scale};
+  for (void *q : p) if (q) cudaFree(q);
+  e = EamTables();
+}
+
+template <typename T>
+static int upload(T *&dst, const std::vector<T> &h) {
+  CUDA_TRY(cudaMalloc(&dst, sizeof(T) * h.size()));
+  CUDA_TRY(cudaMemcpy(dst, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice));
+  return B200MD_OK;
+}
+
+int pair_eam_config_impl(b200md_ctx *c, int ntypes, int nrho, int nr, double rdr, double rdrho, double rhomax,
+                         double cutforcesq, int nfrho, const double *frho_spline, int nrhor,
+                         const double *rhor_spline, int nz2r, const double *z2r_spline, const int *type2frho,
+                         const int *type2rhor, const int *type2z2r, const double *scale) {
+  pair_eam_free(c);
+  EamTables &e = c->eam;
+  e.ntypes = ntypes; e.nrho = nrho; e.nr = nr; e.nfrho = nfrho; e.nrhor = nrhor; e.nz2r = nz2r;
+  e.rdr = rdr; e.rdrho = rdrho; e.rhomax = rhomax; e.cutforcesq = cutforcesq;
+  std::vector<double> frho((size_t)nfrho * (nrho + 1) * 8, 0.0), rhoA((size_t)nrhor * (nr + 1) * 4, 0.0),
+      rhoD((size_t)nrhor * (nr + 1) * 4, 0.0), z2r((size_t)nz2r * (nr + 1) * 8, 0.0);
+  for (int t = 0; t < nfrho; t++)
+    for (int m = 0; m <= nrho; m++)
+      for (int k = 0; k < 7; k++) frho[((size_t)t * (nrho + 1) + m) * 8 + k] = frho_spline[((size_t)t * (nrho + 1) + m) * 7 + k];
+  for (int t = 0; t < nrhor; t++)
+    for (int m = 0; m <= nr; m++) {
+      const double *s = &rhor_spline[((size_t)t * (nr + 1) + m) * 7];
+      double *a = &rhoA[((size_t)t * (nr + 1) + m) * 4], *d = &rhoD[((size_t)t * (nr + 1) + m) * 4];
+      a[0] = s[3]; a[1] = s[4]; a[2] = s[5]; a[3] = s[6];
+      d[0] = s[0]; d[1] = s[1]; d[2] = s[2];
+    }
+  for (int t = 0; t < nz2r; t++)
+    for (int m = 0; m <= nr; m++)
+      for (int k = 0; k < 7; k++) z2r[((size_t)t * (nr + 1) + m) * 8 + k] = z2r_spline[((size_t)t * (nr + 1) + m) * 7 + k];
+  const size_t nt = (size_t)(ntypes + 1) * (ntypes + 1);
+  std::vector<int> t2f(type2frho, type2frho + ntypes + 1), t2r(type2rhor, type2rhor + nt), t2z(type2z2r, type2z2r + nt);
+  std::vector<double> sc(nt, 1.0);
+  if (scale) sc.assign(scale, scale + nt);
+  TRY(upload(e.frho, frho)); TRY(upload(e.rhoA, rhoA)); TRY(upload(e.rhoD, rhoD)); TRY(upload(e.z2r, z2r));
+  TRY(upload(e.type2frho, t2f)); TRY(upload(e.type2rhor, t2r)); TRY(upload(e.type2z2r, t2z)); TRY(upload(e.scale, sc));
+  return B200MD_OK;
+}
+
+struct EamParams {
+  int ntypes, nrho, nr;
+  double rdr, rdrho, rhomax, cutforcesq;
+  const double *frho, *rhoA, *rhoD, *z2r, *scale;
+  const int *type2frho, *type2rhor, *type2z2r;
+};
+
+__device__ __forceinline__ double4 ld4(const double *p) {
+  const double2 *q = reinterpret_cast<const double2 *>(p);
+  const double2 a = q[0], b = q[1];
+  return make_double4(a.x, a.y, b.x, b.y);
+}
+
+// ---- pass 1 + embedding ----
+template <int TPA, bool EV, bool SMEM>
+__global__ void __launch_bounds__(EAM_THREADS)
+k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh, const int *__restrict__ numneigh,
+             int pitch, EamParams P, double *__restrict__ rho, double *__restrict__ fp, double *__restrict__ partials) {
+  constexpr int A = 32 / TPA;
+  extern __shared__ double s_dyn[];
+  const double *rhoA = P.rhoA;
+  if (SMEM) {
+    const int n4 = (P.nr + 1) * 4;
+    for (int k = threadIdx.x; k < n4; k += blockDim.x) s_dyn[k] = P.rhoA[k];
+    __syncthreads();
+    rhoA = s_dyn;
+  }
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / TPA, l = lane % TPA;
+  const int tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int i = tile * A + sub;
+  const bool active = i < nlocal;
+  const int nt1 = P.ntypes + 1;
+  double r_acc = 0;
+  int itype = 1;
+  if (active) {
+    const double4 qi = xq[i];
+    itype = xq_type(qi);
+    const int n = numneigh[i];
+    const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
+    const int niter = (n + TPA - 1) / TPA;
+#pragma unroll 4
+    for (int it = 0; it < niter; it++) {
+      if (it * TPA + l < n) {
+        const int j = __ldg(nb + it * 32);
+        const double4 qj = ld_xq(&xq[j]);
+        const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
+        const double rsq = rsq_nofma(dx, dy, dz);
+        if (rsq < P.cutforcesq) {
+          double p = sqrt(rsq) * P.rdr + 1.0;
+          int m = (int)p;
+          m = min(m, P.nr - 1);
+          p -= m;
+          p = fmin(p, 1.0);
+          const int tab = SMEM ? 0 : P.type2rhor[xq_type(qj) * nt1 + itype];
+          const double4 cf = ld4(rhoA + ((size_t)tab * (P.nr + 1) + m) * 4);
+          r_acc += ((cf.x * p + cf.y) * p + cf.z) * p + cf.w;
+        }
+      }
+    }
+  }
+  __syncwarp();
+  r_acc = group_sum<TPA>(r_acc);
+  double ev[1] = {0};
+  if (active && l == 0) {
+    rho[i] = r_acc;
+    double p = r_acc * P.rdrho + 1.0;
+    int m = (int)p;
+    m = max(1, min(m, P.nrho - 1));
+    p -= m;
+    p = fmin(p, 1.0);
+    const double *cf = P.frho + ((size_t)P.type2frho[itype] * (P.nrho + 1) + m) * 8;
+    const double fpi = (cf[0] * p + cf[1]) * p + cf[2];
+    fp[i] = fpi;
+    if (EV) {
+      double phi = ((cf[3] * p + cf[4]) * p + cf[5]) * p + cf[6];
+      if (r_acc > P.rhomax) phi += fpi * (r_acc - P.rhomax);
+      phi *= P.scale[itype * nt1 + itype];
+      ev[0] = phi;
+    }
+  }
+  if (EV) block_reduce_store<1>(ev, partials);
+}
+
+// ---- pass 3: forces ----
+template <int TPA, bool EV, bool SMEM>
+__global__ void __launch_bounds__(EAM_THREADS)
+k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict__ neigh,
+            const int *__restrict__ numneigh, int pitch, EamParams P, const double *__restrict__ fp,
+            double *__restrict__ f, double *__restrict__ partials) {
+  constexpr int A = 32 / TPA;
+  extern __shared__ double s_dyn[];
+  const double *rhoD = P.rhoD, *z2r = P.z2r;
+  if (SMEM) {
+    const int n4 = (P.nr + 1) * 4, n8 = (P.nr + 1) * 8;
+    for (int k = threadIdx.x; k < n4; k += blockDim.x) s_dyn[k] = P.rhoD[k];
+    for (int k = threadIdx.x; k < n8; k += blockDim.x) s_dyn[n4 + k] = P.z2r[k];
+    __syncthreads();
+    rhoD = s_dyn; z2r = s_dyn + n4;
+  }
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / TPA, l = lane % TPA;
+  const int tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int i = tile * A + sub;
+  const bool active = i < nlocal;
+  const int nt1 = P.ntypes + 1;
+  double fx = 0, fy = 0, fz = 0;
+  double ev[7] = {0, 0, 0, 0, 0, 0, 0};
+  if (active) {
+    const double4 qi = xq[i];
+    const int itype = xq_type(qi);
+    const double fpi = fp[i];
+    const int n = numneigh[i];
+    const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
+    const int niter = (n + TPA - 1) / TPA;
+#pragma unroll 2
+    for (int it = 0; it < niter; it++) {
+      if (it * TPA + l < n) {
+        const int j = __ldg(nb + it * 32);
+        const double4 qj = ld_xq(&xq[j]);
+        const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
+        const double rsq = rsq_nofma(dx, dy, dz);
+        if (rsq < P.cutforcesq) {
+          const double fpj = __ldg(&fp[j]);
+          const double r = sqrt(rsq);
+          double p = r * P.rdr + 1.0;
+          int m = (int)p;
+          m = min(m, P.nr - 1);
+          p -= m;
+          p = fmin(p, 1.0);
+          double rhoip, rhojp, scl = 1.0;
+          const double *zrow;
+          if (SMEM) {
+            const double4 d = ld4(rhoD + (size_t)m * 4);
+            rhoip = rhojp = (d.x * p + d.y) * p + d.z;
+            zrow = z2r + (size_t)m * 8;
+            scl = P.scale[nt1 + 1];
+          } else {
+            const int jtype = xq_type(qj);
+            const int tij = P.type2rhor[itype * nt1 + jtype], tji = P.type2rhor[jtype * nt1 + itype];
+            const double4 d = ld4(rhoD + ((size_t)tij * (P.nr + 1) + m) * 4);
+            rhoip = (d.x * p + d.y) * p + d.z;
+            if (tji == tij) rhojp = rhoip;
+            else { const double4 d2 = ld4(rhoD + ((size_t)tji * (P.nr + 1) + m) * 4); rhojp = (d2.x * p + d2.y) * p + d2.z; }
+            zrow = z2r + ((size_t)P.type2z2r[itype * nt1 + jtype] * (P.nr + 1) + m) * 8;
+            scl = P.scale[itype * nt1 + jtype];
+          }
+          const double4 za = ld4(zrow), zb = ld4(zrow + 4);
+          const double z2p = (za.x * p + za.y) * p + za.z;
+          const double z2 = ((za.w * p + zb.x) * p + zb.y) * p + zb.z;
+          const double recip = 1.0 / r;
+          const double phi = z2 * recip;
+          const double phip = z2p * recip - phi * recip;
+          const double psip = fpi * rhojp + fpj * rhoip + phip;
+          const double fpair = -scl * psip * recip;
+          fx += dx * fpair; fy += dy * fpair; fz += dz * fpair;
+          if (EV) {
+            ev[0] += scl * phi;
+            ev[1] += dx * dx * fpair; ev[2] += dy * dy * fpair; ev[3] += dz * dz * fpair;
+            ev[4] += dx * dy * fpair; ev[5] += dx * dz * fpair; ev[6] += dy * dz * fpair;
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+  fx = group_sum<TPA>(fx); fy = group_sum<TPA>(fy); fz = group_sum<TPA>(fz);
+  if (active && l == 0) { f[i] = fx; f[i + nmax] = fy; f[i + 2 * (size_t)nmax] = fz; }
+  if (EV) block_reduce_store<7>(ev, partials);
+}
+
+template <int TPA, bool EV, bool SMEM>
+static int launch_eam(b200md_ctx *c, int nblocks, const EamParams &P, size_t smemA, size_t smemC, double *e_embed,
+                      double *out7) {
+  auto kA = k_eam_rho_fp<TPA, EV, SMEM>;
+  auto kC = k_eam_force<TPA, EV, SMEM>;
+  if (SMEM) {
+    CUDA_TRY(cudaFuncSetAttribute(kA, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemA));
+    CUDA_TRY(cudaFuncSetAttribute(kC, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemC));
+  }
+  kA<<<nblocks, EAM_THREADS, SMEM ? smemA : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, P, c->rho,
+                                                            c->fp, c->partials);
+  c->launches++; c->pair_launches++;
+  CUDA_TRY(cudaGetLastError());
+  if (EV) { double e1[1]; TRY(reduce_partials(c, nblocks, 1, e1)); *e_embed = e1[0]; }
+  // PairEAM::compute's forward_comm(this): fp of owners -> ghosts (pair_eam.cpp:251, pack :855-876)
+  TRY(comm_forward_scalar(c, c->fp));
+  kC<<<nblocks, EAM_THREADS, SMEM ? smemC : 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->neigh, c->numneigh, c->pitch, P,
+                                                            c->fp, c->f, c->partials);
+  c->launches++; c->pair_launches++;
+  CUDA_TRY(cudaGetLastError());
+  if (EV) TRY(reduce_partials(c, nblocks, 7, out7));
+  return B200MD_OK;
+}
+
+template <int TPA>
+static int launch_eam_tpa(b200md_ctx *c, int nblocks, const EamParams &P, bool ev, bool smem, size_t smemA, size_t smemC,
+                          double *e_embed, double *out7) {
+  if (ev) return smem ? launch_eam<TPA, true, true>(c, nblocks, P, smemA, smemC, e_embed, out7)
+                      : launch_eam<TPA, true, false>(c, nblocks, P, smemA, smemC, e_embed, out7);
+  return smem ? launch_eam<TPA, false, true>(c, nblocks, P, smemA, smemC, e_embed, out7)
+              : launch_eam<TPA, false, false>(c, nblocks, P, smemA, smemC, e_embed, out7);
+}
+
+int pair_eam_compute(b200md_ctx *c, int eflag, int vflag) {
+  if (c->list_kind != B200MD_LIST_FULL) {
+    b200md_set_error("b200md: eam runs on the full neighbor list (newton off) only");
+    return B200MD_ERR;
+  }
+  const EamTables &e = c->eam;
+  const bool ev = eflag || vflag;
+  const int A = 32 / c->tpa;
+  const int ntiles = (c->nlocal + A - 1) / A;
+  const int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
+  c->ev_valid = false;
+  if (nblocks == 0) {
+    if (ev) { c->eng_vdwl = 0; for (int k = 0; k < 6; k++) c->virial[k] = 0; c->ev_valid = true; }
+    return comm_forward_scalar(c, c->fp);
+  }
+  if (ev) TRY(ensure_partials(c, nblocks));
+  EamParams P = {e.ntypes, e.nrho, e.nr, e.rdr, e.rdrho, e.rhomax, e.cutforcesq, e.frho, e.rhoA, e.rhoD, e.z2r,
+                 e.scale, e.type2frho, e.type2rhor, e.type2z2r};
+  const size_t smemA = (size_t)(e.nr + 1) * 4 * sizeof(double);
+  const size_t smemC = (size_t)(e.nr + 1) * 12 * sizeof(double);
+  const char *nosm = getenv("B200MD_EAM_NOSMEM");
+  const bool smem = e.ntypes == 1 && e.nrhor == 1 && e.nz2r == 1 && smemC <= 96 * 1024 && !(nosm && nosm[0] == '1');
+  double e_embed = 0, out7[7] = {0, 0, 0, 0, 0, 0, 0};
+  switch (c->tpa) {
+    case 4: TRY(launch_eam_tpa<4>(c, nblocks, P, ev, smem, smemA, smemC, &e_embed, out7)); break;
+    case 8: TRY(launch_eam_tpa<8>(c, nblocks, P, ev, smem, smemA, smemC, &e_embed, out7)); break;
+    case 16: TRY(launch_eam_tpa<16>(c, nblocks, P, ev, smem, smemA, smemC, &e_embed, out7)); break;
+    case 32: TRY(launch_eam_tpa<32>(c, nblocks, P, ev, smem, smemA, smemC, &e_embed, out7)); break;
+    default: b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
+  }
+  if (ev) {
+    c->eng_vdwl = e_embed + 0.5 * out7[0];
+    for (int k = 0; k < 6; k++) c->virial[k] = 0.5 * out7[1 + k];
+    c->ev_valid = true;
+  }
+  return B200MD_OK;
+}

@@ -1,0 +1,153 @@
+// pair_lj.cu — pair_style lj/cut force kernel.
+//
+// Reference: PairLJCut::compute (/root/reference/src/pair_lj_cut.cpp:69-137):
+//   r2inv = 1/rsq; r6inv = r2inv^3; forcelj = r6inv*(lj1*r6inv - lj2); fpair = forcelj*r2inv
+//   evdwl = r6inv*(lj3*r6inv - lj4) - offset          (rsq < cutsq, strict)
+// with Verlet::force_clear (src/verlet.cpp:376-421) fused in (the full-list kernel writes
+// f[i] instead of accumulating; reference Kokkos does the same with ZEROFLAG,
+// src/KOKKOS/pair_kokkos.h:141-145), and the energy/virial tallies of Pair::ev_tally
+// (src/pair.cpp:1013-1108) done as warp- then block-level reductions, no atomics.
+//
+// Full list (newton off): TPA lanes cooperate on atom i, each lane takes every TPA-th
+// neighbor from the warp-tile-transposed list (a warp reads 128 contiguous bytes of indices
+// per iteration), gathers the 32-byte {x,y,z,type} record of j, and the partial forces are
+// shuffle-reduced; lane 0 writes f[i].  Each pair is visited from both sides, so energy and
+// virial take weight 1/2.  Half list (newton on): same traversal, f[j] -= via FP64 RED.
+#include "ctx.h"
+#include "util.cuh"
+
+#define PAIR_THREADS 256
+#define LJ_MAX_TYPES_SMEM 8
+
+struct LJOne { double cutsq, lj1, lj2, lj3, lj4, offset; };
+
+template <int TPA, bool EV, bool HALF, bool ONETYPE>
+__global__ void __launch_bounds__(PAIR_THREADS)
+k_lj(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict__ neigh,
+     const int *__restrict__ numneigh, int pitch, LJOne one, const double *__restrict__ ljtab, int ntypes,
+     double *__restrict__ f, double *__restrict__ partials) {
+  constexpr int A = 32 / TPA;
+  __shared__ double s_tab[ONETYPE ? 1 : (LJ_MAX_TYPES_SMEM + 1) * (LJ_MAX_TYPES_SMEM + 1) * 6];
+  const int nt1 = ntypes + 1;
+  if (!ONETYPE) {
+    for (int r = threadIdx.x; r < nt1 * nt1; r += blockDim.x)
+#pragma unroll
+      for (int k = 0; k < 6; k++) s_tab[r * 6 + k] = ljtab[r * 8 + k];
+    __syncthreads();
+  }
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / TPA, l = lane % TPA;
+  const int tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int i = tile * A + sub;
+  const bool active = i < nlocal;
+
+  double fx = 0, fy = 0, fz = 0;
+  double ev[7] = {0, 0, 0, 0, 0, 0, 0};  // evdwl, vxx, vyy, vzz, vxy, vxz, vyz
+  if (active) {
+    const double4 qi = xq[i];
+    const int n = numneigh[i];
+    const int itype = ONETYPE ? 1 : xq_type(qi);
+    const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
+    const int niter = (n + TPA - 1) / TPA;
+#pragma unroll 4
+    for (int it = 0; it < niter; it++) {
+      if (it * TPA + l < n) {
+        const int j = __ldg(nb + it * 32);
+        const double4 qj = ld_xq(&xq[j]);
+        const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
+        const double rsq = rsq_nofma(dx, dy, dz);
+        double cutsq, lj1, lj2, lj3, lj4, offset;
+        if (ONETYPE) { cutsq = one.cutsq; lj1 = one.lj1; lj2 = one.lj2; lj3 = one.lj3; lj4 = one.lj4; offset = one.offset; }
+        else {
+          const double *t = &s_tab[(itype * nt1 + xq_type(qj)) * 6];
+          cutsq = t[0]; lj1 = t[1]; lj2 = t[2]; lj3 = t[3]; lj4 = t[4]; offset = t[5];
+        }
+        if (rsq < cutsq) {
+          const double r2inv = 1.0 / rsq;
+          const double r6inv = r2inv * r2inv * r2inv;
+          const double forcelj = r6inv * (lj1 * r6inv - lj2);
+          const double fpair = forcelj * r2inv;
+          fx += dx * fpair; fy += dy * fpair; fz += dz * fpair;
+          if (HALF) {
+            atomicAdd(&f[j], -dx * fpair);
+            atomicAdd(&f[j + nmax], -dy * fpair);
+            atomicAdd(&f[j + 2 * (size_t)nmax], -dz * fpair);
+          }
+          if (EV) {
+            ev[0] += r6inv * (lj3 * r6inv - lj4) - offset;
+            ev[1] += dx * dx * fpair; ev[2] += dy * dy * fpair; ev[3] += dz * dz * fpair;
+            ev[4] += dx * dy * fpair; ev[5] += dx * dz * fpair; ev[6] += dy * dz * fpair;
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+  fx = group_sum<TPA>(fx); fy = group_sum<TPA>(fy); fz = group_sum<TPA>(fz);
+  if (active && l == 0) {
+    if (HALF) {
+      atomicAdd(&f[i], fx); atomicAdd(&f[i + nmax], fy); atomicAdd(&f[i + 2 * (size_t)nmax], fz);
+    } else {
+      f[i] = fx; f[i + nmax] = fy; f[i + 2 * (size_t)nmax] = fz;
+    }
+  }
+  if (EV) block_reduce_store<7>(ev, partials);
+}
+
+template <int TPA, bool EV, bool HALF>
+static void launch_lj2(b200md_ctx *c, int nblocks, const LJOne &one) {
+  if (c->ntypes == 1)
+    k_lj<TPA, EV, HALF, true><<<nblocks, PAIR_THREADS, 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->neigh, c->numneigh,
+                                                                      c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials);
+  else
+    k_lj<TPA, EV, HALF, false><<<nblocks, PAIR_THREADS, 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->neigh, c->numneigh,
+                                                                       c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials);
+}
+template <int TPA>
+static void launch_lj(b200md_ctx *c, int nblocks, bool ev, const LJOne &one) {
+  const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON;
+  if (ev) { if (half) launch_lj2<TPA, true, true>(c, nblocks, one); else launch_lj2<TPA, true, false>(c, nblocks, one); }
+  else { if (half) launch_lj2<TPA, false, true>(c, nblocks, one); else launch_lj2<TPA, false, false>(c, nblocks, one); }
+}
+
+int pair_lj_compute(b200md_ctx *c, int eflag, int vflag) {
+  if (c->ntypes > LJ_MAX_TYPES_SMEM) { b200md_set_error("b200md: lj/cut supports at most 8 atom types"); return B200MD_ERR; }
+  const bool ev = eflag || vflag;
+  const int A = 32 / c->tpa;
+  const int ntiles = (c->nlocal + A - 1) / A;
+  const int nblocks = (ntiles + PAIR_THREADS / 32 - 1) / (PAIR_THREADS / 32);
+  const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON;
+  if (half)  // Verlet::force_clear over owned + ghost (src/verlet.cpp:376-421)
+    for (int d = 0; d < 3; d++)
+      CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax, 0, sizeof(double) * (c->nlocal + c->nghost), c->stream));
+  c->ev_valid = false;
+  if (nblocks == 0) {
+    if (ev) { c->eng_vdwl = 0; for (int k = 0; k < 6; k++) c->virial[k] = 0; c->ev_valid = true; }
+    return B200MD_OK;
+  }
+  if (ev) TRY(ensure_partials(c, nblocks));
+  LJOne one = {0, 0, 0, 0, 0, 0};
+  if (c->ntypes == 1) {
+    const double *t = &c->h_ljtab[((size_t)1 * 2 + 1) * 8];  // row (1,1)
+    one = {t[0], t[1], t[2], t[3], t[4], t[5]};
+  }
+  switch (c->tpa) {
+    case 4: launch_lj<4>(c, nblocks, ev, one); break;
+    case 8: launch_lj<8>(c, nblocks, ev, one); break;
+    case 16: launch_lj<16>(c, nblocks, ev, one); break;
+    case 32: launch_lj<32>(c, nblocks, ev, one); break;
+    default: b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
+  }
+  c->launches++;
+  c->pair_launches++;
+  CUDA_TRY(cudaGetLastError());
+  if (ev) {
+    double out[7];
+    TRY(reduce_partials(c, nblocks, 7, out));
+    const double w = half ? 1.0 : 0.5;
+    c->eng_vdwl = w * out[0];
+    for (int k = 0; k < 6; k++) c->virial[k] = w * out[1 + k];
+    c->ev_valid = true;
+  }
+  return B200MD_OK;
+}

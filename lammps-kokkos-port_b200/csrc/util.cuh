@@ -1,0 +1,62 @@
+// util.cuh — device helpers shared by the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define B200_SMS 148
+
+__device__ __forceinline__ int xq_type(const double4 &q) {
+  return (int)(__double_as_longlong(q.w) & 0xffffffffll);
+}
+__device__ __forceinline__ double type_bits(int t) { return __longlong_as_double((long long)t); }
+
+// rsq in the reference's operand order, no FMA contraction:
+// delx*delx + dely*dely + delz*delz  (src/npair_full_bin_atomonly.cpp:74-77)
+__device__ __forceinline__ double rsq_nofma(double dx, double dy, double dz) {
+  return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}
+
+// one 32-byte sector gather of {x,y,z,type}
+__device__ __forceinline__ double4 ld_xq(const double4 *p) {
+  double4 r;
+#if defined(B200MD_LD256)
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];"
+               : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w)
+               : "l"(p));
+#else
+  const double2 *q = reinterpret_cast<const double2 *>(p);
+  double2 a = __ldg(q), b = __ldg(q + 1);
+  r.x = a.x; r.y = a.y; r.z = b.x; r.w = b.y;
+#endif
+  return r;
+}
+
+template <int W>
+__device__ __forceinline__ double group_sum(double v) {
+#pragma unroll
+  for (int o = W / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// block reduction of NV doubles per thread into out[blockIdx.x*NV + k]; blockDim multiple of 32
+template <int NV>
+__device__ __forceinline__ void block_reduce_store(double (&val)[NV], double *out) {
+  __shared__ double s_red[32][NV];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int k = 0; k < NV; k++) val[k] = group_sum<32>(val[k]);
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) s_red[wid][k] = val[k];
+  }
+  __syncthreads();
+  if (wid == 0) {
+#pragma unroll
+    for (int k = 0; k < NV; k++) {
+      double t = lane < nw ? s_red[lane][k] : 0.0;
+      t = group_sum<32>(t);
+      if (lane == 0) out[(size_t)blockIdx.x * NV + k] = t;
+    }
+  }
+}

@@ -1,0 +1,69 @@
+"""The bench inputs of the reference restated as host-side set-up calls on a b200md Context:
+`bench/in.lj` and `bench/in.eam` (/root/reference/bench/in.lj:1-31, in.eam:1-32), scaled by
+-var x/y/z like the originals.  Synthetic fcc lattice data, no files except the EAM potential.
+"""
+import math
+
+import numpy as np
+
+from . import b200md as B  # noqa: F401  (package import)
+
+
+def _decompose(ctx, boxlo, boxhi):
+    prd = [boxhi[d] - boxlo[d] for d in range(3)]
+    grid = B.procgrid(ctx.nranks, prd)
+    ctx.set_box(boxlo, boxhi, (1, 1, 1), grid)
+    return grid
+
+
+def in_lj(ctx, x=1, y=1, z=1, list_kind=B.LIST_FULL, every=20, delay=0, check=0, temperature=1.44, seed=87287):
+    """bench/in.lj: units lj; lattice fcc 0.8442; region box block 0 20x 0 20y 0 20z;
+    create_atoms 1 box; mass 1 1.0; velocity all create 1.44 87287 loop geom;
+    pair_style lj/cut 2.5; pair_coeff 1 1 1.0 1.0 2.5; neighbor 0.3 bin;
+    neigh_modify delay 0 every 20 check no; fix 1 all nve."""
+    ctx.set_units("lj")
+    scale = math.pow(4.0 / 0.8442, 1.0 / 3.0)  # Lattice: (nbasis/volume/rho*)^(1/dim), src/lattice.cpp:256-262
+    nx, ny, nz = 20 * x, 20 * y, 20 * z
+    boxlo = [0.0, 0.0, 0.0]
+    boxhi = [nx * scale, ny * scale, nz * scale]
+    _decompose(ctx, boxlo, boxhi)
+    sublo, subhi = ctx.subbox()
+    mass = np.array([0.0, 1.0])
+    xs, vs, tag = B.lattice_fcc(scale, nx, ny, nz, sublo, subhi, seed, 1.0)
+    ctx.set_atoms(xs, vs, np.ones(len(tag), np.int32), tag, mass)
+    ctx.velocity_finalize(temperature, True)
+    T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 2.5)}, 2.5)
+    ctx.pair_lj_cut_config(T["cutsq"], T["lj1"], T["lj2"], T["lj3"], T["lj4"], T["offset"])
+    skin = 0.3
+    cn, cmax = B.cutneighsq_table(1, T["cutsq"], skin)
+    ctx.neigh_config(cn, cmax, skin, every=every, delay=delay, check=check, list_kind=list_kind)
+    return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=0, units="lj")
+
+
+def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, seed=376847):
+    """bench/in.eam: units metal; lattice fcc 3.615; region box block 0 20x 0 20y 0 20z;
+    create_atoms 1 box; pair_style eam; pair_coeff 1 1 Cu_u3.eam; velocity all create 1600.0
+    376847 loop geom; neighbor 1.0 bin; neigh_modify every 1 delay 5 check yes; fix 1 all nve;
+    timestep 0.005; thermo 50.  style="eam/alloy" takes a setfl file (Cu_mishin1.eam.alloy)."""
+    from . import eam_host
+    ctx.set_units("metal")
+    scale = 3.615
+    nx, ny, nz = 20 * x, 20 * y, 20 * z
+    boxlo = [0.0, 0.0, 0.0]
+    boxhi = [nx * scale, ny * scale, nz * scale]
+    _decompose(ctx, boxlo, boxhi)
+    sublo, subhi = ctx.subbox()
+    if style == "eam":
+        tb = eam_host.tables_from_funcfl([potential])
+    else:
+        tb = eam_host.tables_from_setfl(potential, ["Cu"])
+    mass = np.array([0.0, tb["mass"][1]])
+    xs, vs, tag = B.lattice_fcc(scale, nx, ny, nz, sublo, subhi, seed, mass[1])
+    ctx.set_atoms(xs, vs, np.ones(len(tag), np.int32), tag, mass)
+    ctx.velocity_finalize(temperature, True)
+    ctx.pair_eam_config(tb)
+    skin = 1.0
+    cutsq = np.zeros((2, 2)); cutsq[1, 1] = tb["cutforcesq"]
+    cn, cmax = B.cutneighsq_table(1, cutsq, skin)
+    ctx.neigh_config(cn, cmax, skin, every=1, delay=5, check=1, list_kind=B.LIST_FULL)
+    return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=50, units="metal")
