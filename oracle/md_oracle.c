@@ -1,0 +1,635 @@
+/* md_oracle.c — TEST INFRASTRUCTURE ONLY.  A plain-C, single-process CPU restatement of the
+ * reference's short-range hot path, used by tests/, __graft_entry__.smoke() and bench.py's
+ * cpu_baseline leg as the CHECKER.  The product (libb200md.so) never links or calls this.
+ *
+ * Parity status: PINNED — tests/test_oracle_vs_reference.py checks every function below
+ * against the unmodified reference compiled into oracle/_ref/liblammps_ref.so
+ * (oracle/build_ref.py) and against the thermo printed in the reference's own logs
+ * (bench/log.6Oct16.{lj,eam}.fixed.icc.1), and tests/golden/ holds vectors generated from
+ * that reference build (tests/golden/make_golden.py).
+ *
+ * Each function cites the reference code (paths relative to /root/reference/src) it follows:
+ * same operand order, no FMA contraction (compile with -ffp-contract=off), same comparison
+ * operators, linked-list bins, 6-swap periodic borders, half/newton and full lists.
+ */
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define BIG 1.0e20
+#define SMALL 1.0e-6
+#define MIN(a, b) ((a) < (b) ? (a) : (b))
+#define MAX(a, b) ((a) > (b) ? (a) : (b))
+#define IMGMASK 1023
+#define IMGBITS 10
+
+typedef struct {
+  /* units (update.cpp:145-200) */
+  double boltz, mvv2e, ftm2v, nktv2p;
+  /* domain */
+  double boxlo[3], boxhi[3], prd[3];
+  /* atoms: owned 0..nlocal-1, ghosts nlocal..nlocal+nghost-1 */
+  int nlocal, nghost, nmax, ntypes;
+  double *x, *v, *f; /* [nmax][3] */
+  int *type, *tag, *image;
+  int *owner; /* ghost -> owned index it images (for rho/f reverse, fp forward on one proc) */
+  double *mass;
+  /* neighbor */
+  double *cutneighsq; /* (ntypes+1)^2 */
+  double cutneighmax, skin, triggersq;
+  int every, delay, check, half;
+  int ago, nbuilds, ndanger;
+  double *xhold;
+  int nbinx, nbiny, nbinz, mbinx, mbiny, mbinz, mbinxlo, mbinylo, mbinzlo, mbins;
+  double binsizex, binsizey, binsizez, bininvx, bininvy, bininvz;
+  int *binhead, *bins, *atom2bin;
+  int nstencil, *stencil;
+  int *numneigh, *firstoff, *neigh;
+  long neighcap;
+  /* swaps (6, one proc, periodic) */
+  int nswap, sendnum[6], firstrecv[6], *sendlist[6], sendcap[6], pbcdim[6], pbcsign[6];
+  /* pair */
+  int pair_style; /* 1 lj, 2 eam */
+  double *cutsq, *lj1, *lj2, *lj3, *lj4, *offset;
+  int nrho, nr, nfrho, nrhor, nz2r;
+  double rdr, rdrho, rhomax, cutforcesq;
+  double *frho_spline, *rhor_spline, *z2r_spline, *scale;
+  int *type2frho, *type2rhor, *type2z2r;
+  double *rho, *fp;
+  double eng_vdwl, virial[6];
+  long step;
+} ora_sim;
+
+typedef struct {
+  long step;
+  double natoms, temp, pe, ke, press, virial[6];
+} ora_thermo;
+
+static void grow(ora_sim *s, int need) {
+  if (need <= s->nmax) return;
+  int n = need + need / 4 + 1024;
+  s->x = realloc(s->x, sizeof(double) * 3 * n);
+  s->v = realloc(s->v, sizeof(double) * 3 * n);
+  s->f = realloc(s->f, sizeof(double) * 3 * n);
+  s->xhold = realloc(s->xhold, sizeof(double) * 3 * n);
+  s->type = realloc(s->type, sizeof(int) * n);
+  s->tag = realloc(s->tag, sizeof(int) * n);
+  s->image = realloc(s->image, sizeof(int) * n);
+  s->owner = realloc(s->owner, sizeof(int) * n);
+  s->bins = realloc(s->bins, sizeof(int) * n);
+  s->atom2bin = realloc(s->atom2bin, sizeof(int) * n);
+  s->numneigh = realloc(s->numneigh, sizeof(int) * n);
+  s->firstoff = realloc(s->firstoff, sizeof(int) * n);
+  s->rho = realloc(s->rho, sizeof(double) * n);
+  s->fp = realloc(s->fp, sizeof(double) * n);
+  s->nmax = n;
+}
+
+ora_sim *ora_create(const double *boxlo, const double *boxhi, int n, const double *x, const double *v,
+                    const int *type, const int *tag, int ntypes, const double *mass, double boltz,
+                    double mvv2e, double ftm2v, double nktv2p) {
+  ora_sim *s = calloc(1, sizeof(ora_sim));
+  s->boltz = boltz; s->mvv2e = mvv2e; s->ftm2v = ftm2v; s->nktv2p = nktv2p;
+  for (int d = 0; d < 3; d++) { s->boxlo[d] = boxlo[d]; s->boxhi[d] = boxhi[d]; s->prd[d] = boxhi[d] - boxlo[d]; }
+  s->ntypes = ntypes;
+  s->mass = malloc(sizeof(double) * (ntypes + 1));
+  memcpy(s->mass, mass, sizeof(double) * (ntypes + 1));
+  grow(s, n * 2);
+  s->nlocal = n;
+  memcpy(s->x, x, sizeof(double) * 3 * n);
+  if (v) memcpy(s->v, v, sizeof(double) * 3 * n); else memset(s->v, 0, sizeof(double) * 3 * n);
+  memset(s->f, 0, sizeof(double) * 3 * n);
+  memcpy(s->type, type, sizeof(int) * n);
+  memcpy(s->tag, tag, sizeof(int) * n);
+  for (int i = 0; i < n; i++) s->image[i] = (512 << 20) | (512 << 10) | 512;
+  return s;
+}
+
+void ora_destroy(ora_sim *s) {
+  if (!s) return;
+  free(s->x); free(s->v); free(s->f); free(s->xhold); free(s->type); free(s->tag); free(s->image); free(s->owner);
+  free(s->bins); free(s->atom2bin); free(s->numneigh); free(s->firstoff); free(s->rho); free(s->fp); free(s->mass);
+  free(s->cutneighsq); free(s->binhead); free(s->stencil); free(s->neigh);
+  for (int k = 0; k < 6; k++) free(s->sendlist[k]);
+  free(s->cutsq); free(s->lj1); free(s->lj2); free(s->lj3); free(s->lj4); free(s->offset);
+  free(s->frho_spline); free(s->rhor_spline); free(s->z2r_spline); free(s->scale);
+  free(s->type2frho); free(s->type2rhor); free(s->type2z2r);
+  free(s);
+}
+
+/* Velocity::zero_momentum + rescale with ComputeTemp (velocity.cpp:358-368; compute_temp.cpp:72-99) */
+static double temp_scalar(ora_sim *s) {
+  double t = 0.0;
+  for (int i = 0; i < s->nlocal; i++) {
+    double *v = &s->v[3 * i];
+    t += (v[0] * v[0] + v[1] * v[1] + v[2] * v[2]) * s->mass[s->type[i]];
+  }
+  double dof = 3.0 * s->nlocal - 3.0;
+  double tfactor = dof > 0 ? s->mvv2e / (dof * s->boltz) : 0.0;
+  return t * tfactor;
+}
+void ora_velocity_finalize(ora_sim *s, double t_desired) {
+  double p[3] = {0, 0, 0}, masstotal = 0;
+  for (int i = 0; i < s->nlocal; i++) {
+    double m = s->mass[s->type[i]];
+    for (int d = 0; d < 3; d++) p[d] += s->v[3 * i + d] * m;
+    masstotal += m;
+  }
+  for (int d = 0; d < 3; d++) p[d] /= masstotal;
+  for (int i = 0; i < s->nlocal; i++)
+    for (int d = 0; d < 3; d++) s->v[3 * i + d] -= p[d];
+  double t = temp_scalar(s);
+  double factor = sqrt(t_desired / t);
+  for (int i = 0; i < 3 * s->nlocal; i++) s->v[i] *= factor;
+}
+
+/* Domain::pbc (domain.cpp:530-650), orthogonal, fully periodic */
+static void pbc(ora_sim *s) {
+  for (int i = 0; i < s->nlocal; i++)
+    for (int d = 0; d < 3; d++) {
+      double *xc = &s->x[3 * i + d];
+      int sh = d * IMGBITS;
+      if (*xc < s->boxlo[d]) {
+        *xc += s->prd[d];
+        int idim = (s->image[i] >> sh) & IMGMASK, other = s->image[i] ^ (idim << sh);
+        idim--; idim &= IMGMASK;
+        s->image[i] = other | (idim << sh);
+      }
+      if (*xc >= s->boxhi[d]) {
+        *xc -= s->prd[d];
+        *xc = MAX(*xc, s->boxlo[d]);
+        int idim = (s->image[i] >> sh) & IMGMASK, other = s->image[i] ^ (idim << sh);
+        idim++; idim &= IMGMASK;
+        s->image[i] = other | (idim << sh);
+      }
+    }
+}
+
+/* CommBrick::setup + borders on one periodic process (comm_brick.cpp:412-482, 771-979;
+ * AtomVec::pack_border atom_vec.cpp:794-830): 6 self-swaps, maxneed = 1 required. */
+static int borders(ora_sim *s) {
+  const double cut = s->cutneighmax;
+  s->nghost = 0;
+  int iswap = 0;
+  for (int dim = 0; dim < 3; dim++) {
+    if ((int)(cut * 1 / s->prd[dim]) + 1 != 1) return -1; /* box smaller than cutoff: not restated */
+    int nlast = 0, nfirst = 0;
+    for (int ineed = 0; ineed < 2; ineed++, iswap++) {
+      double lo, hi;
+      int sign;
+      if (ineed % 2 == 0) { lo = -BIG; hi = s->boxlo[dim] + cut; sign = 1; nfirst = nlast; nlast = s->nlocal + s->nghost; }
+      else { lo = s->boxhi[dim] - cut; hi = BIG; sign = -1; }
+      int nsend = 0;
+      for (int i = nfirst; i < nlast; i++)
+        if (s->x[3 * i + dim] >= lo && s->x[3 * i + dim] <= hi) {
+          if (nsend == s->sendcap[iswap]) {
+            s->sendcap[iswap] = s->sendcap[iswap] * 2 + 1024;
+            s->sendlist[iswap] = realloc(s->sendlist[iswap], sizeof(int) * s->sendcap[iswap]);
+          }
+          s->sendlist[iswap][nsend++] = i;
+        }
+      int first = s->nlocal + s->nghost;
+      grow(s, first + nsend);
+      for (int k = 0; k < nsend; k++) {
+        int j = s->sendlist[iswap][k], g = first + k;
+        for (int d = 0; d < 3; d++) s->x[3 * g + d] = s->x[3 * j + d];
+        s->x[3 * g + dim] = s->x[3 * j + dim] + sign * s->prd[dim];
+        s->tag[g] = s->tag[j]; s->type[g] = s->type[j];
+        s->owner[g] = j < s->nlocal ? j : s->owner[j];
+      }
+      s->sendnum[iswap] = nsend; s->firstrecv[iswap] = first;
+      s->pbcdim[iswap] = dim; s->pbcsign[iswap] = sign;
+      s->nghost += nsend;
+    }
+  }
+  s->nswap = 6;
+  return 0;
+}
+/* CommBrick::forward_comm (comm_brick.cpp:538-591) + AtomVec::pack_comm (atom_vec.cpp:349-378) */
+static void forward_comm(ora_sim *s) {
+  for (int iswap = 0; iswap < s->nswap; iswap++)
+    for (int k = 0; k < s->sendnum[iswap]; k++) {
+      int j = s->sendlist[iswap][k], g = s->firstrecv[iswap] + k, dim = s->pbcdim[iswap];
+      for (int d = 0; d < 3; d++) s->x[3 * g + d] = s->x[3 * j + d];
+      s->x[3 * g + dim] = s->x[3 * j + dim] + s->pbcsign[iswap] * s->prd[dim];
+    }
+}
+/* CommBrick::reverse_comm (comm_brick.cpp:598-639): swaps in reverse order, += into senders */
+static void reverse_comm_vec(ora_sim *s, double *a, int nv) {
+  for (int iswap = s->nswap - 1; iswap >= 0; iswap--)
+    for (int k = 0; k < s->sendnum[iswap]; k++) {
+      int j = s->sendlist[iswap][k], g = s->firstrecv[iswap] + k;
+      for (int d = 0; d < nv; d++) a[nv * j + d] += a[nv * g + d];
+    }
+}
+static void forward_comm_scalar(ora_sim *s, double *a) {
+  for (int iswap = 0; iswap < s->nswap; iswap++)
+    for (int k = 0; k < s->sendnum[iswap]; k++) a[s->firstrecv[iswap] + k] = a[s->sendlist[iswap][k]];
+}
+
+/* NBinStandard::setup_bins (nbin_standard.cpp:82-214), one process: sub-box = box */
+static void setup_bins(ora_sim *s) {
+  double bbox[3], lo[3], hi[3];
+  for (int d = 0; d < 3; d++) { bbox[d] = s->prd[d]; lo[d] = s->boxlo[d] - s->cutneighmax; hi[d] = s->boxhi[d] + s->cutneighmax; }
+  double binsize_optimal = 0.5 * s->cutneighmax;
+  double binsizeinv = 1.0 / binsize_optimal;
+  int nb[3]; double bs[3], bi[3]; int mlo[3], mhi[3];
+  for (int d = 0; d < 3; d++) {
+    nb[d] = (int)(bbox[d] * binsizeinv);
+    if (nb[d] == 0) nb[d] = 1;
+    bs[d] = bbox[d] / nb[d];
+    bi[d] = 1.0 / bs[d];
+    double coord = lo[d] - SMALL * bbox[d];
+    mlo[d] = (int)((coord - s->boxlo[d]) * bi[d]);
+    if (coord < s->boxlo[d]) mlo[d] = mlo[d] - 1;
+    coord = hi[d] + SMALL * bbox[d];
+    mhi[d] = (int)((coord - s->boxlo[d]) * bi[d]);
+    mlo[d] -= 1; mhi[d] += 1;
+  }
+  s->nbinx = nb[0]; s->nbiny = nb[1]; s->nbinz = nb[2];
+  s->binsizex = bs[0]; s->binsizey = bs[1]; s->binsizez = bs[2];
+  s->bininvx = bi[0]; s->bininvy = bi[1]; s->bininvz = bi[2];
+  s->mbinxlo = mlo[0]; s->mbinylo = mlo[1]; s->mbinzlo = mlo[2];
+  s->mbinx = mhi[0] - mlo[0] + 1; s->mbiny = mhi[1] - mlo[1] + 1; s->mbinz = mhi[2] - mlo[2] + 1;
+  s->mbins = s->mbinx * s->mbiny * s->mbinz;
+  s->binhead = realloc(s->binhead, sizeof(int) * (s->mbins + 1));
+}
+
+/* NBin::coord2bin (nbin.cpp:139-168) */
+static int coord2bin(const ora_sim *s, const double *x) {
+  int ix, iy, iz;
+  if (x[0] >= s->boxhi[0]) ix = (int)((x[0] - s->boxhi[0]) * s->bininvx) + s->nbinx;
+  else if (x[0] >= s->boxlo[0]) { ix = (int)((x[0] - s->boxlo[0]) * s->bininvx); ix = MIN(ix, s->nbinx - 1); }
+  else ix = (int)((x[0] - s->boxlo[0]) * s->bininvx) - 1;
+  if (x[1] >= s->boxhi[1]) iy = (int)((x[1] - s->boxhi[1]) * s->bininvy) + s->nbiny;
+  else if (x[1] >= s->boxlo[1]) { iy = (int)((x[1] - s->boxlo[1]) * s->bininvy); iy = MIN(iy, s->nbiny - 1); }
+  else iy = (int)((x[1] - s->boxlo[1]) * s->bininvy) - 1;
+  if (x[2] >= s->boxhi[2]) iz = (int)((x[2] - s->boxhi[2]) * s->bininvz) + s->nbinz;
+  else if (x[2] >= s->boxlo[2]) { iz = (int)((x[2] - s->boxlo[2]) * s->bininvz); iz = MIN(iz, s->nbinz - 1); }
+  else iz = (int)((x[2] - s->boxlo[2]) * s->bininvz) - 1;
+  return (iz - s->mbinzlo) * s->mbiny * s->mbinx + (iy - s->mbinylo) * s->mbinx + (ix - s->mbinxlo);
+}
+
+/* NBinStandard::bin_atoms (nbin_standard.cpp:221-260): linked lists, ghosts end up last */
+static void bin_atoms(ora_sim *s) {
+  int nall = s->nlocal + s->nghost;
+  for (int i = 0; i < s->mbins; i++) s->binhead[i] = -1;
+  for (int i = nall - 1; i >= 0; i--) {
+    int ibin = coord2bin(s, &s->x[3 * i]);
+    s->atom2bin[i] = ibin;
+    s->bins[i] = s->binhead[ibin];
+    s->binhead[ibin] = i;
+  }
+}
+
+/* NStencil::bin_distance (nstencil.cpp:405-422) */
+static double bin_distance(const ora_sim *s, int i, int j, int k) {
+  double delx, dely, delz;
+  if (i > 0) delx = (i - 1) * s->binsizex; else if (i == 0) delx = 0.0; else delx = (i + 1) * s->binsizex;
+  if (j > 0) dely = (j - 1) * s->binsizey; else if (j == 0) dely = 0.0; else dely = (j + 1) * s->binsizey;
+  if (k > 0) delz = (k - 1) * s->binsizez; else if (k == 0) delz = 0.0; else delz = (k + 1) * s->binsizez;
+  return delx * delx + dely * dely + delz * delz;
+}
+/* NStencil::create_setup (nstencil.cpp:213-247) + NStencilFullBin3d::create
+ * (nstencil_full_bin_3d.cpp:26-37) / NStencilHalfBin3d::create (nstencil_half_bin_3d.cpp:26-38) */
+static void create_stencil(ora_sim *s) {
+  int sx = (int)(s->cutneighmax * s->bininvx); if (sx * s->binsizex < s->cutneighmax) sx++;
+  int sy = (int)(s->cutneighmax * s->bininvy); if (sy * s->binsizey < s->cutneighmax) sy++;
+  int sz = (int)(s->cutneighmax * s->bininvz); if (sz * s->binsizez < s->cutneighmax) sz++;
+  double cutsq = s->cutneighmax * s->cutneighmax;
+  s->stencil = realloc(s->stencil, sizeof(int) * (2 * sx + 1) * (2 * sy + 1) * (2 * sz + 1));
+  s->nstencil = 0;
+  if (!s->half) {
+    for (int k = -sz; k <= sz; k++)
+      for (int j = -sy; j <= sy; j++)
+        for (int i = -sx; i <= sx; i++)
+          if (bin_distance(s, i, j, k) < cutsq) s->stencil[s->nstencil++] = k * s->mbiny * s->mbinx + j * s->mbinx + i;
+  } else {
+    for (int k = 0; k <= sz; k++)
+      for (int j = -sy; j <= sy; j++)
+        for (int i = -sx; i <= sx; i++)
+          if (k > 0 || j > 0 || (j == 0 && i > 0))
+            if (bin_distance(s, i, j, k) < cutsq) s->stencil[s->nstencil++] = k * s->mbiny * s->mbinx + j * s->mbinx + i;
+  }
+}
+
+static void push_neigh(ora_sim *s, long *n, int j) {
+  if (*n == s->neighcap) { s->neighcap = s->neighcap * 2 + (1 << 20); s->neigh = realloc(s->neigh, sizeof(int) * s->neighcap); }
+  s->neigh[(*n)++] = j;
+}
+
+/* NPairFullBinAtomonly::build (npair_full_bin_atomonly.cpp:32-92) and
+ * NPairHalfBinAtomonlyNewton::build (npair_half_bin_atomonly_newton.cpp:33-113) */
+static void build_list(ora_sim *s) {
+  const int nlocal = s->nlocal, nt1 = s->ntypes + 1;
+  const double *x = s->x;
+  long n = 0;
+  for (int i = 0; i < nlocal; i++) {
+    long start = n;
+    int itype = s->type[i];
+    double xtmp = x[3 * i], ytmp = x[3 * i + 1], ztmp = x[3 * i + 2];
+    if (s->half) {
+      for (int j = s->bins[i]; j >= 0; j = s->bins[j]) {
+        if (j >= nlocal) {
+          if (x[3 * j + 2] < ztmp) continue;
+          if (x[3 * j + 2] == ztmp) {
+            if (x[3 * j + 1] < ytmp) continue;
+            if (x[3 * j + 1] == ytmp && x[3 * j] < xtmp) continue;
+          }
+        }
+        double delx = xtmp - x[3 * j], dely = ytmp - x[3 * j + 1], delz = ztmp - x[3 * j + 2];
+        double rsq = delx * delx + dely * dely + delz * delz;
+        if (rsq <= s->cutneighsq[itype * nt1 + s->type[j]]) push_neigh(s, &n, j);
+      }
+    }
+    int ibin = s->atom2bin[i];
+    for (int k = 0; k < s->nstencil; k++)
+      for (int j = s->binhead[ibin + s->stencil[k]]; j >= 0; j = s->bins[j]) {
+        if (!s->half && i == j) continue;
+        double delx = xtmp - x[3 * j], dely = ytmp - x[3 * j + 1], delz = ztmp - x[3 * j + 2];
+        double rsq = delx * delx + dely * dely + delz * delz;
+        if (rsq <= s->cutneighsq[itype * nt1 + s->type[j]]) push_neigh(s, &n, j);
+      }
+    s->firstoff[i] = (int)start;
+    s->numneigh[i] = (int)(n - start);
+  }
+}
+
+void ora_neigh_config(ora_sim *s, const double *cutneighsq, double cutneighmax, double skin, int every, int delay,
+                      int check, int half) {
+  int nt = (s->ntypes + 1) * (s->ntypes + 1);
+  s->cutneighsq = realloc(s->cutneighsq, sizeof(double) * nt);
+  memcpy(s->cutneighsq, cutneighsq, sizeof(double) * nt);
+  s->cutneighmax = cutneighmax; s->skin = skin; s->triggersq = 0.25 * skin * skin; /* neighbor.cpp:348 */
+  s->every = every; s->delay = delay; s->check = check; s->half = half;
+  setup_bins(s);
+  create_stencil(s);
+}
+
+/* the reneighbor branch of Verlet::run (verlet.cpp:289-307) + Neighbor::build (neighbor.cpp:2398-2492) */
+int ora_neigh_build(ora_sim *s) {
+  pbc(s);
+  if (borders(s)) return -1;
+  for (int i = 0; i < 3 * s->nlocal; i++) s->xhold[i] = s->x[i];
+  bin_atoms(s);
+  build_list(s);
+  s->ago = 0;
+  s->nbuilds++;
+  return 0;
+}
+
+/* Neighbor::decide + check_distance (neighbor.cpp:2309-2390) */
+static int decide(ora_sim *s) {
+  s->ago++;
+  if (s->ago >= s->delay && s->ago % s->every == 0) {
+    if (!s->check) return 1;
+    int flag = 0;
+    for (int i = 0; i < s->nlocal; i++) {
+      double delx = s->x[3 * i] - s->xhold[3 * i], dely = s->x[3 * i + 1] - s->xhold[3 * i + 1],
+             delz = s->x[3 * i + 2] - s->xhold[3 * i + 2];
+      double rsq = delx * delx + dely * dely + delz * delz;
+      if (rsq > s->triggersq) flag = 1;
+    }
+    if (flag && s->ago == MAX(s->every, s->delay)) s->ndanger++;
+    return flag;
+  }
+  return 0;
+}
+
+/* ---- pair styles ------------------------------------------------------------------------ */
+static double *dup_d(const double *p, long n) { double *q = malloc(sizeof(double) * n); memcpy(q, p, sizeof(double) * n); return q; }
+static int *dup_i(const int *p, long n) { int *q = malloc(sizeof(int) * n); memcpy(q, p, sizeof(int) * n); return q; }
+
+void ora_pair_lj(ora_sim *s, const double *cutsq, const double *lj1, const double *lj2, const double *lj3,
+                 const double *lj4, const double *offset) {
+  long nt = (s->ntypes + 1) * (s->ntypes + 1);
+  s->cutsq = dup_d(cutsq, nt); s->lj1 = dup_d(lj1, nt); s->lj2 = dup_d(lj2, nt); s->lj3 = dup_d(lj3, nt);
+  s->lj4 = dup_d(lj4, nt); s->offset = dup_d(offset, nt);
+  s->pair_style = 1;
+}
+void ora_pair_eam(ora_sim *s, int nrho, int nr, double rdr, double rdrho, double rhomax, double cutforcesq, int nfrho,
+                  const double *frho_spline, int nrhor, const double *rhor_spline, int nz2r, const double *z2r_spline,
+                  const int *type2frho, const int *type2rhor, const int *type2z2r, const double *scale) {
+  long nt = (s->ntypes + 1) * (s->ntypes + 1);
+  s->nrho = nrho; s->nr = nr; s->rdr = rdr; s->rdrho = rdrho; s->rhomax = rhomax; s->cutforcesq = cutforcesq;
+  s->nfrho = nfrho; s->nrhor = nrhor; s->nz2r = nz2r;
+  s->frho_spline = dup_d(frho_spline, (long)nfrho * (nrho + 1) * 7);
+  s->rhor_spline = dup_d(rhor_spline, (long)nrhor * (nr + 1) * 7);
+  s->z2r_spline = dup_d(z2r_spline, (long)nz2r * (nr + 1) * 7);
+  s->type2frho = dup_i(type2frho, s->ntypes + 1); s->type2rhor = dup_i(type2rhor, nt); s->type2z2r = dup_i(type2z2r, nt);
+  s->scale = dup_d(scale, nt);
+  s->pair_style = 2;
+}
+
+/* Pair::virial_fdotr_compute (pair.cpp:1735-1782): sum over owned + ghost before reverse_comm */
+static void virial_fdotr(ora_sim *s) {
+  int nall = s->nlocal + s->nghost;
+  for (int k = 0; k < 6; k++) s->virial[k] = 0.0;
+  for (int i = 0; i < nall; i++) {
+    const double *f = &s->f[3 * i], *x = &s->x[3 * i];
+    s->virial[0] += f[0] * x[0]; s->virial[1] += f[1] * x[1]; s->virial[2] += f[2] * x[2];
+    s->virial[3] += f[1] * x[0]; s->virial[4] += f[2] * x[0]; s->virial[5] += f[2] * x[1];
+  }
+}
+
+/* PairLJCut::compute (pair_lj_cut.cpp:69-137) on the half list with newton_pair on */
+static void compute_lj(ora_sim *s, int eflag, int vflag) {
+  const int nt1 = s->ntypes + 1;
+  double *x = s->x, *f = s->f;
+  s->eng_vdwl = 0.0;
+  for (int i = 0; i < s->nlocal; i++) {
+    double xtmp = x[3 * i], ytmp = x[3 * i + 1], ztmp = x[3 * i + 2];
+    int itype = s->type[i];
+    const int *jlist = &s->neigh[s->firstoff[i]];
+    for (int jj = 0; jj < s->numneigh[i]; jj++) {
+      int j = jlist[jj];
+      double delx = xtmp - x[3 * j], dely = ytmp - x[3 * j + 1], delz = ztmp - x[3 * j + 2];
+      double rsq = delx * delx + dely * dely + delz * delz;
+      int ij = itype * nt1 + s->type[j];
+      if (rsq < s->cutsq[ij]) {
+        double r2inv = 1.0 / rsq;
+        double r6inv = r2inv * r2inv * r2inv;
+        double forcelj = r6inv * (s->lj1[ij] * r6inv - s->lj2[ij]);
+        double fpair = forcelj * r2inv;
+        f[3 * i] += delx * fpair; f[3 * i + 1] += dely * fpair; f[3 * i + 2] += delz * fpair;
+        f[3 * j] -= delx * fpair; f[3 * j + 1] -= dely * fpair; f[3 * j + 2] -= delz * fpair;
+        if (eflag) s->eng_vdwl += r6inv * (s->lj3[ij] * r6inv - s->lj4[ij]) - s->offset[ij];
+      }
+    }
+  }
+  if (vflag) virial_fdotr(s);
+}
+
+/* PairEAM::compute (MANYBODY/pair_eam.cpp:142-328), half list, newton_pair on */
+static void compute_eam(ora_sim *s, int eflag, int vflag) {
+  const int nt1 = s->ntypes + 1, nlocal = s->nlocal, nall = s->nlocal + s->nghost;
+  double *x = s->x, *f = s->f, *rho = s->rho, *fp = s->fp;
+  const int nr = s->nr, nrho = s->nrho;
+  s->eng_vdwl = 0.0;
+  for (int i = 0; i < nall; i++) rho[i] = 0.0;
+  for (int i = 0; i < nlocal; i++) { /* :187-220 */
+    double xtmp = x[3 * i], ytmp = x[3 * i + 1], ztmp = x[3 * i + 2];
+    int itype = s->type[i];
+    const int *jlist = &s->neigh[s->firstoff[i]];
+    for (int jj = 0; jj < s->numneigh[i]; jj++) {
+      int j = jlist[jj];
+      double delx = xtmp - x[3 * j], dely = ytmp - x[3 * j + 1], delz = ztmp - x[3 * j + 2];
+      double rsq = delx * delx + dely * dely + delz * delz;
+      if (rsq < s->cutforcesq) {
+        int jtype = s->type[j];
+        double p = sqrt(rsq) * s->rdr + 1.0;
+        int m = (int)p;
+        m = MIN(m, nr - 1);
+        p -= m;
+        p = MIN(p, 1.0);
+        const double *coeff = &s->rhor_spline[((long)s->type2rhor[jtype * nt1 + itype] * (nr + 1) + m) * 7];
+        rho[i] += ((coeff[3] * p + coeff[4]) * p + coeff[5]) * p + coeff[6];
+        coeff = &s->rhor_spline[((long)s->type2rhor[itype * nt1 + jtype] * (nr + 1) + m) * 7];
+        rho[j] += ((coeff[3] * p + coeff[4]) * p + coeff[5]) * p + coeff[6];
+      }
+    }
+  }
+  reverse_comm_vec(s, rho, 1); /* :224 */
+  for (int i = 0; i < nlocal; i++) { /* :231-247 */
+    double p = rho[i] * s->rdrho + 1.0;
+    int m = (int)p;
+    m = MAX(1, MIN(m, nrho - 1));
+    p -= m;
+    p = MIN(p, 1.0);
+    const double *coeff = &s->frho_spline[((long)s->type2frho[s->type[i]] * (nrho + 1) + m) * 7];
+    fp[i] = (coeff[0] * p + coeff[1]) * p + coeff[2];
+    if (eflag) {
+      double phi = ((coeff[3] * p + coeff[4]) * p + coeff[5]) * p + coeff[6];
+      if (rho[i] > s->rhomax) phi += fp[i] * (rho[i] - s->rhomax);
+      phi *= s->scale[s->type[i] * nt1 + s->type[i]];
+      s->eng_vdwl += phi;
+    }
+  }
+  forward_comm_scalar(s, fp); /* :251 */
+  for (int i = 0; i < nlocal; i++) { /* :257-325 */
+    double xtmp = x[3 * i], ytmp = x[3 * i + 1], ztmp = x[3 * i + 2];
+    int itype = s->type[i];
+    const int *jlist = &s->neigh[s->firstoff[i]];
+    for (int jj = 0; jj < s->numneigh[i]; jj++) {
+      int j = jlist[jj];
+      double delx = xtmp - x[3 * j], dely = ytmp - x[3 * j + 1], delz = ztmp - x[3 * j + 2];
+      double rsq = delx * delx + dely * dely + delz * delz;
+      if (rsq < s->cutforcesq) {
+        int jtype = s->type[j];
+        double r = sqrt(rsq);
+        double p = r * s->rdr + 1.0;
+        int m = (int)p;
+        m = MIN(m, nr - 1);
+        p -= m;
+        p = MIN(p, 1.0);
+        const double *coeff = &s->rhor_spline[((long)s->type2rhor[itype * nt1 + jtype] * (nr + 1) + m) * 7];
+        double rhoip = (coeff[0] * p + coeff[1]) * p + coeff[2];
+        coeff = &s->rhor_spline[((long)s->type2rhor[jtype * nt1 + itype] * (nr + 1) + m) * 7];
+        double rhojp = (coeff[0] * p + coeff[1]) * p + coeff[2];
+        coeff = &s->z2r_spline[((long)s->type2z2r[itype * nt1 + jtype] * (nr + 1) + m) * 7];
+        double z2p = (coeff[0] * p + coeff[1]) * p + coeff[2];
+        double z2 = ((coeff[3] * p + coeff[4]) * p + coeff[5]) * p + coeff[6];
+        double recip = 1.0 / r;
+        double phi = z2 * recip;
+        double phip = z2p * recip - phi * recip;
+        double psip = fp[i] * rhojp + fp[j] * rhoip + phip;
+        double fpair = -s->scale[itype * nt1 + jtype] * psip * recip;
+        f[3 * i] += delx * fpair; f[3 * i + 1] += dely * fpair; f[3 * i + 2] += delz * fpair;
+        f[3 * j] -= delx * fpair; f[3 * j + 1] -= dely * fpair; f[3 * j + 2] -= delz * fpair;
+        if (eflag) s->eng_vdwl += s->scale[itype * nt1 + jtype] * phi;
+      }
+    }
+  }
+  if (vflag) virial_fdotr(s);
+}
+
+/* Verlet::force_clear + pair->compute + comm->reverse_comm (verlet.cpp:311-330) */
+int ora_compute(ora_sim *s, int eflag, int vflag) {
+  if (!s->half) return -1; /* the reference's pair styles consume the half list */
+  int nall = s->nlocal + s->nghost;
+  memset(s->f, 0, sizeof(double) * 3 * nall);
+  if (s->pair_style == 1) compute_lj(s, eflag, vflag);
+  else if (s->pair_style == 2) compute_eam(s, eflag, vflag);
+  else return -1;
+  reverse_comm_vec(s, s->f, 3);
+  return 0;
+}
+
+/* FixNVE::initial_integrate / final_integrate (fix_nve.cpp:64-141) */
+static void nve_initial(ora_sim *s, double dtv, double dtf) {
+  for (int i = 0; i < s->nlocal; i++) {
+    double dtfm = dtf / s->mass[s->type[i]];
+    for (int d = 0; d < 3; d++) {
+      s->v[3 * i + d] += dtfm * s->f[3 * i + d];
+      s->x[3 * i + d] += dtv * s->v[3 * i + d];
+    }
+  }
+}
+static void nve_final(ora_sim *s, double dtf) {
+  for (int i = 0; i < s->nlocal; i++) {
+    double dtfm = dtf / s->mass[s->type[i]];
+    for (int d = 0; d < 3; d++) s->v[3 * i + d] += dtfm * s->f[3 * i + d];
+  }
+}
+
+/* ComputeTemp / ComputePE / ComputePressure (compute_temp.cpp:72-99, compute_pe.cpp:84-112,
+ * compute_pressure.cpp:228-262) */
+void ora_thermo_compute(ora_sim *s, ora_thermo *t) {
+  double dof = 3.0 * s->nlocal - 3.0;
+  double temp = temp_scalar(s);
+  double vol = s->prd[0] * s->prd[1] * s->prd[2];
+  t->step = s->step; t->natoms = s->nlocal; t->temp = temp; t->pe = s->eng_vdwl;
+  t->ke = temp * 0.5 * dof * s->boltz;
+  for (int k = 0; k < 6; k++) t->virial[k] = s->virial[k];
+  t->press = (dof * s->boltz * temp + s->virial[0] + s->virial[1] + s->virial[2]) / 3.0 * (1.0 / vol) * s->nktv2p;
+}
+
+/* Verlet::setup (verlet.cpp:93-162) */
+int ora_setup(ora_sim *s) {
+  if (ora_neigh_build(s)) return -1;
+  return ora_compute(s, 1, 1);
+}
+
+/* Verlet::run (verlet.cpp:229-360) with fix nve; thermo every `thermo_every` steps and at the end */
+int ora_run(ora_sim *s, int nsteps, double dt, int thermo_every, ora_thermo *out, int max_out) {
+  double dtv = dt, dtf = 0.5 * dt * s->ftm2v;
+  long first = s->step, last = s->step + nsteps;
+  int nout = 0;
+  for (int i = 0; i < nsteps; i++) {
+    s->step++;
+    int out_step = (thermo_every > 0 && (s->step - first) % thermo_every == 0) || s->step == last;
+    nve_initial(s, dtv, dtf);
+    if (!decide(s)) forward_comm(s);
+    else if (ora_neigh_build(s)) return -1;
+    if (ora_compute(s, out_step, out_step)) return -1;
+    nve_final(s, dtf);
+    if (out_step && out && nout < max_out) ora_thermo_compute(s, &out[nout++]);
+  }
+  return nout;
+}
+
+/* ---- accessors --------------------------------------------------------------------------- */
+int ora_nlocal(ora_sim *s) { return s->nlocal; }
+int ora_nghost(ora_sim *s) { return s->nghost; }
+int ora_nbuilds(ora_sim *s) { return s->nbuilds; }
+double *ora_x(ora_sim *s) { return s->x; }
+double *ora_v(ora_sim *s) { return s->v; }
+double *ora_f(ora_sim *s) { return s->f; }
+int *ora_tag(ora_sim *s) { return s->tag; }
+int *ora_type(ora_sim *s) { return s->type; }
+int *ora_image(ora_sim *s) { return s->image; }
+int *ora_numneigh(ora_sim *s) { return s->numneigh; }
+long ora_neigh_total(ora_sim *s) { long n = 0; for (int i = 0; i < s->nlocal; i++) n += s->numneigh[i]; return n; }
+/* neighbors as tags, atom after atom in local order */
+void ora_neigh_tags(ora_sim *s, int *out) {
+  long n = 0;
+  for (int i = 0; i < s->nlocal; i++)
+    for (int k = 0; k < s->numneigh[i]; k++) out[n++] = s->tag[s->neigh[s->firstoff[i] + k]];
+}
+void ora_bin_geometry(ora_sim *s, int *out12, double *out6) {
+  int v[12] = {s->nbinx, s->nbiny, s->nbinz, s->mbinx, s->mbiny, s->mbinz, s->mbinxlo, s->mbinylo, s->mbinzlo, s->nstencil, 0, 0};
+  memcpy(out12, v, sizeof(v));
+  double d[6] = {s->binsizex, s->binsizey, s->binsizez, s->bininvx, s->bininvy, s->bininvz};
+  memcpy(out6, d, sizeof(d));
+}
