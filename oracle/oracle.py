@@ -207,11 +207,7 @@ class Reference:
         row0 = C.cast(ptr, C.POINTER(C.POINTER(C.c_double)))[0]
         return np.ctypeslib.as_array(row0, shape=(nall * 3,)).reshape(nall, 3).copy()
 
-    def neighlist_by_tag(self, style):
-        """perpetual pair list of `style` as (tag_i, [tag_j...]) using library.h:219-223"""
-        idx = self.L.lammps_find_pair_neighlist(self.h, style.encode(), 1, 0, 0)
-        if idx < 0:
-            raise RuntimeError("reference: no neighbor list for pair style " + style)
+    def _list_by_tag(self, idx):
         ids = self.local_ids()
         n = self.L.lammps_neighlist_num_elements(self.h, idx)
         out = {}
@@ -221,6 +217,20 @@ class Reference:
             js = np.ctypeslib.as_array(ptr, shape=(nn.value,)) & 0x1FFFFFFF if nn.value else np.empty(0, np.int32)
             out[int(ids[iatom.value])] = ids[js].copy()
         return out
+
+    def neighlist_by_tag(self, style):
+        """perpetual (half, newton on) pair list of `style` as {tag_i: [tag_j...]} (library.h:219-223)"""
+        idx = self.L.lammps_find_pair_neighlist(self.h, style.encode(), 1, 0, 0)
+        if idx < 0:
+            raise RuntimeError("reference: no neighbor list for pair style " + style)
+        return self._list_by_tag(idx)
+
+    def full_neighlist_by_tag(self, compute_id):
+        """the full list (NPairFullBinAtomonly) requested by a `compute coord/atom` with that id"""
+        idx = self.L.lammps_find_compute_neighlist(self.h, compute_id.encode(), 0)
+        if idx < 0:
+            raise RuntimeError("reference: no neighbor list for compute " + compute_id)
+        return self._list_by_tag(idx)
 
 
 IN_LJ = """

@@ -1,0 +1,192 @@
+"""GPU (-m gpu): the CUDA path through the C ABI (libb200md.so via ctypes) against
+  (1) the golden vectors generated from the unmodified reference (tests/golden/*.npz),
+  (2) the C oracle on seeded inputs at sizes it finishes in seconds,
+  (3) the thermo the reference's own logs print for bench/in.lj and bench/in.eam (32k atoms),
+  (4) size-independent properties at the bench's full 2M-atom size.
+Tolerances (BASELINE.json north_star): neighbor lists bit-exact as sorted per-atom sets;
+forces 1e-10 relative (to max |f|) on a single step; thermo 1e-8 relative over 100 steps.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import common as Cm
+from test_oracle_golden import CASES, build_oracle, system_from_golden, tables_for
+
+pytestmark = pytest.mark.gpu
+F_TOL, T_TOL = 1e-10, 1e-8
+KEYS = ("temp", "pe", "ke", "press")
+
+
+def make_ctx(pkg, O, g, kind, list_kind, tpa=8):
+    B = pkg.b200md
+    T = tables_for(pkg, O, kind)
+    s = system_from_golden(pkg, g, kind)
+    if kind != "lj":
+        s["mass"] = np.array([0.0, T["mass"][1]])
+    ctx = B.Context(0)
+    ctx.set_lanes_per_atom(tpa)
+    ctx.set_units("lj" if kind == "lj" else "metal")
+    ctx.set_box(s["boxlo"], s["boxhi"])
+    ctx.set_atoms(s["x"], s["v"], s["type"], s["tag"], s["mass"], image=g["image"])
+    if kind == "lj":
+        ctx.pair_lj_cut_config(*[T[k] for k in ("cutsq", "lj1", "lj2", "lj3", "lj4", "offset")])
+        cutsq = T["cutsq"]; sched = (20, 0, 0)
+    else:
+        ctx.pair_eam_config(T)
+        cutsq = np.zeros((2, 2)); cutsq[1, 1] = T["cutforcesq"]; sched = (1, 5, 1)
+    cn, cmax = B.cutneighsq_table(1, cutsq, s["skin"])
+    ctx.neigh_config(cn, cmax, s["skin"], every=sched[0], delay=sched[1], check=sched[2], list_kind=list_kind)
+    return ctx, s
+
+
+@pytest.mark.parametrize("tpa", [4, 8, 16, 32])
+@pytest.mark.parametrize("name,kind", CASES)
+def test_golden_full_list_forces_thermo(pkg, oracle_mod, name, kind, tpa):
+    B = pkg.b200md
+    g = np.load(os.path.join(Cm.GOLDEN, name + ".npz"))
+    ctx, s = make_ctx(pkg, oracle_mod, g, kind, B.LIST_FULL, tpa)
+    ctx.setup()
+    a = ctx.get_atoms()
+    nn, flat = ctx.neigh_export(by_tag=True)
+    got = Cm.full_sets(a["tag"], nn, flat)
+    want = np.sort(g["full_i"].astype(np.int64) * (1 << 32) + g["full_j"].astype(np.int64))
+    assert np.array_equal(got, want)  # bit-exact per-atom sets
+    order = np.argsort(a["tag"])
+    fmax = np.abs(g["f"]).max()
+    assert np.abs(a["f"][order] - g["f"]).max() <= F_TOL * fmax
+    t = ctx.thermo()
+    for k, key in enumerate(KEYS):
+        assert abs(t[key] - g["thermo0"][k]) <= T_TOL * abs(g["thermo0"][k]), key
+    for row in g["thermo_series"]:
+        ctx.setup()
+        t = ctx.run(10, s["dt"], 0)[-1]
+        for k, key in enumerate(KEYS):
+            assert abs(t[key] - row[k]) <= T_TOL * abs(row[k]), (key, t[key], row[k])
+    ctx.close()
+
+
+def test_golden_half_list_lj(pkg, oracle_mod):
+    B = pkg.b200md
+    g = np.load(os.path.join(Cm.GOLDEN, "lj_n5.npz"))
+    ctx, s = make_ctx(pkg, oracle_mod, g, "lj", B.LIST_HALF_NEWTON)
+    ctx.setup()
+    a = ctx.get_atoms()
+    nn, flat = ctx.neigh_export(by_tag=True)
+    got = Cm.pairs_from_lists(a["tag"], nn, flat)
+    want = np.sort(g["half_lo"].astype(np.int64) * (1 << 32) + g["half_hi"].astype(np.int64))
+    assert np.array_equal(got, want)
+    order = np.argsort(a["tag"])
+    assert np.abs(a["f"][order] - g["f"]).max() <= F_TOL * np.abs(g["f"]).max()
+    t = ctx.thermo()
+    for k, key in enumerate(KEYS):
+        assert abs(t[key] - g["thermo0"][k]) <= T_TOL * abs(g["thermo0"][k]), key
+    ctx.close()
+
+
+def test_lattice_and_velocity_match_oracle_input(pkg, oracle_mod):
+    """x, v after `velocity ... loop geom` + zero momentum + rescale: GPU state vs oracle state."""
+    B = pkg.b200md
+    s = Cm.lj_system(pkg, 8)
+    T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 2.5)}, 2.5)
+    o = Cm.make_oracle(oracle_mod, pkg, s, "lj", T, 20, 0, 0)
+    ctx = B.Context(0)
+    pkg.inputs.in_lj(ctx, 1, 1, 1) if False else None
+    ctx.set_units("lj"); ctx.set_box(s["boxlo"], s["boxhi"])
+    ctx.set_atoms(s["x"], s["v"], s["type"], s["tag"], s["mass"])
+    ctx.velocity_finalize(1.44, True)
+    a, b = ctx.get_atoms(), o.atoms()
+    assert np.array_equal(a["x"], b["x"])
+    assert np.abs(a["v"] - b["v"]).max() <= 1e-13 * np.abs(b["v"]).max()
+    ctx.close(); o.close()
+
+
+@pytest.mark.parametrize("kind", ["lj", "eam"])
+def test_32k_vs_oracle(pkg, oracle_mod, kind):
+    """bench size (32 000 atoms): lists, single-step forces and 100-step thermo vs the oracle."""
+    B = pkg.b200md
+    ctx = B.Context(0)
+    if kind == "lj":
+        cfg = pkg.inputs.in_lj(ctx, 1, 1, 1)
+        s = Cm.lj_system(pkg, 20)
+        T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 2.5)}, 2.5)
+        sched = (20, 0, 0)
+    else:
+        pot = os.path.join(oracle_mod.POT_DIR, "Cu_u3.eam")
+        cfg = pkg.inputs.in_eam(ctx, 1, 1, 1, potential=pot)
+        T = pkg.eam_host.tables_from_funcfl([pot])
+        s = Cm.eam_system(pkg, 20, T["mass"][1])
+        sched = (1, 5, 1)
+    o = Cm.make_oracle(oracle_mod, pkg, s, kind, T, *sched, half=True)
+    ofull = Cm.make_oracle(oracle_mod, pkg, s, kind, T, *sched, half=False)
+    ctx.setup(); o.setup(); ofull.neigh_build()
+    a, b = ctx.get_atoms(), o.atoms()
+    nn, flat = ctx.neigh_export(True)
+    nno, flo = ofull.neigh_tags()
+    assert np.array_equal(Cm.full_sets(a["tag"], nn, flat), Cm.full_sets(ofull.atoms()["tag"], nno, flo))
+    # a perfect lattice has zero net force: step 30 steps first so forces are O(10)
+    ctx.run(30, cfg["dt"], 0); o.run(30, cfg["dt"], 0)
+    a, b = ctx.get_atoms(), o.atoms()
+    fa, fb = a["f"][np.argsort(a["tag"])], b["f"][np.argsort(b["tag"])]
+    assert np.abs(fa - fb).max() <= 1e-9 * np.abs(fb).max()  # 30 steps of round-off growth
+    ta = ctx.run(70, cfg["dt"], 0)[-1]; tb = o.run(70, cfg["dt"], 0)[-1]
+    for key in KEYS:
+        assert abs(ta[key] - tb[key]) <= T_TOL * abs(tb[key]), (key, ta[key], tb[key])
+    assert ctx.neigh_stats()["nbuilds"] == o.nbuilds()
+    ctx.close(); o.close(); ofull.close()
+
+
+# thermo printed by the reference's own logs (bench/log.6Oct16.{lj,eam}.fixed.icc.1), 8 digits
+LOG_LJ = {0: (1.44, -6.7733681, -4.6134356, -5.0197073), 100: (0.7574531, -5.7585055, -4.6223613, 0.20726105)}
+LOG_EAM = {0: (1600.0, -113280.0, -106662.09, 18703.573), 50: (781.69049, -109873.35, -106640.13, 52273.088),
+           100: (801.832, -109957.3, -106640.77, 51322.821)}
+
+
+def _fmt8(v):
+    return float("%.8g" % v)
+
+
+@pytest.mark.parametrize("kind", ["lj", "eam"])
+def test_bench_logs_reproduced(pkg, oracle_mod, kind):
+    B = pkg.b200md
+    ctx = B.Context(0)
+    if kind == "lj":
+        cfg = pkg.inputs.in_lj(ctx); log = LOG_LJ; per = 32000.0
+    else:
+        cfg = pkg.inputs.in_eam(ctx, potential=os.path.join(oracle_mod.POT_DIR, "Cu_u3.eam")); log = LOG_EAM; per = 1.0
+    ctx.setup()
+    recs = {0: ctx.thermo()}
+    for t in ctx.run(100, cfg["dt"], 50):
+        recs[t["step"]] = t
+    for step, (temp, epair, etot, press) in log.items():
+        t = recs[step]
+        got = (t["temp"], t["pe"] / per, (t["pe"] + t["ke"]) / per, t["press"])
+        for a, b in zip(got, (temp, epair, etot, press)):
+            assert _fmt8(a) == pytest.approx(b, rel=2e-8), (step, got)
+    ctx.close()
+
+
+def test_full_size_properties(pkg):
+    """2 048 000 atoms (the bench workload): list symmetry checksum, zero net force, energy
+    conservation, rebuild count — properties that need no oracle."""
+    B = pkg.b200md
+    ctx = B.Context(0)
+    cfg = pkg.inputs.in_lj(ctx, 4, 4, 4)
+    ctx.setup()
+    a = ctx.get_atoms(("tag",))
+    nn, flat = ctx.neigh_export(True)
+    i = np.repeat(a["tag"].astype(np.int64), nn); j = flat.astype(np.int64)
+    # full list is symmetric: multiset of (i,j) equals multiset of (j,i) -> order-free checksums agree
+    h1 = np.bitwise_xor.reduce((i * 1000003 + j) * 0x9E3779B97F4A7C15 % (1 << 61))
+    h2 = np.bitwise_xor.reduce((j * 1000003 + i) * 0x9E3779B97F4A7C15 % (1 << 61))
+    assert h1 == h2 and (i + j).sum() == (j + i).sum()
+    assert abs(len(j) / cfg["natoms"] - 75.1) < 0.5
+    t0 = ctx.thermo()
+    t1 = ctx.run(100, cfg["dt"], 0)[-1]
+    f = ctx.get_atoms(("f",))["f"]
+    assert np.abs(f.sum(axis=0)).max() <= 1e-9 * np.abs(f).sum()
+    e0, e1 = t0["pe"] + t0["ke"], t1["pe"] + t1["ke"]
+    assert abs(e1 - e0) <= 5e-3 * abs(e0)
+    assert ctx.neigh_stats()["nbuilds"] == 6  # setup + every 20 steps
+    ctx.close()
