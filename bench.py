@@ -1,0 +1,261 @@
+#!/usr/bin/env python3
+"""bench.py — atom-steps/s of the short-range MD hot path (neighbor build -> lj/cut | eam -> fix nve)
+on N B200s of one node, measured on the reference's own bench inputs.
+
+  python bench.py --gpus N --steps K --warmup W [--workload lj|eam] [--impl reference]
+
+A "step" is one MD timestep of the workload (Verlet::run body, /root/reference/src/verlet.cpp:246-359)
+including the neighbor rebuilds that fall inside the K steps.  Workload at N GPUs: bench/in.lj scaled to
+2 048 000 atoms per GPU (-var x/y/z = 4,4,4 / 8,4,4 / 8,8,4 / 8,8,8), weak scaling, one process per GPU,
+spatial decomposition with NCCL halo exchange.  One JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SCALE = {1: (4, 4, 4), 2: (8, 4, 4), 4: (8, 8, 4), 8: (8, 8, 8)}
+# algorithmic bytes: force pass per atom per launch, and whole step per atom-step
+N_FULL = {"lj": 75.2, "eam": 75.5}
+BYTES_KERNEL = {"lj": 28 * 75.2 + 52, "eam": 64 * 75.5 + 104}     # LJ force pass; EAM rho+fp and force passes
+BYTES_STEP = {"lj": 2480.0, "eam": 5510.0}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (via NVML)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.01)
+
+    def result(self):
+        self.stop_flag = True
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def ref_script(workload, xyz, warm, steps):
+    from oracle import oracle as O
+    if workload == "lj":
+        body = O.IN_LJ.format(nx=20 * xyz[0], ny=20 * xyz[1], nz=20 * xyz[2])
+    else:
+        body = O.IN_EAM.format(nx=20 * xyz[0], ny=20 * xyz[1], nz=20 * xyz[2], style="eam",
+                               coeff="1 1 " + os.path.join(O.POT_DIR, "Cu_u3.eam"))
+    body = body.replace("atom_modify map array\n", "")
+    return body + ("run %d\n" % warm if warm > 0 else "") + "run %d\n" % steps
+
+
+def run_reference(workload, xyz, warm, steps, cores):
+    """the reference's own CPU implementation (oracle/_ref/lmp, OPENMP package on all host cores)"""
+    import re
+    from oracle import oracle as O
+    t0 = time.time()
+    _, atoms, nst, out = O.ref_exe_run(ref_script(workload, xyz, warm, steps), threads=cores, omp=True, timeout=3000)
+    loops = re.findall(r"Loop time of ([0-9.eE+-]+) on \d+ procs for (\d+) steps with (\d+) atoms", out)
+    lt, nst, atoms = float(loops[-1][0]), int(loops[-1][1]), int(loops[-1][2])
+    return atoms * nst / lt, lt, atoms, time.time() - t0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--workload", default="lj", choices=["lj", "eam"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--lanes", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    ngpus = a.gpus
+    xyz = SCALE.get(ngpus, (4 * ngpus, 4, 4))
+    natoms = 4 * 8000 * xyz[0] * xyz[1] * xyz[2]
+    wl = a.workload
+    config = {"workload": "bench/in.%s -var x %d -var y %d -var z %d (%d atoms, fcc lattice, %s, NVE)" % (
+        wl, xyz[0], xyz[1], xyz[2], natoms, "lj/cut 2.5, neigh every 20" if wl == "lj" else "eam Cu_u3, neigh check yes"),
+        "atoms_per_gpu": natoms // ngpus, "decomposition": None,
+        "l2": "working set (neighbor list >= 1 GB/GPU) exceeds the 126 MB L2; no flush needed"}
+    cores = os.cpu_count() or 1
+
+    if a.impl == "reference":
+        if rank != 0:
+            return 0
+        val, lt, atoms, wall = run_reference(wl, xyz, a.warmup, a.steps, cores)
+        line = {"impl": "reference", "metric": "atom-steps/s", "value": val, "unit": "atom-steps/s", "n_gpus": ngpus,
+                "steps": a.steps, "warmup": a.warmup, "ms_per_step": lt / a.steps * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": val, "unit": "atom-steps/s", "cores": cores, "kind": "reference",
+                                 "sample": "full workload, %d steps, oracle/_ref/lmp -sf omp -pk omp %d" % (a.steps, cores)},
+                "e2e": {"value": val, "unit": "atom-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    import b200pkg
+    P = b200pkg.load()
+    B = P.b200md
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = B.Context(local_rank, rank, world)
+    if world > 1:
+        import torch
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt = torch.frombuffer(bytearray(B.Context.unique_id()), dtype=torch.uint8).cuda()
+        dist.broadcast(idt, 0)
+        ctx.comm_init(bytes(idt.cpu().numpy().tobytes()))
+    if a.lanes:
+        ctx.set_lanes_per_atom(a.lanes)
+    if wl == "lj":
+        cfg = P.inputs.in_lj(ctx, *xyz)
+    else:
+        cfg = P.inputs.in_eam(ctx, *xyz, potential=os.path.join(ROOT, "oracle", "_ref", "potentials", "Cu_u3.eam"))
+    config["decomposition"] = "x".join(str(g) for g in B.procgrid(world, [20.0 * xyz[0], 20.0 * xyz[1], 20.0 * xyz[2]]))
+    ctx.setup()
+
+    def barrier():
+        if dist is not None:
+            import torch
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def maxr(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident loop: W warm-up steps, K timed steps ----
+    ctx.run(max(a.warmup, 3), cfg["dt"], 0)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    ctx.run(a.steps, cfg["dt"], 0)
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    tm = ctx.timing()
+    clocks = sampler.result()
+    dev_ms = maxr(tm["total_ms"])
+    ms = max(dev_ms, 0.0) if world == 1 else maxr(wall_ms)
+    value = natoms * a.steps / (ms / 1e3)
+
+    # ---- dominant kernel: pair force kernel(s), CUDA events around each launch on its stream ----
+    os.environ["B200MD_PHASE_TIMING"] = "1"
+    ctx.run(20, cfg["dt"], 0)
+    os.environ["B200MD_PHASE_TIMING"] = "0"
+    tp = ctx.timing()
+    n_eval = 20
+    pair_ms = tp["pair_ms"] / n_eval  # per timestep (LJ: one launch; EAM: rho+fp, fp halo, force)
+    nloc = ctx.nlocal()[0]
+    hbm, which = peaks()
+    achieved = BYTES_KERNEL[wl] * nloc / (pair_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_lj" if wl == "lj" else "k_eam_rho_fp+k_eam_force", "achieved": achieved,
+                "peak": hbm, "peak_source": which, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
+                "kernel_ms": pair_ms, "bytes_per_atom_launch": BYTES_KERNEL[wl],
+                "step_achieved": BYTES_STEP[wl] * (value / ngpus) / 1e9, "step_frac": BYTES_STEP[wl] * (value / ngpus) / 1e9 / hbm,
+                "phases_ms_per_step": {k: tp[k + "_ms"] / n_eval for k in ("pair", "neigh", "comm", "modify")}}
+    tr = os.path.join(ROOT, "profiles", "traffic_%s.json" % wl)
+    if os.path.exists(tr):
+        roofline["traffic"] = json.load(open(tr)).get("dram_bytes_per_launch")
+
+    # ---- end to end through the C ABI with HOST buffers: every step uploads x,v (pinned) and
+    # downloads x,v,f,tag of the step's result ----
+    n = ctx.nlocal()[0]
+    cap = int(n * 1.05) + 1024
+    hx, hv, hf = B.pinned_empty((cap, 3)), B.pinned_empty((cap, 3)), B.pinned_empty((cap, 3))
+    htag = B.pinned_empty((cap,), np.int32)
+    ctx.get_atoms_into(hx, hv, hf, htag)
+    e2e_steps = a.steps
+    for _ in range(3):
+        ctx.put_atoms(hx, hv); ctx.run(1, cfg["dt"], 0); ctx.get_atoms_into(hx, hv, hf, htag)
+    barrier()
+    t0 = time.perf_counter()
+    h2d = d2h = 0
+    for _ in range(e2e_steps):
+        n = ctx.nlocal()[0]
+        ctx.put_atoms(hx, hv)
+        ctx.run(1, cfg["dt"], 0)
+        n = ctx.nlocal()[0]
+        ctx.get_atoms_into(hx, hv, hf, htag)
+        h2d += 48 * n; d2h += 76 * n
+    barrier()
+    e2e_ms = maxr((time.perf_counter() - t0) * 1e3)
+    e2e = {"value": natoms * e2e_steps / (e2e_ms / 1e3), "unit": "atom-steps/s", "h2d_bytes_per_step": h2d // e2e_steps,
+           "d2h_bytes_per_step": d2h // e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
+           "api": "b200md_put_atoms(x,v) + b200md_run(1) + b200md_get_atoms(x,v,f,tag), pinned host buffers"}
+
+    line = {"metric": "atom-steps/s", "value": value, "unit": "atom-steps/s", "n_gpus": ngpus, "steps": a.steps,
+            "warmup": max(a.warmup, 3), "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config, "roofline": roofline, "e2e": e2e,
+            "gpu_launches": int(tm["launches"]), "clocks": clocks, "device_ms": dev_ms, "wall_ms": wall_ms,
+            "rebuilds_in_timed_region": int(tm["nbuilds"])}
+    if rank == 0 and not a.no_cpu_baseline and ngpus == 1:
+        try:
+            sample_steps = 20
+            val, lt, atoms, wall = run_reference(wl, xyz, 0, sample_steps, cores)
+            line["cpu_baseline"] = {"value": val, "unit": "atom-steps/s", "cores": cores, "kind": "reference",
+                                    "sample": "same workload (%d atoms), %d steps, oracle/_ref/lmp -sf omp -pk omp %d, Loop time %.3f s"
+                                              % (atoms, sample_steps, cores, lt)}
+        except Exception as e:  # the checker is optional for the measurement itself
+            line["cpu_baseline"] = {"value": None, "unit": "atom-steps/s", "cores": cores, "kind": "reference",
+                                    "sample": "unavailable: %s" % str(e)[:200]}
+    ctx.close()
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

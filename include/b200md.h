@@ -21,6 +21,8 @@
 #ifndef B200MD_H
 #define B200MD_H
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -125,6 +127,14 @@ int b200md_set_atoms(b200md_ctx *ctx, int nlocal, const double *x_aos, const dou
 int b200md_get_nlocal(b200md_ctx *ctx, int *nlocal, int *nghost);
 int b200md_get_atoms(b200md_ctx *ctx, double *x_aos, double *v_aos, double *f_aos, int *type,
                      int *tag, int *image);
+/* Overwrite x and/or v of the owned atoms IN CURRENT LOCAL ORDER (the order b200md_get_atoms
+ * returns) from host arrays: the per-step upload of a host-resident integrator, like the
+ * reference GPU package's per-step `host_x` (src/GPU/pair_lj_cut_gpu.cpp:98-102).  Asynchronous
+ * on the context's stream when the host memory is pinned. */
+int b200md_put_atoms(b200md_ctx *ctx, const double *x_aos, const double *v_aos);
+/* pinned host memory for put/get */
+int b200md_host_alloc(void **ptr, size_t bytes);
+int b200md_host_free(void *ptr);
 /* ghost atoms (x with periodic shift applied, tag, type) in local order nlocal..nall-1 */
 int b200md_get_ghosts(b200md_ctx *ctx, double *x_aos, int *type, int *tag);
 

@@ -139,6 +139,15 @@ def lattice_fcc(scale, nx, ny, nz, sublo, subhi, seed, mass):
     return x, v, tag
 
 
+def pinned_empty(shape, dtype=np.float64):
+    """numpy array over cudaMallocHost memory (b200md_host_alloc); kept alive by the array's base."""
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    ptr = C.c_void_p()
+    _chk(lib().b200md_host_alloc(C.byref(ptr), C.c_size_t(max(n, 8))))
+    buf = (C.c_char * max(n, 8)).from_address(ptr.value)
+    return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+
 # ---- unit systems (src/update.cpp:145-200) ---------------------------------------------------
 UNITS = {
     "lj": dict(boltz=1.0, mvv2e=1.0, ftm2v=1.0, nktv2p=1.0, dt=0.005, skin=0.3),
@@ -216,6 +225,15 @@ class Context:
         for k in fields:
             out[k] = arr[k]
         return out
+
+    def get_atoms_into(self, x=None, v=None, f=None, tag=None):
+        """download into caller-provided (pinned) arrays; no allocation"""
+        g = lambda a: _p(a) if a is not None else None
+        _chk(self.L.b200md_get_atoms(self.h, g(x), g(v), g(f), None, g(tag), None))
+
+    def put_atoms(self, x=None, v=None):
+        g = lambda a: _p(a) if a is not None else None
+        _chk(self.L.b200md_put_atoms(self.h, g(x), g(v)))
 
     def get_ghosts(self):
         _, n = self.nlocal()

@@ -66,7 +66,7 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
                   c->image_tmp, c->mass, c->cutneighsq, c->atom_bin, c->cell_count, c->cell_start, c->cell_fill,
                   c->cell_atoms, c->perm, c->scan_block, c->row_off, c->row_sx, c->row_flag, c->neigh, c->numneigh,
                   c->ghost_src, c->ghost_pbc, c->sendbuf, c->recvbuf, c->ljtab, c->rho, c->fp, c->partials,
-                  c->d_result, c->d_flags};
+                  c->d_result, c->d_flags, c->stage};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->h_result) cudaFreeHost(c->h_result);
   if (c->h_flags) cudaFreeHost(c->h_flags);
@@ -187,24 +187,66 @@ extern "C" int b200md_get_nlocal(b200md_ctx *c, int *nlocal, int *nghost) {
   return B200MD_OK;
 }
 
+static int stage(b200md_ctx *c, size_t bytes) {
+  if (bytes <= c->stage_cap) return B200MD_OK;
+  if (c->stage) CUDA_TRY(cudaFree(c->stage));
+  c->stage_cap = bytes + bytes / 4 + (1 << 20);
+  CUDA_TRY(cudaMalloc(&c->stage, c->stage_cap));
+  return B200MD_OK;
+}
+
 static int download(b200md_ctx *c, int first, int n, double *x, double *v, double *f, int *type, int *tag, int *image) {
   if (n == 0) return B200MD_OK;
   CUDA_TRY(cudaSetDevice(c->device));
-  double *dx = nullptr, *dv = nullptr, *df = nullptr; int *dt = nullptr;
-  if (x) CUDA_TRY(cudaMalloc(&dx, sizeof(double) * 3 * n));
-  if (v) CUDA_TRY(cudaMalloc(&dv, sizeof(double) * 3 * n));
-  if (f) CUDA_TRY(cudaMalloc(&df, sizeof(double) * 3 * n));
-  if (type) CUDA_TRY(cudaMalloc(&dt, sizeof(int) * n));
+  const size_t n3 = sizeof(double) * 3 * (size_t)n;
+  TRY(stage(c, 3 * n3 + sizeof(int) * (size_t)n));
+  double *dx = x ? (double *)c->stage : nullptr;
+  double *dv = v ? (double *)(c->stage + n3) : nullptr;
+  double *df = f ? (double *)(c->stage + 2 * n3) : nullptr;
+  int *dt = type ? (int *)(c->stage + 3 * n3) : nullptr;
   k_download_atoms<<<(n + 255) / 256, 256, 0, c->stream>>>(n, first, c->nmax, c->xq, c->v, c->f, dx, dv, df, dt);
+  c->launches++;
   CUDA_TRY(cudaGetLastError());
-  if (x) CUDA_TRY(cudaMemcpyAsync(x, dx, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, c->stream));
-  if (v) CUDA_TRY(cudaMemcpyAsync(v, dv, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, c->stream));
-  if (f) CUDA_TRY(cudaMemcpyAsync(f, df, sizeof(double) * 3 * n, cudaMemcpyDeviceToHost, c->stream));
+  if (x) CUDA_TRY(cudaMemcpyAsync(x, dx, n3, cudaMemcpyDeviceToHost, c->stream));
+  if (v) CUDA_TRY(cudaMemcpyAsync(v, dv, n3, cudaMemcpyDeviceToHost, c->stream));
+  if (f) CUDA_TRY(cudaMemcpyAsync(f, df, n3, cudaMemcpyDeviceToHost, c->stream));
   if (type) CUDA_TRY(cudaMemcpyAsync(type, dt, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
   if (tag) CUDA_TRY(cudaMemcpyAsync(tag, c->tag + first, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
   if (image) CUDA_TRY(cudaMemcpyAsync(image, c->image + first, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
-  if (dx) cudaFree(dx); if (dv) cudaFree(dv); if (df) cudaFree(df); if (dt) cudaFree(dt);
+  return B200MD_OK;
+}
+
+__global__ void k_put_xv(int n, int nmax, const double *__restrict__ x, const double *__restrict__ v,
+                         double4 *__restrict__ xq, double *__restrict__ vo) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (x) { double4 q = xq[i]; q.x = x[3 * i]; q.y = x[3 * i + 1]; q.z = x[3 * i + 2]; xq[i] = q; }
+  if (v) { const size_t s = (size_t)nmax; vo[i] = v[3 * i]; vo[i + s] = v[3 * i + 1]; vo[i + 2 * s] = v[3 * i + 2]; }
+}
+
+extern "C" int b200md_put_atoms(b200md_ctx *c, const double *x, const double *v) {
+  NEED(c, "b200md: null context");
+  const int n = c->nlocal;
+  if (n == 0 || (!x && !v)) return B200MD_OK;
+  CUDA_TRY(cudaSetDevice(c->device));
+  const size_t n3 = sizeof(double) * 3 * (size_t)n;
+  TRY(stage(c, 2 * n3));
+  double *dx = x ? (double *)c->stage : nullptr, *dv = v ? (double *)(c->stage + n3) : nullptr;
+  if (x) CUDA_TRY(cudaMemcpyAsync(dx, x, n3, cudaMemcpyHostToDevice, c->stream));
+  if (v) CUDA_TRY(cudaMemcpyAsync(dv, v, n3, cudaMemcpyHostToDevice, c->stream));
+  k_put_xv<<<(n + 255) / 256, 256, 0, c->stream>>>(n, c->nmax, dx, dv, c->xq, c->v);
+  c->launches++;
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
+extern "C" int b200md_host_alloc(void **ptr, size_t bytes) {
+  CUDA_TRY(cudaMallocHost(ptr, bytes));
+  return B200MD_OK;
+}
+extern "C" int b200md_host_free(void *ptr) {
+  CUDA_TRY(cudaFreeHost(ptr));
   return B200MD_OK;
 }
 

@@ -122,6 +122,8 @@ struct b200md_ctx {
   double *h_result = nullptr;  // pinned [16]
   int *d_flags = nullptr;      // device [8]: 0 rebuild flag, 1 overflow, 2 nonfinite, 3 counter
   int *h_flags = nullptr;      // pinned [8]
+  char *stage = nullptr;  // device staging for host<->device atom transfers
+  size_t stage_cap = 0;
   // last energies
   double eng_vdwl = 0, virial[6] = {0, 0, 0, 0, 0, 0};
   bool ev_valid = false;

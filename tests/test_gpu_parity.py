@@ -178,9 +178,11 @@ def test_full_size_properties(pkg):
     nn, flat = ctx.neigh_export(True)
     i = np.repeat(a["tag"].astype(np.int64), nn); j = flat.astype(np.int64)
     # full list is symmetric: multiset of (i,j) equals multiset of (j,i) -> order-free checksums agree
-    h1 = np.bitwise_xor.reduce((i * 1000003 + j) * 0x9E3779B97F4A7C15 % (1 << 61))
-    h2 = np.bitwise_xor.reduce((j * 1000003 + i) * 0x9E3779B97F4A7C15 % (1 << 61))
-    assert h1 == h2 and (i + j).sum() == (j + i).sum()
+    iu, ju, K = i.astype(np.uint64), j.astype(np.uint64), np.uint64(0x9E3779B97F4A7C15)
+    h1 = np.bitwise_xor.reduce((iu * np.uint64(1000003) + ju) * K)  # uint64 wrap-around hash
+    h2 = np.bitwise_xor.reduce((ju * np.uint64(1000003) + iu) * K)
+    s1 = ((iu * np.uint64(1000003) + ju) * K).sum(); s2 = ((ju * np.uint64(1000003) + iu) * K).sum()
+    assert h1 == h2 and s1 == s2
     assert abs(len(j) / cfg["natoms"] - 75.1) < 0.5
     t0 = ctx.thermo()
     t1 = ctx.run(100, cfg["dt"], 0)[-1]
