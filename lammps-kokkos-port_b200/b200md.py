@@ -62,6 +62,15 @@ def lib():
     if _lib is None:
         if not os.path.exists(LIB_PATH):
             raise B200MDError("libb200md.so is not built (%s); run __graft_entry__.build()" % LIB_PATH)
+        # bind the same NCCL torch ships (site-packages/nvidia/nccl) so that load order of torch and
+        # this library does not matter; falls back to the system libnccl.so.2
+        try:
+            import importlib.util
+            spec = importlib.util.find_spec("nvidia.nccl")
+            if spec and spec.submodule_search_locations:
+                C.CDLL(os.path.join(list(spec.submodule_search_locations)[0], "lib", "libnccl.so.2"), mode=C.RTLD_GLOBAL)
+        except OSError:
+            pass
         _lib = C.CDLL(LIB_PATH)
         _lib.b200md_last_error.restype = C.c_char_p
         _lib.b200md_version.restype = C.c_char_p

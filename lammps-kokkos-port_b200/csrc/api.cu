@@ -46,6 +46,16 @@ extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out)
   memset(&c->bin, 0, sizeof(c->bin));
   memset(&c->sched, 0, sizeof(c->sched));
   CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  {  // halo traffic gets the highest priority so its small kernels slip in between force blocks
+    int lo = 0, hi = 0;
+    CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CUDA_TRY(cudaStreamCreateWithPriority(&c->comm_stream, cudaStreamNonBlocking, hi));
+  }
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_x, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_fp, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_fphalo, cudaEventDisableTiming));
+  { const char *ov = getenv("B200MD_OVERLAP"); c->overlap = !(ov && ov[0] == '0'); }
   CUDA_TRY(cudaMalloc(&c->d_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMallocHost(&c->h_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMalloc(&c->d_flags, 8 * sizeof(int)));
@@ -66,11 +76,14 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
                   c->image_tmp, c->mass, c->cutneighsq, c->atom_bin, c->cell_count, c->cell_start, c->cell_fill,
                   c->cell_atoms, c->perm, c->scan_block, c->row_off, c->row_sx, c->row_flag, c->neigh, c->numneigh,
                   c->ghost_src, c->ghost_pbc, c->sendbuf, c->recvbuf, c->ljtab, c->rho, c->fp, c->partials,
-                  c->d_result, c->d_flags, c->stage};
+                  c->d_result, c->d_flags, c->stage, c->tile_ghost, c->tile_pos, c->tiles_int, c->tiles_bnd};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->h_result) cudaFreeHost(c->h_result);
   if (c->h_flags) cudaFreeHost(c->h_flags);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
+  cudaEvent_t evs[] = {c->ev_x, c->ev_halo, c->ev_fp, c->ev_fphalo};
+  for (auto e : evs) if (e) cudaEventDestroy(e);
+  if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
   cudaStreamDestroy(c->stream);
   delete c;
   return B200MD_OK;
@@ -524,6 +537,45 @@ extern "C" int b200md_setup(b200md_ctx *c) {
   return B200MD_OK;
 }
 
+// Non-rebuild, non-thermo step on several ranks: the forward halo (and EAM's fp halo) runs on the
+// comm stream while the tiles without ghost neighbors are evaluated; boundary tiles follow.
+// Same kernels, same per-atom arithmetic and order as the unsplit launch -> identical results.
+static bool can_overlap(const b200md_ctx *c) {
+  return c->overlap && !c->all_self && c->list_kind == B200MD_LIST_FULL && c->n_tiles_int > 0;
+}
+static int on_comm_stream(b200md_ctx *c, int (*fn)(b200md_ctx *)) {
+  cudaStream_t saved = c->stream;
+  c->stream = c->comm_stream;
+  int r = fn(c);
+  c->stream = saved;
+  return r;
+}
+static int forces_overlapped(b200md_ctx *c) {
+  cudaStream_t s = c->stream, cs = c->comm_stream;
+  CUDA_TRY(cudaEventRecord(c->ev_x, s));               // positions integrated
+  CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_x, 0));
+  TRY(on_comm_stream(c, comm_forward));                // x halo on the comm stream
+  CUDA_TRY(cudaEventRecord(c->ev_halo, cs));
+  c->ev_valid = false;
+  if (c->pair_style == B200MD_PAIR_LJ_CUT) {
+    TRY(pair_lj_launch(c, false, c->tiles_int, c->n_tiles_int));
+    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
+    TRY(pair_lj_launch(c, false, c->tiles_bnd, c->n_tiles_bnd));
+  } else {
+    TRY(pair_eam_launch(c, false, 0, c->tiles_int, c->n_tiles_int));
+    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
+    TRY(pair_eam_launch(c, false, 0, c->tiles_bnd, c->n_tiles_bnd));
+    CUDA_TRY(cudaEventRecord(c->ev_fp, s));            // fp of every owned atom is final
+    CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_fp, 0));
+    TRY(on_comm_stream(c, pair_eam_fp_comm));          // fp halo on the comm stream
+    CUDA_TRY(cudaEventRecord(c->ev_fphalo, cs));
+    TRY(pair_eam_launch(c, false, 1, c->tiles_int, c->n_tiles_int));
+    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_fphalo, 0));
+    TRY(pair_eam_launch(c, false, 1, c->tiles_bnd, c->n_tiles_bnd));
+  }
+  return B200MD_OK;
+}
+
 struct PhaseTimer {
   b200md_ctx *c; bool on; size_t *used; std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> spans;
   cudaEvent_t get() {
@@ -555,9 +607,13 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     T.begin(4); TRY(b200md_nve_initial(c, dtv, dtf)); T.end();
     int nflag = 0;
     TRY(b200md_neigh_decide(c, &nflag));
-    if (!nflag) { T.begin(3); TRY(comm_forward(c)); T.end(); }
-    else { T.begin(2); TRY(b200md_neigh_build(c)); T.end(); }
-    T.begin(1); TRY(b200md_pair_compute(c, ev, ev, nullptr, nullptr)); T.end();
+    if (!nflag && !ev && can_overlap(c)) {
+      T.begin(1); TRY(forces_overlapped(c)); T.end();
+    } else {
+      if (!nflag) { T.begin(3); TRY(comm_forward(c)); T.end(); }
+      else { T.begin(2); TRY(b200md_neigh_build(c)); T.end(); }
+      T.begin(1); TRY(b200md_pair_compute(c, ev, ev, nullptr, nullptr)); T.end();
+    }
     T.begin(3); TRY(comm_reverse_force(c)); T.end();
     T.begin(4); TRY(nve_final(c, dtf)); T.end();
     if (out_step && thermo_out && nth < max_thermo) { TRY(b200md_thermo_compute(c, &thermo_out[nth])); nth++; }

@@ -102,6 +102,12 @@ struct b200md_ctx {
   int *neigh = nullptr;
   size_t neigh_cap = 0;
   int *numneigh = nullptr;  // [nmax]
+  // tiles (warps) split by 'has a ghost neighbor' for compute/halo overlap
+  int *tile_ghost = nullptr, *tile_pos = nullptr, *tiles_int = nullptr, *tiles_bnd = nullptr;
+  int tile_cap = 0, n_tiles_int = 0, n_tiles_bnd = 0;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_x = nullptr, ev_halo = nullptr, ev_fp = nullptr, ev_fphalo = nullptr;
+  bool overlap = true;
   // comm
   b200md_swap_schedule sched;
   std::vector<Swap> swaps;
@@ -177,6 +183,9 @@ int comm_allreduce_max_int(b200md_ctx *c, int *hostval);
 void comm_free(b200md_ctx *c);
 // pair_lj.cu / pair_eam.cu
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag);
+int pair_lj_launch(b200md_ctx *c, bool ev, const int *tiles, int ntl);
+int pair_eam_launch(b200md_ctx *c, bool ev, int pass, const int *tiles, int ntl);
+int pair_eam_fp_comm(b200md_ctx *c);
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);
 // nve.cu
 int nve_initial(b200md_ctx *c, double dtv, double dtf, bool check_dist);

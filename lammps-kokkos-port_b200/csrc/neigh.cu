@@ -430,7 +430,7 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
         const double4 *__restrict__ cell_xq, int nrows, const int *__restrict__ row_off,
         const int *__restrict__ row_sx, const int *__restrict__ row_flag,
         const double *__restrict__ cutneighsq, int ntypes, int *__restrict__ neigh,
-        int *__restrict__ numneigh, int pitch, int *flags) {
+        int *__restrict__ numneigh, int pitch, int *flags, int *__restrict__ tile_ghost) {
   constexpr int A = 32 / TPA;
   __shared__ int s_off[MAX_ROWS], s_sx[MAX_ROWS], s_flag[MAX_ROWS];
   __shared__ double s_cut[(MAX_TYPES_SMEM + 1) * (MAX_TYPES_SMEM + 1)];
@@ -455,6 +455,7 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
   if (active) { qi = xq[i]; ibin = atom_bin[i]; itype = xq_type(qi); }
   const double *cutrow = cut_smem ? &s_cut[itype * nt1] : &cutneighsq[itype * nt1];
   int cnt = 0;
+  bool has_ghost = false;
 
   for (int r = 0; r < nrows; r++) {
     int lo = 0, hi = 0;
@@ -494,6 +495,7 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
       }
       const unsigned m = __ballot_sync(0xffffffffu, keep) & submask_all;
       if (keep) {
+        has_ghost |= (j >= nlocal);
         const int k = cnt + __popc(m & below);
         if (k < pitch) out[(k / TPA) * 32 + (k % TPA)] = j;
       }
@@ -505,6 +507,9 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
     numneigh[i] = cnt;
     if (cnt > pitch) atomicMax(&flags[1], cnt);
   }
+  // tiles whose atoms have no ghost neighbor can be evaluated while the halo is in flight
+  const bool any_ghost = __any_sync(0xffffffffu, has_ghost);
+  if (tile_ghost && lane == 0 && tile * A < nlocal) tile_ghost[tile] = any_ghost ? 1 : 0;
 }
 
 template <int TPA>
@@ -517,11 +522,11 @@ static void launch_build(b200md_ctx *c) {
   if (c->list_kind == B200MD_LIST_HALF_NEWTON)
     k_build<TPA, true><<<nblocks, BUILD_THREADS, 0, c->stream>>>(
         c->nlocal, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, c->cell_xq, c->nrows, c->row_off,
-        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags);
+        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost);
   else
     k_build<TPA, false><<<nblocks, BUILD_THREADS, 0, c->stream>>>(
         c->nlocal, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, c->cell_xq, c->nrows, c->row_off,
-        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags);
+        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost);
 }
 
 static int ensure_neigh_storage(b200md_ctx *c) {
@@ -533,6 +538,39 @@ static int ensure_neigh_storage(b200md_ctx *c) {
     c->neigh_cap = need + need / 8;
     CUDA_TRY(cudaMalloc(&c->neigh, c->neigh_cap * sizeof(int)));
   }
+  if ((int)ntiles + 1 > c->tile_cap) {
+    int *p[] = {c->tile_ghost, c->tile_pos, c->tiles_int, c->tiles_bnd};
+    for (int *q : p) if (q) CUDA_TRY(cudaFree(q));
+    c->tile_cap = (int)ntiles + 1 + (int)ntiles / 8;
+    CUDA_TRY(cudaMalloc(&c->tile_ghost, sizeof(int) * c->tile_cap));
+    CUDA_TRY(cudaMalloc(&c->tile_pos, sizeof(int) * c->tile_cap));
+    CUDA_TRY(cudaMalloc(&c->tiles_int, sizeof(int) * c->tile_cap));
+    CUDA_TRY(cudaMalloc(&c->tiles_bnd, sizeof(int) * c->tile_cap));
+  }
+  return B200MD_OK;
+}
+
+__global__ void k_split_tiles(int ntiles, const int *__restrict__ flag, const int *__restrict__ pos,
+                              int *__restrict__ tiles_int, int *__restrict__ tiles_bnd) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= ntiles) return;
+  if (flag[t]) tiles_bnd[pos[t]] = t; else tiles_int[t - pos[t]] = t;
+}
+
+// interior / boundary tile lists for compute-halo overlap (multi-rank runs only)
+static int neigh_split_tiles(b200md_ctx *c) {
+  c->n_tiles_int = c->n_tiles_bnd = 0;
+  if (c->all_self || c->nlocal == 0) return B200MD_OK;
+  const int A = 32 / c->tpa;
+  const int ntiles = (c->nlocal + A - 1) / A;
+  CUDA_TRY(cudaMemsetAsync(c->tile_ghost + ntiles, 0, sizeof(int), c->stream));
+  TRY(dev_exclusive_scan(c, c->tile_ghost, c->tile_pos, ntiles + 1));
+  k_split_tiles<<<(ntiles + 255) / 256, 256, 0, c->stream>>>(ntiles, c->tile_ghost, c->tile_pos, c->tiles_int, c->tiles_bnd);
+  c->launches++;
+  CUDA_TRY(cudaMemcpyAsync(c->h_flags + 5, c->tile_pos + ntiles, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  c->n_tiles_bnd = c->h_flags[5];
+  c->n_tiles_int = ntiles - c->n_tiles_bnd;
   return B200MD_OK;
 }
 
@@ -563,7 +601,7 @@ int neigh_build_list(b200md_ctx *c) {
     CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     if (c->h_flags[2]) { b200md_set_error("Non-numeric positions - simulation unstable"); return B200MD_ERR; }
-    if (c->h_flags[1] == 0) return B200MD_OK;
+    if (c->h_flags[1] == 0) return neigh_split_tiles(c);
     // overflow: regrow the pitch like the reference's Kokkos path (npair_kokkos.cpp:302-316)
     int p = (int)(c->h_flags[1] * 1.2) + 8;
     c->pitch = (p + 31) / 32 * 32;

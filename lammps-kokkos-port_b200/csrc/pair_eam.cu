@@ -100,7 +100,7 @@ template <int TPA, bool EV, bool ONE, bool SMEM>
 __global__ void __launch_bounds__(EAM_THREADS)
 k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh, const int *__restrict__ numneigh,
              int pitch, EamParams P, double *__restrict__ rho, double *__restrict__ fp, double4 *__restrict__ xfp,
-             double *__restrict__ partials) {
+             double *__restrict__ partials, const int *__restrict__ tile_list, int ntile_list) {
   constexpr int A = 32 / TPA;
   extern __shared__ double s_dyn[];
   const double *tab = ONE ? P.tabC : P.rhoA;
@@ -112,9 +112,11 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
   }
   const int lane = threadIdx.x & 31;
   const int sub = lane / TPA, l = lane % TPA;
-  const int tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const bool in_list = !tile_list || w < ntile_list;
+  const int tile = tile_list ? (in_list ? tile_list[w] : 0) : w;
   const int i = tile * A + sub;
-  const bool active = i < nlocal;
+  const bool active = in_list && i < nlocal;
   const int nt1 = P.ntypes + 1;
   double r_acc = 0;
   int itype = 1;
@@ -184,7 +186,8 @@ template <int TPA, bool EV, bool ONE, bool SMEM>
 __global__ void __launch_bounds__(EAM_THREADS)
 k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 *__restrict__ xfp,
             const int *__restrict__ neigh, const int *__restrict__ numneigh, int pitch, EamParams P,
-            const double *__restrict__ fp, double *__restrict__ f, double *__restrict__ partials) {
+            const double *__restrict__ fp, double *__restrict__ f, double *__restrict__ partials,
+            const int *__restrict__ tile_list, int ntile_list) {
   constexpr int A = 32 / TPA;
   extern __shared__ double s_dyn[];
   const double *tab = P.tabC;
@@ -196,9 +199,11 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
   }
   const int lane = threadIdx.x & 31;
   const int sub = lane / TPA, l = lane % TPA;
-  const int tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const bool in_list = !tile_list || w < ntile_list;
+  const int tile = tile_list ? (in_list ? tile_list[w] : 0) : w;
   const int i = tile * A + sub;
-  const bool active = i < nlocal;
+  const bool active = in_list && i < nlocal;
   const int nt1 = P.ntypes + 1;
   double fx = 0, fy = 0, fz = 0;
   double ev[7] = {0, 0, 0, 0, 0, 0, 0};
@@ -268,45 +273,85 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
   if (EV) block_reduce_store<7>(ev, partials);
 }
 
+struct EamLaunch {
+  EamParams P;
+  int mode;      // 0 general (multi-type), 1 one element / tables via L1, 2 one element / tables in shared memory
+  size_t smem;
+};
+
 template <int TPA, bool EV, bool ONE, bool SMEM>
-static int launch_eam(b200md_ctx *c, int nblocks, const EamParams &P, size_t smem, double *e_embed, double *out7) {
-  auto kA = k_eam_rho_fp<TPA, EV, ONE, SMEM>;
-  auto kC = k_eam_force<TPA, EV, ONE, SMEM>;
-  if (SMEM) {
-    CUDA_TRY(cudaFuncSetAttribute(kA, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CUDA_TRY(cudaFuncSetAttribute(kC, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+static int launch_pass(b200md_ctx *c, const EamLaunch &L, int pass, const int *tiles, int ntl) {
+  const int A = 32 / TPA;
+  const int ntiles = tiles ? ntl : (c->nlocal + A - 1) / A;
+  const int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
+  if (nblocks == 0) return B200MD_OK;
+  if (pass == 0) {
+    auto k = k_eam_rho_fp<TPA, EV, ONE, SMEM>;
+    if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem));
+    k<<<nblocks, EAM_THREADS, SMEM ? L.smem : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, L.P, c->rho,
+                                                            c->fp, c->eam.xfp, c->partials, tiles, ntl);
+  } else {
+    auto k = k_eam_force<TPA, EV, ONE, SMEM>;
+    if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem));
+    k<<<nblocks, EAM_THREADS, SMEM ? L.smem : 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh,
+                                                            c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl);
   }
-  kA<<<nblocks, EAM_THREADS, SMEM ? smem : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, P, c->rho,
-                                                           c->fp, c->eam.xfp, c->partials);
   c->launches++; c->pair_launches++;
   CUDA_TRY(cudaGetLastError());
-  if (EV) { double e1[1]; TRY(reduce_partials(c, nblocks, 1, e1)); *e_embed = e1[0]; }
-  // PairEAM::compute's forward_comm(this): fp of owners -> ghosts (pair_eam.cpp:251, pack :855-876)
-  TRY(comm_forward_scalar(c, c->fp));
-  if (ONE && c->nghost > 0) {
-    k_pack_xfp<<<(c->nghost + 255) / 256, 256, 0, c->stream>>>(c->nghost, c->nlocal, c->xq, c->fp, c->eam.xfp);
-    c->launches++;
+  return B200MD_OK;
+}
+template <int TPA, bool EV>
+static int launch_mode(b200md_ctx *c, const EamLaunch &L, int pass, const int *tiles, int ntl) {
+  if (L.mode == 2) return launch_pass<TPA, EV, true, true>(c, L, pass, tiles, ntl);
+  if (L.mode == 1) return launch_pass<TPA, EV, true, false>(c, L, pass, tiles, ntl);
+  return launch_pass<TPA, EV, false, false>(c, L, pass, tiles, ntl);
+}
+template <int TPA>
+static int launch_tpa(b200md_ctx *c, const EamLaunch &L, bool ev, int pass, const int *tiles, int ntl) {
+  return ev ? launch_mode<TPA, true>(c, L, pass, tiles, ntl) : launch_mode<TPA, false>(c, L, pass, tiles, ntl);
+}
+
+static int eam_prepare(b200md_ctx *c, EamLaunch &L) {
+  EamTables &e = c->eam;
+  if (e.one && e.xfp_cap < c->nmax) {
+    if (e.xfp) CUDA_TRY(cudaFree(e.xfp));
+    CUDA_TRY(cudaMalloc(&e.xfp, sizeof(double4) * (size_t)c->nmax));
+    e.xfp_cap = c->nmax;
   }
-  kC<<<nblocks, EAM_THREADS, SMEM ? smem : 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh,
-                                                           c->pitch, P, c->fp, c->f, c->partials);
-  c->launches++; c->pair_launches++;
-  CUDA_TRY(cudaGetLastError());
-  if (EV) TRY(reduce_partials(c, nblocks, 7, out7));
+  L.P = {e.ntypes, e.nrho, e.nr, e.rdr, e.rdrho, e.rhomax, e.cutforcesq, e.scale11, e.frho, e.rhoA, e.z2rV,
+         e.tabC, e.scale, e.type2frho, e.type2rhor, e.type2z2r};
+  L.smem = (size_t)(e.nr + 1) * 8 * sizeof(double);
+  // measured on B200 (2.05 M atoms, Cu_u3): tabC through L1 752 Matom-steps/s, staged in shared
+  // memory 681 (bank conflicts on the random rows + lower occupancy) -> global is the default
+  const char *sm = getenv("B200MD_EAM_SMEM");
+  L.mode = 0;
+  if (e.one) L.mode = (L.smem <= 64 * 1024 && sm && sm[0] == '1') ? 2 : 1;
   return B200MD_OK;
 }
 
-template <int TPA, bool EV>
-static int launch_eam_mode(b200md_ctx *c, int nblocks, const EamParams &P, int mode, size_t smem, double *e_embed,
-                           double *out7) {
-  if (mode == 2) return launch_eam<TPA, EV, true, true>(c, nblocks, P, smem, e_embed, out7);
-  if (mode == 1) return launch_eam<TPA, EV, true, false>(c, nblocks, P, smem, e_embed, out7);
-  return launch_eam<TPA, EV, false, false>(c, nblocks, P, smem, e_embed, out7);
+// pass: 0 = density + embedding (k_eam_rho_fp), 1 = forces (k_eam_force)
+int pair_eam_launch(b200md_ctx *c, bool ev, int pass, const int *tiles, int ntl) {
+  EamLaunch L;
+  TRY(eam_prepare(c, L));
+  switch (c->tpa) {
+    case 4: return launch_tpa<4>(c, L, ev, pass, tiles, ntl);
+    case 8: return launch_tpa<8>(c, L, ev, pass, tiles, ntl);
+    case 16: return launch_tpa<16>(c, L, ev, pass, tiles, ntl);
+    case 32: return launch_tpa<32>(c, L, ev, pass, tiles, ntl);
+  }
+  b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32");
+  return B200MD_ERR;
 }
-template <int TPA>
-static int launch_eam_tpa(b200md_ctx *c, int nblocks, const EamParams &P, bool ev, int mode, size_t smem,
-                          double *e_embed, double *out7) {
-  return ev ? launch_eam_mode<TPA, true>(c, nblocks, P, mode, smem, e_embed, out7)
-            : launch_eam_mode<TPA, false>(c, nblocks, P, mode, smem, e_embed, out7);
+
+// PairEAM::compute's forward_comm(this): fp of owners -> ghosts (pair_eam.cpp:251, pack :855-876)
+int pair_eam_fp_comm(b200md_ctx *c) {
+  TRY(comm_forward_scalar(c, c->fp));
+  if (c->eam.one && c->nghost > 0) {
+    k_pack_xfp<<<(c->nghost + 255) / 256, 256, 0, c->stream>>>(c->nghost, c->nlocal, c->xq, c->fp, c->eam.xfp);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+  }
+  return B200MD_OK;
 }
 
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag) {
@@ -314,38 +359,18 @@ int pair_eam_compute(b200md_ctx *c, int eflag, int vflag) {
     b200md_set_error("b200md: eam runs on the full neighbor list (newton off) only");
     return B200MD_ERR;
   }
-  EamTables &e = c->eam;
   const bool ev = eflag || vflag;
   const int A = 32 / c->tpa;
   const int ntiles = (c->nlocal + A - 1) / A;
   const int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
   c->ev_valid = false;
-  if (e.one && e.xfp_cap < c->nmax) {
-    if (e.xfp) CUDA_TRY(cudaFree(e.xfp));
-    CUDA_TRY(cudaMalloc(&e.xfp, sizeof(double4) * (size_t)c->nmax));
-    e.xfp_cap = c->nmax;
-  }
-  if (nblocks == 0) {
-    if (ev) { c->eng_vdwl = 0; for (int k = 0; k < 6; k++) c->virial[k] = 0; c->ev_valid = true; }
-    return comm_forward_scalar(c, c->fp);
-  }
-  if (ev) TRY(ensure_partials(c, nblocks));
-  EamParams P = {e.ntypes, e.nrho, e.nr, e.rdr, e.rdrho, e.rhomax, e.cutforcesq, e.scale11, e.frho, e.rhoA, e.z2rV,
-                 e.tabC, e.scale, e.type2frho, e.type2rhor, e.type2z2r};
-  const size_t smem = (size_t)(e.nr + 1) * 8 * sizeof(double);
-  // measured on B200 (2.05 M atoms, Cu_u3): tabC through L1 752 Matom-steps/s, staged in shared
-  // memory 681 (bank conflicts on the random rows + lower occupancy) -> global is the default
-  const char *sm = getenv("B200MD_EAM_SMEM");
-  int mode = 0;
-  if (e.one) mode = (smem <= 64 * 1024 && sm && sm[0] == '1') ? 2 : 1;
+  if (ev && nblocks) TRY(ensure_partials(c, nblocks));
   double e_embed = 0, out7[7] = {0, 0, 0, 0, 0, 0, 0};
-  switch (c->tpa) {
-    case 4: TRY(launch_eam_tpa<4>(c, nblocks, P, ev, mode, smem, &e_embed, out7)); break;
-    case 8: TRY(launch_eam_tpa<8>(c, nblocks, P, ev, mode, smem, &e_embed, out7)); break;
-    case 16: TRY(launch_eam_tpa<16>(c, nblocks, P, ev, mode, smem, &e_embed, out7)); break;
-    case 32: TRY(launch_eam_tpa<32>(c, nblocks, P, ev, mode, smem, &e_embed, out7)); break;
-    default: b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
-  }
+  TRY(pair_eam_launch(c, ev, 0, nullptr, 0));
+  if (ev && nblocks) { double e1[1]; TRY(reduce_partials(c, nblocks, 1, e1)); e_embed = e1[0]; }
+  TRY(pair_eam_fp_comm(c));
+  TRY(pair_eam_launch(c, ev, 1, nullptr, 0));
+  if (ev && nblocks) TRY(reduce_partials(c, nblocks, 7, out7));
   if (ev) {
     c->eng_vdwl = e_embed + 0.5 * out7[0];
     for (int k = 0; k < 6; k++) c->virial[k] = 0.5 * out7[1 + k];

@@ -25,7 +25,7 @@ template <int TPA, bool EV, bool HALF, bool ONETYPE>
 __global__ void __launch_bounds__(PAIR_THREADS)
 k_lj(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict__ neigh,
      const int *__restrict__ numneigh, int pitch, LJOne one, const double *__restrict__ ljtab, int ntypes,
-     double *__restrict__ f, double *__restrict__ partials) {
+     double *__restrict__ f, double *__restrict__ partials, const int *__restrict__ tile_list, int ntile_list) {
   constexpr int A = 32 / TPA;
   __shared__ double s_tab[ONETYPE ? 1 : (LJ_MAX_TYPES_SMEM + 1) * (LJ_MAX_TYPES_SMEM + 1) * 6];
   const int nt1 = ntypes + 1;
@@ -37,9 +37,11 @@ k_lj(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict
   }
   const int lane = threadIdx.x & 31;
   const int sub = lane / TPA, l = lane % TPA;
-  const int tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const bool in_list = !tile_list || w < ntile_list;
+  const int tile = tile_list ? (in_list ? tile_list[w] : 0) : w;
   const int i = tile * A + sub;
-  const bool active = i < nlocal;
+  const bool active = in_list && i < nlocal;
 
   double fx = 0, fy = 0, fz = 0;
   double ev[7] = {0, 0, 0, 0, 0, 0, 0};  // evdwl, vxx, vyy, vzz, vxy, vxz, vyz
@@ -95,19 +97,43 @@ k_lj(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict
 }
 
 template <int TPA, bool EV, bool HALF>
-static void launch_lj2(b200md_ctx *c, int nblocks, const LJOne &one) {
+static void launch_lj2(b200md_ctx *c, int nblocks, const LJOne &one, const int *tiles, int ntl) {
   if (c->ntypes == 1)
     k_lj<TPA, EV, HALF, true><<<nblocks, PAIR_THREADS, 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->neigh, c->numneigh,
-                                                                      c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials);
+                                                                      c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials, tiles, ntl);
   else
     k_lj<TPA, EV, HALF, false><<<nblocks, PAIR_THREADS, 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->neigh, c->numneigh,
-                                                                       c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials);
+                                                                       c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials, tiles, ntl);
 }
 template <int TPA>
-static void launch_lj(b200md_ctx *c, int nblocks, bool ev, const LJOne &one) {
+static void launch_lj(b200md_ctx *c, int nblocks, bool ev, const LJOne &one, const int *tiles, int ntl) {
   const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON;
-  if (ev) { if (half) launch_lj2<TPA, true, true>(c, nblocks, one); else launch_lj2<TPA, true, false>(c, nblocks, one); }
-  else { if (half) launch_lj2<TPA, false, true>(c, nblocks, one); else launch_lj2<TPA, false, false>(c, nblocks, one); }
+  if (ev) { if (half) launch_lj2<TPA, true, true>(c, nblocks, one, tiles, ntl); else launch_lj2<TPA, true, false>(c, nblocks, one, tiles, ntl); }
+  else { if (half) launch_lj2<TPA, false, true>(c, nblocks, one, tiles, ntl); else launch_lj2<TPA, false, false>(c, nblocks, one, tiles, ntl); }
+}
+
+// one launch over all tiles (tiles == nullptr) or over a tile list (interior / boundary split)
+int pair_lj_launch(b200md_ctx *c, bool ev, const int *tiles, int ntl) {
+  const int A = 32 / c->tpa;
+  const int ntiles = tiles ? ntl : (c->nlocal + A - 1) / A;
+  const int nblocks = (ntiles + PAIR_THREADS / 32 - 1) / (PAIR_THREADS / 32);
+  if (nblocks == 0) return B200MD_OK;
+  LJOne one = {0, 0, 0, 0, 0, 0};
+  if (c->ntypes == 1) {
+    const double *t = &c->h_ljtab[((size_t)1 * 2 + 1) * 8];  // row (1,1)
+    one = {t[0], t[1], t[2], t[3], t[4], t[5]};
+  }
+  switch (c->tpa) {
+    case 4: launch_lj<4>(c, nblocks, ev, one, tiles, ntl); break;
+    case 8: launch_lj<8>(c, nblocks, ev, one, tiles, ntl); break;
+    case 16: launch_lj<16>(c, nblocks, ev, one, tiles, ntl); break;
+    case 32: launch_lj<32>(c, nblocks, ev, one, tiles, ntl); break;
+    default: b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
+  }
+  c->launches++;
+  c->pair_launches++;
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
 }
 
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag) {
@@ -126,21 +152,7 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag) {
     return B200MD_OK;
   }
   if (ev) TRY(ensure_partials(c, nblocks));
-  LJOne one = {0, 0, 0, 0, 0, 0};
-  if (c->ntypes == 1) {
-    const double *t = &c->h_ljtab[((size_t)1 * 2 + 1) * 8];  // row (1,1)
-    one = {t[0], t[1], t[2], t[3], t[4], t[5]};
-  }
-  switch (c->tpa) {
-    case 4: launch_lj<4>(c, nblocks, ev, one); break;
-    case 8: launch_lj<8>(c, nblocks, ev, one); break;
-    case 16: launch_lj<16>(c, nblocks, ev, one); break;
-    case 32: launch_lj<32>(c, nblocks, ev, one); break;
-    default: b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
-  }
-  c->launches++;
-  c->pair_launches++;
-  CUDA_TRY(cudaGetLastError());
+  TRY(pair_lj_launch(c, ev, nullptr, 0));
   if (ev) {
     double out[7];
     TRY(reduce_partials(c, nblocks, 7, out));
