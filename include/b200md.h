@@ -101,6 +101,9 @@ int b200md_lattice_fcc(double scale, int nx, int ny, int nz, const double sublo[
 
 /* ---- context ------------------------------------------------------------------------- */
 
+/* number of visible CUDA devices (hosts map rank -> device as rank % count, like
+ * src/KOKKOS/kokkos.cpp:144-199) */
+int b200md_device_count(int *count);
 int b200md_create(int device, int rank, int nranks, b200md_ctx **out);
 int b200md_destroy(b200md_ctx *ctx);
 
@@ -184,6 +187,10 @@ int b200md_pair_eam_config(b200md_ctx *ctx, int ntypes, int nrho, int nr, double
  * contributions, written only when the corresponding flag is set. */
 int b200md_pair_compute(b200md_ctx *ctx, int eflag, int vflag, double *eng_vdwl,
                         double virial[6]);
+/* This rank's Pair::eng_vdwl and Pair::virial[6] (src/pair.h:45-46) as left by the last force
+ * evaluation that tallied them (b200md_setup, an output step of b200md_run, or
+ * b200md_pair_compute with flags set). */
+int b200md_pair_tallies(b200md_ctx *ctx, double *eng_vdwl, double virial[6]);
 /* Comm::reverse_comm of forces (src/comm_brick.cpp:598-639); no-op for full lists. */
 int b200md_reverse_comm(b200md_ctx *ctx);
 

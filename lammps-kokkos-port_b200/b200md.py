@@ -310,6 +310,11 @@ class Context:
         _chk(self.L.b200md_pair_compute(self.h, int(eflag), int(vflag), C.byref(e), vir))
         return e.value, list(vir)
 
+    def pair_tallies(self):
+        e = C.c_double(); vir = (C.c_double * 6)()
+        _chk(self.L.b200md_pair_tallies(self.h, C.byref(e), vir))
+        return e.value, list(vir)
+
     # fix nve / thermo / loop
     def nve_initial(self, dtv, dtf):
         _chk(self.L.b200md_nve_initial(self.h, C.c_double(dtv), C.c_double(dtf)))

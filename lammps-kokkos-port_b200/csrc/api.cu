@@ -23,6 +23,14 @@ extern "C" const char *b200md_version(void) { return "b200md 0.1 (sm_100a)"; }
 
 #define NEED(cond, msg) do { if (!(cond)) { b200md_set_error(msg); return B200MD_ERR; } } while (0)
 
+extern "C" int b200md_device_count(int *count) {
+  if (!count) { b200md_set_error("b200md: null argument"); return B200MD_ERR; }
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }
+  *count = n;
+  return B200MD_OK;
+}
+
 extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out) {
   NEED(out, "b200md: null output pointer");
   *out = nullptr;
@@ -486,6 +494,14 @@ extern "C" int b200md_pair_compute(b200md_ctx *c, int eflag, int vflag, double *
   else { b200md_set_error("b200md: no pair style configured"); return B200MD_ERR; }
   if (eflag && eng_vdwl) *eng_vdwl = c->eng_vdwl;
   if (vflag && virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];
+  return B200MD_OK;
+}
+
+extern "C" int b200md_pair_tallies(b200md_ctx *c, double *eng_vdwl, double virial[6]) {
+  NEED(c, "b200md: null context");
+  NEED(c->ev_valid, "Energy was not tallied on needed timestep");
+  if (eng_vdwl) *eng_vdwl = c->eng_vdwl;
+  if (virial) for (int k = 0; k < 6; k++) virial[k] = c->virial[k];
   return B200MD_OK;
 }
 

@@ -1,0 +1,24 @@
+// b200_styles.h — shared by the LAMMPS-side suffix styles (`-sf b200`) that bind libb200md.so.
+// These files are compiled AGAINST the reference's headers (they subclass its style classes);
+// they contain no reference code.  See INTEGRATION.md.
+#ifndef LMP_B200_STYLES_H
+#define LMP_B200_STYLES_H
+
+#include "b200md.h"
+
+namespace LAMMPS_NS {
+
+// a pair style that can hand its coefficient tables to the device library
+class B200PairStyle {
+ public:
+  virtual ~B200PairStyle() = default;
+  virtual int b200_push(b200md_ctx *ctx) = 0;   // returns the library's status code
+};
+
+// the one device context of this LAMMPS instance (owned by VerletB200)
+struct B200Shared {
+  static b200md_ctx *ctx;
+};
+
+}    // namespace LAMMPS_NS
+#endif

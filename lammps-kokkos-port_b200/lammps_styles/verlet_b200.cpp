@@ -1,0 +1,277 @@
+// run_style verlet/b200 — see verlet_b200.h.  Written against the reference's public class
+// interfaces (Integrate/Verlet, Atom, Neighbor, Force, Modify, Output); the physics is in
+// libb200md.so.
+
+#include "verlet_b200.h"
+
+#include "atom.h"
+#include "atom_vec.h"
+#include "comm.h"
+#include "domain.h"
+#include "error.h"
+#include "fix.h"
+#include "force.h"
+#include "modify.h"
+#include "neighbor.h"
+#include "output.h"
+#include "pair.h"
+#include "timer.h"
+#include "update.h"
+
+#include <algorithm>
+#include <cstring>
+
+using namespace LAMMPS_NS;
+
+b200md_ctx *B200Shared::ctx = nullptr;
+
+/* ---------------------------------------------------------------------- */
+
+VerletB200::VerletB200(LAMMPS *lmp, int narg, char **arg) :
+    Verlet(lmp, narg, arg), ctx(nullptr), host_stale(false), builds_at_setup(0)
+{
+}
+
+VerletB200::~VerletB200()
+{
+  if (ctx) {
+    b200md_destroy(ctx);
+    if (B200Shared::ctx == ctx) B200Shared::ctx = nullptr;
+  }
+}
+
+void VerletB200::fail()
+{
+  error->all(FLERR, b200md_last_error());
+}
+
+/* ----------------------------------------------------------------------
+   what the device loop covers: SURVEY.md section 8 -- atomic systems, orthogonal periodic
+   or non-periodic 3-d box, one pair style with a b200 variant, fix nve on all atoms
+------------------------------------------------------------------------- */
+
+void VerletB200::check_supported()
+{
+  if (domain->triclinic) error->all(FLERR, "Run style verlet/b200 requires an orthogonal box");
+  if (domain->dimension != 3) error->all(FLERR, "Run style verlet/b200 requires a 3d system");
+  if (atom->molecular != Atom::ATOMIC || force->bond || force->angle || force->dihedral ||
+      force->improper || force->kspace)
+    error->all(FLERR, "Run style verlet/b200 supports atomic systems with a pair style only");
+  if (atom->rmass_flag || atom->torque_flag)
+    error->all(FLERR, "Run style verlet/b200 requires per-type masses and point particles");
+  if (!force->pair || !dynamic_cast<B200PairStyle *>(force->pair))
+    error->all(FLERR, "Run style verlet/b200 requires a pair style with the b200 suffix");
+  if (domain->box_change) error->all(FLERR, "Run style verlet/b200 requires a fixed box");
+
+  int nintegrate = 0;
+  for (const auto &fix : modify->get_fix_list()) {
+    if (fix->time_integrate) {
+      if (!utils::strmatch(fix->style, "^nve/b200$") || fix->igroup != 0)
+        error->all(FLERR, "Run style verlet/b200 requires fix nve/b200 on group all");
+      nintegrate++;
+    }
+  }
+  if (nintegrate != 1) error->all(FLERR, "Run style verlet/b200 requires exactly one fix nve/b200");
+  if (modify->n_initial_integrate != 1 || modify->n_final_integrate != 1 ||
+      modify->n_post_integrate || modify->n_pre_exchange || modify->n_pre_neighbor ||
+      modify->n_post_neighbor || modify->n_pre_force || modify->n_pre_reverse ||
+      modify->n_post_force_any || modify->n_end_of_step)
+    error->all(FLERR, "Run style verlet/b200 does not support fixes that act during the step");
+}
+
+/* ---------------------------------------------------------------------- */
+
+void VerletB200::init()
+{
+  Verlet::init();
+
+  if (!ctx) {
+    int ngpu = 0;
+    b200md_device_count(&ngpu);
+    if (ngpu < 1) error->all(FLERR, "Run style verlet/b200: no CUDA device");
+    if (b200md_create(comm->me % ngpu, comm->me, comm->nprocs, &ctx)) fail();
+    if (comm->nprocs > 1) {
+      char id[128];
+      memset(id, 0, sizeof(id));
+      if (comm->me == 0 && b200md_comm_unique_id(id)) fail();
+      MPI_Bcast(id, 128, MPI_BYTE, 0, world);
+      if (b200md_comm_init(ctx, id)) fail();
+    }
+    B200Shared::ctx = ctx;
+  }
+  if (b200md_set_units(ctx, force->boltz, force->mvv2e, force->ftm2v, force->nktv2p)) fail();
+  if (b200md_set_box(ctx, domain->boxlo, domain->boxhi, domain->periodicity, comm->procgrid)) fail();
+}
+
+/* ----------------------------------------------------------------------
+   upload atoms + settings, first build, first force evaluation with tallies
+------------------------------------------------------------------------- */
+
+void VerletB200::device_setup()
+{
+  check_supported();    // Modify::init has filled its per-hook fix lists by now
+  atom->setup();
+  domain->pbc();
+  domain->reset_box();
+  comm->setup();
+
+  const int nlocal = atom->nlocal;
+  const int *mask = atom->mask;
+  bool uniform = true;
+  for (int i = 1; i < nlocal; i++)
+    if (mask[i] != mask[0]) { uniform = false; break; }
+  mask_by_tag.clear();
+  if (!uniform) {
+    mask_by_tag.reserve(nlocal);
+    for (int i = 0; i < nlocal; i++) mask_by_tag.emplace_back((int) atom->tag[i], mask[i]);
+    std::sort(mask_by_tag.begin(), mask_by_tag.end());
+  }
+
+  const double *x = nlocal ? &atom->x[0][0] : nullptr;
+  const double *v = nlocal ? &atom->v[0][0] : nullptr;
+  if (b200md_set_atoms(ctx, nlocal, x, v, atom->type, atom->tag, atom->image, atom->ntypes, atom->mass))
+    fail();
+  // full list, newton off on the device whatever the `newton` setting: same forces, no atomics
+  // (what the reference's Kokkos GPU path defaults to, src/KOKKOS/kokkos.cpp:257-260)
+  if (b200md_neigh_config(ctx, atom->ntypes, &neighbor->cutneighsq[0][0], neighbor->cutneighmax,
+                          neighbor->skin, neighbor->every, neighbor->delay, neighbor->dist_check,
+                          B200MD_LIST_FULL))
+    fail();
+  if (dynamic_cast<B200PairStyle *>(force->pair)->b200_push(ctx)) fail();
+  if (b200md_setup(ctx)) fail();
+
+  long long nb = 0, nd = 0, tot = 0;
+  int pitch = 0;
+  b200md_neigh_stats(ctx, &nb, &nd, &tot, &pitch);
+  builds_at_setup = nb;
+  neighbor->ncalls = 0;
+  neighbor->ndanger = 0;
+
+  force->setup();
+  ev_set(update->ntimestep);
+  publish_tallies();
+  host_stale = true;
+  sync_host();
+}
+
+void VerletB200::setup(int flag)
+{
+  if (comm->me == 0 && screen) {
+    fputs("Setting up Verlet/b200 run ...\n", screen);
+    if (flag) {
+      fmt::print(screen, "  Unit style    : {}\n  Current step  : {}\n  Time step     : {}\n",
+                 update->unit_style, update->ntimestep, update->dt);
+      timer->print_timeout(screen);
+    }
+  }
+  update->setupflag = 1;
+  device_setup();
+  modify->setup(vflag);
+  output->setup(flag);
+  update->setupflag = 0;
+}
+
+void VerletB200::setup_minimal(int /*flag*/)
+{
+  update->setupflag = 1;
+  device_setup();
+  modify->setup(vflag);
+  update->setupflag = 0;
+}
+
+/* ----------------------------------------------------------------------
+   Pair::eng_vdwl / Pair::virial of this rank, read by compute pe / compute pressure
+------------------------------------------------------------------------- */
+
+void VerletB200::publish_tallies()
+{
+  Pair *pair = force->pair;
+  pair->eng_vdwl = pair->eng_coul = 0.0;
+  if (b200md_pair_tallies(ctx, &pair->eng_vdwl, pair->virial)) fail();
+}
+
+/* ----------------------------------------------------------------------
+   host copies of the owned atoms, in the device's (bin-sorted) order
+------------------------------------------------------------------------- */
+
+void VerletB200::sync_host()
+{
+  if (!host_stale) return;
+  int nlocal = 0, nghost = 0;
+  if (b200md_get_nlocal(ctx, &nlocal, &nghost)) fail();
+  while (nlocal > atom->nmax) atom->avec->grow(0);
+  atom->nlocal = nlocal;
+  atom->nghost = 0;
+  if (nlocal) {
+    if (b200md_get_atoms(ctx, &atom->x[0][0], &atom->v[0][0], &atom->f[0][0], atom->type, atom->tag,
+                         atom->image))
+      fail();
+  }
+  int *mask = atom->mask;
+  if (mask_by_tag.empty()) {
+    const int m = (nlocal && comm->nprocs == 1) ? mask[0] : 1;    // uniform: keep; group all = bit 0
+    for (int i = 0; i < nlocal; i++) mask[i] = m;
+  } else {
+    if (comm->nprocs > 1)
+      error->all(FLERR, "Run style verlet/b200: non-uniform group masks need a single rank");
+    for (int i = 0; i < nlocal; i++) {
+      auto it = std::lower_bound(mask_by_tag.begin(), mask_by_tag.end(), std::make_pair((int) atom->tag[i], 0));
+      mask[i] = it->second;
+    }
+  }
+  if (atom->map_style != Atom::MAP_NONE) {
+    atom->map_init();
+    atom->map_set();
+  }
+  host_stale = false;
+}
+
+/* ----------------------------------------------------------------------
+   run for N steps: device chunks that end on the host's next output step
+------------------------------------------------------------------------- */
+
+void VerletB200::run(int n)
+{
+  int done = 0;
+  while (done < n) {
+    if (timer->check_timeout(done)) {
+      update->nsteps = done;
+      break;
+    }
+    bigint togo = output->next - update->ntimestep;
+    int chunk = n - done;
+    if (togo > 0 && togo < (bigint) chunk) chunk = (int) togo;
+
+    timer->stamp();
+    int nth = 0;
+    if (b200md_run(ctx, chunk, update->dt, 0, nullptr, 0, &nth)) fail();
+    timer->stamp(Timer::PAIR);    // device time of the whole chunk (pair + neigh + comm + nve)
+    update->ntimestep += chunk;
+    done += chunk;
+    host_stale = true;
+
+    long long nb = 0, nd = 0, tot = 0;
+    int pitch = 0;
+    b200md_neigh_stats(ctx, &nb, &nd, &tot, &pitch);
+    neighbor->ncalls = (bigint) (nb - builds_at_setup);
+    neighbor->ndanger = (bigint) nd;
+
+    if (update->ntimestep == output->next) {
+      // the last step of a chunk is evaluated with energy/virial tallies (Integrate::ev_set)
+      ev_set(update->ntimestep);
+      publish_tallies();
+      sync_host();
+      timer->stamp();
+      output->write(update->ntimestep);
+      timer->stamp(Timer::OUTPUT);
+    }
+  }
+}
+
+/* ---------------------------------------------------------------------- */
+
+void VerletB200::cleanup()
+{
+  sync_host();
+  Verlet::cleanup();
+}

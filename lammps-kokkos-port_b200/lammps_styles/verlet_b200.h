@@ -1,0 +1,45 @@
+#ifdef INTEGRATE_CLASS
+// clang-format off
+IntegrateStyle(verlet/b200,VerletB200);
+// clang-format on
+#else
+#ifndef LMP_VERLET_B200_H
+#define LMP_VERLET_B200_H
+
+#include "b200_styles.h"
+#include "verlet.h"
+
+#include <utility>
+#include <vector>
+
+namespace LAMMPS_NS {
+
+// run_style verlet/b200: Verlet::setup / Verlet::run (src/verlet.cpp:93-162, 229-360) with the
+// whole step loop on the device.  Host arrays are refreshed on output steps only, the way
+// verlet/kk syncs them (src/KOKKOS/verlet_kokkos.cpp:287,516).
+class VerletB200 : public Verlet {
+ public:
+  VerletB200(class LAMMPS *lmp, int narg, char **arg);
+  ~VerletB200() override;
+  void init() override;
+  void setup(int flag) override;
+  void setup_minimal(int flag) override;
+  void run(int n) override;
+  void cleanup() override;
+
+ private:
+  b200md_ctx *ctx;
+  bool host_stale;
+  long long builds_at_setup;
+  std::vector<std::pair<int, int>> mask_by_tag;    // only when group masks are not uniform
+
+  void fail();
+  void check_supported();
+  void device_setup();
+  void publish_tallies();
+  void sync_host();
+};
+
+}    // namespace LAMMPS_NS
+#endif
+#endif
