@@ -162,6 +162,8 @@ UNITS = {
     "lj": dict(boltz=1.0, mvv2e=1.0, ftm2v=1.0, nktv2p=1.0, dt=0.005, skin=0.3),
     "metal": dict(boltz=8.617343e-5, mvv2e=1.0364269e-4, ftm2v=1.0 / 1.0364269e-4, nktv2p=1.6021765e6,
                   dt=0.001, skin=2.0),
+    "real": dict(boltz=0.0019872067, mvv2e=48.88821291 * 48.88821291, ftm2v=1.0 / 48.88821291 / 48.88821291,
+                 nktv2p=68568.415, dt=1.0, skin=2.0),
 }
 
 

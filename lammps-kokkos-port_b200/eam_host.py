@@ -7,6 +7,10 @@ Mirrors (same names, same arithmetic order) the reference's one-time set-up:
   PairEAM::interpolate      pair_eam.cpp:769-797
   PairEAMAlloy::read_file   pair_eam_alloy.cpp:109-219 (setfl)
   PairEAMAlloy::file2array  pair_eam_alloy.cpp:225-337
+  PairEAMFS::read_file      pair_eam_fs.cpp:111-220    (setfl with per-pair densities)
+  PairEAMFS::file2array     pair_eam_fs.cpp:226-345
+  unit conversion metal<->real (utils.cpp:1500-1510 factor 23.060549): applied like the readers do,
+  loop bounds included (eam/alloy leaves the last table entry unconverted, pair_eam_alloy.cpp:161,169)
 The product of this module is the table set handed to b200md_pair_eam_config.
 """
 import numpy as np
@@ -18,7 +22,20 @@ def _tokens(path, skip):
     return lines[:skip], " ".join(lines[skip:]).split()
 
 
-def read_funcfl(path):
+METAL2REAL = 23.060549
+
+
+def _conv(units_file, units_run):
+    if units_file == units_run:
+        return None
+    if units_file == "metal" and units_run == "real":
+        return METAL2REAL
+    if units_file == "real" and units_run == "metal":
+        return 1.0 / METAL2REAL
+    raise ValueError("unsupported unit conversion %s -> %s" % (units_file, units_run))
+
+
+def read_funcfl(path, conv=None):
     with open(path) as fh:
         lines = fh.read().split("\n")
     l2 = lines[1].split()
@@ -34,10 +51,41 @@ def read_funcfl(path):
     f["frho"] = np.concatenate([[0.0], rest[:nrho]])
     f["zr"] = np.concatenate([[0.0], rest[nrho:nrho + nr]])
     f["rhor"] = np.concatenate([[0.0], rest[nrho + nr:nrho + 2 * nr]])
+    if conv is not None:
+        f["frho"][1:] *= conv
+        f["zr"][1:] *= np.sqrt(conv)
     return f
 
 
-def read_setfl(path):
+def read_fs(path, conv=None):
+    """DYNAMO setfl, Finnis-Sinclair form: rhor[i][j] per element pair."""
+    _, tok = _tokens(path, 3)
+    it = iter(tok)
+    ne = int(next(it))
+    s = dict(nelements=ne, elements=[next(it) for _ in range(ne)])
+    s["nrho"] = int(next(it)); s["drho"] = float(next(it)); s["nr"] = int(next(it))
+    s["dr"] = float(next(it)); s["cut"] = float(next(it))
+    nrho, nr = s["nrho"], s["nr"]
+    s["mass"] = []; s["frho"] = np.zeros((ne, nrho + 1)); s["rhor"] = np.zeros((ne, ne, nr + 1))
+    s["z2r"] = np.zeros((ne, ne, nr + 1))
+    for i in range(ne):
+        next(it)
+        s["mass"].append(float(next(it)))
+        next(it); next(it)
+        s["frho"][i, 1:] = [float(next(it)) for _ in range(nrho)]
+        if conv is not None:
+            s["frho"][i, 1:] *= conv
+        for j in range(ne):
+            s["rhor"][i, j, 1:] = [float(next(it)) for _ in range(nr)]
+    for i in range(ne):
+        for j in range(i + 1):
+            s["z2r"][i, j, 1:] = [float(next(it)) for _ in range(nr)]
+            if conv is not None:
+                s["z2r"][i, j, 1:] *= conv
+    return s
+
+
+def read_setfl(path, conv=None):
     _, tok = _tokens(path, 3)
     it = iter(tok)
     ne = int(next(it))
@@ -53,9 +101,13 @@ def read_setfl(path):
         next(it); next(it)  # lattice constant, lattice type
         s["frho"][i, 1:] = [float(next(it)) for _ in range(nrho)]
         s["rhor"][i, 1:] = [float(next(it)) for _ in range(nr)]
+        if conv is not None:
+            s["frho"][i, 1:nrho] *= conv          # j = 1 .. nrho-1, as the reference does
     for i in range(ne):
         for j in range(i + 1):
             s["z2r"][i, j, 1:] = [float(next(it)) for _ in range(nr)]
+            if conv is not None:
+                s["z2r"][i, j, 1:nr] *= conv      # k = 1 .. nr-1
     return s
 
 
@@ -102,12 +154,14 @@ def interpolate(n, delta, f):
     return sp
 
 
-def _type_maps(ntypes, map_):
+def _type_maps(ntypes, map_, fs_nelements=0):
     n1 = ntypes + 1
     type2rhor = np.zeros((n1, n1), np.int32); type2z2r = np.zeros((n1, n1), np.int32)
     for i in range(1, n1):
         for j in range(1, n1):
-            type2rhor[i, j] = map_[i]
+            # eam, eam/alloy: density of the SOURCE atom's element (pair_eam.cpp:672,
+            # pair_eam_alloy.cpp:296); eam/fs: per ordered element pair (pair_eam_fs.cpp:307)
+            type2rhor[i, j] = map_[i] * fs_nelements + map_[j] if fs_nelements else map_[i]
             irow, icol = map_[i], map_[j]
             if irow == -1 or icol == -1:
                 type2z2r[i, j] = 0
@@ -119,12 +173,12 @@ def _type_maps(ntypes, map_):
     return type2rhor, type2z2r
 
 
-def _finish(ntypes, map_, nrho, nr, drho, dr, rhomax, cutmax, frho, rhor, z2r, masses):
+def _finish(ntypes, map_, nrho, nr, drho, dr, rhomax, cutmax, frho, rhor, z2r, masses, fs_nelements=0):
     nfrho = frho.shape[0]
     type2frho = np.zeros(ntypes + 1, np.int32)
     for i in range(1, ntypes + 1):
         type2frho[i] = map_[i] if map_[i] >= 0 else nfrho - 1
-    type2rhor, type2z2r = _type_maps(ntypes, map_)
+    type2rhor, type2z2r = _type_maps(ntypes, map_, fs_nelements)
     tb = dict(nrho=nrho, nr=nr, rdr=1.0 / dr, rdrho=1.0 / drho, rhomax=rhomax, cutforcesq=cutmax * cutmax,
               cutmax=cutmax,
               frho_spline=np.stack([interpolate(nrho, drho, frho[i]) for i in range(nfrho)]),
@@ -135,8 +189,9 @@ def _finish(ntypes, map_, nrho, nr, drho, dr, rhomax, cutmax, frho, rhor, z2r, m
     return tb
 
 
-def tables_from_funcfl(files_by_type):
+def tables_from_funcfl(files_by_type, units="metal"):
     """pair_style eam; pair_coeff i i file_i  (files_by_type[i-1] is the funcfl file of type i)."""
+    conv = _conv("metal", units)
     uniq = []
     map_ = [-1]
     for p in files_by_type:
@@ -144,7 +199,7 @@ def tables_from_funcfl(files_by_type):
             uniq.append(p)
         map_.append(uniq.index(p))
     ntypes = len(files_by_type)
-    F = [read_funcfl(p) for p in uniq]
+    F = [read_funcfl(p, conv) for p in uniq]
     dr = max(f["dr"] for f in F); drho = max(f["drho"] for f in F)
     rmax = max((f["nr"] - 1) * f["dr"] for f in F); rhomax = max((f["nrho"] - 1) * f["drho"] for f in F)
     nr = int(rmax / dr + 0.5); nrho = int(rhomax / drho + 0.5)
@@ -164,10 +219,7 @@ def tables_from_funcfl(files_by_type):
     return _finish(ntypes, map_, nrho, nr, drho, dr, rhomax, cutmax, frho, rhor, np.stack(z2r), masses)
 
 
-def tables_from_setfl(path, elements_by_type):
-    """pair_style eam/alloy; pair_coeff * * file E1 E2 ...  (NULL -> None)."""
-    s = read_setfl(path)
-    ntypes = len(elements_by_type)
+def _element_map(s, elements_by_type):
     map_ = [-1]
     for e in elements_by_type:
         if e is None:
@@ -176,6 +228,28 @@ def tables_from_setfl(path, elements_by_type):
             if e not in s["elements"]:
                 raise ValueError("No matching element in EAM potential file")
             map_.append(s["elements"].index(e))
+    return map_
+
+
+def tables_from_fs(path, elements_by_type, units="metal"):
+    """pair_style eam/fs; pair_coeff * * file E1 E2 ..."""
+    s = read_fs(path, _conv("metal", units))
+    ntypes = len(elements_by_type)
+    map_ = _element_map(s, elements_by_type)
+    ne, nrho, nr = s["nelements"], s["nrho"], s["nr"]
+    frho = np.zeros((ne + 1, nrho + 1)); frho[:ne] = s["frho"]
+    rhor = s["rhor"].reshape(ne * ne, nr + 1)
+    z2r = np.stack([s["z2r"][i, j] for i in range(ne) for j in range(i + 1)])
+    masses = [s["mass"][map_[i]] if map_[i] >= 0 else 1.0 for i in range(1, ntypes + 1)]
+    return _finish(ntypes, map_, nrho, nr, s["drho"], s["dr"], (nrho - 1) * s["drho"], s["cut"], frho, rhor,
+                   z2r, masses, fs_nelements=ne)
+
+
+def tables_from_setfl(path, elements_by_type, units="metal"):
+    """pair_style eam/alloy; pair_coeff * * file E1 E2 ...  (NULL -> None)."""
+    s = read_setfl(path, _conv("metal", units))
+    ntypes = len(elements_by_type)
+    map_ = _element_map(s, elements_by_type)
     ne, nrho, nr = s["nelements"], s["nrho"], s["nr"]
     frho = np.zeros((ne + 1, nrho + 1)); frho[:ne] = s["frho"]
     z2r = np.stack([s["z2r"][i, j] for i in range(ne) for j in range(i + 1)])

@@ -59,7 +59,7 @@ def main():
     os.makedirs(OBJ, exist_ok=True)
     ref_srcs = sorted(glob.glob(os.path.join(SRC, "*.cpp")))
     ref_srcs += [os.path.join(SRC, "STUBS", "mpi.cpp")]
-    ref_srcs += [os.path.join(SRC, "MANYBODY", f) for f in ("pair_eam.cpp", "pair_eam_alloy.cpp")]
+    ref_srcs += [os.path.join(SRC, "MANYBODY", f) for f in ("pair_eam.cpp", "pair_eam_alloy.cpp", "pair_eam_fs.cpp")]
     own_srcs = sorted(glob.glob(os.path.join(HERE, "*_b200.cpp")))
     headers = [s[:-4] + ".h" for s in ref_srcs + own_srcs if os.path.exists(s[:-4] + ".h")]
     for macro, prefix, name in STYLES:

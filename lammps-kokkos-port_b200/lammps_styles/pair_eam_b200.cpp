@@ -22,3 +22,5 @@ int PairEAMB200::b200_push(b200md_ctx *ctx) { return B200_EAM_PUSH(); }
 void PairEAMB200::compute(int eflag, int vflag) { B200_EAM_COMPUTE("eam/b200"); }
 int PairEAMAlloyB200::b200_push(b200md_ctx *ctx) { return B200_EAM_PUSH(); }
 void PairEAMAlloyB200::compute(int eflag, int vflag) { B200_EAM_COMPUTE("eam/alloy/b200"); }
+int PairEAMFSB200::b200_push(b200md_ctx *ctx) { return B200_EAM_PUSH(); }
+void PairEAMFSB200::compute(int eflag, int vflag) { B200_EAM_COMPUTE("eam/fs/b200"); }

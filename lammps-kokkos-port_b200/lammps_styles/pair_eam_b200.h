@@ -2,6 +2,7 @@
 // clang-format off
 PairStyle(eam/b200,PairEAMB200);
 PairStyle(eam/alloy/b200,PairEAMAlloyB200);
+PairStyle(eam/fs/b200,PairEAMFSB200);
 // clang-format on
 #else
 #ifndef LMP_PAIR_EAM_B200_H
@@ -10,10 +11,11 @@ PairStyle(eam/alloy/b200,PairEAMAlloyB200);
 #include "b200_styles.h"
 #include "pair_eam.h"
 #include "pair_eam_alloy.h"
+#include "pair_eam_fs.h"
 
 namespace LAMMPS_NS {
 
-// pair_style eam/b200 and eam/alloy/b200: potential-file reading and spline construction are the
+// pair_style eam/b200, eam/alloy/b200 and eam/fs/b200: potential-file reading and spline construction are the
 // reference's (src/MANYBODY/pair_eam.cpp:370-797, pair_eam_alloy.cpp:43-337); the three passes
 // of PairEAM::compute (pair_eam.cpp:142-328) run in libb200md.so.
 class PairEAMB200 : public PairEAM, public B200PairStyle {
@@ -26,6 +28,13 @@ class PairEAMB200 : public PairEAM, public B200PairStyle {
 class PairEAMAlloyB200 : public PairEAMAlloy, public B200PairStyle {
  public:
   PairEAMAlloyB200(class LAMMPS *lmp) : PairEAM(lmp), PairEAMAlloy(lmp) { no_virial_fdotr_compute = 1; }
+  void compute(int, int) override;
+  int b200_push(b200md_ctx *ctx) override;
+};
+
+class PairEAMFSB200 : public PairEAMFS, public B200PairStyle {
+ public:
+  PairEAMFSB200(class LAMMPS *lmp) : PairEAM(lmp), PairEAMFS(lmp) { no_virial_fdotr_compute = 1; }
   void compute(int, int) override;
   int b200_push(b200md_ctx *ctx) override;
 };

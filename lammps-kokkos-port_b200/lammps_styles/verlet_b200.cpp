@@ -71,8 +71,10 @@ void VerletB200::check_supported()
       nintegrate++;
     }
   }
-  if (nintegrate != 1) error->all(FLERR, "Run style verlet/b200 requires exactly one fix nve/b200");
-  if (modify->n_initial_integrate != 1 || modify->n_final_integrate != 1 ||
+  // `run 0` (forces and tallies only) needs no integrator
+  if (nintegrate > 1 || (nintegrate == 0 && update->nsteps > 0))
+    error->all(FLERR, "Run style verlet/b200 requires exactly one fix nve/b200");
+  if (modify->n_initial_integrate != nintegrate || modify->n_final_integrate != nintegrate ||
       modify->n_post_integrate || modify->n_pre_exchange || modify->n_pre_neighbor ||
       modify->n_post_neighbor || modify->n_pre_force || modify->n_pre_reverse ||
       modify->n_post_force_any || modify->n_end_of_step)

@@ -11,7 +11,7 @@ and two two-line version stubs; they live under oracle/_ref/gen/.
 
 Selected sources:
   * every core file src/*.cpp (the serial MPI stub src/STUBS/mpi.cpp replaces MPI)
-  * MANYBODY: pair_eam.cpp pair_eam_alloy.cpp           (the hot path's EAM styles)
+  * MANYBODY: pair_eam.cpp pair_eam_alloy.cpp pair_eam_fs.cpp   (the hot path's EAM styles)
   * OPENMP : the threaded variants of exactly the hot-path styles, used as the timed
              CPU baseline (`-sf omp -pk omp N`)
 
@@ -38,7 +38,7 @@ GEN = os.path.join(OUT, "gen")
 OBJ = os.path.join(OUT, "obj")
 CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
 
-MANYBODY = ["pair_eam.cpp", "pair_eam_alloy.cpp"]
+MANYBODY = ["pair_eam.cpp", "pair_eam_alloy.cpp", "pair_eam_fs.cpp"]
 OPENMP = [
     "fix_omp.cpp", "thr_omp.cpp", "thr_data.cpp", "domain_omp.cpp",
     "pair_lj_cut_omp.cpp", "pair_eam_omp.cpp", "pair_eam_alloy_omp.cpp",
@@ -143,7 +143,9 @@ def main():
     os.makedirs(pot, exist_ok=True)
     for src in [os.path.join(REF, "bench", "Cu_u3.eam"),
                 os.path.join(REF, "potentials", "Cu_mishin1.eam.alloy"),
-                os.path.join(REF, "potentials", "Al_jnp.eam")]:
+                os.path.join(REF, "potentials", "Al_jnp.eam"),
+                os.path.join(REF, "potentials", "CuNi.eam.alloy"),
+                os.path.join(REF, "potentials", "AlFe_mm.eam.fs")]:
         dst = os.path.join(pot, os.path.basename(src))
         if os.path.exists(src) and not os.path.exists(dst):
             shutil.copyfile(src, dst)

@@ -17,6 +17,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#define MAXSWAP 30
 #define BIG 1.0e20
 #define SMALL 1.0e-6
 #define MIN(a, b) ((a) < (b) ? (a) : (b))
@@ -48,7 +49,7 @@ typedef struct {
   int *numneigh, *firstoff, *neigh;
   long neighcap;
   /* swaps (6, one proc, periodic) */
-  int nswap, sendnum[6], firstrecv[6], *sendlist[6], sendcap[6], pbcdim[6], pbcsign[6];
+  int nswap, sendnum[MAXSWAP], firstrecv[MAXSWAP], *sendlist[MAXSWAP], sendcap[MAXSWAP], pbcdim[MAXSWAP], pbcsign[MAXSWAP];
   /* pair */
   int pair_style; /* 1 lj, 2 eam */
   double *cutsq, *lj1, *lj2, *lj3, *lj4, *offset;
@@ -111,7 +112,7 @@ void ora_destroy(ora_sim *s) {
   free(s->x); free(s->v); free(s->f); free(s->xhold); free(s->type); free(s->tag); free(s->image); free(s->owner);
   free(s->bins); free(s->atom2bin); free(s->numneigh); free(s->firstoff); free(s->rho); free(s->fp); free(s->mass);
   free(s->cutneighsq); free(s->binhead); free(s->stencil); free(s->neigh);
-  for (int k = 0; k < 6; k++) free(s->sendlist[k]);
+  for (int k = 0; k < MAXSWAP; k++) free(s->sendlist[k]);
   free(s->cutsq); free(s->lj1); free(s->lj2); free(s->lj3); free(s->lj4); free(s->offset);
   free(s->frho_spline); free(s->rhor_spline); free(s->z2r_spline); free(s->scale);
   free(s->type2frho); free(s->type2rhor); free(s->type2z2r);
@@ -167,19 +168,25 @@ static void pbc(ora_sim *s) {
 }
 
 /* CommBrick::setup + borders on one periodic process (comm_brick.cpp:412-482, 771-979;
- * AtomVec::pack_border atom_vec.cpp:794-830): 6 self-swaps, maxneed = 1 required. */
+ * AtomVec::pack_border atom_vec.cpp:794-830): 2*maxneed self-swaps per dimension,
+ * maxneed = int(cutghost/prd)+1; swaps after the first pair of a dimension forward only the
+ * ghosts that arrived in the previous pair and cut their slab at the box middle. */
 static int borders(ora_sim *s) {
   const double cut = s->cutneighmax;
   s->nghost = 0;
   int iswap = 0;
   for (int dim = 0; dim < 3; dim++) {
-    if ((int)(cut * 1 / s->prd[dim]) + 1 != 1) return -1; /* box smaller than cutoff: not restated */
+    const int maxneed = (int)(cut * 1 / s->prd[dim]) + 1;
+    if (iswap + 2 * maxneed > MAXSWAP) return -1;
+    const double mid = 0.5 * (s->boxlo[dim] + s->boxhi[dim]);
     int nlast = 0, nfirst = 0;
-    for (int ineed = 0; ineed < 2; ineed++, iswap++) {
+    for (int ineed = 0; ineed < 2 * maxneed; ineed++, iswap++) {
       double lo, hi;
       int sign;
-      if (ineed % 2 == 0) { lo = -BIG; hi = s->boxlo[dim] + cut; sign = 1; nfirst = nlast; nlast = s->nlocal + s->nghost; }
-      else { lo = s->boxhi[dim] - cut; hi = BIG; sign = -1; }
+      if (ineed % 2 == 0) {
+        lo = ineed < 2 ? -BIG : mid; hi = s->boxlo[dim] + cut; sign = 1;
+        nfirst = nlast; nlast = s->nlocal + s->nghost;
+      } else { lo = s->boxhi[dim] - cut; hi = ineed < 2 ? BIG : mid; sign = -1; }
       int nsend = 0;
       for (int i = nfirst; i < nlast; i++)
         if (s->x[3 * i + dim] >= lo && s->x[3 * i + dim] <= hi) {
@@ -203,7 +210,7 @@ static int borders(ora_sim *s) {
       s->nghost += nsend;
     }
   }
-  s->nswap = 6;
+  s->nswap = iswap;
   return 0;
 }
 /* CommBrick::forward_comm (comm_brick.cpp:538-591) + AtomVec::pack_comm (atom_vec.cpp:349-378) */

@@ -88,7 +88,7 @@ class Oracle:
 
     def neigh_build(self):
         if self.L.ora_neigh_build(self.h):
-            raise RuntimeError("oracle: box smaller than the ghost cutoff is not restated")
+            raise RuntimeError("oracle: neighbor build failed (too many ghost swaps)")
 
     def compute(self, eflag=1, vflag=1):
         if self.L.ora_compute(self.h, eflag, vflag):
