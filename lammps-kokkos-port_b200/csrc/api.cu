@@ -435,8 +435,11 @@ extern "C" int b200md_neigh_stats(b200md_ctx *c, long long *nbuilds, long long *
 
 extern "C" int b200md_set_lanes_per_atom(b200md_ctx *c, int lanes) {
   NEED(c, "b200md: null context");
-  NEED(lanes == 4 || lanes == 8 || lanes == 16 || lanes == 32, "b200md: lanes per atom must be 4, 8, 16 or 32");
+  NEED(lanes == 1 || lanes == 2 || lanes == 4 || lanes == 8 || lanes == 16 || lanes == 32,
+       "b200md: lanes per atom must be 1, 2, 4, 8, 16 or 32");
   c->tpa = lanes;
+  const char *bl = getenv("B200MD_BUILD_LANES");   // tuning only; default 4 (8 when the force kernels use more)
+  c->tpa_build = bl ? atoi(bl) : (lanes < 4 ? 4 : lanes);
   return B200MD_OK;
 }
 extern "C" int b200md_get_stream(b200md_ctx *c, void **stream) {

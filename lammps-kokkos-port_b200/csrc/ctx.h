@@ -97,7 +97,8 @@ struct b200md_ctx {
   int *row_sx = nullptr;   // device [nrows]
   int *row_flag = nullptr; // device [nrows] half-stencil role (0 skip,1 full row,2 own row)
   // neighbor list
-  int tpa = 4;
+  int tpa = 2;        // lanes per atom in the force kernels (1..32); measured best on B200
+  int tpa_build = 4;  // lanes per atom in the list build (4..32)
   int pitch = 0;  // max neighbors per atom (multiple of tpa)
   int *neigh = nullptr;
   size_t neigh_cap = 0;

@@ -430,8 +430,11 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
         const double4 *__restrict__ cell_xq, int nrows, const int *__restrict__ row_off,
         const int *__restrict__ row_sx, const int *__restrict__ row_flag,
         const double *__restrict__ cutneighsq, int ntypes, int *__restrict__ neigh,
-        int *__restrict__ numneigh, int pitch, int *flags, int *__restrict__ tile_ghost) {
+        int *__restrict__ numneigh, int pitch, int *flags, int *__restrict__ tile_ghost, int F) {
+  // TPA lanes scan the candidates of one atom; the list is written in the layout of the force
+  // kernels, which use F lanes per atom (AF atoms per warp tile)
   constexpr int A = 32 / TPA;
+  const int AF = 32 / F;
   __shared__ int s_off[MAX_ROWS], s_sx[MAX_ROWS], s_flag[MAX_ROWS];
   __shared__ double s_cut[(MAX_TYPES_SMEM + 1) * (MAX_TYPES_SMEM + 1)];
   for (int r = threadIdx.x; r < nrows; r += blockDim.x) { s_off[r] = row_off[r]; s_sx[r] = row_sx[r]; s_flag[r] = row_flag[r]; }
@@ -448,7 +451,7 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
   const int tile = warp_global;           // one warp = one tile of A atoms
   const int i = tile * A + sub;
   const bool active = i < nlocal;
-  int *out = neigh + (size_t)tile * pitch * A + sub * TPA;
+  int *out = neigh + (size_t)(i / AF) * pitch * AF + (i % AF) * F;
 
   double4 qi = make_double4(0, 0, 0, 0);
   int ibin = 0, itype = 1;
@@ -497,7 +500,7 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
       if (keep) {
         has_ghost |= (j >= nlocal);
         const int k = cnt + __popc(m & below);
-        if (k < pitch) out[(k / TPA) * 32 + (k % TPA)] = j;
+        if (k < pitch) out[(k / F) * 32 + (k % F)] = j;
       }
       cnt += __popc(m);
       cidx += TPA;
@@ -508,8 +511,8 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
     if (cnt > pitch) atomicMax(&flags[1], cnt);
   }
   // tiles whose atoms have no ghost neighbor can be evaluated while the halo is in flight
-  const bool any_ghost = __any_sync(0xffffffffu, has_ghost);
-  if (tile_ghost && lane == 0 && tile * A < nlocal) tile_ghost[tile] = any_ghost ? 1 : 0;
+  // (tile_ghost is cleared before the launch; all writers store the same value)
+  if (tile_ghost && has_ghost) tile_ghost[i / AF] = 1;
 }
 
 template <int TPA>
@@ -522,11 +525,11 @@ static void launch_build(b200md_ctx *c) {
   if (c->list_kind == B200MD_LIST_HALF_NEWTON)
     k_build<TPA, true><<<nblocks, BUILD_THREADS, 0, c->stream>>>(
         c->nlocal, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, c->cell_xq, c->nrows, c->row_off,
-        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost);
+        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost, c->tpa);
   else
     k_build<TPA, false><<<nblocks, BUILD_THREADS, 0, c->stream>>>(
         c->nlocal, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, c->cell_xq, c->nrows, c->row_off,
-        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost);
+        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost, c->tpa);
 }
 
 static int ensure_neigh_storage(b200md_ctx *c) {
@@ -589,12 +592,13 @@ int neigh_build_list(b200md_ctx *c) {
     TRY(ensure_neigh_storage(c));
     c->h_flags[1] = 0;
     CUDA_TRY(cudaMemsetAsync(c->d_flags + 1, 0, sizeof(int), c->stream));
-    switch (c->tpa) {
+    CUDA_TRY(cudaMemsetAsync(c->tile_ghost, 0, sizeof(int) * ((c->nlocal + 32 / c->tpa - 1) / (32 / c->tpa) + 1), c->stream));
+    switch (c->tpa_build) {
       case 4: launch_build<4>(c); break;
       case 8: launch_build<8>(c); break;
       case 16: launch_build<16>(c); break;
       case 32: launch_build<32>(c); break;
-      default: b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
+      default: b200md_set_error("b200md: build lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
     }
     c->launches++;
     CUDA_TRY(cudaGetLastError());

@@ -6,7 +6,10 @@
 //   embed  (:231-247)  fp_i = F'(rho_i); phi = F(rho_i) (+ linear extrapolation past rhomax)
 //   comm   (:251)      forward_comm(fp)
 //   pass 3 (:257-325)  psip = fp_i*rhojp + fp_j*rhoip + phip; fpair = -scale*psip/r
-// B200 design: full list / newton off, so pass 1 needs no reverse_comm of rho and pass 1 and
+// Half list / newton on (the reference's CPU default) is also provided:
+//   k_eam_rho_half (rho_i and rho_j per listed pair, FP64 RED) -> reverse_comm(rho)
+//   (pair_eam.cpp:224) -> k_eam_embed -> forward_comm(fp) -> k_eam_force<...,HALF> (f_j via RED)
+// Default B200 design: full list / newton off, so pass 1 needs no reverse_comm of rho and pass 1 and
 // the embedding are one kernel (what the reference's Kokkos port calls KernelAB,
 // src/KOKKOS/pair_eam_kokkos.cpp:839-921): TPA lanes gather, shuffle-reduce rho_i, lane 0
 // evaluates F and F'.  Tables are repacked so that each lookup is whole 32-byte sectors:
@@ -172,6 +175,95 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
   if (EV) block_reduce_store<1>(ev, partials);
 }
 
+// ---- half list: pass 1 without the embedding (every listed pair adds to both atoms) ---------
+template <int TPA, bool ONE>
+__global__ void __launch_bounds__(EAM_THREADS)
+k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh,
+               const int *__restrict__ numneigh, int pitch, EamParams P, double *__restrict__ rho) {
+  constexpr int A = 32 / TPA;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / TPA, l = lane % TPA;
+  const int tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int i = tile * A + sub;
+  const bool active = i < nlocal;
+  const int nt1 = P.ntypes + 1;
+  double r_acc = 0;
+  if (active) {
+    const double4 qi = xq[i];
+    const int itype = ONE ? 1 : xq_type(qi);
+    const int n = numneigh[i];
+    const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
+    const int niter = (n + TPA - 1) / TPA;
+#pragma unroll 4
+    for (int it = 0; it < niter; it++) {
+      if (it * TPA + l < n) {
+        const int j = __ldg(nb + it * 32);
+        const double4 qj = ld_xq(&xq[j]);
+        const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
+        const double rsq = rsq_nofma(dx, dy, dz);
+        if (rsq < P.cutforcesq) {
+          double p = sqrt(rsq) * P.rdr + 1.0;
+          int m = (int)p;
+          m = min(m, P.nr - 1);
+          p -= m;
+          p = fmin(p, 1.0);
+          if (ONE) {
+            const double4 cf = ld4(P.tabC + (size_t)m * 8);
+            const double d = ((cf.x * p + cf.y) * p + cf.z) * p + cf.w;
+            r_acc += d;
+            atomicAdd(&rho[j], d);
+          } else {
+            const int jtype = xq_type(qj);
+            const int tji = P.type2rhor[jtype * nt1 + itype], tij = P.type2rhor[itype * nt1 + jtype];
+            const double4 cf = ld4(P.rhoA + ((size_t)tji * (P.nr + 1) + m) * 4);
+            const double di = ((cf.x * p + cf.y) * p + cf.z) * p + cf.w;
+            r_acc += di;
+            double dj = di;
+            if (tij != tji) {
+              const double4 cg = ld4(P.rhoA + ((size_t)tij * (P.nr + 1) + m) * 4);
+              dj = ((cg.x * p + cg.y) * p + cg.z) * p + cg.w;
+            }
+            atomicAdd(&rho[j], dj);
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+  r_acc = group_sum<TPA>(r_acc);
+  if (active && l == 0) atomicAdd(&rho[i], r_acc);
+}
+
+// embedding for the half-list path (pair_eam.cpp:231-247), one thread per owned atom
+template <bool EV, bool ONE>
+__global__ void __launch_bounds__(EAM_THREADS)
+k_eam_embed(int nlocal, const double4 *__restrict__ xq, EamParams P, const double *__restrict__ rho,
+            double *__restrict__ fp, double4 *__restrict__ xfp, double *__restrict__ partials) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int nt1 = P.ntypes + 1;
+  double ev[1] = {0};
+  if (i < nlocal) {
+    const double4 qi = xq[i];
+    const int itype = ONE ? 1 : xq_type(qi);
+    const double r = rho[i];
+    double p = r * P.rdrho + 1.0;
+    int m = (int)p;
+    m = max(1, min(m, P.nrho - 1));
+    p -= m;
+    p = fmin(p, 1.0);
+    const double *cf = P.frho + ((size_t)P.type2frho[itype] * (P.nrho + 1) + m) * 8;
+    const double fpi = (cf[0] * p + cf[1]) * p + cf[2];
+    fp[i] = fpi;
+    if (ONE) xfp[i] = make_double4(qi.x, qi.y, qi.z, fpi);
+    if (EV) {
+      double phi = ((cf[3] * p + cf[4]) * p + cf[5]) * p + cf[6];
+      if (r > P.rhomax) phi += fpi * (r - P.rhomax);
+      ev[0] = phi * P.scale[itype * nt1 + itype];
+    }
+  }
+  if (EV) block_reduce_store<1>(ev, partials);
+}
+
 // ghosts of one-element runs: packed record from the ghost position and the communicated fp
 __global__ void k_pack_xfp(int nghost, int nlocal, const double4 *__restrict__ xq, const double *__restrict__ fp,
                            double4 *__restrict__ xfp) {
@@ -182,7 +274,7 @@ __global__ void k_pack_xfp(int nghost, int nlocal, const double4 *__restrict__ x
 }
 
 // ---- pass 3: forces -------------------------------------------------------------------------
-template <int TPA, bool EV, bool ONE, bool SMEM>
+template <int TPA, bool EV, bool ONE, bool SMEM, bool HALF>
 __global__ void __launch_bounds__(EAM_THREADS)
 k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 *__restrict__ xfp,
             const int *__restrict__ neigh, const int *__restrict__ numneigh, int pitch, EamParams P,
@@ -258,6 +350,11 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
           const double psip = fpi * rhojp + fpj * rhoip + phip;
           const double fpair = -scl * psip * recip;
           fx += dx * fpair; fy += dy * fpair; fz += dz * fpair;
+          if (HALF) {
+            atomicAdd(&f[j], -dx * fpair);
+            atomicAdd(&f[j + nmax], -dy * fpair);
+            atomicAdd(&f[j + 2 * (size_t)nmax], -dz * fpair);
+          }
           if (EV) {
             ev[0] += scl * phi;
             ev[1] += dx * dx * fpair; ev[2] += dy * dy * fpair; ev[3] += dz * dz * fpair;
@@ -269,7 +366,10 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
   }
   __syncwarp();
   fx = group_sum<TPA>(fx); fy = group_sum<TPA>(fy); fz = group_sum<TPA>(fz);
-  if (active && l == 0) { f[i] = fx; f[i + nmax] = fy; f[i + 2 * (size_t)nmax] = fz; }
+  if (active && l == 0) {
+    if (HALF) { atomicAdd(&f[i], fx); atomicAdd(&f[i + nmax], fy); atomicAdd(&f[i + 2 * (size_t)nmax], fz); }
+    else { f[i] = fx; f[i + nmax] = fy; f[i + 2 * (size_t)nmax] = fz; }
+  }
   if (EV) block_reduce_store<7>(ev, partials);
 }
 
@@ -290,11 +390,17 @@ static int launch_pass(b200md_ctx *c, const EamLaunch &L, int pass, const int *t
     if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem));
     k<<<nblocks, EAM_THREADS, SMEM ? L.smem : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, L.P, c->rho,
                                                             c->fp, c->eam.xfp, c->partials, tiles, ntl);
-  } else {
-    auto k = k_eam_force<TPA, EV, ONE, SMEM>;
+  } else if (pass == 1) {
+    auto k = k_eam_force<TPA, EV, ONE, SMEM, false>;
     if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem));
     k<<<nblocks, EAM_THREADS, SMEM ? L.smem : 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh,
                                                             c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl);
+  } else if (pass == 2) {   // half list, density of both atoms of a pair
+    k_eam_rho_half<TPA, ONE><<<nblocks, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch,
+                                                                   L.P, c->rho);
+  } else {                  // half list, forces
+    k_eam_force<TPA, EV, ONE, false, true><<<nblocks, EAM_THREADS, 0, c->stream>>>(
+        c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh, c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl);
   }
   c->launches++; c->pair_launches++;
   CUDA_TRY(cudaGetLastError());
@@ -329,17 +435,19 @@ static int eam_prepare(b200md_ctx *c, EamLaunch &L) {
   return B200MD_OK;
 }
 
-// pass: 0 = density + embedding (k_eam_rho_fp), 1 = forces (k_eam_force)
+// pass: 0 = density + embedding (k_eam_rho_fp), 1 = forces (k_eam_force); half list: 2 = density, 3 = forces
 int pair_eam_launch(b200md_ctx *c, bool ev, int pass, const int *tiles, int ntl) {
   EamLaunch L;
   TRY(eam_prepare(c, L));
   switch (c->tpa) {
+    case 1: return launch_tpa<1>(c, L, ev, pass, tiles, ntl);
+    case 2: return launch_tpa<2>(c, L, ev, pass, tiles, ntl);
     case 4: return launch_tpa<4>(c, L, ev, pass, tiles, ntl);
     case 8: return launch_tpa<8>(c, L, ev, pass, tiles, ntl);
     case 16: return launch_tpa<16>(c, L, ev, pass, tiles, ntl);
     case 32: return launch_tpa<32>(c, L, ev, pass, tiles, ntl);
   }
-  b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32");
+  b200md_set_error("b200md: lanes per atom must be 1, 2, 4, 8, 16 or 32");
   return B200MD_ERR;
 }
 
@@ -354,11 +462,49 @@ int pair_eam_fp_comm(b200md_ctx *c) {
   return B200MD_OK;
 }
 
-int pair_eam_compute(b200md_ctx *c, int eflag, int vflag) {
-  if (c->list_kind != B200MD_LIST_FULL) {
-    b200md_set_error("b200md: eam runs on the full neighbor list (newton off) only");
-    return B200MD_ERR;
+// half list / newton on: PairEAM::compute with its reverse_comm(rho) and, via the caller,
+// Comm::reverse_comm of the forces
+static int pair_eam_compute_half(b200md_ctx *c, bool ev) {
+  const int A = 32 / c->tpa;
+  const int ntiles = (c->nlocal + A - 1) / A;
+  const int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
+  const int nall = c->nlocal + c->nghost;
+  const int nb_atoms = (c->nlocal + EAM_THREADS - 1) / EAM_THREADS;
+  c->ev_valid = false;
+  CUDA_TRY(cudaMemsetAsync(c->rho, 0, sizeof(double) * nall, c->stream));
+  for (int d = 0; d < 3; d++) CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax, 0, sizeof(double) * nall, c->stream));
+  double e_embed = 0, out7[7] = {0, 0, 0, 0, 0, 0, 0};
+  if (nblocks) {
+    if (ev) TRY(ensure_partials(c, nblocks > nb_atoms ? nblocks : nb_atoms));
+    TRY(pair_eam_launch(c, false, 2, nullptr, 0));
   }
+  TRY(comm_reverse_scalar(c, c->rho));
+  if (nb_atoms) {
+    EamLaunch L;
+    TRY(eam_prepare(c, L));
+    if (ev) { if (L.mode) k_eam_embed<true, true><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials);
+              else k_eam_embed<true, false><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials); }
+    else { if (L.mode) k_eam_embed<false, true><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials);
+           else k_eam_embed<false, false><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials); }
+    c->launches++; c->pair_launches++;
+    CUDA_TRY(cudaGetLastError());
+    if (ev) { double e1[1]; TRY(reduce_partials(c, nb_atoms, 1, e1)); e_embed = e1[0]; }
+  }
+  TRY(pair_eam_fp_comm(c));
+  if (nblocks) {
+    TRY(pair_eam_launch(c, ev, 3, nullptr, 0));
+    if (ev) TRY(reduce_partials(c, nblocks, 7, out7));
+  }
+  if (ev) {
+    c->eng_vdwl = e_embed + out7[0];
+    for (int k = 0; k < 6; k++) c->virial[k] = out7[1 + k];
+    c->ev_valid = true;
+  }
+  return B200MD_OK;
+}
+
+int pair_eam_compute(b200md_ctx *c, int eflag, int vflag) {
+  if (c->list_kind == B200MD_LIST_HALF_NEWTON) return pair_eam_compute_half(c, eflag || vflag);
   const bool ev = eflag || vflag;
   const int A = 32 / c->tpa;
   const int ntiles = (c->nlocal + A - 1) / A;

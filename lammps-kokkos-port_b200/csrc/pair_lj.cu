@@ -124,11 +124,13 @@ int pair_lj_launch(b200md_ctx *c, bool ev, const int *tiles, int ntl) {
     one = {t[0], t[1], t[2], t[3], t[4], t[5]};
   }
   switch (c->tpa) {
+    case 1: launch_lj<1>(c, nblocks, ev, one, tiles, ntl); break;
+    case 2: launch_lj<2>(c, nblocks, ev, one, tiles, ntl); break;
     case 4: launch_lj<4>(c, nblocks, ev, one, tiles, ntl); break;
     case 8: launch_lj<8>(c, nblocks, ev, one, tiles, ntl); break;
     case 16: launch_lj<16>(c, nblocks, ev, one, tiles, ntl); break;
     case 32: launch_lj<32>(c, nblocks, ev, one, tiles, ntl); break;
-    default: b200md_set_error("b200md: lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
+    default: b200md_set_error("b200md: lanes per atom must be 1, 2, 4, 8, 16 or 32"); return B200MD_ERR;
   }
   c->launches++;
   c->pair_launches++;

@@ -40,7 +40,8 @@ def in_lj(ctx, x=1, y=1, z=1, list_kind=B.LIST_FULL, every=20, delay=0, check=0,
     return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=0, units="lj")
 
 
-def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, seed=376847):
+def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, seed=376847,
+           list_kind=B.LIST_FULL):
     """bench/in.eam: units metal; lattice fcc 3.615; region box block 0 20x 0 20y 0 20z;
     create_atoms 1 box; pair_style eam; pair_coeff 1 1 Cu_u3.eam; velocity all create 1600.0
     376847 loop geom; neighbor 1.0 bin; neigh_modify every 1 delay 5 check yes; fix 1 all nve;
@@ -65,5 +66,5 @@ def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, 
     skin = 1.0
     cutsq = np.zeros((2, 2)); cutsq[1, 1] = tb["cutforcesq"]
     cn, cmax = B.cutneighsq_table(1, cutsq, skin)
-    ctx.neigh_config(cn, cmax, skin, every=1, delay=5, check=1, list_kind=B.LIST_FULL)
+    ctx.neigh_config(cn, cmax, skin, every=1, delay=5, check=1, list_kind=list_kind)
     return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=50, units="metal")

@@ -133,11 +133,13 @@ void VerletB200::device_setup()
   const double *v = nlocal ? &atom->v[0][0] : nullptr;
   if (b200md_set_atoms(ctx, nlocal, x, v, atom->type, atom->tag, atom->image, atom->ntypes, atom->mass))
     fail();
-  // full list, newton off on the device whatever the `newton` setting: same forces, no atomics
-  // (what the reference's Kokkos GPU path defaults to, src/KOKKOS/kokkos.cpp:257-260)
+  // `newton on` (the default) -> half list with f_j / rho_j accumulated by FP64 RED and
+  // reverse_comm (the reference's half/bin/atomonly/newton, chosen from the same flag in
+  // Neighbor::choose_pair, src/neighbor.cpp:2073-2077); `newton off` -> full list, no atomics,
+  // no reverse_comm (same forces as the reference's newtoff half list)
   if (b200md_neigh_config(ctx, atom->ntypes, &neighbor->cutneighsq[0][0], neighbor->cutneighmax,
                           neighbor->skin, neighbor->every, neighbor->delay, neighbor->dist_check,
-                          B200MD_LIST_FULL))
+                          force->newton_pair ? B200MD_LIST_HALF_NEWTON : B200MD_LIST_FULL))
     fail();
   if (dynamic_cast<B200PairStyle *>(force->pair)->b200_push(ctx)) fail();
   if (b200md_setup(ctx)) fail();

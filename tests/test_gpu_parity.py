@@ -41,7 +41,7 @@ def make_ctx(pkg, O, g, kind, list_kind, tpa=8):
     return ctx, s
 
 
-@pytest.mark.parametrize("tpa", [4, 8, 16, 32])
+@pytest.mark.parametrize("tpa", [1, 2, 4, 8, 16, 32])
 @pytest.mark.parametrize("name,kind", CASES)
 def test_golden_full_list_forces_thermo(pkg, oracle_mod, name, kind, tpa):
     B = pkg.b200md
@@ -67,10 +67,14 @@ def test_golden_full_list_forces_thermo(pkg, oracle_mod, name, kind, tpa):
     ctx.close()
 
 
-def test_golden_half_list_lj(pkg, oracle_mod):
+@pytest.mark.parametrize("tpa", [1, 2, 4, 16])
+@pytest.mark.parametrize("name,kind", CASES)
+def test_golden_half_list_forces_thermo(pkg, oracle_mod, name, kind, tpa):
+    """half/bin/atomonly/newton (the reference's default list) for lj/cut, eam and eam/alloy:
+    pair membership bit-exact, forces after reverse_comm, thermo series."""
     B = pkg.b200md
-    g = np.load(os.path.join(Cm.GOLDEN, "lj_n5.npz"))
-    ctx, s = make_ctx(pkg, oracle_mod, g, "lj", B.LIST_HALF_NEWTON)
+    g = np.load(os.path.join(Cm.GOLDEN, name + ".npz"))
+    ctx, s = make_ctx(pkg, oracle_mod, g, kind, B.LIST_HALF_NEWTON, tpa)
     ctx.setup()
     a = ctx.get_atoms()
     nn, flat = ctx.neigh_export(by_tag=True)
@@ -82,6 +86,11 @@ def test_golden_half_list_lj(pkg, oracle_mod):
     t = ctx.thermo()
     for k, key in enumerate(KEYS):
         assert abs(t[key] - g["thermo0"][k]) <= T_TOL * abs(g["thermo0"][k]), key
+    for row in g["thermo_series"]:
+        ctx.setup()
+        t = ctx.run(10, s["dt"], 0)[-1]
+        for k, key in enumerate(KEYS):
+            assert abs(t[key] - row[k]) <= T_TOL * abs(row[k]), (key, t[key], row[k])
     ctx.close()
 
 

@@ -91,8 +91,8 @@ def test_oracle_matches_yaml(pkg, oracle_mod, case):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("case", CASES)
-@pytest.mark.parametrize("lanes", [4, 32])
-def test_cuda_matches_yaml(pkg, case, lanes):
+@pytest.mark.parametrize("lanes,half", [(4, False), (32, False), (8, True), (1, False), (2, True)])
+def test_cuda_matches_yaml(pkg, case, lanes, half):
     B = pkg.b200md
     g = load(case)
     T = tables(pkg, g)
@@ -103,7 +103,7 @@ def test_cuda_matches_yaml(pkg, case, lanes):
     ctx.set_atoms(g["x"], g["v"], g["type"], np.arange(1, n + 1, dtype=np.int32), T["mass"])
     ctx.pair_eam_config(T)
     cn, cmax = cutneigh(pkg, T, 2)
-    ctx.neigh_config(cn, cmax, SKIN, every=EVERY, delay=DELAY, check=CHECK, list_kind=B.LIST_FULL)
+    ctx.neigh_config(cn, cmax, SKIN, every=EVERY, delay=DELAY, check=CHECK, list_kind=B.LIST_HALF_NEWTON if half else B.LIST_FULL)
     ctx.setup()
     a = ctx.get_atoms(("tag", "f")); e, vir = ctx.pair_tallies()
     check(g, by_tag(a["tag"], a["f"]), e, vir, "init")
