@@ -26,6 +26,16 @@ SCALE = {1: (4, 4, 4), 2: (8, 4, 4), 4: (8, 8, 4), 8: (8, 8, 8)}
 N_FULL = {"lj": 75.2, "eam": 75.5}
 BYTES_KERNEL = {"lj": 28 * 75.2 + 52, "eam": 64 * 75.5 + 104}     # LJ force pass; EAM rho+fp and force passes
 BYTES_STEP = {"lj": 2480.0, "eam": 5510.0}
+# (the figures above are SURVEY 8(d)'s yardstick, defined on the full list; the half-list kernels do
+#  the same physical work -- every pair once instead of twice -- and are rated with the same figure)
+# measured choice by workload and world size (2 = "two or more"), profiles/r01_summary.md: in.lj at N>1
+# keeps the full list (halo overlapped with the interior tiles, no reverse_comm); eam is faster on
+# the half list everywhere
+LIST_AUTO = {"lj": {1: "half", 2: "full"}, "eam": {1: "half", 2: "half"}}
+# algorithmic bytes of the half-list kernels per atom per step (N_h listed pairs per atom, each:
+# 4 index + 24 x_j [+ 8 fp_j] gathered, 24 f_j [8 rho_j] as RED payload; plus the per-atom terms)
+N_HALF = {"lj": 37.6, "eam": 37.75}
+BYTES_KERNEL_HALF = {"lj": 52 * 37.6 + 52, "eam": (36 + 60) * 37.75 + 104}
 
 
 def peaks():
@@ -106,6 +116,8 @@ def main():
     ap.add_argument("--workload", default="lj", choices=["lj", "eam"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--lanes", type=int, default=0)
+    ap.add_argument("--list", default="auto", choices=["auto", "half", "full"],
+                    help="half = half/bin/atomonly/newton (the input scripts' default, newton on); full = newton off")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -153,10 +165,17 @@ def main():
         ctx.comm_init(bytes(idt.cpu().numpy().tobytes()))
     if a.lanes:
         ctx.set_lanes_per_atom(a.lanes)
+    # list kind: the scripts run with `newton on` -> half list (f_j, rho_j by FP64 RED + reverse_comm);
+    # measured on B200 (profiles/): half wins on one GPU; with several ranks the full list lets the
+    # force kernel overlap the halo and needs no reverse_comm
+    lk = a.list if a.list != "auto" else LIST_AUTO[wl][min(world, 2)]
+    list_kind = B.LIST_HALF_NEWTON if lk == "half" else B.LIST_FULL
+    config["neighbor_list"] = "half/bin/atomonly/newton" if lk == "half" else "full/bin/atomonly (newton off)"
     if wl == "lj":
-        cfg = P.inputs.in_lj(ctx, *xyz)
+        cfg = P.inputs.in_lj(ctx, *xyz, list_kind=list_kind)
     else:
-        cfg = P.inputs.in_eam(ctx, *xyz, potential=os.path.join(ROOT, "oracle", "_ref", "potentials", "Cu_u3.eam"))
+        cfg = P.inputs.in_eam(ctx, *xyz, potential=os.path.join(ROOT, "oracle", "_ref", "potentials", "Cu_u3.eam"),
+                              list_kind=list_kind)
     config["decomposition"] = "x".join(str(g) for g in B.procgrid(world, [20.0 * xyz[0], 20.0 * xyz[1], 20.0 * xyz[2]]))
     ctx.setup()
 
@@ -198,13 +217,17 @@ def main():
     pair_ms = tp["pair_ms"] / n_eval  # per timestep (LJ: one launch; EAM: rho+fp, fp halo, force)
     nloc = ctx.nlocal()[0]
     hbm, which = peaks()
-    achieved = BYTES_KERNEL[wl] * nloc / (pair_ms / 1e3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "k_lj" if wl == "lj" else "k_eam_rho_fp+k_eam_force", "achieved": achieved,
+    bytes_kernel = BYTES_KERNEL_HALF[wl] if lk == "half" else BYTES_KERNEL[wl]
+    achieved = bytes_kernel * nloc / (pair_ms / 1e3) / 1e9
+    roofline = {"bound": "hbm", "kernel": ("k_lj" if wl == "lj" else ("k_eam_rho_half+k_eam_embed+k_eam_force" if lk == "half" else "k_eam_rho_fp+k_eam_force")),
+                "list": lk, "achieved": achieved,
                 "peak": hbm, "peak_source": which, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
-                "kernel_ms": pair_ms, "bytes_per_atom_launch": BYTES_KERNEL[wl],
+                "kernel_ms": pair_ms, "bytes_per_atom_launch": bytes_kernel,
                 "step_achieved": BYTES_STEP[wl] * (value / ngpus) / 1e9, "step_frac": BYTES_STEP[wl] * (value / ngpus) / 1e9 / hbm,
                 "phases_ms_per_step": {k: tp[k + "_ms"] / n_eval for k in ("pair", "neigh", "comm", "modify")}}
-    tr = os.path.join(ROOT, "profiles", "traffic_%s.json" % wl)
+    tr = os.path.join(ROOT, "profiles", "traffic_%s_%s.json" % (wl, lk))
+    if not os.path.exists(tr):
+        tr = os.path.join(ROOT, "profiles", "traffic_%s.json" % wl)
     if os.path.exists(tr):
         roofline["traffic"] = json.load(open(tr)).get("dram_bytes_per_launch")
 

@@ -16,11 +16,12 @@ def mk():
     ctx.comm_init(bytes(idt.cpu().numpy().tobytes()))
     return ctx
 x = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+lk = B.LIST_HALF_NEWTON if (len(sys.argv) > 2 and sys.argv[2] == "half") else B.LIST_FULL
 ok = True
 for wl in ("lj", "eam"):
     ctx = mk()
-    if wl == "lj": cfg = P.inputs.in_lj(ctx, x, x, x); per = cfg["natoms"]
-    else: cfg = P.inputs.in_eam(ctx, x, x, x, potential="oracle/_ref/potentials/Cu_u3.eam"); per = 1.0
+    if wl == "lj": cfg = P.inputs.in_lj(ctx, x, x, x, list_kind=lk); per = cfg["natoms"]
+    else: cfg = P.inputs.in_eam(ctx, x, x, x, potential="oracle/_ref/potentials/Cu_u3.eam", list_kind=lk); per = 1.0
     ctx.setup()
     recs = [ctx.thermo()] + ctx.run(100, cfg["dt"], 50)
     nl, ng = ctx.nlocal()

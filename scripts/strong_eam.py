@@ -16,7 +16,8 @@ if world > 1:
     if rank == 0: idt = torch.frombuffer(bytearray(B.Context.unique_id()), dtype=torch.uint8).cuda()
     dist.broadcast(idt, 0)
     ctx.comm_init(bytes(idt.cpu().numpy().tobytes()))
-cfg = P.inputs.in_eam(ctx, x, x, x, potential="oracle/_ref/potentials/Cu_mishin1.eam.alloy", style="eam/alloy")
+lk = B.LIST_HALF_NEWTON if (len(sys.argv) > 2 and sys.argv[2] == "half") else B.LIST_FULL
+cfg = P.inputs.in_eam(ctx, x, x, x, potential="oracle/_ref/potentials/Cu_mishin1.eam.alloy", style="eam/alloy", list_kind=lk)
 ctx.setup()
 t0 = ctx.thermo()
 ctx.run(10, cfg["dt"], 0)
@@ -26,7 +27,7 @@ if world > 1:
     t = torch.tensor([tm["total_ms"]], dtype=torch.float64, device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t)
 else: ms = tm["total_ms"]
 if rank == 0:
-    print("eam/alloy Cu_mishin1 %d atoms N=%d: %.3f ms/step %.1f Matom-steps/s builds %d rank0 nlocal %d nghost %d | step0 T %.8g PE %.10g P %.8g | step110 T %.8g PE %.10g P %.8g" % (
+    print("eam/alloy Cu_mishin1 " + ("half" if lk == B.LIST_HALF_NEWTON else "full") + " %d atoms N=%d: %.3f ms/step %.1f Matom-steps/s builds %d rank0 nlocal %d nghost %d | step0 T %.8g PE %.10g P %.8g | step110 T %.8g PE %.10g P %.8g" % (
         cfg["natoms"], world, ms / 100, cfg["natoms"] * 100 / ms / 1e3, tm["nbuilds"], nl, ng, t0["temp"], t0["pe"], t0["press"], th[-1]["temp"], th[-1]["pe"], th[-1]["press"]), flush=True)
 ctx.close()
 if world > 1: dist.destroy_process_group()
