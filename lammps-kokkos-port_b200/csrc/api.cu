@@ -438,6 +438,7 @@ extern "C" int b200md_set_lanes_per_atom(b200md_ctx *c, int lanes) {
   NEED(lanes == 1 || lanes == 2 || lanes == 4 || lanes == 8 || lanes == 16 || lanes == 32,
        "b200md: lanes per atom must be 1, 2, 4, 8, 16 or 32");
   c->tpa = lanes;
+  c->tpa_user = true;
   const char *bl = getenv("B200MD_BUILD_LANES");   // tuning only; default 4 (8 when the force kernels use more)
   c->tpa_build = bl ? atoi(bl) : (lanes < 4 ? 4 : lanes);
   return B200MD_OK;
@@ -486,6 +487,7 @@ extern "C" int b200md_pair_eam_config(b200md_ctx *c, int ntypes, int nrho, int n
                            rhor_spline, nz2r, z2r_spline, type2frho, type2rhor, type2z2r, scale));
   c->cutforcemax = sqrt(cutforcesq);
   c->pair_style = B200MD_PAIR_EAM;
+  if (!c->tpa_user) { c->tpa = 1; c->tpa_build = 4; }   // measured: one lane per atom is best for the eam passes
   return B200MD_OK;
 }
 

@@ -565,11 +565,36 @@ static int reverse_staged(b200md_ctx *c, double *arr) {
   return B200MD_OK;
 }
 
+// single rank: every ghost adds straight into its flattened owner (ghost_src), one launch instead
+// of one per swap; same sum as the staged order up to FP64 RED ordering
+template <int NV>
+__global__ void k_reverse_flat(int nghost, int nlocal, int nmax, double *__restrict__ a, const int *__restrict__ ghost_src) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= nghost) return;
+  const int o = ghost_src[nlocal + g];
+#pragma unroll
+  for (int d = 0; d < NV; d++) atomicAdd(&a[o + d * (size_t)nmax], a[nlocal + g + d * (size_t)nmax]);
+}
+
 int comm_reverse_force(b200md_ctx *c) {
   if (c->list_kind == B200MD_LIST_FULL) return B200MD_OK;  // newton off: nothing on ghosts
+  if (c->all_self) {
+    if (c->nghost == 0) return B200MD_OK;
+    k_reverse_flat<3><<<nblk(c->nghost), 256, 0, c->stream>>>(c->nghost, c->nlocal, c->nmax, c->f, c->ghost_src);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return B200MD_OK;
+  }
   return reverse_staged<3>(c, c->f);
 }
 int comm_reverse_scalar(b200md_ctx *c, double *arr) {
   if (c->list_kind == B200MD_LIST_FULL) return B200MD_OK;
+  if (c->all_self) {
+    if (c->nghost == 0) return B200MD_OK;
+    k_reverse_flat<1><<<nblk(c->nghost), 256, 0, c->stream>>>(c->nghost, c->nlocal, c->nmax, arr, c->ghost_src);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return B200MD_OK;
+  }
   return reverse_staged<1>(c, arr);
 }

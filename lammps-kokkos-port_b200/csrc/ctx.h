@@ -99,6 +99,7 @@ struct b200md_ctx {
   // neighbor list
   int tpa = 2;        // lanes per atom in the force kernels (1..32); measured best on B200
   int tpa_build = 4;  // lanes per atom in the list build (4..32)
+  bool tpa_user = false;  // set by b200md_set_lanes_per_atom; otherwise the pair style picks (lj 2, eam 1)
   int pitch = 0;  // max neighbors per atom (multiple of tpa)
   int *neigh = nullptr;
   size_t neigh_cap = 0;

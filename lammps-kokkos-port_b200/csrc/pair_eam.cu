@@ -28,6 +28,21 @@
 #include "util.cuh"
 
 #define EAM_THREADS 256
+// tuning macros (see pair_lj.cu): unroll depth and minimum resident blocks per SM of the pair loops
+// measured best on B200: density pass 32 registers / 8 blocks per SM / no unroll; force pass 64
+// registers / unroll 2 (it needs the registers: 40-register builds spill and lose 15 %)
+#ifndef EAM_RHO_UNROLL
+#define EAM_RHO_UNROLL 1
+#endif
+#ifndef EAM_RHO_MINBLOCKS
+#define EAM_RHO_MINBLOCKS 8
+#endif
+#ifndef EAM_FORCE_UNROLL
+#define EAM_FORCE_UNROLL 2
+#endif
+#ifndef EAM_FORCE_MINBLOCKS
+#define EAM_FORCE_MINBLOCKS 4
+#endif
 
 void pair_eam_free(b200md_ctx *c) {
   EamTables &e = c->eam;
@@ -84,6 +99,8 @@ int pair_eam_config_impl(b200md_ctx *c, int ntypes, int nrho, int nr, double rdr
   return B200MD_OK;
 }
 
+constexpr int kRhoUnroll = EAM_RHO_UNROLL, kForceUnroll = EAM_FORCE_UNROLL;
+
 struct EamParams {
   int ntypes, nrho, nr;
   double rdr, rdrho, rhomax, cutforcesq, scale11;
@@ -92,6 +109,9 @@ struct EamParams {
 };
 
 __device__ __forceinline__ double4 ld4(const double *p) {
+#if defined(B200MD_LD256)
+  return ld_xq(reinterpret_cast<const double4 *>(p));   // one 256-bit load per 32-byte table row
+#endif
   const double2 *q = reinterpret_cast<const double2 *>(p);
   const double2 a = q[0], b = q[1];
   return make_double4(a.x, a.y, b.x, b.y);
@@ -100,7 +120,7 @@ __device__ __forceinline__ double4 ld4(const double *p) {
 // ---- pass 1 + embedding -------------------------------------------------------------------
 // ONE: single element (tabC, optional shared-memory staging, writes the packed xfp record)
 template <int TPA, bool EV, bool ONE, bool SMEM>
-__global__ void __launch_bounds__(EAM_THREADS)
+__global__ void __launch_bounds__(EAM_THREADS, (EV || !ONE) ? 4 : EAM_RHO_MINBLOCKS)
 k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh, const int *__restrict__ numneigh,
              int pitch, EamParams P, double *__restrict__ rho, double *__restrict__ fp, double4 *__restrict__ xfp,
              double *__restrict__ partials, const int *__restrict__ tile_list, int ntile_list) {
@@ -130,7 +150,7 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
     const int n = numneigh[i];
     const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
     const int niter = (n + TPA - 1) / TPA;
-#pragma unroll 4
+#pragma unroll kRhoUnroll
     for (int it = 0; it < niter; it++) {
       if (it * TPA + l < n) {
         const int j = __ldg(nb + it * 32);
@@ -177,7 +197,7 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
 
 // ---- half list: pass 1 without the embedding (every listed pair adds to both atoms) ---------
 template <int TPA, bool ONE>
-__global__ void __launch_bounds__(EAM_THREADS)
+__global__ void __launch_bounds__(EAM_THREADS, ONE ? EAM_RHO_MINBLOCKS : 4)
 k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh,
                const int *__restrict__ numneigh, int pitch, EamParams P, double *__restrict__ rho) {
   constexpr int A = 32 / TPA;
@@ -194,7 +214,7 @@ k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict
     const int n = numneigh[i];
     const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
     const int niter = (n + TPA - 1) / TPA;
-#pragma unroll 4
+#pragma unroll kRhoUnroll
     for (int it = 0; it < niter; it++) {
       if (it * TPA + l < n) {
         const int j = __ldg(nb + it * 32);
@@ -275,7 +295,7 @@ __global__ void k_pack_xfp(int nghost, int nlocal, const double4 *__restrict__ x
 
 // ---- pass 3: forces -------------------------------------------------------------------------
 template <int TPA, bool EV, bool ONE, bool SMEM, bool HALF>
-__global__ void __launch_bounds__(EAM_THREADS)
+__global__ void __launch_bounds__(EAM_THREADS, EAM_FORCE_MINBLOCKS)
 k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 *__restrict__ xfp,
             const int *__restrict__ neigh, const int *__restrict__ numneigh, int pitch, EamParams P,
             const double *__restrict__ fp, double *__restrict__ f, double *__restrict__ partials,
@@ -306,7 +326,7 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
     const int n = numneigh[i];
     const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
     const int niter = (n + TPA - 1) / TPA;
-#pragma unroll 2
+#pragma unroll kForceUnroll
     for (int it = 0; it < niter; it++) {
       if (it * TPA + l < n) {
         const int j = __ldg(nb + it * 32);

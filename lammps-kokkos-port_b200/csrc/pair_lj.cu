@@ -18,15 +18,28 @@
 
 #define PAIR_THREADS 256
 #define LJ_MAX_TYPES_SMEM 8
+// tuning macros (profiles/r01_summary.md has the sweep on B200): neighbors in flight per lane and
+// minimum resident blocks per SM (a software prefetch of the next index batch was tried and lost
+// to plain occupancy).  The kernel
+// is latency-bound (ncu: long-scoreboard stalls, no unit above 70 %), and thread-level
+// parallelism beats unrolling: 32 registers / 8 blocks per SM / no unroll is +23 % over
+// 48 registers / unroll 4.  The tally variants (thermo steps only) keep 4 blocks per SM.
+#ifndef LJ_UNROLL
+#define LJ_UNROLL 1
+#endif
+#ifndef LJ_MINBLOCKS
+#define LJ_MINBLOCKS 8
+#endif
 
 struct LJOne { double cutsq, lj1, lj2, lj3, lj4, offset; };
 
 template <int TPA, bool EV, bool HALF, bool ONETYPE>
-__global__ void __launch_bounds__(PAIR_THREADS)
+__global__ void __launch_bounds__(PAIR_THREADS, (EV || !ONETYPE) ? 4 : LJ_MINBLOCKS)
 k_lj(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict__ neigh,
      const int *__restrict__ numneigh, int pitch, LJOne one, const double *__restrict__ ljtab, int ntypes,
      double *__restrict__ f, double *__restrict__ partials, const int *__restrict__ tile_list, int ntile_list) {
   constexpr int A = 32 / TPA;
+  constexpr int kUnroll = LJ_UNROLL;
   __shared__ double s_tab[ONETYPE ? 1 : (LJ_MAX_TYPES_SMEM + 1) * (LJ_MAX_TYPES_SMEM + 1) * 6];
   const int nt1 = ntypes + 1;
   if (!ONETYPE) {
@@ -51,7 +64,7 @@ k_lj(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict
     const int itype = ONETYPE ? 1 : xq_type(qi);
     const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
     const int niter = (n + TPA - 1) / TPA;
-#pragma unroll 4
+#pragma unroll kUnroll
     for (int it = 0; it < niter; it++) {
       if (it * TPA + l < n) {
         const int j = __ldg(nb + it * 32);
