@@ -63,6 +63,11 @@ extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out)
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_fp, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_fphalo, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_bnd, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rev, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rb, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rr, cudaEventDisableTiming));
+  if (const char *sp = getenv("B200MD_SPLIT")) c->split = atof(sp);
   { const char *ov = getenv("B200MD_OVERLAP"); c->overlap = !(ov && ov[0] == '0'); }
   CUDA_TRY(cudaMalloc(&c->d_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMallocHost(&c->h_result, 16 * sizeof(double)));
@@ -89,7 +94,7 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
   if (c->h_result) cudaFreeHost(c->h_result);
   if (c->h_flags) cudaFreeHost(c->h_flags);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
-  cudaEvent_t evs[] = {c->ev_x, c->ev_halo, c->ev_fp, c->ev_fphalo};
+  cudaEvent_t evs[] = {c->ev_x, c->ev_halo, c->ev_fp, c->ev_fphalo, c->ev_bnd, c->ev_rev, c->ev_rb, c->ev_rr};
   for (auto e : evs) if (e) cudaEventDestroy(e);
   if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
   cudaStreamDestroy(c->stream);
@@ -562,7 +567,7 @@ extern "C" int b200md_setup(b200md_ctx *c) {
 // comm stream while the tiles without ghost neighbors are evaluated; boundary tiles follow.
 // Same kernels, same per-atom arithmetic and order as the unsplit launch -> identical results.
 static bool can_overlap(const b200md_ctx *c) {
-  return c->overlap && !c->all_self && c->list_kind == B200MD_LIST_FULL && c->n_tiles_int > 0;
+  return c->overlap && !c->all_self && c->n_tiles_int > 0;
 }
 static int on_comm_stream(b200md_ctx *c, int (*fn)(b200md_ctx *)) {
   cudaStream_t saved = c->stream;
@@ -571,6 +576,51 @@ static int on_comm_stream(b200md_ctx *c, int (*fn)(b200md_ctx *)) {
   c->stream = saved;
   return r;
 }
+// Half/newton list with compute/halo overlap.  Interior tiles (no ghost neighbor) are split in two
+// parts: part 1 runs while the forward halo is in flight, then the boundary tiles, then part 2 runs
+// while the ghost contributions travel back (reverse_comm on the comm stream, RED into f / rho).
+static int forces_overlapped_half(b200md_ctx *c) {
+  cudaStream_t s = c->stream, cs = c->comm_stream;
+  const int nall = c->nlocal + c->nghost;
+  const int n1 = (int)(c->n_tiles_int * c->split), n2 = c->n_tiles_int - n1;
+  const int *int1 = c->tiles_int, *int2 = c->tiles_int + n1;
+  const bool eam = c->pair_style == B200MD_PAIR_EAM;
+  for (int d = 0; d < 3; d++) CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax, 0, sizeof(double) * nall, s));
+  if (eam) CUDA_TRY(cudaMemsetAsync(c->rho, 0, sizeof(double) * nall, s));
+  if (!eam) {
+    TRY(pair_lj_launch(c, false, int1, n1));
+    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
+    TRY(pair_lj_launch(c, false, c->tiles_bnd, c->n_tiles_bnd));
+  } else {
+    TRY(pair_eam_launch(c, false, 2, int1, n1));
+    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
+    TRY(pair_eam_launch(c, false, 2, c->tiles_bnd, c->n_tiles_bnd));
+    CUDA_TRY(cudaEventRecord(c->ev_rb, s));              // ghost rho complete
+    CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_rb, 0));
+    TRY(on_comm_stream(c, comm_reverse_rho));
+    CUDA_TRY(cudaEventRecord(c->ev_rr, cs));
+    TRY(pair_eam_launch(c, false, 2, int2, n2));
+    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_rr, 0));
+    TRY(pair_eam_embed(c, false, nullptr));
+    CUDA_TRY(cudaEventRecord(c->ev_fp, s));
+    CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_fp, 0));
+    TRY(on_comm_stream(c, pair_eam_fp_comm));
+    CUDA_TRY(cudaEventRecord(c->ev_fphalo, cs));
+    TRY(pair_eam_launch(c, false, 3, int1, n1));
+    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_fphalo, 0));
+    TRY(pair_eam_launch(c, false, 3, c->tiles_bnd, c->n_tiles_bnd));
+  }
+  CUDA_TRY(cudaEventRecord(c->ev_bnd, s));               // ghost forces complete
+  CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_bnd, 0));
+  TRY(on_comm_stream(c, comm_reverse_force));
+  CUDA_TRY(cudaEventRecord(c->ev_rev, cs));
+  if (!eam) TRY(pair_lj_launch(c, false, int2, n2));
+  else TRY(pair_eam_launch(c, false, 3, int2, n2));
+  CUDA_TRY(cudaStreamWaitEvent(s, c->ev_rev, 0));
+  return B200MD_OK;
+}
+
+// non-rebuild, non-tally step on several ranks; on return f is complete (reverse_comm included)
 static int forces_overlapped(b200md_ctx *c) {
   cudaStream_t s = c->stream, cs = c->comm_stream;
   CUDA_TRY(cudaEventRecord(c->ev_x, s));               // positions integrated
@@ -578,6 +628,7 @@ static int forces_overlapped(b200md_ctx *c) {
   TRY(on_comm_stream(c, comm_forward));                // x halo on the comm stream
   CUDA_TRY(cudaEventRecord(c->ev_halo, cs));
   c->ev_valid = false;
+  if (c->list_kind == B200MD_LIST_HALF_NEWTON) return forces_overlapped_half(c);
   if (c->pair_style == B200MD_PAIR_LJ_CUT) {
     TRY(pair_lj_launch(c, false, c->tiles_int, c->n_tiles_int));
     CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
@@ -629,13 +680,13 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     int nflag = 0;
     TRY(b200md_neigh_decide(c, &nflag));
     if (!nflag && !ev && can_overlap(c)) {
-      T.begin(1); TRY(forces_overlapped(c)); T.end();
+      T.begin(1); TRY(forces_overlapped(c)); T.end();   // includes reverse_comm on half lists
     } else {
       if (!nflag) { T.begin(3); TRY(comm_forward(c)); T.end(); }
       else { T.begin(2); TRY(b200md_neigh_build(c)); T.end(); }
       T.begin(1); TRY(b200md_pair_compute(c, ev, ev, nullptr, nullptr)); T.end();
+      T.begin(3); TRY(comm_reverse_force(c)); T.end();
     }
-    T.begin(3); TRY(comm_reverse_force(c)); T.end();
     T.begin(4); TRY(nve_final(c, dtf)); T.end();
     if (out_step && thermo_out && nth < max_thermo) { TRY(b200md_thermo_compute(c, &thermo_out[nth])); nth++; }
   }

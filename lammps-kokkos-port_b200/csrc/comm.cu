@@ -504,12 +504,12 @@ __global__ void k_rev_self3(int n, const int *__restrict__ list, int first, int 
   if (k >= n) return;
   const int j = list[k];
 #pragma unroll
-  for (int d = 0; d < 3; d++) f[j + d * (size_t)nmax] += f[first + k + d * (size_t)nmax];
+  for (int d = 0; d < 3; d++) atomicAdd(&f[j + d * (size_t)nmax], f[first + k + d * (size_t)nmax]);
 }
 __global__ void k_rev_self1(int n, const int *__restrict__ list, int first, double *__restrict__ a) {
   int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
-  a[list[k]] += a[first + k];
+  atomicAdd(&a[list[k]], a[first + k]);
 }
 __global__ void k_rev_pack3(int n, int first, int nmax, const double *__restrict__ f, double *__restrict__ buf) {
   int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -522,17 +522,17 @@ __global__ void k_rev_unpack3(int n, const int *__restrict__ list, int nmax, dou
   if (k >= n) return;
   const int j = list[k];
 #pragma unroll
-  for (int d = 0; d < 3; d++) f[j + d * (size_t)nmax] += buf[(size_t)k * 3 + d];
+  for (int d = 0; d < 3; d++) atomicAdd(&f[j + d * (size_t)nmax], buf[(size_t)k * 3 + d]);
 }
 __global__ void k_rev_unpack1(int n, const int *__restrict__ list, double *__restrict__ a, const double *__restrict__ buf) {
   int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
-  a[list[k]] += buf[k];
+  atomicAdd(&a[list[k]], buf[k]);
 }
 
-// swaps in reverse order, one at a time: a send list may name the same atom only once per
-// swap, so the += of one swap is race-free; later (earlier-numbered) swaps see its result
-// exactly like comm_brick.cpp:610-638.
+// swaps in reverse order, one at a time; later (earlier-numbered) swaps see the result of this
+// one exactly like comm_brick.cpp:610-638.  The adds are FP64 RED because, with compute/halo
+// overlap, interior tiles of the force kernel accumulate into the same owned atoms concurrently.
 template <int NV>
 static int reverse_staged(b200md_ctx *c, double *arr) {
   cudaStream_t st = c->stream;
@@ -598,3 +598,4 @@ int comm_reverse_scalar(b200md_ctx *c, double *arr) {
   }
   return reverse_staged<1>(c, arr);
 }
+int comm_reverse_rho(b200md_ctx *c) { return comm_reverse_scalar(c, c->rho); }

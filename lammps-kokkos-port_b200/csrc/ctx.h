@@ -109,6 +109,8 @@ struct b200md_ctx {
   int tile_cap = 0, n_tiles_int = 0, n_tiles_bnd = 0;
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t ev_x = nullptr, ev_halo = nullptr, ev_fp = nullptr, ev_fphalo = nullptr;
+  cudaEvent_t ev_bnd = nullptr, ev_rev = nullptr, ev_rb = nullptr, ev_rr = nullptr;  // half-list overlap
+  double split = 0.5;  // share of the interior tiles evaluated before the boundary tiles (half-list overlap)
   bool overlap = true;
   // comm
   b200md_swap_schedule sched;
@@ -180,6 +182,7 @@ int comm_forward(b200md_ctx *c);
 int comm_forward_scalar(b200md_ctx *c, double *arr);  // EAM fp
 int comm_reverse_force(b200md_ctx *c);
 int comm_reverse_scalar(b200md_ctx *c, double *arr);  // EAM rho (half lists)
+int comm_reverse_rho(b200md_ctx *c);
 int comm_allreduce_sum(b200md_ctx *c, double *hostvals, int n);
 int comm_allreduce_max_int(b200md_ctx *c, int *hostval);
 void comm_free(b200md_ctx *c);
@@ -188,6 +191,7 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag);
 int pair_lj_launch(b200md_ctx *c, bool ev, const int *tiles, int ntl);
 int pair_eam_launch(b200md_ctx *c, bool ev, int pass, const int *tiles, int ntl);
 int pair_eam_fp_comm(b200md_ctx *c);
+int pair_eam_embed(b200md_ctx *c, bool ev, double *e_embed);  // half-list path: F(rho), F'(rho) of owned atoms
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);
 // nve.cu
 int nve_initial(b200md_ctx *c, double dtv, double dtf, bool check_dist);

@@ -199,13 +199,16 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
 template <int TPA, bool ONE>
 __global__ void __launch_bounds__(EAM_THREADS, ONE ? EAM_RHO_MINBLOCKS : 4)
 k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh,
-               const int *__restrict__ numneigh, int pitch, EamParams P, double *__restrict__ rho) {
+               const int *__restrict__ numneigh, int pitch, EamParams P, double *__restrict__ rho,
+               const int *__restrict__ tile_list, int ntile_list) {
   constexpr int A = 32 / TPA;
   const int lane = threadIdx.x & 31;
   const int sub = lane / TPA, l = lane % TPA;
-  const int tile = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const bool in_list = !tile_list || w < ntile_list;
+  const int tile = tile_list ? (in_list ? tile_list[w] : 0) : w;
   const int i = tile * A + sub;
-  const bool active = i < nlocal;
+  const bool active = in_list && i < nlocal;
   const int nt1 = P.ntypes + 1;
   double r_acc = 0;
   if (active) {
@@ -417,7 +420,7 @@ static int launch_pass(b200md_ctx *c, const EamLaunch &L, int pass, const int *t
                                                             c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl);
   } else if (pass == 2) {   // half list, density of both atoms of a pair
     k_eam_rho_half<TPA, ONE><<<nblocks, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch,
-                                                                   L.P, c->rho);
+                                                                   L.P, c->rho, tiles, ntl);
   } else {                  // half list, forces
     k_eam_force<TPA, EV, ONE, false, true><<<nblocks, EAM_THREADS, 0, c->stream>>>(
         c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh, c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl);
@@ -482,6 +485,22 @@ int pair_eam_fp_comm(b200md_ctx *c) {
   return B200MD_OK;
 }
 
+int pair_eam_embed(b200md_ctx *c, bool ev, double *e_embed) {
+  const int nb_atoms = (c->nlocal + EAM_THREADS - 1) / EAM_THREADS;
+  if (!nb_atoms) return B200MD_OK;
+  EamLaunch L;
+  TRY(eam_prepare(c, L));
+  if (ev) TRY(ensure_partials(c, nb_atoms));
+  if (ev) { if (L.mode) k_eam_embed<true, true><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials);
+            else k_eam_embed<true, false><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials); }
+  else { if (L.mode) k_eam_embed<false, true><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials);
+         else k_eam_embed<false, false><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials); }
+  c->launches++; c->pair_launches++;
+  CUDA_TRY(cudaGetLastError());
+  if (ev && e_embed) { double e1[1]; TRY(reduce_partials(c, nb_atoms, 1, e1)); *e_embed = e1[0]; }
+  return B200MD_OK;
+}
+
 // half list / newton on: PairEAM::compute with its reverse_comm(rho) and, via the caller,
 // Comm::reverse_comm of the forces
 static int pair_eam_compute_half(b200md_ctx *c, bool ev) {
@@ -499,17 +518,7 @@ static int pair_eam_compute_half(b200md_ctx *c, bool ev) {
     TRY(pair_eam_launch(c, false, 2, nullptr, 0));
   }
   TRY(comm_reverse_scalar(c, c->rho));
-  if (nb_atoms) {
-    EamLaunch L;
-    TRY(eam_prepare(c, L));
-    if (ev) { if (L.mode) k_eam_embed<true, true><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials);
-              else k_eam_embed<true, false><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials); }
-    else { if (L.mode) k_eam_embed<false, true><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials);
-           else k_eam_embed<false, false><<<nb_atoms, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, L.P, c->rho, c->fp, c->eam.xfp, c->partials); }
-    c->launches++; c->pair_launches++;
-    CUDA_TRY(cudaGetLastError());
-    if (ev) { double e1[1]; TRY(reduce_partials(c, nb_atoms, 1, e1)); e_embed = e1[0]; }
-  }
+  TRY(pair_eam_embed(c, ev, &e_embed));
   TRY(pair_eam_fp_comm(c));
   if (nblocks) {
     TRY(pair_eam_launch(c, ev, 3, nullptr, 0));
