@@ -194,6 +194,32 @@ int b200md_pair_tallies(b200md_ctx *ctx, double *eng_vdwl, double virial[6]);
 /* Comm::reverse_comm of forces (src/comm_brick.cpp:598-639); no-op for full lists. */
 int b200md_reverse_comm(b200md_ctx *ctx);
 
+/* ---- molecular topology (bench/in.chain) ------------------------------------------------ */
+
+/* Bonds and special neighbors of an `atom_style bond` system, keyed by atom TAG and replicated on
+ * every rank (nothing per-atom migrates).  CSR tables: *_offset has natoms+2 entries, row t (1-based
+ * tag) spans [offset[t], offset[t+1]).  bond_* lists the bonds STORED on tag t (newton_bond on:
+ * each bond once, src/atom_vec_bond.cpp data_atom / Atom::data_bonds src/atom.cpp:1408-1470);
+ * special_* is Atom::special with its level (1 = 1-2, 2 = 1-3, 3 = 1-4; src/special.cpp:50-120).
+ * special_lj / special_coul are Force::special_lj/coul[4] (index 0 unused); weights must be 0 or
+ * 1 (special_bonds fene/lj 0 1 1: 1-2 pairs leave the pair list, src/npair.h:125-160).  The bond
+ * list of the reference (NTopoBondAll::build, src/ntopo_bond_all.cpp:37-80) is implicit: each
+ * owned atom evaluates the bonds stored on its tag through a tag->index map rebuilt with the
+ * neighbor list. */
+int b200md_set_topology(b200md_ctx *ctx, long long natoms, const int *bond_offset,
+                        const int *bond_partner_tag, const int *bond_type,
+                        const int *special_offset, const int *special_tag,
+                        const int *special_level, const double special_lj[4],
+                        const double special_coul[4]);
+/* bond_style fene coefficients, 1-based [nbondtypes+1] (BondFENE::coeff,
+ * src/MOLECULE/bond_fene.cpp:146-170). */
+int b200md_bond_fene_config(b200md_ctx *ctx, int nbondtypes, const double *k, const double *r0,
+                            const double *epsilon, const double *sigma);
+/* Bond::compute(eflag,vflag) (src/MOLECULE/bond_fene.cpp:53-129): adds the bond forces to f
+ * (call after b200md_pair_compute, before b200md_reverse_comm); energy / virial[6] are this
+ * rank's Bond::energy and Bond::virial, written when the flag is set. */
+int b200md_bond_compute(b200md_ctx *ctx, int eflag, int vflag, double *energy, double virial[6]);
+
 /* ---- fix nve + thermo ---------------------------------------------------------------- */
 
 /* FixNVE::initial_integrate / final_integrate (src/fix_nve.cpp:64-141). dtf = 0.5*dt*ftm2v. */
@@ -205,8 +231,9 @@ int b200md_nve_final(b200md_ctx *ctx, double dtf);
 typedef struct b200md_thermo {
   long long step;
   double natoms;
-  double temp, pe, ke, press; /* pe, ke extensive (not divided by N) */
-  double virial[6];
+  double temp, pe, ke, press; /* pe, ke extensive (not divided by N); pe = pair + bond */
+  double virial[6];           /* pair + bond */
+  double emol;                /* bond energy (thermo keyword emol), 0 for atomic systems */
 } b200md_thermo;
 int b200md_thermo_compute(b200md_ctx *ctx, b200md_thermo *out);
 

@@ -40,11 +40,11 @@ class BinGeometry(C.Structure):
 
 class Thermo(C.Structure):
     _fields_ = [("step", C.c_longlong), ("natoms", C.c_double), ("temp", C.c_double), ("pe", C.c_double),
-                ("ke", C.c_double), ("press", C.c_double), ("virial", C.c_double * 6)]
+                ("ke", C.c_double), ("press", C.c_double), ("virial", C.c_double * 6), ("emol", C.c_double)]
 
     def as_dict(self):
         return dict(step=self.step, natoms=self.natoms, temp=self.temp, pe=self.pe, ke=self.ke,
-                    press=self.press, virial=list(self.virial))
+                    press=self.press, virial=list(self.virial), emol=self.emol)
 
 
 class Timing(C.Structure):
@@ -310,6 +310,27 @@ class Context:
     def pair_compute(self, eflag=1, vflag=1):
         e = C.c_double(); vir = (C.c_double * 6)()
         _chk(self.L.b200md_pair_compute(self.h, int(eflag), int(vflag), C.byref(e), vir))
+        return e.value, list(vir)
+
+    # molecular topology / bonds
+    def set_topology(self, tp):
+        """tp: dict from molecule_host.build_topology"""
+        a = {k: _i(tp[k]) for k in ("bond_offset", "bond_partner", "bond_type", "special_offset", "special_tag",
+                                     "special_level")}
+        slj = (C.c_double * 4)(*[float(t) for t in tp["special_lj"]])
+        sco = (C.c_double * 4)(*[float(t) for t in tp["special_coul"]])
+        _chk(self.L.b200md_set_topology(self.h, C.c_longlong(int(tp["natoms"])), _p(a["bond_offset"]),
+                                        _p(a["bond_partner"]), _p(a["bond_type"]), _p(a["special_offset"]),
+                                        _p(a["special_tag"]), _p(a["special_level"]), slj, sco))
+
+    def bond_fene_config(self, k, r0, epsilon, sigma):
+        """1-based per-bond-type arrays (index 0 unused)"""
+        a = [_d(t) for t in (k, r0, epsilon, sigma)]
+        _chk(self.L.b200md_bond_fene_config(self.h, len(a[0]) - 1, *[_p(t) for t in a]))
+
+    def bond_compute(self, eflag=1, vflag=1):
+        e = C.c_double(); vir = (C.c_double * 6)()
+        _chk(self.L.b200md_bond_compute(self.h, int(eflag), int(vflag), C.byref(e), vir))
         return e.value, list(vir)
 
     def pair_tallies(self):

@@ -85,6 +85,7 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
   cudaStreamSynchronize(c->stream);
   comm_free(c);
   pair_eam_free(c);
+  topo_free(c);
   void *ptrs[] = {c->xq, c->xq_tmp, c->cell_xq, c->v, c->v_tmp, c->f, c->xhold, c->tag, c->tag_tmp, c->image,
                   c->image_tmp, c->mass, c->cutneighsq, c->atom_bin, c->cell_count, c->cell_start, c->cell_fill,
                   c->cell_atoms, c->perm, c->scan_block, c->row_off, c->row_sx, c->row_flag, c->neigh, c->numneigh,
@@ -367,6 +368,7 @@ extern "C" int b200md_neigh_build(b200md_ctx *c) {
   TRY(comm_borders(c));
   TRY(neigh_bin_all(c));
   TRY(neigh_build_list(c));
+  TRY(topo_build_map(c));
   TRY(neigh_save_xhold(c));
   CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, sizeof(int), c->stream));
   c->ago = 0;
@@ -516,6 +518,34 @@ extern "C" int b200md_pair_tallies(b200md_ctx *c, double *eng_vdwl, double viria
 }
 
 // ---------------------------------------------------------------------------------------
+// molecular topology, bonds
+// ---------------------------------------------------------------------------------------
+extern "C" int b200md_set_topology(b200md_ctx *c, long long natoms, const int *bond_offset, const int *bond_partner_tag,
+                                   const int *bond_type, const int *special_offset, const int *special_tag,
+                                   const int *special_level, const double special_lj[4], const double special_coul[4]) {
+  NEED(c && natoms > 0 && bond_offset && special_offset && special_lj && special_coul, "b200md: null argument");
+  NEED(natoms < 2147483647LL, "b200md: tags must fit 32 bits");
+  CUDA_TRY(cudaSetDevice(c->device));
+  return topo_set(c, natoms, bond_offset, bond_partner_tag, bond_type, special_offset, special_tag, special_level,
+                  special_lj, special_coul);
+}
+extern "C" int b200md_bond_fene_config(b200md_ctx *c, int nbondtypes, const double *k, const double *r0,
+                                       const double *epsilon, const double *sigma) {
+  NEED(c && nbondtypes >= 1 && k && r0 && epsilon && sigma, "All bond coeffs are not set");
+  CUDA_TRY(cudaSetDevice(c->device));
+  return bond_fene_set(c, nbondtypes, k, r0, epsilon, sigma);
+}
+extern "C" int b200md_bond_compute(b200md_ctx *c, int eflag, int vflag, double *energy, double virial[6]) {
+  NEED(c && c->nbuilds > 0, "b200md: bond_compute before the first neighbor build");
+  NEED(c->topo.molecular && c->topo.fene, "b200md: no topology / bond style configured");
+  CUDA_TRY(cudaSetDevice(c->device));
+  TRY(bond_compute(c, eflag, vflag));
+  if (eflag && energy) *energy = c->topo.eng_bond;
+  if (vflag && virial) for (int k = 0; k < 6; k++) virial[k] = c->topo.virial_bond[k];
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
 // fix nve, thermo
 // ---------------------------------------------------------------------------------------
 extern "C" int b200md_nve_initial(b200md_ctx *c, double dtv, double dtf) {
@@ -535,8 +565,11 @@ extern "C" int b200md_thermo_compute(b200md_ctx *c, b200md_thermo *out) {
   CUDA_TRY(cudaSetDevice(c->device));
   double s[5];
   TRY(thermo_ke(c, s));
-  double red[8] = {s[0], c->eng_vdwl, c->virial[0], c->virial[1], c->virial[2], c->virial[3], c->virial[4], c->virial[5]};
-  TRY(comm_allreduce_sum(c, red, 8));
+  const Topology &tp = c->topo;
+  double red[9] = {s[0], c->eng_vdwl + tp.eng_bond, c->virial[0] + tp.virial_bond[0], c->virial[1] + tp.virial_bond[1],
+                   c->virial[2] + tp.virial_bond[2], c->virial[3] + tp.virial_bond[3], c->virial[4] + tp.virial_bond[4],
+                   c->virial[5] + tp.virial_bond[5], tp.eng_bond};
+  TRY(comm_allreduce_sum(c, red, 9));
   const double dof = 3.0 * c->natoms_global - 3.0;  // ComputeTemp::dof_compute, extra_dof = 3
   const double tfactor = dof > 0 ? c->mvv2e / (dof * c->boltz) : 0.0;
   const double t = red[0] * tfactor;
@@ -547,6 +580,7 @@ extern "C" int b200md_thermo_compute(b200md_ctx *c, b200md_thermo *out) {
   out->pe = red[1];
   out->ke = t * 0.5 * dof * c->boltz;  // Thermo::compute_ke
   for (int k = 0; k < 6; k++) out->virial[k] = red[2 + k];
+  out->emol = red[8];
   out->press = (dof * c->boltz * t + red[2] + red[3] + red[4]) / 3.0 * (1.0 / vol) * c->nktv2p;
   return B200MD_OK;
 }
@@ -559,6 +593,7 @@ extern "C" int b200md_setup(b200md_ctx *c) {
   NEED(c->pair_style != B200MD_PAIR_NONE, "b200md: no pair style configured");
   TRY(b200md_neigh_build(c));
   TRY(b200md_pair_compute(c, 1, 1, nullptr, nullptr));
+  TRY(bond_compute(c, 1, 1));
   TRY(b200md_reverse_comm(c));
   return B200MD_OK;
 }
@@ -567,7 +602,7 @@ extern "C" int b200md_setup(b200md_ctx *c) {
 // comm stream while the tiles without ghost neighbors are evaluated; boundary tiles follow.
 // Same kernels, same per-atom arithmetic and order as the unsplit launch -> identical results.
 static bool can_overlap(const b200md_ctx *c) {
-  return c->overlap && !c->all_self && c->n_tiles_int > 0;
+  return c->overlap && !c->all_self && c->n_tiles_int > 0 && !c->topo.molecular;
 }
 static int on_comm_stream(b200md_ctx *c, int (*fn)(b200md_ctx *)) {
   cudaStream_t saved = c->stream;
@@ -684,7 +719,7 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     } else {
       if (!nflag) { T.begin(3); TRY(comm_forward(c)); T.end(); }
       else { T.begin(2); TRY(b200md_neigh_build(c)); T.end(); }
-      T.begin(1); TRY(b200md_pair_compute(c, ev, ev, nullptr, nullptr)); T.end();
+      T.begin(1); TRY(b200md_pair_compute(c, ev, ev, nullptr, nullptr)); TRY(bond_compute(c, ev, ev)); T.end();
       T.begin(3); TRY(comm_reverse_force(c)); T.end();
     }
     T.begin(4); TRY(nve_final(c, dtf)); T.end();

@@ -40,6 +40,20 @@ struct EamTables {
   double *scale = nullptr;  // [(ntypes+1)^2]
 };
 
+// molecular topology keyed by atom tag (bond.cu); CSR offsets are [natoms+2], row t = tag t
+struct Topology {
+  bool molecular = false;
+  long long natoms = 0;
+  int *bond_off = nullptr, *bond_partner = nullptr, *bond_type = nullptr;  // bonds stored on tag t (newton_bond on)
+  int *spec_off = nullptr, *spec_tag = nullptr, *spec_which = nullptr;     // special neighbors of tag t: tag, 1/2/3
+  int special_flag[4] = {1, 1, 1, 1};
+  double special_lj[4] = {1, 1, 1, 1};
+  int *map = nullptr;            // [natoms+1] tag -> local index (owned copy preferred), -1 if absent
+  int nbondtypes = 0;
+  double *fene = nullptr;        // [nbondtypes+1][4] k, r0, epsilon, sigma
+  double eng_bond = 0, virial_bond[6] = {0, 0, 0, 0, 0, 0};
+};
+
 struct Swap {
   int dim, ineed, sendflag, sendproc, recvproc;
   int pbc[3];
@@ -127,6 +141,7 @@ struct b200md_ctx {
   std::vector<double> h_ljtab;
   double cutforcemax = 0;
   EamTables eam;
+  Topology topo;
   double *rho = nullptr, *fp = nullptr;  // [nmax]
   // reductions
   double *partials = nullptr;  // device [npartial_blocks*8]
@@ -193,6 +208,14 @@ int pair_eam_launch(b200md_ctx *c, bool ev, int pass, const int *tiles, int ntl)
 int pair_eam_fp_comm(b200md_ctx *c);
 int pair_eam_embed(b200md_ctx *c, bool ev, double *e_embed);  // half-list path: F(rho), F'(rho) of owned atoms
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);
+// bond.cu
+void topo_free(b200md_ctx *c);
+int topo_set(b200md_ctx *c, long long natoms, const int *bond_off, const int *bond_partner, const int *bond_type,
+             const int *spec_off, const int *spec_tag, const int *spec_which, const double special_lj[4],
+             const double special_coul[4]);
+int bond_fene_set(b200md_ctx *c, int nbondtypes, const double *k, const double *r0, const double *eps, const double *sigma);
+int topo_build_map(b200md_ctx *c);
+int bond_compute(b200md_ctx *c, int eflag, int vflag);
 // nve.cu
 int nve_initial(b200md_ctx *c, double dtv, double dtf, bool check_dist);
 int nve_final(b200md_ctx *c, double dtf);

@@ -423,14 +423,22 @@ int neigh_save_xhold(b200md_ctx *c) {
 #define MAX_ROWS 128
 #define MAX_TYPES_SMEM 8
 
-template <int TPA, bool HALF>
+// special-bond handling of the molecular builders (NPairHalfBinNewton / NPairFullBin,
+// src/npair_half_bin_newton.cpp:98-113, find_special src/npair.h:125-160)
+struct MolParams {
+  const int *tag, *spec_off, *spec_tag, *spec_which;
+  int flag1, flag2, flag3;
+  double hx, hy, hz;   // half box lengths; <= 0 for a non-periodic dimension
+};
+
+template <int TPA, bool HALF, bool MOL>
 __global__ void __launch_bounds__(BUILD_THREADS)
 k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom_bin,
         const int *__restrict__ cell_start, const int *__restrict__ cell_atoms,
         const double4 *__restrict__ cell_xq, int nrows, const int *__restrict__ row_off,
         const int *__restrict__ row_sx, const int *__restrict__ row_flag,
         const double *__restrict__ cutneighsq, int ntypes, int *__restrict__ neigh,
-        int *__restrict__ numneigh, int pitch, int *flags, int *__restrict__ tile_ghost, int F) {
+        int *__restrict__ numneigh, int pitch, int *flags, int *__restrict__ tile_ghost, int F, MolParams M) {
   // TPA lanes scan the candidates of one atom; the list is written in the layout of the force
   // kernels, which use F lanes per atom (AF atoms per warp tile)
   constexpr int A = 32 / TPA;
@@ -455,7 +463,9 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
 
   double4 qi = make_double4(0, 0, 0, 0);
   int ibin = 0, itype = 1;
+  int s0 = 0, s1 = 0;
   if (active) { qi = xq[i]; ibin = atom_bin[i]; itype = xq_type(qi); }
+  if (MOL && active) { const int ti = M.tag[i]; s0 = M.spec_off[ti]; s1 = M.spec_off[ti + 1]; }
   const double *cutrow = cut_smem ? &s_cut[itype * nt1] : &cutneighsq[itype * nt1];
   int cnt = 0;
   bool has_ghost = false;
@@ -495,6 +505,21 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
         } else {
           if (j == i) keep = false;
         }
+        if (MOL && keep && s1 > s0) {
+          // find_special: excluded (flag 0) unless the pair is more than half a box apart
+          const int tj = M.tag[j];
+          for (int sp = s0; sp < s1; sp++) {
+            if (M.spec_tag[sp] == tj) {
+              const int wh = M.spec_which[sp];
+              const int fl = wh == 1 ? M.flag1 : (wh == 2 ? M.flag2 : M.flag3);
+              if (fl == 0) {
+                const bool far = (M.hx > 0 && fabs(dx) > M.hx) || (M.hy > 0 && fabs(dy) > M.hy) || (M.hz > 0 && fabs(dz) > M.hz);
+                if (!far) keep = false;
+              }
+              break;
+            }
+          }
+        }
       }
       const unsigned m = __ballot_sync(0xffffffffu, keep) & submask_all;
       if (keep) {
@@ -515,6 +540,12 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
   if (tile_ghost && has_ghost) tile_ghost[i / AF] = 1;
 }
 
+template <int TPA, bool HALF, bool MOL>
+static void launch_build3(b200md_ctx *c, int nblocks, const MolParams &M) {
+  k_build<TPA, HALF, MOL><<<nblocks, BUILD_THREADS, 0, c->stream>>>(
+      c->nlocal, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, c->cell_xq, c->nrows, c->row_off,
+      c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost, c->tpa, M);
+}
 template <int TPA>
 static void launch_build(b200md_ctx *c) {
   constexpr int A = 32 / TPA;
@@ -522,14 +553,13 @@ static void launch_build(b200md_ctx *c) {
   const int warps_per_block = BUILD_THREADS / 32;
   const int nblocks = (ntiles + warps_per_block - 1) / warps_per_block;
   if (nblocks == 0) return;
-  if (c->list_kind == B200MD_LIST_HALF_NEWTON)
-    k_build<TPA, true><<<nblocks, BUILD_THREADS, 0, c->stream>>>(
-        c->nlocal, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, c->cell_xq, c->nrows, c->row_off,
-        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost, c->tpa);
-  else
-    k_build<TPA, false><<<nblocks, BUILD_THREADS, 0, c->stream>>>(
-        c->nlocal, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, c->cell_xq, c->nrows, c->row_off,
-        c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost, c->tpa);
+  const Topology &t = c->topo;
+  MolParams M = {c->tag, t.spec_off, t.spec_tag, t.spec_which, t.special_flag[1], t.special_flag[2], t.special_flag[3],
+                 c->periodic[0] ? 0.5 * c->prd[0] : -1.0, c->periodic[1] ? 0.5 * c->prd[1] : -1.0,
+                 c->periodic[2] ? 0.5 * c->prd[2] : -1.0};
+  const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON;
+  if (t.molecular) { if (half) launch_build3<TPA, true, true>(c, nblocks, M); else launch_build3<TPA, false, true>(c, nblocks, M); }
+  else { if (half) launch_build3<TPA, true, false>(c, nblocks, M); else launch_build3<TPA, false, false>(c, nblocks, M); }
 }
 
 static int ensure_neigh_storage(b200md_ctx *c) {

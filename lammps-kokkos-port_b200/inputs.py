@@ -68,3 +68,32 @@ def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, 
     cn, cmax = B.cutneighsq_table(1, cutsq, skin)
     ctx.neigh_config(cn, cmax, skin, every=1, delay=5, check=1, list_kind=list_kind)
     return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=50, units="metal")
+
+
+def in_chain(ctx, data_path, list_kind=B.LIST_HALF_NEWTON):
+    """bench/in.chain (/root/reference/bench/in.chain:1-28) WITHOUT `fix langevin`: units lj;
+    atom_style bond; special_bonds fene; read_data data.chain; neighbor 0.4 bin;
+    neigh_modify every 1 delay 1; bond_style fene; bond_coeff 1 30.0 1.5 1.0 1.0;
+    pair_style lj/cut 1.12; pair_modify shift yes; pair_coeff 1 1 1.0 1.0 1.12; fix 1 all nve;
+    timestep 0.012.  (fix langevin draws its RanMars numbers in the reference's local atom
+    order, src/fix_langevin.cpp:85 — not reproducible under another ordering)"""
+    from . import molecule_host as M
+    d = M.read_data(data_path)
+    ctx.set_units("lj")
+    boxlo, boxhi = list(d["boxlo"]), list(d["boxhi"])
+    _decompose(ctx, boxlo, boxhi)
+    sublo, subhi = ctx.subbox()
+    x = d["x"]
+    own = np.ones(len(x), bool)
+    for k in range(3):
+        own &= (x[:, k] >= sublo[k]) & (x[:, k] < subhi[k])
+    ctx.set_atoms(x[own], d["v"][own], d["type"][own], d["tag"][own], d["mass"], image=d["image"][own])
+    tp = M.build_topology(d["natoms"], d["bonds"])          # special_bonds fene: lj = coul = 0 1 1
+    ctx.set_topology(tp)
+    ctx.bond_fene_config([0.0, 30.0], [0.0, 1.5], [0.0, 1.0], [0.0, 1.0])
+    T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 1.12)}, 1.12, shift=True)
+    ctx.pair_lj_cut_config(T["cutsq"], T["lj1"], T["lj2"], T["lj3"], T["lj4"], T["offset"])
+    skin = 0.4
+    cn, cmax = B.cutneighsq_table(1, T["cutsq"], skin)
+    ctx.neigh_config(cn, cmax, skin, every=1, delay=1, check=1, list_kind=list_kind)
+    return dict(natoms=d["natoms"], dt=0.012, thermo=100, units="lj", data=d, topology=tp, tables=T)

@@ -12,13 +12,14 @@ and two two-line version stubs; they live under oracle/_ref/gen/.
 Selected sources:
   * every core file src/*.cpp (the serial MPI stub src/STUBS/mpi.cpp replaces MPI)
   * MANYBODY: pair_eam.cpp pair_eam_alloy.cpp pair_eam_fs.cpp   (the hot path's EAM styles)
+  * MOLECULE: atom_vec_bond.cpp bond_fene.cpp                     (bench/in.chain)
   * OPENMP : the threaded variants of exactly the hot-path styles, used as the timed
              CPU baseline (`-sf omp -pk omp N`)
 
 Outputs (all under oracle/_ref/, git-ignored, shipped to the GPU box by gpurun):
   liblammps_ref.so   reference as a shared library (C API of src/library.h, via ctypes)
   lmp                reference executable (src/main.cpp)
-  potentials/        Cu_u3.eam, Cu_mishin1.eam.alloy   (data the bench inputs name)
+  potentials/, data/ Cu_u3.eam, Cu_mishin1.eam.alloy, ..., data.chain   (data the bench inputs name)
 
 Flags: -O3 -DNDEBUG -ffp-contract=off (FMA-free like the survey's build),
 -fopenmp, -DLAMMPS_SMALLBIG -DLAMMPS_EXCEPTIONS -DLMP_OPENMP.
@@ -39,7 +40,9 @@ OBJ = os.path.join(OUT, "obj")
 CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
 
 MANYBODY = ["pair_eam.cpp", "pair_eam_alloy.cpp", "pair_eam_fs.cpp"]
+MOLECULE = ["atom_vec_bond.cpp", "bond_fene.cpp"]      # bench/in.chain
 OPENMP = [
+    "bond_fene_omp.cpp",
     "fix_omp.cpp", "thr_omp.cpp", "thr_data.cpp", "domain_omp.cpp",
     "pair_lj_cut_omp.cpp", "pair_eam_omp.cpp", "pair_eam_alloy_omp.cpp",
     "fix_nve_omp.cpp",
@@ -66,6 +69,7 @@ def selected_sources():
     srcs = sorted(glob.glob(os.path.join(SRC, "*.cpp")))
     srcs += [os.path.join(SRC, "STUBS", "mpi.cpp")]
     srcs += [os.path.join(SRC, "MANYBODY", f) for f in MANYBODY]
+    srcs += [os.path.join(SRC, "MOLECULE", f) for f in MOLECULE]
     srcs += [os.path.join(SRC, "OPENMP", f) for f in OPENMP]
     return srcs
 
@@ -96,7 +100,7 @@ def gen_headers(srcs):
         write_if_changed(os.path.join(GEN, "packages_%s.h" % name), "")
     write_if_changed(os.path.join(GEN, "lmpinstalledpkgs.h"),
                      'const char * LAMMPS_NS::LAMMPS::installed_packages[] = '
-                     '{"MANYBODY", "OPENMP", NULL};\n')
+                     '{"MANYBODY", "MOLECULE", "OPENMP", NULL};\n')
     write_if_changed(os.path.join(GEN, "lmpgitversion.h"),
                      'bool LAMMPS_NS::LAMMPS::has_git_info() { return false; }\n'
                      'const char *LAMMPS_NS::LAMMPS::git_commit() { return "(unknown)"; }\n'
@@ -112,14 +116,16 @@ def main():
     srcs = selected_sources()
     gen_headers(srcs)
     inc = ["-I" + GEN, "-I" + SRC, "-I" + os.path.join(SRC, "STUBS"),
-           "-I" + os.path.join(SRC, "MANYBODY"), "-I" + os.path.join(SRC, "OPENMP")]
+           "-I" + os.path.join(SRC, "MANYBODY"), "-I" + os.path.join(SRC, "MOLECULE"),
+           "-I" + os.path.join(SRC, "OPENMP")]
     flags = ["-O3", "-DNDEBUG", "-ffp-contract=off", "-fopenmp", "-fPIC", "-std=c++11",
              "-DLAMMPS_SMALLBIG", "-DLAMMPS_EXCEPTIONS", "-DLMP_OPENMP", "-w"]
     nj = ["cxx = %s" % CXX, "flags = %s %s" % (" ".join(flags), " ".join(inc)),
           "rule cc", "  command = $cxx $flags -MMD -MF $out.d -c $in -o $out",
           "  depfile = $out.d", "  deps = gcc", "  description = CC $in",
-          "rule so", "  command = $cxx -shared -fopenmp -o $out $in",
+          "rule so", "  command = $cxx -shared -fopenmp -o $out $in", "  description = LINK $out",
           "rule exe", "  command = $cxx -fopenmp -o $out $in -Wl,-rpath,'$$ORIGIN' -L%s -llammps_ref" % OUT,
+          "  description = LINK $out",
           ""]
     objs = []
     main_obj = None
@@ -149,6 +155,10 @@ def main():
         dst = os.path.join(pot, os.path.basename(src))
         if os.path.exists(src) and not os.path.exists(dst):
             shutil.copyfile(src, dst)
+    data = os.path.join(OUT, "data")
+    os.makedirs(data, exist_ok=True)
+    if not os.path.exists(os.path.join(data, "data.chain")):
+        shutil.copyfile(os.path.join(REF, "bench", "data.chain"), os.path.join(data, "data.chain"))
     print("build_ref: ok ->", OUT)
     return 0
 

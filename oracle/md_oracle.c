@@ -59,12 +59,22 @@ typedef struct {
   int *type2frho, *type2rhor, *type2z2r;
   double *rho, *fp;
   double eng_vdwl, virial[6];
+  /* molecular topology keyed by tag (CSR, rows 1..natoms) + bond_style fene */
+  int molecular, topo_natoms;
+  int *bond_off, *bond_partner, *bond_type, *spec_off, *spec_tag, *spec_level;
+  int special_flag[4];
+  int *map, *sametag;          /* Atom::map_set (atom_map.cpp:220-300): tag -> lowest local index, image chain */
+  int nbondlist, maxbond, *bondlist; /* [n][3] i1,i2,type */
+  int nbondtypes;
+  double *fene_k, *fene_r0, *fene_eps, *fene_sigma;
+  double eng_bond, virial_bond[6];
+  int bond_error;
   long step;
 } ora_sim;
 
 typedef struct {
   long step;
-  double natoms, temp, pe, ke, press, virial[6];
+  double natoms, temp, pe, ke, press, virial[6], emol;
 } ora_thermo;
 
 static void grow(ora_sim *s, int need) {
@@ -326,8 +336,34 @@ static void push_neigh(ora_sim *s, long *n, int j) {
   s->neigh[(*n)++] = j;
 }
 
-/* NPairFullBinAtomonly::build (npair_full_bin_atomonly.cpp:32-92) and
- * NPairHalfBinAtomonlyNewton::build (npair_half_bin_atomonly_newton.cpp:33-113) */
+/* NPair::find_special (npair.h:125-160) on the tag-keyed special table: 0 keep, -1 exclude
+ * (weights with flag 2 are not restated: ora_set_topology refuses them) */
+static int find_special(const ora_sim *s, int itag, int jtag) {
+  for (int k = s->spec_off[itag]; k < s->spec_off[itag + 1]; k++)
+    if (s->spec_tag[k] == jtag) return s->special_flag[s->spec_level[k]] == 0 ? -1 : 0;
+  return 0;
+}
+/* Domain::minimum_image_check (domain.h:165-171), fully periodic box */
+static int minimum_image_check(const ora_sim *s, double dx, double dy, double dz) {
+  if (fabs(dx) > 0.5 * s->prd[0]) return 1;
+  if (fabs(dy) > 0.5 * s->prd[1]) return 1;
+  if (fabs(dz) > 0.5 * s->prd[2]) return 1;
+  return 0;
+}
+/* the molecular branch of NPairHalfBinNewton::build (npair_half_bin_newton.cpp:98-113) */
+static void push_pair(ora_sim *s, long *n, int i, int j, double delx, double dely, double delz) {
+  if (s->molecular) {
+    int which = find_special(s, s->tag[i], s->tag[j]);
+    if (which == 0) push_neigh(s, n, j);
+    else if (minimum_image_check(s, delx, dely, delz)) push_neigh(s, n, j);
+    return;
+  }
+  push_neigh(s, n, j);
+}
+
+/* NPairFullBinAtomonly::build (npair_full_bin_atomonly.cpp:32-92),
+ * NPairHalfBinAtomonlyNewton::build (npair_half_bin_atomonly_newton.cpp:33-113) and, with a
+ * topology, NPairHalfBinNewton::build (npair_half_bin_newton.cpp:36-161) */
 static void build_list(ora_sim *s) {
   const int nlocal = s->nlocal, nt1 = s->ntypes + 1;
   const double *x = s->x;
@@ -347,7 +383,7 @@ static void build_list(ora_sim *s) {
         }
         double delx = xtmp - x[3 * j], dely = ytmp - x[3 * j + 1], delz = ztmp - x[3 * j + 2];
         double rsq = delx * delx + dely * dely + delz * delz;
-        if (rsq <= s->cutneighsq[itype * nt1 + s->type[j]]) push_neigh(s, &n, j);
+        if (rsq <= s->cutneighsq[itype * nt1 + s->type[j]]) push_pair(s, &n, i, j, delx, dely, delz);
       }
     }
     int ibin = s->atom2bin[i];
@@ -356,7 +392,7 @@ static void build_list(ora_sim *s) {
         if (!s->half && i == j) continue;
         double delx = xtmp - x[3 * j], dely = ytmp - x[3 * j + 1], delz = ztmp - x[3 * j + 2];
         double rsq = delx * delx + dely * dely + delz * delz;
-        if (rsq <= s->cutneighsq[itype * nt1 + s->type[j]]) push_neigh(s, &n, j);
+        if (rsq <= s->cutneighsq[itype * nt1 + s->type[j]]) push_pair(s, &n, i, j, delx, dely, delz);
       }
     s->firstoff[i] = (int)start;
     s->numneigh[i] = (int)(n - start);
@@ -374,6 +410,8 @@ void ora_neigh_config(ora_sim *s, const double *cutneighsq, double cutneighmax, 
   create_stencil(s);
 }
 
+static void map_set(ora_sim *s);
+static int bond_list_build(ora_sim *s);
 /* the reneighbor branch of Verlet::run (verlet.cpp:289-307) + Neighbor::build (neighbor.cpp:2398-2492) */
 int ora_neigh_build(ora_sim *s) {
   pbc(s);
@@ -381,6 +419,7 @@ int ora_neigh_build(ora_sim *s) {
   for (int i = 0; i < 3 * s->nlocal; i++) s->xhold[i] = s->x[i];
   bin_atoms(s);
   build_list(s);
+  if (s->molecular) { map_set(s); if (bond_list_build(s)) return -1; }
   s->ago = 0;
   s->nbuilds++;
   return 0;
@@ -551,6 +590,100 @@ static void compute_eam(ora_sim *s, int eflag, int vflag) {
   if (vflag) virial_fdotr(s);
 }
 
+/* ---- molecular topology, bond_style fene -------------------------------------------------- */
+int ora_set_topology(ora_sim *s, int natoms, const int *bond_off, const int *bond_partner, const int *bond_type,
+                     const int *spec_off, const int *spec_tag, const int *spec_level, const double *special_lj,
+                     const double *special_coul) {
+  s->topo_natoms = natoms;
+  s->bond_off = dup_i(bond_off, natoms + 2); s->bond_partner = dup_i(bond_partner, bond_off[natoms + 1]);
+  s->bond_type = dup_i(bond_type, bond_off[natoms + 1]);
+  s->spec_off = dup_i(spec_off, natoms + 2); s->spec_tag = dup_i(spec_tag, spec_off[natoms + 1]);
+  s->spec_level = dup_i(spec_level, spec_off[natoms + 1]);
+  for (int k = 1; k <= 3; k++) { /* Neighbor::init special_flag (neighbor.cpp:430-452) */
+    if (special_lj[k] == 0.0 && special_coul[k] == 0.0) s->special_flag[k] = 0;
+    else if (special_lj[k] == 1.0 && special_coul[k] == 1.0) s->special_flag[k] = 1;
+    else return -1;
+  }
+  s->map = malloc(sizeof(int) * (natoms + 1));
+  s->molecular = 1;
+  return 0;
+}
+void ora_bond_fene(ora_sim *s, int nbondtypes, const double *k, const double *r0, const double *eps, const double *sigma) {
+  s->nbondtypes = nbondtypes;
+  s->fene_k = dup_d(k, nbondtypes + 1); s->fene_r0 = dup_d(r0, nbondtypes + 1);
+  s->fene_eps = dup_d(eps, nbondtypes + 1); s->fene_sigma = dup_d(sigma, nbondtypes + 1);
+}
+/* Atom::map_set, array style (atom_map.cpp:220-260): loop from the last atom down so the map
+ * holds the lowest index (owned before ghost) and sametag chains to the next image */
+static void map_set(ora_sim *s) {
+  int nall = s->nlocal + s->nghost;
+  s->sametag = realloc(s->sametag, sizeof(int) * (nall + 1));
+  for (int t = 0; t <= s->topo_natoms; t++) s->map[t] = -1;
+  for (int i = nall - 1; i >= 0; i--) { s->sametag[i] = s->map[s->tag[i]]; s->map[s->tag[i]] = i; }
+}
+/* Domain::closest_image (domain.cpp:1123-1151) */
+static int closest_image(const ora_sim *s, int i, int j) {
+  if (j < 0) return j;
+  const double *xi = &s->x[3 * i];
+  int closest = j;
+  double delx = xi[0] - s->x[3 * j], dely = xi[1] - s->x[3 * j + 1], delz = xi[2] - s->x[3 * j + 2];
+  double rsqmin = delx * delx + dely * dely + delz * delz;
+  while (s->sametag[j] >= 0) {
+    j = s->sametag[j];
+    delx = xi[0] - s->x[3 * j]; dely = xi[1] - s->x[3 * j + 1]; delz = xi[2] - s->x[3 * j + 2];
+    double rsq = delx * delx + dely * dely + delz * delz;
+    if (rsq < rsqmin) { rsqmin = rsq; closest = j; }
+  }
+  return closest;
+}
+/* NTopoBondAll::build (ntopo_bond_all.cpp:37-80), newton_bond on */
+static int bond_list_build(ora_sim *s) {
+  s->nbondlist = 0;
+  for (int i = 0; i < s->nlocal; i++) {
+    int t = s->tag[i];
+    for (int m = s->bond_off[t]; m < s->bond_off[t + 1]; m++) {
+      int atom1 = s->map[s->bond_partner[m]];
+      if (atom1 == -1) return -1; /* "Bond atoms missing" */
+      atom1 = closest_image(s, i, atom1);
+      if (s->nbondlist == s->maxbond) { s->maxbond = s->maxbond * 2 + 4096; s->bondlist = realloc(s->bondlist, sizeof(int) * 3 * s->maxbond); }
+      int *b = &s->bondlist[3 * s->nbondlist++];
+      b[0] = i; b[1] = atom1; b[2] = s->bond_type[m];
+    }
+  }
+  return 0;
+}
+/* BondFENE::compute (MOLECULE/bond_fene.cpp:53-129) + Bond::ev_tally (bond.cpp:174-256), newton_bond on */
+static void compute_fene(ora_sim *s, int eflag, int vflag) {
+  const double cuberoot2 = 1.25992104989487316476;
+  s->eng_bond = 0; for (int k = 0; k < 6; k++) s->virial_bond[k] = 0;
+  for (int n = 0; n < s->nbondlist; n++) {
+    int i1 = s->bondlist[3 * n], i2 = s->bondlist[3 * n + 1], type = s->bondlist[3 * n + 2];
+    double delx = s->x[3 * i1] - s->x[3 * i2], dely = s->x[3 * i1 + 1] - s->x[3 * i2 + 1], delz = s->x[3 * i1 + 2] - s->x[3 * i2 + 2];
+    double rsq = delx * delx + dely * dely + delz * delz;
+    double r0sq = s->fene_r0[type] * s->fene_r0[type];
+    double rlogarg = 1.0 - rsq / r0sq;
+    if (rlogarg < 0.1) { if (rlogarg <= -3.0) s->bond_error = 1; rlogarg = 0.1; }
+    double fbond = -s->fene_k[type] / rlogarg, sr6 = 0.0, ebond = 0.0;
+    if (rsq < cuberoot2 * s->fene_sigma[type] * s->fene_sigma[type]) {
+      double sr2 = s->fene_sigma[type] * s->fene_sigma[type] / rsq;
+      sr6 = sr2 * sr2 * sr2;
+      fbond += 48.0 * s->fene_eps[type] * sr6 * (sr6 - 0.5) / rsq;
+    }
+    if (eflag) {
+      ebond = -0.5 * s->fene_k[type] * r0sq * log(rlogarg);
+      if (rsq < cuberoot2 * s->fene_sigma[type] * s->fene_sigma[type])
+        ebond += 4.0 * s->fene_eps[type] * sr6 * (sr6 - 1.0) + s->fene_eps[type];
+    }
+    s->f[3 * i1] += delx * fbond; s->f[3 * i1 + 1] += dely * fbond; s->f[3 * i1 + 2] += delz * fbond;
+    s->f[3 * i2] -= delx * fbond; s->f[3 * i2 + 1] -= dely * fbond; s->f[3 * i2 + 2] -= delz * fbond;
+    if (eflag) s->eng_bond += ebond;
+    if (vflag) {
+      s->virial_bond[0] += delx * delx * fbond; s->virial_bond[1] += dely * dely * fbond; s->virial_bond[2] += delz * delz * fbond;
+      s->virial_bond[3] += delx * dely * fbond; s->virial_bond[4] += delx * delz * fbond; s->virial_bond[5] += dely * delz * fbond;
+    }
+  }
+}
+
 /* Verlet::force_clear + pair->compute + comm->reverse_comm (verlet.cpp:311-330) */
 int ora_compute(ora_sim *s, int eflag, int vflag) {
   if (!s->half) return -1; /* the reference's pair styles consume the half list */
@@ -559,8 +692,9 @@ int ora_compute(ora_sim *s, int eflag, int vflag) {
   if (s->pair_style == 1) compute_lj(s, eflag, vflag);
   else if (s->pair_style == 2) compute_eam(s, eflag, vflag);
   else return -1;
+  if (s->molecular && s->fene_k) compute_fene(s, eflag, vflag);
   reverse_comm_vec(s, s->f, 3);
-  return 0;
+  return s->bond_error ? -1 : 0;
 }
 
 /* FixNVE::initial_integrate / final_integrate (fix_nve.cpp:64-141) */
@@ -586,10 +720,10 @@ void ora_thermo_compute(ora_sim *s, ora_thermo *t) {
   double dof = 3.0 * s->nlocal - 3.0;
   double temp = temp_scalar(s);
   double vol = s->prd[0] * s->prd[1] * s->prd[2];
-  t->step = s->step; t->natoms = s->nlocal; t->temp = temp; t->pe = s->eng_vdwl;
+  t->step = s->step; t->natoms = s->nlocal; t->temp = temp; t->pe = s->eng_vdwl + s->eng_bond; t->emol = s->eng_bond;
   t->ke = temp * 0.5 * dof * s->boltz;
-  for (int k = 0; k < 6; k++) t->virial[k] = s->virial[k];
-  t->press = (dof * s->boltz * temp + s->virial[0] + s->virial[1] + s->virial[2]) / 3.0 * (1.0 / vol) * s->nktv2p;
+  for (int k = 0; k < 6; k++) t->virial[k] = s->virial[k] + s->virial_bond[k];
+  t->press = (dof * s->boltz * temp + t->virial[0] + t->virial[1] + t->virial[2]) / 3.0 * (1.0 / vol) * s->nktv2p;
 }
 
 /* Verlet::setup (verlet.cpp:93-162) */

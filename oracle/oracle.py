@@ -27,11 +27,11 @@ def build_oracle():
 
 class OraThermo(C.Structure):
     _fields_ = [("step", C.c_long), ("natoms", C.c_double), ("temp", C.c_double), ("pe", C.c_double),
-                ("ke", C.c_double), ("press", C.c_double), ("virial", C.c_double * 6)]
+                ("ke", C.c_double), ("press", C.c_double), ("virial", C.c_double * 6), ("emol", C.c_double)]
 
     def as_dict(self):
         return dict(step=self.step, natoms=self.natoms, temp=self.temp, pe=self.pe, ke=self.ke, press=self.press,
-                    virial=list(self.virial))
+                    virial=list(self.virial), emol=self.emol)
 
 
 def _d(a):
@@ -85,6 +85,19 @@ class Oracle:
         self.L.ora_pair_eam(self.h, int(tb["nrho"]), int(tb["nr"]), C.c_double(tb["rdr"]), C.c_double(tb["rdrho"]),
                             C.c_double(tb["rhomax"]), C.c_double(tb["cutforcesq"]), fr.shape[0], _p(fr), rr.shape[0],
                             _p(rr), zr.shape[0], _p(zr), _p(t2f), _p(t2r), _p(t2z), _p(sc))
+
+    def set_topology(self, tp):
+        a = {k: _i(tp[k]) for k in ("bond_offset", "bond_partner", "bond_type", "special_offset", "special_tag",
+                                     "special_level")}
+        slj, sco = _d(tp["special_lj"]), _d(tp["special_coul"])
+        if self.L.ora_set_topology(self.h, int(tp["natoms"]), _p(a["bond_offset"]), _p(a["bond_partner"]),
+                                   _p(a["bond_type"]), _p(a["special_offset"]), _p(a["special_tag"]),
+                                   _p(a["special_level"]), _p(slj), _p(sco)):
+            raise RuntimeError("oracle: special_bonds weights other than 0 or 1 are not restated")
+
+    def bond_fene(self, k, r0, epsilon, sigma):
+        a = [_d(t) for t in (k, r0, epsilon, sigma)]
+        self.L.ora_bond_fene(self.h, len(a[0]) - 1, *[_p(t) for t in a])
 
     def neigh_build(self):
         if self.L.ora_neigh_build(self.h):

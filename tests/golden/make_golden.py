@@ -56,7 +56,74 @@ def make(name, script, style, n, cutoff):
     print(name, out["natoms"], len(out["half_lo"]), len(out["full_i"]), out["thermo0"], out["thermo_series"][-1])
 
 
+IN_CHAIN = """
+units lj
+atom_style bond
+atom_modify map array
+special_bonds fene
+read_data {data}
+neighbor 0.4 bin
+neigh_modify every 1 delay 1
+bond_style fene
+bond_coeff 1 30.0 1.5 1.0 1.0
+pair_style lj/cut 1.12
+pair_modify shift yes
+pair_coeff 1 1 1.0 1.0 1.12
+fix 1 all nve
+timestep 0.012
+"""
+
+
+def pair_hash(lo, hi):
+    """two independent 64-bit digests of the set of (lo,hi) tag pairs (order-free)"""
+    k = lo.astype(np.uint64) * np.uint64(1 << 32) + hi.astype(np.uint64)
+    m = k * np.uint64(0x9E3779B97F4A7C15)
+    m ^= m >> np.uint64(29)
+    m *= np.uint64(0xBF58476D1CE4E5B9)
+    return np.array([np.bitwise_xor.reduce(m), m.sum(dtype=np.uint64)], dtype=np.uint64)
+
+
+def make_chain():
+    """bench/in.chain WITHOUT `fix langevin` (its RanMars stream is drawn in local-index order,
+    src/fix_langevin.cpp:85, which no other ordering of the atoms can replay): state of
+    data.chain itself.  32 000 atoms are too many for a fixture, so: forces of every 8th tag,
+    |f| checksums, numneigh per tag, digests of the half pair list, thermo (incl. evdwl / emol)
+    at step 0 and after 10 x `run 10`."""
+    # (no "-screen none": this fork's AtomVec border debug print dereferences the screen handle)
+    R = O.Reference(args=("-log", "none", "-echo", "none", "-nocite"))
+    R.command(IN_CHAIN.format(data=os.path.join(os.path.dirname(O.POT_DIR), "data", "data.chain")))
+    kw = ("temp", "pe", "ke", "press", "evdwl", "emol")
+    R.command("thermo_style custom step temp pe ke press evdwl emol")
+    R.command("thermo_modify norm no")
+    R.command("run 0")
+    out = dict(natoms=R.natoms())
+    f = R.gather("f", 3)
+    out["f_every8"] = f[::8].copy()
+    out["f_abs_sum"] = np.abs(f).sum(axis=0)
+    out["f_sq_sum"] = (f * f).sum()
+    out["thermo0"] = np.array([R.thermo(k) for k in kw])
+    nl = R.neighlist_by_tag("lj/cut")
+    i, j = keys(nl)
+    lo, hi = np.minimum(i, j), np.maximum(i, j)
+    out["npairs"] = len(lo)
+    out["pair_digest"] = pair_hash(lo, hi)
+    cnt = np.zeros(out["natoms"] + 1, np.int32)
+    np.add.at(cnt, lo, 1); np.add.at(cnt, hi, 1)
+    out["pairs_per_tag"] = cnt.astype(np.uint8)          # appearances of each tag in the pair set
+    series = []
+    for _ in range(10):
+        R.command("run 10")
+        series.append([R.thermo(k) for k in kw])
+    out["thermo_series"] = np.array(series)
+    R.close()
+    np.savez_compressed(os.path.join(HERE, "chain.npz"), **out)
+    print("chain", out["natoms"], out["npairs"], out["pair_digest"], out["thermo0"], out["thermo_series"][-1])
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "chain":
+        make_chain()
+        sys.exit(0)
     make("lj_n5", O.IN_LJ.format(nx=5, ny=5, nz=5), "lj/cut", 5, 2.5)
     pot = os.path.join(O.POT_DIR, "Cu_u3.eam")
     make("eam_n4", O.IN_EAM.format(nx=4, ny=4, nz=4, style="eam", coeff="1 1 " + pot), "eam", 4, 4.9)
