@@ -23,19 +23,22 @@ sys.path.insert(0, ROOT)
 
 SCALE = {1: (4, 4, 4), 2: (8, 4, 4), 4: (8, 8, 4), 8: (8, 8, 8)}
 # algorithmic bytes: force pass per atom per launch, and whole step per atom-step
-N_FULL = {"lj": 75.2, "eam": 75.5}
-BYTES_KERNEL = {"lj": 28 * 75.2 + 52, "eam": 64 * 75.5 + 104}     # LJ force pass; EAM rho+fp and force passes
-BYTES_STEP = {"lj": 2480.0, "eam": 5510.0}
+N_FULL = {"lj": 75.2, "eam": 75.5, "chain": 9.74}
+BYTES_KERNEL = {"lj": 28 * 75.2 + 52, "eam": 64 * 75.5 + 104,    # LJ force pass; EAM rho+fp and force passes
+                "chain": 28 * 9.74 + 52 + 1 * (8 + 24 + 24) + 52}  # + FENE: 0.99 bonds/atom x (tag,map + x_j + f_j RED) + own x,f
+# in.chain (SURVEY's method applied to C3, N=9.74, rebuild every ~4 steps): force passes 381 + NVE 192
+# + check_distance 48 + rebuild (4N list + 24 xhold + 176 sort + 28N candidates + 8 map)/4 = 128
+BYTES_STEP = {"lj": 2480.0, "eam": 5510.0, "chain": 750.0}
 # (the figures above are SURVEY 8(d)'s yardstick, defined on the full list; the half-list kernels do
 #  the same physical work -- every pair once instead of twice -- and are rated with the same figure)
 # measured choice by workload and world size (2 = "two or more"), profiles/r01_summary.md: in.lj at N>1
 # keeps the full list (halo overlapped with the interior tiles, no reverse_comm); eam is faster on
 # the half list everywhere
-LIST_AUTO = {"lj": {1: "half", 2: "full"}, "eam": {1: "half", 2: "half"}}
+LIST_AUTO = {"lj": {1: "half", 2: "full"}, "eam": {1: "half", 2: "half"}, "chain": {1: "half", 2: "half"}}
 # algorithmic bytes of the half-list kernels per atom per step (N_h listed pairs per atom, each:
 # 4 index + 24 x_j [+ 8 fp_j] gathered, 24 f_j [8 rho_j] as RED payload; plus the per-atom terms)
-N_HALF = {"lj": 37.6, "eam": 37.75}
-BYTES_KERNEL_HALF = {"lj": 52 * 37.6 + 52, "eam": (36 + 60) * 37.75 + 104}
+N_HALF = {"lj": 37.6, "eam": 37.75, "chain": 4.87}
+BYTES_KERNEL_HALF = {"lj": 52 * 37.6 + 52, "eam": (36 + 60) * 37.75 + 104, "chain": 52 * 4.87 + 52 + 56 + 52}
 
 
 def peaks():
@@ -90,6 +93,11 @@ def ref_script(workload, xyz, warm, steps):
     from oracle import oracle as O
     if workload == "lj":
         body = O.IN_LJ.format(nx=20 * xyz[0], ny=20 * xyz[1], nz=20 * xyz[2])
+    elif workload == "chain":   # bench/in.chain.scaled without fix langevin (what the B200 arm runs)
+        body = ("units lj\natom_style bond\nspecial_bonds fene\nread_data %s\nreplicate %d %d %d\n"
+                "neighbor 0.4 bin\nneigh_modify every 1 delay 1\nbond_style fene\nbond_coeff 1 30.0 1.5 1.0 1.0\n"
+                "pair_style lj/cut 1.12\npair_modify shift yes\npair_coeff 1 1 1.0 1.0 1.12\nfix 1 all nve\n"
+                "timestep 0.012\n" % (os.path.join(os.path.dirname(O.POT_DIR), "data", "data.chain"), *xyz))
     else:
         body = O.IN_EAM.format(nx=20 * xyz[0], ny=20 * xyz[1], nz=20 * xyz[2], style="eam",
                                coeff="1 1 " + os.path.join(O.POT_DIR, "Cu_u3.eam"))
@@ -113,7 +121,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--workload", default="lj", choices=["lj", "eam"])
+    ap.add_argument("--workload", default="lj", choices=["lj", "eam", "chain"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--lanes", type=int, default=0)
     ap.add_argument("--list", default="auto", choices=["auto", "half", "full"],
@@ -127,8 +135,10 @@ def main():
     xyz = SCALE.get(ngpus, (4 * ngpus, 4, 4))
     natoms = 4 * 8000 * xyz[0] * xyz[1] * xyz[2]
     wl = a.workload
-    config = {"workload": "bench/in.%s -var x %d -var y %d -var z %d (%d atoms, fcc lattice, %s, NVE)" % (
-        wl, xyz[0], xyz[1], xyz[2], natoms, "lj/cut 2.5, neigh every 20" if wl == "lj" else "eam Cu_u3, neigh check yes"),
+    desc = {"lj": "fcc lattice, lj/cut 2.5, neigh every 20", "eam": "fcc lattice, eam Cu_u3, neigh check yes",
+            "chain": "data.chain replicated, FENE bonds + lj/cut 1.12, special_bonds fene, fix langevin left out"}[wl]
+    config = {"workload": "bench/in.%s -var x %d -var y %d -var z %d (%d atoms, %s, NVE)" % (
+        wl + (".scaled" if wl == "chain" else ""), xyz[0], xyz[1], xyz[2], natoms, desc),
         "atoms_per_gpu": natoms // ngpus, "decomposition": None,
         "l2": "working set (neighbor list >= 1 GB/GPU) exceeds the 126 MB L2; no flush needed"}
     cores = os.cpu_count() or 1
@@ -173,6 +183,8 @@ def main():
     config["neighbor_list"] = "half/bin/atomonly/newton" if lk == "half" else "full/bin/atomonly (newton off)"
     if wl == "lj":
         cfg = P.inputs.in_lj(ctx, *xyz, list_kind=list_kind)
+    elif wl == "chain":
+        cfg = P.inputs.in_chain(ctx, os.path.join(ROOT, "oracle", "_ref", "data", "data.chain"), *xyz, list_kind=list_kind)
     else:
         cfg = P.inputs.in_eam(ctx, *xyz, potential=os.path.join(ROOT, "oracle", "_ref", "potentials", "Cu_u3.eam"),
                               list_kind=list_kind)
@@ -219,7 +231,7 @@ def main():
     hbm, which = peaks()
     bytes_kernel = BYTES_KERNEL_HALF[wl] if lk == "half" else BYTES_KERNEL[wl]
     achieved = bytes_kernel * nloc / (pair_ms / 1e3) / 1e9
-    roofline = {"bound": "hbm", "kernel": ("k_lj" if wl == "lj" else ("k_eam_rho_half+k_eam_embed+k_eam_force" if lk == "half" else "k_eam_rho_fp+k_eam_force")),
+    roofline = {"bound": "hbm", "kernel": ("k_lj" if wl == "lj" else "k_lj+k_bond_fene" if wl == "chain" else ("k_eam_rho_half+k_eam_embed+k_eam_force" if lk == "half" else "k_eam_rho_fp+k_eam_force")),
                 "list": lk, "achieved": achieved,
                 "peak": hbm, "peak_source": which, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
                 "kernel_ms": pair_ms, "bytes_per_atom_launch": bytes_kernel,

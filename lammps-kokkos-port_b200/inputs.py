@@ -70,24 +70,25 @@ def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, 
     return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=50, units="metal")
 
 
-def in_chain(ctx, data_path, list_kind=B.LIST_HALF_NEWTON):
-    """bench/in.chain (/root/reference/bench/in.chain:1-28) WITHOUT `fix langevin`: units lj;
+def in_chain(ctx, data_path, x=1, y=1, z=1, list_kind=B.LIST_HALF_NEWTON):
+    """bench/in.chain / in.chain.scaled (`replicate x y z`) WITHOUT `fix langevin`
+    (/root/reference/bench/in.chain:1-28, in.chain.scaled:1-33): units lj;
     atom_style bond; special_bonds fene; read_data data.chain; neighbor 0.4 bin;
     neigh_modify every 1 delay 1; bond_style fene; bond_coeff 1 30.0 1.5 1.0 1.0;
     pair_style lj/cut 1.12; pair_modify shift yes; pair_coeff 1 1 1.0 1.0 1.12; fix 1 all nve;
     timestep 0.012.  (fix langevin draws its RanMars numbers in the reference's local atom
     order, src/fix_langevin.cpp:85 — not reproducible under another ordering)"""
     from . import molecule_host as M
-    d = M.read_data(data_path)
+    d = M.replicate(M.read_data(data_path), x, y, z)
     ctx.set_units("lj")
     boxlo, boxhi = list(d["boxlo"]), list(d["boxhi"])
     _decompose(ctx, boxlo, boxhi)
     sublo, subhi = ctx.subbox()
-    x = d["x"]
-    own = np.ones(len(x), bool)
+    xs = d["x"]
+    own = np.ones(len(xs), bool)
     for k in range(3):
-        own &= (x[:, k] >= sublo[k]) & (x[:, k] < subhi[k])
-    ctx.set_atoms(x[own], d["v"][own], d["type"][own], d["tag"][own], d["mass"], image=d["image"][own])
+        own &= (xs[:, k] >= sublo[k]) & (xs[:, k] < subhi[k])
+    ctx.set_atoms(xs[own], d["v"][own], d["type"][own], d["tag"][own], d["mass"], image=d["image"][own])
     tp = M.build_topology(d["natoms"], d["bonds"])          # special_bonds fene: lj = coul = 0 1 1
     ctx.set_topology(tp)
     ctx.bond_fene_config([0.0, 30.0], [0.0, 1.5], [0.0, 1.0], [0.0, 1.0])

@@ -67,6 +67,48 @@ def read_data(path):
                 tag=np.arange(1, n + 1, dtype=np.int32), bonds=bonds, nbondtypes=hdr.get("bond types", 0))
 
 
+def replicate(d, nx, ny, nz):
+    """`replicate nx ny nz` (src/replicate.cpp:146-150, 430-640): unmap by the image flags, copy
+    into every replica cell (loops ix, iy, iz), remap into the enlarged box, tags / bond partners /
+    molecule ids offset by (iz*ny*nx + iy*nx + ix) * maxtag."""
+    if (nx, ny, nz) == (1, 1, 1):
+        return d
+    n = d["natoms"]
+    prd = d["boxhi"] - d["boxlo"]
+    img = d["image"]
+    ib = np.stack([(img & 1023) - 512, ((img >> 10) & 1023) - 512, ((img >> 20) & 1023) - 512], axis=1)
+    xu = d["x"] + ib * prd                                      # Domain::unmap
+    newhi = d["boxlo"] + prd * np.array([nx, ny, nz])
+    newprd = newhi - d["boxlo"]
+    maxtag = int(d["tag"].max()); maxmol = int(d["molecule"].max())
+    X, V, T, TAG, MOL, IMG, BONDS = [], [], [], [], [], [], []
+    for ix in range(nx):
+        for iy in range(ny):
+            for iz in range(nz):
+                off = iz * ny * nx + iy * nx + ix
+                x = xu + prd * np.array([ix, iy, iz])
+                k = np.floor((x - d["boxlo"]) / newprd).astype(np.int64)   # Domain::remap
+                x = x - k * newprd
+                # guard the half-open interval against rounding at the upper face
+                hi = x >= newhi
+                x[hi] -= np.broadcast_to(newprd, x.shape)[hi]; k[hi] += 1
+                lo = x < d["boxlo"]
+                x[lo] += np.broadcast_to(newprd, x.shape)[lo]; k[lo] -= 1
+                X.append(x); V.append(d["v"]); T.append(d["type"]); TAG.append(d["tag"] + off * maxtag)
+                MOL.append(d["molecule"] + off * maxmol)
+                IMG.append(((k[:, 0] + 512) & 1023) | (((k[:, 1] + 512) & 1023) << 10) | (((k[:, 2] + 512) & 1023) << 20))
+                b = d["bonds"].copy(); b[:, 1:] += off * maxtag
+                BONDS.append(b)
+    tag = np.concatenate(TAG)
+    o = np.argsort(tag, kind="stable")
+    out = dict(d)
+    out.update(natoms=n * nx * ny * nz, boxhi=newhi, x=np.concatenate(X)[o], v=np.concatenate(V)[o],
+               type=np.concatenate(T)[o].astype(np.int32), tag=tag[o].astype(np.int32),
+               molecule=np.concatenate(MOL)[o].astype(np.int32), image=np.concatenate(IMG)[o].astype(np.int32),
+               bonds=np.concatenate(BONDS))
+    return out
+
+
 def _csr(natoms, owner, cols):
     """rows keyed by 1-based tag; offsets have natoms+2 entries; stable in input order"""
     order = np.argsort(owner, kind="stable")
@@ -82,10 +124,15 @@ def build_topology(natoms, bonds, special_lj=(0.0, 0.0, 1.0, 1.0), special_coul=
     bond_off, (bond_partner, bond_type) = _csr(natoms, a1, [a2, btype])
     # 1-2: both directions
     own = np.concatenate([a1, a2]); oth = np.concatenate([a2, a1])
+    need_far = not (special_lj[2] == 1.0 and special_coul[2] == 1.0 and special_lj[3] == 1.0 and special_coul[3] == 1.0)
+    if not need_far:                                      # Special::build returns after the 1-2 pass
+        spec_off, (spec_tag, spec_lev) = _csr(natoms, own, [oth, np.ones(len(own), np.int64)])
+        return dict(natoms=natoms, bond_offset=bond_off, bond_partner=bond_partner, bond_type=bond_type,
+                    special_offset=spec_off, special_tag=spec_tag, special_level=spec_lev,
+                    special_lj=np.array(special_lj, dtype=np.float64), special_coul=np.array(special_coul, dtype=np.float64))
     sets = [dict() for _ in range(natoms + 1)]            # tag -> {partner tag: level}
     for o, p in zip(own.tolist(), oth.tolist()):
         sets[o].setdefault(p, 1)
-    need_far = not (special_lj[2] == 1.0 and special_coul[2] == 1.0 and special_lj[3] == 1.0 and special_coul[3] == 1.0)
     if need_far:
         one2 = [list(s.keys()) for s in sets]
         for level in (2, 3):

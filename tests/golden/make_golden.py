@@ -116,6 +116,20 @@ def make_chain():
         series.append([R.thermo(k) for k in kw])
     out["thermo_series"] = np.array(series)
     R.close()
+    # in.chain.scaled with -var x 2 -var y 1 -var z 2 (128 000 atoms): thermo only
+    R = O.Reference(args=("-log", "none", "-echo", "none", "-nocite"))
+    R.command(IN_CHAIN.format(data=os.path.join(os.path.dirname(O.POT_DIR), "data", "data.chain")).replace(
+        "neighbor 0.4 bin", "replicate 2 1 2\nneighbor 0.4 bin"))
+    R.command("thermo_style custom step temp pe ke press evdwl emol")
+    R.command("thermo_modify norm no")
+    R.command("run 0")
+    out["rep212_thermo0"] = np.array([R.thermo(k) for k in kw])
+    series = []
+    for _ in range(3):
+        R.command("run 10")
+        series.append([R.thermo(k) for k in kw])
+    out["rep212_series"] = np.array(series)
+    R.close()
     np.savez_compressed(os.path.join(HERE, "chain.npz"), **out)
     print("chain", out["natoms"], out["npairs"], out["pair_digest"], out["thermo0"], out["thermo_series"][-1])
 

@@ -88,6 +88,26 @@ def test_oracle_matches_reference(pkg, oracle_mod):
     o.close()
 
 
+def test_oracle_replicated_matches_reference(pkg, oracle_mod):
+    """in.chain.scaled -var x 2 -var y 1 -var z 2: host-side `replicate` + the oracle against the
+    reference's thermo (128 000 atoms)"""
+    need_data()
+    g = golden()
+    M, B = pkg.molecule_host, pkg.b200md
+    d = M.replicate(M.read_data(DATA), 2, 1, 2)
+    assert d["natoms"] == 128000 and len(d["bonds"]) == 4 * 31680
+    tp = M.build_topology(d["natoms"], d["bonds"])
+    o = oracle_mod.Oracle(d["boxlo"], d["boxhi"], d["x"], d["v"], d["type"], d["tag"], d["mass"], B.UNITS["lj"])
+    T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 1.12)}, 1.12, shift=True)
+    o.pair_lj(T); o.set_topology(tp)
+    o.bond_fene([0.0, 30.0], [0.0, 1.5], [0.0, 1.0], [0.0, 1.0])
+    cn, cmax = B.cutneighsq_table(1, T["cutsq"], 0.4)
+    o.neigh_config(cn, cmax, 0.4, 1, 1, 1, True)
+    o.setup()
+    check_thermo(thermo_vec(o.thermo()), g["rep212_thermo0"], 1e-10)
+    o.close()
+
+
 def test_special_tables_match_reference_counts(pkg):
     """Ave special neighs/atom = 1.98 and 31680 bonds in the reference's log for data.chain"""
     need_data()
@@ -127,6 +147,22 @@ def test_cuda_matches_reference(pkg, lanes, half):
     mine = np.array([t0[0], t0[4] / n, t0[5] / n, (t0[1] + t0[2]) / n, t0[3]])
     assert np.allclose(mine, log0, rtol=6e-8)
     for row in g["thermo_series"]:
+        ctx.setup()
+        check_thermo(thermo_vec(ctx.run(10, cfg["dt"], 0)[-1]), row)
+    ctx.close()
+
+
+@pytest.mark.gpu
+def test_cuda_replicated_matches_reference(pkg):
+    need_data()
+    g = golden()
+    B = pkg.b200md
+    ctx = B.Context(0)
+    cfg = pkg.inputs.in_chain(ctx, DATA, 2, 1, 2)
+    assert cfg["natoms"] == 128000
+    ctx.setup()
+    check_thermo(thermo_vec(ctx.thermo()), g["rep212_thermo0"], 1e-10)
+    for row in g["rep212_series"]:
         ctx.setup()
         check_thermo(thermo_vec(ctx.run(10, cfg["dt"], 0)[-1]), row)
     ctx.close()
