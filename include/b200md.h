@@ -258,7 +258,7 @@ typedef struct b200md_timing {
 } b200md_timing;
 int b200md_get_timing(b200md_ctx *ctx, b200md_timing *out);
 /* tuning knob: lanes cooperating on one atom in the pair kernels (1,2,4,8,16,32); the list
- * build uses max(4, lanes). Call before b200md_setup. */
+ * build has its own lane count (default 1). Call before b200md_setup. */
 int b200md_set_lanes_per_atom(b200md_ctx *ctx, int lanes);
 /* cudaStream_t of the context (as void*), for callers that time with their own events. */
 int b200md_get_stream(b200md_ctx *ctx, void **stream);

@@ -68,6 +68,7 @@ extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out)
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rb, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rr, cudaEventDisableTiming));
   if (const char *sp = getenv("B200MD_SPLIT")) c->split = atof(sp);
+  if (const char *bl = getenv("B200MD_BUILD_LANES")) { c->tpa_build = atoi(bl); c->tpa_build_user = true; }   // tuning
   { const char *ov = getenv("B200MD_OVERLAP"); c->overlap = !(ov && ov[0] == '0'); }
   CUDA_TRY(cudaMalloc(&c->d_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMallocHost(&c->h_result, 16 * sizeof(double)));
@@ -446,8 +447,6 @@ extern "C" int b200md_set_lanes_per_atom(b200md_ctx *c, int lanes) {
        "b200md: lanes per atom must be 1, 2, 4, 8, 16 or 32");
   c->tpa = lanes;
   c->tpa_user = true;
-  const char *bl = getenv("B200MD_BUILD_LANES");   // tuning only; default 4 (8 when the force kernels use more)
-  c->tpa_build = bl ? atoi(bl) : (lanes < 4 ? 4 : lanes);
   return B200MD_OK;
 }
 extern "C" int b200md_get_stream(b200md_ctx *c, void **stream) {
@@ -494,7 +493,7 @@ extern "C" int b200md_pair_eam_config(b200md_ctx *c, int ntypes, int nrho, int n
                            rhor_spline, nz2r, z2r_spline, type2frho, type2rhor, type2z2r, scale));
   c->cutforcemax = sqrt(cutforcesq);
   c->pair_style = B200MD_PAIR_EAM;
-  if (!c->tpa_user) { c->tpa = 1; c->tpa_build = 4; }   // measured: one lane per atom is best for the eam passes
+  if (!c->tpa_user) c->tpa = 1;   // measured: one lane per atom is best for the eam passes
   return B200MD_OK;
 }
 

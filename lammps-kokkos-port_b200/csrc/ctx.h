@@ -112,7 +112,8 @@ struct b200md_ctx {
   int *row_flag = nullptr; // device [nrows] half-stencil role (0 skip,1 full row,2 own row)
   // neighbor list
   int tpa = 2;        // lanes per atom in the force kernels (1..32); measured best on B200
-  int tpa_build = 4;  // lanes per atom in the list build (4..32)
+  int tpa_build = 1;  // lanes per atom in the list build (1..32); measured best on B200 for lj, eam and chain
+  bool tpa_build_user = false;
   bool tpa_user = false;  // set by b200md_set_lanes_per_atom; otherwise the pair style picks (lj 2, eam 1)
   int pitch = 0;  // max neighbors per atom (multiple of tpa)
   int *neigh = nullptr;

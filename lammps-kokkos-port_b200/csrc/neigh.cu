@@ -624,11 +624,13 @@ int neigh_build_list(b200md_ctx *c) {
     CUDA_TRY(cudaMemsetAsync(c->d_flags + 1, 0, sizeof(int), c->stream));
     CUDA_TRY(cudaMemsetAsync(c->tile_ghost, 0, sizeof(int) * ((c->nlocal + 32 / c->tpa - 1) / (32 / c->tpa) + 1), c->stream));
     switch (c->tpa_build) {
+      case 1: launch_build<1>(c); break;
+      case 2: launch_build<2>(c); break;
       case 4: launch_build<4>(c); break;
       case 8: launch_build<8>(c); break;
       case 16: launch_build<16>(c); break;
       case 32: launch_build<32>(c); break;
-      default: b200md_set_error("b200md: build lanes per atom must be 4, 8, 16 or 32"); return B200MD_ERR;
+      default: b200md_set_error("b200md: build lanes per atom must be 1, 2, 4, 8, 16 or 32"); return B200MD_ERR;
     }
     c->launches++;
     CUDA_TRY(cudaGetLastError());

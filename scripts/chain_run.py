@@ -5,8 +5,9 @@ import b200pkg
 P = b200pkg.load(); B = P.b200md
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 100
 lk = B.LIST_FULL if (len(sys.argv) > 2 and sys.argv[2] == "full") else B.LIST_HALF_NEWTON
+rep = int(sys.argv[2]) if (len(sys.argv) > 2 and sys.argv[2].isdigit()) else 1
 ctx = B.Context(0)
-cfg = P.inputs.in_chain(ctx, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "data", "data.chain"), list_kind=lk)
+cfg = P.inputs.in_chain(ctx, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "data", "data.chain"), rep, rep, rep, list_kind=lk)
 ctx.setup()
 n = cfg["natoms"]
 t = ctx.thermo()
