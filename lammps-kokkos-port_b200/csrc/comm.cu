@@ -213,6 +213,106 @@ static inline int nblk(int n) { return (n + 255) / 256; }
 // ---------------------------------------------------------------------------------------
 // borders
 // ---------------------------------------------------------------------------------------
+// slab selection of the two swaps of a pair (the - and + direction of one dimension scan the same
+// atom range): count per 1024-atom tile, offsets by one small scan, ordered compaction.  One pass
+// over the positions for the counts, one for the compaction; the send lists come out ascending
+// like the reference's loop (comm_brick.cpp:836-842), so the ghost order is deterministic.
+#define SLAB_T 256
+#define SLAB_ITEMS 4
+#define SLAB_TILE (SLAB_T * SLAB_ITEMS)
+struct SlabPair { double lo[2], hi[2]; int use[2]; };
+
+__device__ __forceinline__ int slab_bits(const double4 *__restrict__ xq, int idx, int dim, const SlabPair &P) {
+  const double x = comp(xq[idx], dim);
+  int b = 0;
+  if (P.use[0] && x >= P.lo[0] && x <= P.hi[0]) b |= 1;   // comm_brick.cpp:838
+  if (P.use[1] && x >= P.lo[1] && x <= P.hi[1]) b |= 2;
+  return b;
+}
+__global__ void __launch_bounds__(SLAB_T) k_slab_count2(const double4 *__restrict__ xq, int nfirst, int n, int dim, SlabPair P,
+                                                        int *__restrict__ tile_cnt, int ntiles) {
+  __shared__ int s_cnt[2];
+  if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  int ca = 0, cb = 0;
+  const int base = blockIdx.x * SLAB_TILE;
+#pragma unroll
+  for (int it = 0; it < SLAB_ITEMS; it++) {
+    const int k = base + it * SLAB_T + threadIdx.x;
+    if (k < n) { const int b = slab_bits(xq, nfirst + k, dim, P); ca += b & 1; cb += b >> 1; }
+  }
+  ca = __reduce_add_sync(0xffffffffu, ca); cb = __reduce_add_sync(0xffffffffu, cb);
+  if ((threadIdx.x & 31) == 0) { if (ca) atomicAdd(&s_cnt[0], ca); if (cb) atomicAdd(&s_cnt[1], cb); }
+  __syncthreads();
+  if (threadIdx.x < 2) tile_cnt[threadIdx.x * ntiles + blockIdx.x] = s_cnt[threadIdx.x];
+}
+// one block: exclusive scan of both count rows in place, totals to totals[0..1]
+__global__ void __launch_bounds__(SLAB_T) k_slab_offsets(int *tile_cnt, int ntiles, int *totals) {
+  __shared__ int s_warp[33];
+  for (int row = 0; row < 2; row++) {
+    int carry = 0;
+    int *t = tile_cnt + row * ntiles;
+    for (int base = 0; base < ntiles; base += SLAB_T) {
+      const int i = base + threadIdx.x;
+      const int v = i < ntiles ? t[i] : 0;
+      // block exclusive scan
+      const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+      int inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+      if (lane == 31) s_warp[wid] = inc;
+      __syncthreads();
+      if (wid == 0) {
+        int w = lane < SLAB_T / 32 ? s_warp[lane] : 0, winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += y; }
+        if (lane < SLAB_T / 32) s_warp[lane] = winc - w;
+        if (lane == SLAB_T / 32 - 1) s_warp[32] = winc;
+      }
+      __syncthreads();
+      if (i < ntiles) t[i] = carry + s_warp[wid] + inc - v;
+      carry += s_warp[32];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) totals[row] = carry;
+  }
+}
+__global__ void __launch_bounds__(SLAB_T) k_slab_compact2(const double4 *__restrict__ xq, int nfirst, int n, int dim, SlabPair P,
+                                                          const int *__restrict__ tile_off, int ntiles,
+                                                          int *__restrict__ list_a, int *__restrict__ list_b) {
+  __shared__ int s_w[2][SLAB_T / 32];
+  __shared__ int s_run[2];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (threadIdx.x < 2) s_run[threadIdx.x] = tile_off[threadIdx.x * ntiles + blockIdx.x];
+  __syncthreads();
+  const int base = blockIdx.x * SLAB_TILE;
+  for (int it = 0; it < SLAB_ITEMS; it++) {
+    const int k = base + it * SLAB_T + threadIdx.x;
+    const int b = k < n ? slab_bits(xq, nfirst + k, dim, P) : 0;
+    const unsigned ma = __ballot_sync(0xffffffffu, b & 1), mb = __ballot_sync(0xffffffffu, b & 2);
+    if (lane == 0) { s_w[0][wid] = __popc(ma); s_w[1][wid] = __popc(mb); }
+    __syncthreads();
+    int wa = 0, wb = 0, ta = 0, tb = 0;
+#pragma unroll
+    for (int w = 0; w < SLAB_T / 32; w++) { if (w < wid) { wa += s_w[0][w]; wb += s_w[1][w]; } ta += s_w[0][w]; tb += s_w[1][w]; }
+    const unsigned below = (1u << lane) - 1u;
+    if (b & 1) list_a[s_run[0] + wa + __popc(ma & below)] = nfirst + k;
+    if (b & 2) list_b[s_run[1] + wb + __popc(mb & below)] = nfirst + k;
+    __syncthreads();
+    if (threadIdx.x == 0) { s_run[0] += ta; s_run[1] += tb; }
+    __syncthreads();
+  }
+}
+
+static int grow_sendlist(Swap &s, int nsend) {
+  if (nsend > s.sendcap) {
+    if (s.sendlist) CUDA_TRY(cudaFree(s.sendlist));
+    s.sendcap = nsend + nsend / 4 + 256;
+    CUDA_TRY(cudaMalloc(&s.sendlist, sizeof(int) * s.sendcap));
+  }
+  return B200MD_OK;
+}
+
 int comm_borders(b200md_ctx *c) {
   cudaStream_t st = c->stream;
   c->nghost = 0;
@@ -222,76 +322,90 @@ int comm_borders(b200md_ctx *c) {
   for (int dim = 0; dim < 3; dim++) {
     int nlast = 0, nfirst = 0;
     const int twoneed = 2 * c->sched.maxneed[dim];
-    for (int ineed = 0; ineed < twoneed; ineed++, iswap++) {
-      Swap &s = c->swaps[iswap];
-      if (ineed % 2 == 0) { nfirst = nlast; nlast = c->nlocal + c->nghost; }
-      int nsend = 0;
+    for (int ineed = 0; ineed < twoneed; ineed += 2, iswap += 2) {
+      Swap *sw[2] = {&c->swaps[iswap], &c->swaps[iswap + 1]};
+      nfirst = nlast; nlast = c->nlocal + c->nghost;
       const int n = nlast - nfirst;
-      if (s.sendflag && n > 0) {
-        if (n + 1 > c->nmax) TRY(neigh_grow_atoms(c, n + 1));
-        // flag + scan + compact: deterministic ascending send list (comm_brick.cpp:836-842)
-        int *flag = c->perm, *pos = c->atom_bin;
-        k_slab_flag<<<nblk(n + 1), 256, 0, st>>>(c->xq, nfirst, n, s.dim, s.slablo, s.slabhi, flag);
-        TRY(dev_exclusive_scan(c, flag, pos, n + 1));
-        CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4, pos + n, sizeof(int), cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(cudaStreamSynchronize(st));
-        nsend = c->h_flags[4];
-        if (nsend > s.sendcap) {
-          if (s.sendlist) CUDA_TRY(cudaFree(s.sendlist));
-          s.sendcap = nsend + nsend / 4 + 256;
-          CUDA_TRY(cudaMalloc(&s.sendlist, sizeof(int) * s.sendcap));
+      int nsend[2] = {0, 0}, nrecv[2] = {0, 0};
+      SlabPair P;
+      for (int k = 0; k < 2; k++) { P.lo[k] = sw[k]->slablo; P.hi[k] = sw[k]->slabhi; P.use[k] = sw[k]->sendflag ? 1 : 0; }
+      const int ntiles = (n + SLAB_TILE - 1) / SLAB_TILE;
+      if ((P.use[0] || P.use[1]) && n > 0) {
+        if (2 * ntiles + 2 > c->scan_cap) {
+          if (c->scan_block) CUDA_TRY(cudaFree(c->scan_block));
+          c->scan_cap = 2 * ntiles + 64;
+          CUDA_TRY(cudaMalloc(&c->scan_block, sizeof(int) * c->scan_cap));
         }
-        if (nsend) k_compact<<<nblk(n), 256, 0, st>>>(flag, pos, nfirst, n, s.sendlist);
-        c->launches += 2;
+        int *tile_cnt = c->scan_block, *totals = c->d_flags + 6;
+        k_slab_count2<<<ntiles, SLAB_T, 0, st>>>(c->xq, nfirst, n, sw[0]->dim, P, tile_cnt, ntiles);
+        k_slab_offsets<<<1, SLAB_T, 0, st>>>(tile_cnt, ntiles, totals);
+        CUDA_TRY(cudaMemcpyAsync(c->h_flags + 6, totals, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        nsend[0] = c->h_flags[6]; nsend[1] = c->h_flags[7];
+        TRY(grow_sendlist(*sw[0], nsend[0]));
+        TRY(grow_sendlist(*sw[1], nsend[1]));
+        if (nsend[0] + nsend[1])
+          k_slab_compact2<<<ntiles, SLAB_T, 0, st>>>(c->xq, nfirst, n, sw[0]->dim, P, tile_cnt, ntiles, sw[0]->sendlist,
+                                                    sw[1]->sendlist);
+        c->launches += 3;
       }
-      s.sendnum = nsend;
-      int nrecv = nsend;
-      const bool self = (s.sendproc == c->rank);
-      if (!self) {
-        // counts (comm_brick.cpp:917-918)
-        NcclState *nc = c->nccl;
+      bool self[2], any_remote = false;
+      for (int k = 0; k < 2; k++) { sw[k]->sendnum = nsend[k]; nrecv[k] = nsend[k]; self[k] = sw[k]->sendproc == c->rank; any_remote |= !self[k]; }
+      NcclState *nc = c->nccl;
+      if (any_remote) {
+        // counts of both directions in one exchange (comm_brick.cpp:917-918)
         if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
-        nc->h_counts[0] = nsend;
-        CUDA_TRY(cudaMemcpyAsync(nc->d_counts, nc->h_counts, sizeof(int), cudaMemcpyHostToDevice, st));
+        nc->h_counts[0] = nsend[0]; nc->h_counts[1] = nsend[1];
+        CUDA_TRY(cudaMemcpyAsync(nc->d_counts, nc->h_counts, 2 * sizeof(int), cudaMemcpyHostToDevice, st));
         NCCL_TRY(ncclGroupStart());
-        NCCL_TRY(ncclSend(nc->d_counts, 1, ncclInt, s.sendproc, nc->comm, st));
-        NCCL_TRY(ncclRecv(nc->d_counts + 1, 1, ncclInt, s.recvproc, nc->comm, st));
+        for (int k = 0; k < 2; k++) {
+          if (self[k]) continue;
+          NCCL_TRY(ncclSend(nc->d_counts + k, 1, ncclInt, sw[k]->sendproc, nc->comm, st));
+          NCCL_TRY(ncclRecv(nc->d_counts + 2 + k, 1, ncclInt, sw[k]->recvproc, nc->comm, st));
+        }
         NCCL_TRY(ncclGroupEnd());
-        CUDA_TRY(cudaMemcpyAsync(nc->h_counts + 1, nc->d_counts + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(nc->h_counts + 2, nc->d_counts + 2, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
-        nrecv = nc->h_counts[1];
+        for (int k = 0; k < 2; k++) if (!self[k]) nrecv[k] = nc->h_counts[2 + k];
       }
-      const int first = c->nlocal + c->nghost;
-      if (first + nrecv > c->nmax) TRY(neigh_grow_atoms(c, first + nrecv));
-      if (self) {
-        if (nsend)
-          k_self_border<<<nblk(nsend), 256, 0, st>>>(nsend, s.sendlist, first, c->nlocal, c->xq, c->tag, c->ghost_src,
-                                                    c->ghost_pbc, s.pbc[0], s.pbc[1], s.pbc[2], c->prd[0],
-                                                    c->prd[1], c->prd[2]);
-        c->launches++;
-      } else {
-        NcclState *nc = c->nccl;
-        TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)nsend * 5 + 8));
-        double4 *buf = reinterpret_cast<double4 *>(c->sendbuf);
-        int *tagbuf = reinterpret_cast<int *>(c->sendbuf + (size_t)nsend * 4);
-        if (nsend)
-          k_pack_border<<<nblk(nsend), 256, 0, st>>>(nsend, s.sendlist, c->xq, c->tag, buf, tagbuf, s.pbc[0], s.pbc[1],
-                                                    s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
-        c->launches++;
-        NCCL_TRY(ncclGroupStart());
-        if (nsend) {
-          NCCL_TRY(ncclSend(buf, (size_t)nsend * 4, ncclDouble, s.sendproc, nc->comm, st));
-          NCCL_TRY(ncclSend(tagbuf, nsend, ncclInt, s.sendproc, nc->comm, st));
+      const int first0 = c->nlocal + c->nghost;
+      const int first[2] = {first0, first0 + nrecv[0]};
+      if (first[1] + nrecv[1] > c->nmax) TRY(neigh_grow_atoms(c, first[1] + nrecv[1]));
+      size_t off[2] = {0, 0}, need = 0;
+      for (int k = 0; k < 2; k++) if (!self[k]) { off[k] = need; need += (size_t)nsend[k] * 5 + 4; }
+      if (any_remote) TRY(ensure_buf(c->sendbuf, c->sendcap, need + 8));
+      for (int k = 0; k < 2; k++) {
+        Swap &s = *sw[k];
+        if (!nsend[k]) continue;
+        if (self[k]) {
+          k_self_border<<<nblk(nsend[k]), 256, 0, st>>>(nsend[k], s.sendlist, first[k], c->nlocal, c->xq, c->tag, c->ghost_src,
+                                                       c->ghost_pbc, s.pbc[0], s.pbc[1], s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
+        } else {
+          double4 *buf = reinterpret_cast<double4 *>(c->sendbuf + off[k]);
+          int *tagbuf = reinterpret_cast<int *>(c->sendbuf + off[k] + (size_t)nsend[k] * 4);
+          k_pack_border<<<nblk(nsend[k]), 256, 0, st>>>(nsend[k], s.sendlist, c->xq, c->tag, buf, tagbuf, s.pbc[0], s.pbc[1],
+                                                       s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
         }
-        if (nrecv) {
-          NCCL_TRY(ncclRecv(c->xq + first, (size_t)nrecv * 4, ncclDouble, s.recvproc, nc->comm, st));
-          NCCL_TRY(ncclRecv(c->tag + first, nrecv, ncclInt, s.recvproc, nc->comm, st));
+        c->launches++;
+      }
+      if (any_remote) {
+        NCCL_TRY(ncclGroupStart());
+        for (int k = 0; k < 2; k++) {
+          if (self[k]) continue;
+          Swap &s = *sw[k];
+          if (nsend[k]) {
+            NCCL_TRY(ncclSend(c->sendbuf + off[k], (size_t)nsend[k] * 4, ncclDouble, s.sendproc, nc->comm, st));
+            NCCL_TRY(ncclSend(reinterpret_cast<int *>(c->sendbuf + off[k] + (size_t)nsend[k] * 4), nsend[k], ncclInt, s.sendproc, nc->comm, st));
+          }
+          if (nrecv[k]) {
+            NCCL_TRY(ncclRecv(c->xq + first[k], (size_t)nrecv[k] * 4, ncclDouble, s.recvproc, nc->comm, st));
+            NCCL_TRY(ncclRecv(c->tag + first[k], nrecv[k], ncclInt, s.recvproc, nc->comm, st));
+          }
         }
         NCCL_TRY(ncclGroupEnd());
       }
-      s.recvnum = nrecv;
-      s.firstrecv = first;
-      c->nghost += nrecv;
+      for (int k = 0; k < 2; k++) { sw[k]->recvnum = nrecv[k]; sw[k]->firstrecv = first[k]; }
+      c->nghost += nrecv[0] + nrecv[1];
     }
   }
   CUDA_TRY(cudaGetLastError());
@@ -537,27 +651,53 @@ template <int NV>
 static int reverse_staged(b200md_ctx *c, double *arr) {
   cudaStream_t st = c->stream;
   NcclState *nc = c->nccl;
-  for (int iswap = (int)c->swaps.size() - 1; iswap >= 0; iswap--) {
-    Swap &s = c->swaps[iswap];
-    if (s.sendproc == c->rank) {
-      if (!s.sendnum) continue;
-      if (NV == 3) k_rev_self3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, c->nmax, arr);
-      else k_rev_self1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, arr);
-      c->launches++;
-      continue;
+  // the two swaps of a pair (ineed 2m, 2m+1: the -/+ directions of one dimension) draw their send
+  // lists from the same atom range, so they are independent: one NCCL group for both
+  for (int ipair = (int)c->swaps.size() / 2 - 1; ipair >= 0; ipair--) {
+    Swap *sw[2] = {&c->swaps[2 * ipair + 1], &c->swaps[2 * ipair]};
+    size_t soff[2] = {0, 0}, roff[2] = {0, 0}, stot = 0, rtot = 0;
+    bool remote = false;
+    for (int k = 0; k < 2; k++) {
+      Swap &s = *sw[k];
+      if (s.sendproc == c->rank) {
+        if (!s.sendnum) continue;
+        if (NV == 3) k_rev_self3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, c->nmax, arr);
+        else k_rev_self1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, arr);
+        c->launches++;
+        continue;
+      }
+      remote = true;
+      soff[k] = stot; stot += (size_t)s.recvnum * NV;
+      roff[k] = rtot; rtot += (size_t)s.sendnum * NV;
     }
+    if (!remote) continue;
     if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
-    TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)s.recvnum * NV + 8));
-    TRY(ensure_buf(c->recvbuf, c->recvcap, (size_t)s.sendnum * NV + 8));
-    const double *src = arr + s.firstrecv;
-    if (NV == 3 && s.recvnum) { k_rev_pack3<<<nblk(s.recvnum), 256, 0, st>>>(s.recvnum, s.firstrecv, c->nmax, arr, c->sendbuf); src = c->sendbuf; c->launches++; }
+    TRY(ensure_buf(c->sendbuf, c->sendcap, stot + 8));
+    TRY(ensure_buf(c->recvbuf, c->recvcap, rtot + 8));
+    const double *src[2] = {nullptr, nullptr};
+    for (int k = 0; k < 2; k++) {
+      Swap &s = *sw[k];
+      if (s.sendproc == c->rank) continue;
+      src[k] = arr + s.firstrecv;
+      if (NV == 3 && s.recvnum) {
+        k_rev_pack3<<<nblk(s.recvnum), 256, 0, st>>>(s.recvnum, s.firstrecv, c->nmax, arr, c->sendbuf + soff[k]);
+        src[k] = c->sendbuf + soff[k];
+        c->launches++;
+      }
+    }
     NCCL_TRY(ncclGroupStart());
-    if (s.recvnum) NCCL_TRY(ncclSend(src, (size_t)s.recvnum * NV, ncclDouble, s.recvproc, nc->comm, st));
-    if (s.sendnum) NCCL_TRY(ncclRecv(c->recvbuf, (size_t)s.sendnum * NV, ncclDouble, s.sendproc, nc->comm, st));
+    for (int k = 0; k < 2; k++) {
+      Swap &s = *sw[k];
+      if (s.sendproc == c->rank) continue;
+      if (s.recvnum) NCCL_TRY(ncclSend(src[k], (size_t)s.recvnum * NV, ncclDouble, s.recvproc, nc->comm, st));
+      if (s.sendnum) NCCL_TRY(ncclRecv(c->recvbuf + roff[k], (size_t)s.sendnum * NV, ncclDouble, s.sendproc, nc->comm, st));
+    }
     NCCL_TRY(ncclGroupEnd());
-    if (s.sendnum) {
-      if (NV == 3) k_rev_unpack3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, c->nmax, arr, c->recvbuf);
-      else k_rev_unpack1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, arr, c->recvbuf);
+    for (int k = 0; k < 2; k++) {
+      Swap &s = *sw[k];
+      if (s.sendproc == c->rank || !s.sendnum) continue;
+      if (NV == 3) k_rev_unpack3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, c->nmax, arr, c->recvbuf + roff[k]);
+      else k_rev_unpack1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, arr, c->recvbuf + roff[k]);
       c->launches++;
     }
   }
