@@ -326,7 +326,7 @@ int comm_borders(b200md_ctx *c) {
       Swap *sw[2] = {&c->swaps[iswap], &c->swaps[iswap + 1]};
       nfirst = nlast; nlast = c->nlocal + c->nghost;
       const int n = nlast - nfirst;
-      int nsend[2] = {0, 0}, nrecv[2] = {0, 0};
+      int nsend[2] = {0, 0};
       SlabPair P;
       for (int k = 0; k < 2; k++) { P.lo[k] = sw[k]->slablo; P.hi[k] = sw[k]->slabhi; P.use[k] = sw[k]->sendflag ? 1 : 0; }
       const int ntiles = (n + SLAB_TILE - 1) / SLAB_TILE;
@@ -349,63 +349,57 @@ int comm_borders(b200md_ctx *c) {
                                                     sw[1]->sendlist);
         c->launches += 3;
       }
-      bool self[2], any_remote = false;
-      for (int k = 0; k < 2; k++) { sw[k]->sendnum = nsend[k]; nrecv[k] = nsend[k]; self[k] = sw[k]->sendproc == c->rank; any_remote |= !self[k]; }
-      NcclState *nc = c->nccl;
-      if (any_remote) {
-        // counts of both directions in one exchange (comm_brick.cpp:917-918)
-        if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
-        nc->h_counts[0] = nsend[0]; nc->h_counts[1] = nsend[1];
-        CUDA_TRY(cudaMemcpyAsync(nc->d_counts, nc->h_counts, 2 * sizeof(int), cudaMemcpyHostToDevice, st));
-        NCCL_TRY(ncclGroupStart());
-        for (int k = 0; k < 2; k++) {
-          if (self[k]) continue;
-          NCCL_TRY(ncclSend(nc->d_counts + k, 1, ncclInt, sw[k]->sendproc, nc->comm, st));
-          NCCL_TRY(ncclRecv(nc->d_counts + 2 + k, 1, ncclInt, sw[k]->recvproc, nc->comm, st));
-        }
-        NCCL_TRY(ncclGroupEnd());
-        CUDA_TRY(cudaMemcpyAsync(nc->h_counts + 2, nc->d_counts + 2, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-        CUDA_TRY(cudaStreamSynchronize(st));
-        for (int k = 0; k < 2; k++) if (!self[k]) nrecv[k] = nc->h_counts[2 + k];
-      }
-      const int first0 = c->nlocal + c->nghost;
-      const int first[2] = {first0, first0 + nrecv[0]};
-      if (first[1] + nrecv[1] > c->nmax) TRY(neigh_grow_atoms(c, first[1] + nrecv[1]));
-      size_t off[2] = {0, 0}, need = 0;
-      for (int k = 0; k < 2; k++) if (!self[k]) { off[k] = need; need += (size_t)nsend[k] * 5 + 4; }
-      if (any_remote) TRY(ensure_buf(c->sendbuf, c->sendcap, need + 8));
+      // exchange per swap, in swap order, exactly like CommBrick::borders (comm_brick.cpp:917-960)
       for (int k = 0; k < 2; k++) {
         Swap &s = *sw[k];
-        if (!nsend[k]) continue;
-        if (self[k]) {
-          k_self_border<<<nblk(nsend[k]), 256, 0, st>>>(nsend[k], s.sendlist, first[k], c->nlocal, c->xq, c->tag, c->ghost_src,
-                                                       c->ghost_pbc, s.pbc[0], s.pbc[1], s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
+        const int ns = nsend[k];
+        s.sendnum = ns;
+        int nrecv = ns;
+        const bool self = (s.sendproc == c->rank);
+        if (!self) {
+          NcclState *nc = c->nccl;
+          if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
+          nc->h_counts[0] = ns;
+          CUDA_TRY(cudaMemcpyAsync(nc->d_counts, nc->h_counts, sizeof(int), cudaMemcpyHostToDevice, st));
+          NCCL_TRY(ncclGroupStart());
+          NCCL_TRY(ncclSend(nc->d_counts, 1, ncclInt, s.sendproc, nc->comm, st));
+          NCCL_TRY(ncclRecv(nc->d_counts + 1, 1, ncclInt, s.recvproc, nc->comm, st));
+          NCCL_TRY(ncclGroupEnd());
+          CUDA_TRY(cudaMemcpyAsync(nc->h_counts + 1, nc->d_counts + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
+          CUDA_TRY(cudaStreamSynchronize(st));
+          nrecv = nc->h_counts[1];
+        }
+        const int first = c->nlocal + c->nghost;
+        if (first + nrecv > c->nmax) TRY(neigh_grow_atoms(c, first + nrecv));
+        if (self) {
+          if (ns)
+            k_self_border<<<nblk(ns), 256, 0, st>>>(ns, s.sendlist, first, c->nlocal, c->xq, c->tag, c->ghost_src,
+                                                   c->ghost_pbc, s.pbc[0], s.pbc[1], s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
+          c->launches++;
         } else {
-          double4 *buf = reinterpret_cast<double4 *>(c->sendbuf + off[k]);
-          int *tagbuf = reinterpret_cast<int *>(c->sendbuf + off[k] + (size_t)nsend[k] * 4);
-          k_pack_border<<<nblk(nsend[k]), 256, 0, st>>>(nsend[k], s.sendlist, c->xq, c->tag, buf, tagbuf, s.pbc[0], s.pbc[1],
-                                                       s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
-        }
-        c->launches++;
-      }
-      if (any_remote) {
-        NCCL_TRY(ncclGroupStart());
-        for (int k = 0; k < 2; k++) {
-          if (self[k]) continue;
-          Swap &s = *sw[k];
-          if (nsend[k]) {
-            NCCL_TRY(ncclSend(c->sendbuf + off[k], (size_t)nsend[k] * 4, ncclDouble, s.sendproc, nc->comm, st));
-            NCCL_TRY(ncclSend(reinterpret_cast<int *>(c->sendbuf + off[k] + (size_t)nsend[k] * 4), nsend[k], ncclInt, s.sendproc, nc->comm, st));
+          NcclState *nc = c->nccl;
+          TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)ns * 5 + 8));
+          double4 *buf = reinterpret_cast<double4 *>(c->sendbuf);
+          int *tagbuf = reinterpret_cast<int *>(c->sendbuf + (size_t)ns * 4);
+          if (ns)
+            k_pack_border<<<nblk(ns), 256, 0, st>>>(ns, s.sendlist, c->xq, c->tag, buf, tagbuf, s.pbc[0], s.pbc[1],
+                                                   s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
+          c->launches++;
+          NCCL_TRY(ncclGroupStart());
+          if (ns) {
+            NCCL_TRY(ncclSend(buf, (size_t)ns * 4, ncclDouble, s.sendproc, nc->comm, st));
+            NCCL_TRY(ncclSend(tagbuf, ns, ncclInt, s.sendproc, nc->comm, st));
           }
-          if (nrecv[k]) {
-            NCCL_TRY(ncclRecv(c->xq + first[k], (size_t)nrecv[k] * 4, ncclDouble, s.recvproc, nc->comm, st));
-            NCCL_TRY(ncclRecv(c->tag + first[k], nrecv[k], ncclInt, s.recvproc, nc->comm, st));
+          if (nrecv) {
+            NCCL_TRY(ncclRecv(c->xq + first, (size_t)nrecv * 4, ncclDouble, s.recvproc, nc->comm, st));
+            NCCL_TRY(ncclRecv(c->tag + first, nrecv, ncclInt, s.recvproc, nc->comm, st));
           }
+          NCCL_TRY(ncclGroupEnd());
         }
-        NCCL_TRY(ncclGroupEnd());
+        s.recvnum = nrecv;
+        s.firstrecv = first;
+        c->nghost += nrecv;
       }
-      for (int k = 0; k < 2; k++) { sw[k]->recvnum = nrecv[k]; sw[k]->firstrecv = first[k]; }
-      c->nghost += nrecv[0] + nrecv[1];
     }
   }
   CUDA_TRY(cudaGetLastError());
@@ -651,53 +645,27 @@ template <int NV>
 static int reverse_staged(b200md_ctx *c, double *arr) {
   cudaStream_t st = c->stream;
   NcclState *nc = c->nccl;
-  // the two swaps of a pair (ineed 2m, 2m+1: the -/+ directions of one dimension) draw their send
-  // lists from the same atom range, so they are independent: one NCCL group for both
-  for (int ipair = (int)c->swaps.size() / 2 - 1; ipair >= 0; ipair--) {
-    Swap *sw[2] = {&c->swaps[2 * ipair + 1], &c->swaps[2 * ipair]};
-    size_t soff[2] = {0, 0}, roff[2] = {0, 0}, stot = 0, rtot = 0;
-    bool remote = false;
-    for (int k = 0; k < 2; k++) {
-      Swap &s = *sw[k];
-      if (s.sendproc == c->rank) {
-        if (!s.sendnum) continue;
-        if (NV == 3) k_rev_self3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, c->nmax, arr);
-        else k_rev_self1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, arr);
-        c->launches++;
-        continue;
-      }
-      remote = true;
-      soff[k] = stot; stot += (size_t)s.recvnum * NV;
-      roff[k] = rtot; rtot += (size_t)s.sendnum * NV;
+  for (int iswap = (int)c->swaps.size() - 1; iswap >= 0; iswap--) {
+    Swap &s = c->swaps[iswap];
+    if (s.sendproc == c->rank) {
+      if (!s.sendnum) continue;
+      if (NV == 3) k_rev_self3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, c->nmax, arr);
+      else k_rev_self1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, s.firstrecv, arr);
+      c->launches++;
+      continue;
     }
-    if (!remote) continue;
     if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
-    TRY(ensure_buf(c->sendbuf, c->sendcap, stot + 8));
-    TRY(ensure_buf(c->recvbuf, c->recvcap, rtot + 8));
-    const double *src[2] = {nullptr, nullptr};
-    for (int k = 0; k < 2; k++) {
-      Swap &s = *sw[k];
-      if (s.sendproc == c->rank) continue;
-      src[k] = arr + s.firstrecv;
-      if (NV == 3 && s.recvnum) {
-        k_rev_pack3<<<nblk(s.recvnum), 256, 0, st>>>(s.recvnum, s.firstrecv, c->nmax, arr, c->sendbuf + soff[k]);
-        src[k] = c->sendbuf + soff[k];
-        c->launches++;
-      }
-    }
+    TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)s.recvnum * NV + 8));
+    TRY(ensure_buf(c->recvbuf, c->recvcap, (size_t)s.sendnum * NV + 8));
+    const double *src = arr + s.firstrecv;
+    if (NV == 3 && s.recvnum) { k_rev_pack3<<<nblk(s.recvnum), 256, 0, st>>>(s.recvnum, s.firstrecv, c->nmax, arr, c->sendbuf); src = c->sendbuf; c->launches++; }
     NCCL_TRY(ncclGroupStart());
-    for (int k = 0; k < 2; k++) {
-      Swap &s = *sw[k];
-      if (s.sendproc == c->rank) continue;
-      if (s.recvnum) NCCL_TRY(ncclSend(src[k], (size_t)s.recvnum * NV, ncclDouble, s.recvproc, nc->comm, st));
-      if (s.sendnum) NCCL_TRY(ncclRecv(c->recvbuf + roff[k], (size_t)s.sendnum * NV, ncclDouble, s.sendproc, nc->comm, st));
-    }
+    if (s.recvnum) NCCL_TRY(ncclSend(src, (size_t)s.recvnum * NV, ncclDouble, s.recvproc, nc->comm, st));
+    if (s.sendnum) NCCL_TRY(ncclRecv(c->recvbuf, (size_t)s.sendnum * NV, ncclDouble, s.sendproc, nc->comm, st));
     NCCL_TRY(ncclGroupEnd());
-    for (int k = 0; k < 2; k++) {
-      Swap &s = *sw[k];
-      if (s.sendproc == c->rank || !s.sendnum) continue;
-      if (NV == 3) k_rev_unpack3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, c->nmax, arr, c->recvbuf + roff[k]);
-      else k_rev_unpack1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, arr, c->recvbuf + roff[k]);
+    if (s.sendnum) {
+      if (NV == 3) k_rev_unpack3<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, c->nmax, arr, c->recvbuf);
+      else k_rev_unpack1<<<nblk(s.sendnum), 256, 0, st>>>(s.sendnum, s.sendlist, arr, c->recvbuf);
       c->launches++;
     }
   }
