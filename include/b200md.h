@@ -219,6 +219,8 @@ int b200md_bond_fene_config(b200md_ctx *ctx, int nbondtypes, const double *k, co
  * (call after b200md_pair_compute, before b200md_reverse_comm); energy / virial[6] are this
  * rank's Bond::energy and Bond::virial, written when the flag is set. */
 int b200md_bond_compute(b200md_ctx *ctx, int eflag, int vflag, double *energy, double virial[6]);
+/* This rank's Bond::energy and Bond::virial[6] (src/bond.h:32-33) of the last tallied evaluation. */
+int b200md_bond_tallies(b200md_ctx *ctx, double *energy, double virial[6]);
 
 /* ---- fix nve + thermo ---------------------------------------------------------------- */
 

@@ -333,6 +333,11 @@ class Context:
         _chk(self.L.b200md_bond_compute(self.h, int(eflag), int(vflag), C.byref(e), vir))
         return e.value, list(vir)
 
+    def bond_tallies(self):
+        e = C.c_double(); vir = (C.c_double * 6)()
+        _chk(self.L.b200md_bond_tallies(self.h, C.byref(e), vir))
+        return e.value, list(vir)
+
     def pair_tallies(self):
         e = C.c_double(); vir = (C.c_double * 6)()
         _chk(self.L.b200md_pair_tallies(self.h, C.byref(e), vir))

@@ -544,6 +544,14 @@ extern "C" int b200md_bond_compute(b200md_ctx *c, int eflag, int vflag, double *
   return B200MD_OK;
 }
 
+extern "C" int b200md_bond_tallies(b200md_ctx *c, double *energy, double virial[6]) {
+  NEED(c, "b200md: null context");
+  NEED(c->ev_valid, "Energy was not tallied on needed timestep");
+  if (energy) *energy = c->topo.eng_bond;
+  if (virial) for (int k = 0; k < 6; k++) virial[k] = c->topo.virial_bond[k];
+  return B200MD_OK;
+}
+
 // ---------------------------------------------------------------------------------------
 // fix nve, thermo
 // ---------------------------------------------------------------------------------------

@@ -15,6 +15,13 @@ class B200PairStyle {
   virtual int b200_push(b200md_ctx *ctx) = 0;   // returns the library's status code
 };
 
+// a bond style that can hand its coefficients to the device library
+class B200BondStyle {
+ public:
+  virtual ~B200BondStyle() = default;
+  virtual int b200_push_bond(b200md_ctx *ctx) = 0;
+};
+
 // the one device context of this LAMMPS instance (owned by VerletB200)
 struct B200Shared {
   static b200md_ctx *ctx;

@@ -60,6 +60,7 @@ def main():
     ref_srcs = sorted(glob.glob(os.path.join(SRC, "*.cpp")))
     ref_srcs += [os.path.join(SRC, "STUBS", "mpi.cpp")]
     ref_srcs += [os.path.join(SRC, "MANYBODY", f) for f in ("pair_eam.cpp", "pair_eam_alloy.cpp", "pair_eam_fs.cpp")]
+    ref_srcs += [os.path.join(SRC, "MOLECULE", f) for f in ("atom_vec_bond.cpp", "bond_fene.cpp")]
     own_srcs = sorted(glob.glob(os.path.join(HERE, "*_b200.cpp")))
     headers = [s[:-4] + ".h" for s in ref_srcs + own_srcs if os.path.exists(s[:-4] + ".h")]
     for macro, prefix, name in STYLES:
@@ -74,14 +75,14 @@ def main():
         write_if_changed(os.path.join(GEN, "packages_%s.h" % name), "")
     write_if_changed(os.path.join(GEN, "lmpinstalledpkgs.h"),
                      'const char * LAMMPS_NS::LAMMPS::installed_packages[] = '
-                     '{"MANYBODY", "B200", NULL};\n')
+                     '{"MANYBODY", "MOLECULE", "B200", NULL};\n')
     write_if_changed(os.path.join(GEN, "lmpgitversion.h"),
                      'bool LAMMPS_NS::LAMMPS::has_git_info() { return false; }\n'
                      'const char *LAMMPS_NS::LAMMPS::git_commit() { return "(unknown)"; }\n'
                      'const char *LAMMPS_NS::LAMMPS::git_branch() { return "(unknown)"; }\n'
                      'const char *LAMMPS_NS::LAMMPS::git_descriptor() { return "(unknown)"; }\n')
     inc = ["-I" + GEN, "-I" + SRC, "-I" + os.path.join(SRC, "STUBS"), "-I" + os.path.join(SRC, "MANYBODY"),
-           "-I" + HERE, "-I" + os.path.join(ROOT, "include")]
+           "-I" + os.path.join(SRC, "MOLECULE"), "-I" + HERE, "-I" + os.path.join(ROOT, "include")]
     flags = ["-O2", "-DNDEBUG", "-ffp-contract=off", "-fPIC", "-std=c++11", "-DLAMMPS_SMALLBIG",
              "-DLAMMPS_EXCEPTIONS", "-w"]
     nj = ["cxx = %s" % CXX, "flags = %s %s" % (" ".join(flags), " ".join(inc)),

@@ -6,6 +6,7 @@
 
 #include "atom.h"
 #include "atom_vec.h"
+#include "bond.h"
 #include "comm.h"
 #include "domain.h"
 #include "error.h"
@@ -54,9 +55,16 @@ void VerletB200::check_supported()
 {
   if (domain->triclinic) error->all(FLERR, "Run style verlet/b200 requires an orthogonal box");
   if (domain->dimension != 3) error->all(FLERR, "Run style verlet/b200 requires a 3d system");
-  if (atom->molecular != Atom::ATOMIC || force->bond || force->angle || force->dihedral ||
-      force->improper || force->kspace)
-    error->all(FLERR, "Run style verlet/b200 supports atomic systems with a pair style only");
+  if (force->angle || force->dihedral || force->improper || force->kspace || atom->molecular == Atom::TEMPLATE)
+    error->all(FLERR, "Run style verlet/b200 supports pair styles and bond styles only");
+  if (atom->molecular != Atom::ATOMIC) {
+    // bench/in.chain: bonds only, newton_bond on, one rank (the host arrays hold the whole topology)
+    if (force->bond && !dynamic_cast<B200BondStyle *>(force->bond))
+      error->all(FLERR, "Run style verlet/b200 requires a bond style with the b200 suffix");
+    if (!force->newton_bond) error->all(FLERR, "Run style verlet/b200 requires newton_bond on");
+    if (comm->nprocs > 1) error->all(FLERR, "Run style verlet/b200: molecular systems run on one rank");
+    if (!atom->tag_consecutive()) error->all(FLERR, "Run style verlet/b200 requires consecutive atom IDs");
+  }
   if (atom->rmass_flag || atom->torque_flag)
     error->all(FLERR, "Run style verlet/b200 requires per-type masses and point particles");
   if (!force->pair || !dynamic_cast<B200PairStyle *>(force->pair))
@@ -129,6 +137,13 @@ void VerletB200::device_setup()
     std::sort(mask_by_tag.begin(), mask_by_tag.end());
   }
 
+  host_index.clear();
+  if (comm->nprocs == 1) {
+    host_index.reserve(nlocal);
+    for (int i = 0; i < nlocal; i++) host_index.emplace_back((int) atom->tag[i], i);
+    std::sort(host_index.begin(), host_index.end());
+  }
+
   const double *x = nlocal ? &atom->x[0][0] : nullptr;
   const double *v = nlocal ? &atom->v[0][0] : nullptr;
   if (b200md_set_atoms(ctx, nlocal, x, v, atom->type, atom->tag, atom->image, atom->ntypes, atom->mass))
@@ -142,6 +157,7 @@ void VerletB200::device_setup()
                           force->newton_pair ? B200MD_LIST_HALF_NEWTON : B200MD_LIST_FULL))
     fail();
   if (dynamic_cast<B200PairStyle *>(force->pair)->b200_push(ctx)) fail();
+  if (atom->molecular != Atom::ATOMIC) push_topology();
   if (b200md_setup(ctx)) fail();
 
   long long nb = 0, nd = 0, tot = 0;
@@ -192,6 +208,43 @@ void VerletB200::publish_tallies()
   Pair *pair = force->pair;
   pair->eng_vdwl = pair->eng_coul = 0.0;
   if (b200md_pair_tallies(ctx, &pair->eng_vdwl, pair->virial)) fail();
+  if (force->bond && atom->molecular != Atom::ATOMIC) {
+    if (b200md_bond_tallies(ctx, &force->bond->energy, force->bond->virial)) fail();
+  }
+}
+
+/* ----------------------------------------------------------------------
+   Atom::num_bond / bond_atom / bond_type and Atom::special / nspecial of the owned atoms,
+   re-keyed by tag (CSR) for b200md_set_topology
+------------------------------------------------------------------------- */
+
+void VerletB200::push_topology()
+{
+  const int nlocal = atom->nlocal;
+  const bigint natoms = atom->natoms;
+  std::vector<int> boff(natoms + 2, 0), soff(natoms + 2, 0);
+  for (int i = 0; i < nlocal; i++) {
+    boff[atom->tag[i] + 1] = atom->num_bond[i];
+    soff[atom->tag[i] + 1] = atom->nspecial[i][2];
+  }
+  for (bigint t = 1; t <= natoms + 1; t++) { boff[t] += boff[t - 1]; soff[t] += soff[t - 1]; }
+  std::vector<int> bpart(boff[natoms + 1] + 1), btype(boff[natoms + 1] + 1), stag(soff[natoms + 1] + 1), slev(soff[natoms + 1] + 1);
+  for (int i = 0; i < nlocal; i++) {
+    const int t = atom->tag[i];
+    for (int m = 0; m < atom->num_bond[i]; m++) {
+      bpart[boff[t] + m] = (int) atom->bond_atom[i][m];
+      btype[boff[t] + m] = atom->bond_type[i][m];
+    }
+    const int *ns = atom->nspecial[i];
+    for (int m = 0; m < ns[2]; m++) {
+      stag[soff[t] + m] = (int) atom->special[i][m];
+      slev[soff[t] + m] = m < ns[0] ? 1 : (m < ns[1] ? 2 : 3);
+    }
+  }
+  if (b200md_set_topology(ctx, natoms, boff.data(), bpart.data(), btype.data(), soff.data(), stag.data(), slev.data(),
+                          force->special_lj, force->special_coul))
+    fail();
+  if (force->bond && dynamic_cast<B200BondStyle *>(force->bond)->b200_push_bond(ctx)) fail();
 }
 
 /* ----------------------------------------------------------------------
@@ -203,6 +256,26 @@ void VerletB200::sync_host()
   if (!host_stale) return;
   int nlocal = 0, nghost = 0;
   if (b200md_get_nlocal(ctx, &nlocal, &nghost)) fail();
+  if (comm->nprocs == 1 && (int) host_index.size() == nlocal) {
+    // one rank: the host keeps its own atom order (so every other per-atom array -- mask,
+    // molecule, bonds, special -- stays attached); device rows are scattered back by tag
+    hx.resize(3 * (size_t) nlocal); hv.resize(3 * (size_t) nlocal); hf.resize(3 * (size_t) nlocal);
+    htype.resize(nlocal); htag.resize(nlocal); himage.resize(nlocal);
+    if (nlocal && b200md_get_atoms(ctx, hx.data(), hv.data(), hf.data(), htype.data(), htag.data(), himage.data())) fail();
+    for (int k = 0; k < nlocal; k++) {
+      auto it = std::lower_bound(host_index.begin(), host_index.end(), std::make_pair(htag[k], 0));
+      const int i = it->second;
+      for (int d = 0; d < 3; d++) {
+        atom->x[i][d] = hx[3 * (size_t) k + d];
+        atom->v[i][d] = hv[3 * (size_t) k + d];
+        atom->f[i][d] = hf[3 * (size_t) k + d];
+      }
+      atom->image[i] = himage[k];
+    }
+    atom->nghost = 0;
+    host_stale = false;
+    return;
+  }
   while (nlocal > atom->nmax) atom->avec->grow(0);
   atom->nlocal = nlocal;
   atom->nghost = 0;

@@ -31,11 +31,15 @@ class VerletB200 : public Verlet {
   b200md_ctx *ctx;
   bool host_stale;
   long long builds_at_setup;
-  std::vector<std::pair<int, int>> mask_by_tag;    // only when group masks are not uniform
+  std::vector<std::pair<int, int>> mask_by_tag;    // several ranks: only when group masks are not uniform
+  std::vector<std::pair<int, int>> host_index;     // one rank: (tag, host index), sorted; host order is kept
+  std::vector<double> hx, hv, hf;                   // staging for the order-preserving sync
+  std::vector<int> htype, htag, himage;
 
   void fail();
   void check_supported();
   void device_setup();
+  void push_topology();
   void publish_tallies();
   void sync_host();
 };

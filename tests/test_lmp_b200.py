@@ -157,6 +157,50 @@ def test_in_eam_32000_matches_reference_log():
     np.testing.assert_allclose(rows[:, 1:], ref, rtol=6e-8, atol=1e-12)  # 8 printed digits
 
 
+IN_CHAIN = """
+units           lj
+atom_style      bond
+special_bonds   fene
+read_data       {data}
+neighbor        0.4 bin
+neigh_modify    every 1 delay 1
+bond_style      fene
+bond_coeff      1 30.0 1.5 1.0 1.0
+pair_style      lj/cut 1.12
+pair_modify     shift yes
+pair_coeff      1 1 1.0 1.0 1.12
+fix             1 all nve
+thermo_modify   format float %.15g
+thermo          20
+timestep        0.012
+run             60
+run             20
+"""
+
+
+@pytest.mark.gpu
+def test_in_chain_matches_reference_executable():
+    """bench/in.chain without `fix langevin` (its RNG stream depends on the host's atom order):
+    atom_style bond, special_bonds fene, bond_style fene/b200 + lj/cut/b200 through lmp_b200.
+    Two `run`s: the second re-uploads atoms and topology from the host arrays the first left."""
+    have_gpu_binary()
+    data = os.path.join(ROOT, "oracle", "_ref", "data", "data.chain")
+    if not (os.path.exists(LMP_REF) and os.path.exists(data)):
+        pytest.skip("oracle/_ref not built")
+    script = IN_CHAIN.format(data=data)
+    rc, out = run_lmp(LMP_B200, script, ("-sf", "b200"))
+    assert rc == 0, out[-2000:]
+    rc2, ref = run_lmp(LMP_REF, script)
+    assert rc2 == 0, ref[-2000:]
+    a, b = thermo_rows(out), thermo_rows(ref)
+    assert a.shape == b.shape == (6, 6)
+    np.testing.assert_allclose(a, b, rtol=1e-8, atol=1e-10)
+    # step 0 as printed in the reference's log (bench/log.6Oct16.chain.fixed.icc.1)
+    np.testing.assert_allclose(a[0, 1:], [0.97029772, 0.44484087, 20.494523, 22.394765, 4.6721833], rtol=6e-8)
+    ma, mb = (re.findall(r"Neighbor list builds = (\d+)", t) for t in (out, ref))
+    assert ma == mb and len(ma) == 2
+
+
 @pytest.mark.gpu
 def test_unsupported_setups_fail_loudly():
     """no silent host fallback: a fix the device loop does not cover is an error"""
