@@ -222,6 +222,23 @@ int b200md_bond_compute(b200md_ctx *ctx, int eflag, int vflag, double *energy, d
 /* This rank's Bond::energy and Bond::virial[6] (src/bond.h:32-33) of the last tallied evaluation. */
 int b200md_bond_tallies(b200md_ctx *ctx, double *energy, double virial[6]);
 
+/* ---- per-atom energy / virial (output steps) -------------------------------------------- */
+
+#define B200MD_PERATOM_PAIR 1 /* force->pair->eatom / vatom */
+#define B200MD_PERATOM_BOND 2 /* force->bond->eatom / vatom */
+/* The eflag_atom / vflag_atom tallies of Pair::ev_tally (src/pair.cpp:1036-1040, 1078-1097),
+ * PairEAM's eatom[i] += phi (src/MANYBODY/pair_eam.cpp:245) and Bond::ev_tally
+ * (src/bond.cpp:186-192, 234-251), summed over the styles selected by `which` and with ghost
+ * contributions already returned to their owners — i.e. what ComputePEAtom::compute_peratom
+ * (src/compute_pe_atom.cpp:92-170) leaves in `energy[]` and ComputeStressAtom::compute_peratom
+ * (src/compute_stress_atom.cpp:140-240) in `stress[][]` BEFORE its kinetic term and its
+ * -nktv2p factor.  Evaluated on the device for the current positions and neighbor list; the
+ * forces must be current (after b200md_setup, b200md_run or b200md_pair_compute at these
+ * positions: EAM reuses their rho / fp).  Forces and global tallies are not touched.
+ * eatom: host [nlocal] or NULL; vatom: host [nlocal][6] (xx yy zz xy xz yz) or NULL; rows in
+ * the device's local order, the order b200md_get_atoms returns. */
+int b200md_peratom(b200md_ctx *ctx, int eflag_atom, int vflag_atom, int which, double *eatom, double *vatom);
+
 /* ---- fix nve + thermo ---------------------------------------------------------------- */
 
 /* FixNVE::initial_integrate / final_integrate (src/fix_nve.cpp:64-141). dtf = 0.5*dt*ftm2v. */

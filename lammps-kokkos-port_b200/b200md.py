@@ -17,6 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("B200MD_LIB", os.path.join(_HERE, "libb200md.so"))
 
 LIST_FULL, LIST_HALF_NEWTON = 0, 1
+PERATOM_PAIR, PERATOM_BOND = 1, 2
 MAXSWAP = 64
 
 
@@ -218,6 +219,7 @@ class Context:
         type_ = _i(type_); tag = _i(tag)
         mass = _d(mass)
         self.ntypes = mass.shape[0] - 1
+        self.mass = mass.copy()
         image = _i(image) if image is not None else None
         _chk(self.L.b200md_set_atoms(self.h, n, _p(x), _p(v), _p(type_), _p(tag), _p(image), self.ntypes, _p(mass)))
 
@@ -342,6 +344,30 @@ class Context:
         e = C.c_double(); vir = (C.c_double * 6)()
         _chk(self.L.b200md_pair_tallies(self.h, C.byref(e), vir))
         return e.value, list(vir)
+
+    def peratom(self, eflag_atom=1, vflag_atom=1, which=PERATOM_PAIR | PERATOM_BOND):
+        """(eatom[nlocal], vatom[nlocal,6]) of the current configuration in get_atoms() order: what
+        `compute pe/atom` holds, and `compute stress/atom` before its kinetic term and -nktv2p factor
+        (src/compute_pe_atom.cpp:92-170, src/compute_stress_atom.cpp:140-240); None for a part not asked for"""
+        n, _ = self.nlocal()
+        e = np.zeros(n) if eflag_atom else None
+        v = np.zeros((n, 6)) if vflag_atom else None
+        _chk(self.L.b200md_peratom(self.h, int(eflag_atom), int(vflag_atom), int(which),
+                                   _p(e) if eflag_atom else None, _p(v) if vflag_atom else None))
+        return e, v
+
+    def stress_atom(self, ke=True, which=PERATOM_PAIR | PERATOM_BOND):
+        """`compute stress/atom NULL [virial]` (src/compute_stress_atom.cpp:255-340): -(m v v + W) * nktv2p, tag order"""
+        _, w = self.peratom(0, 1, which)
+        a = self.get_atoms(("tag", "v", "type"))
+        if ke:
+            m = self.mass[a["type"]][:, None] * self.units["mvv2e"]
+            v = a["v"]
+            w = w + m * np.stack([v[:, 0] * v[:, 0], v[:, 1] * v[:, 1], v[:, 2] * v[:, 2],
+                                  v[:, 0] * v[:, 1], v[:, 0] * v[:, 2], v[:, 1] * v[:, 2]], axis=1)
+        out = np.empty_like(w)
+        out[a["tag"] - 1] = -self.units["nktv2p"] * w
+        return out
 
     # fix nve / thermo / loop
     def nve_initial(self, dtv, dtf):

@@ -87,6 +87,7 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
   comm_free(c);
   pair_eam_free(c);
   topo_free(c);
+  peratom_free(c);
   void *ptrs[] = {c->xq, c->xq_tmp, c->cell_xq, c->v, c->v_tmp, c->f, c->xhold, c->tag, c->tag_tmp, c->image,
                   c->image_tmp, c->mass, c->cutneighsq, c->atom_bin, c->cell_count, c->cell_start, c->cell_fill,
                   c->cell_atoms, c->perm, c->scan_block, c->row_off, c->row_sx, c->row_flag, c->neigh, c->numneigh,
@@ -549,6 +550,26 @@ extern "C" int b200md_bond_tallies(b200md_ctx *c, double *energy, double virial[
   NEED(c->ev_valid, "Energy was not tallied on needed timestep");
   if (energy) *energy = c->topo.eng_bond;
   if (virial) for (int k = 0; k < 6; k++) virial[k] = c->topo.virial_bond[k];
+  return B200MD_OK;
+}
+
+// per-atom energy / virial of the current configuration (peratom.cu)
+extern "C" int b200md_peratom(b200md_ctx *c, int eflag_atom, int vflag_atom, int which, double *eatom, double *vatom) {
+  NEED(c && c->neigh_configured && c->nbuilds > 0, "b200md: per-atom tallies before setup");
+  NEED(which & (B200MD_PERATOM_PAIR | B200MD_PERATOM_BOND), "b200md: nothing selected for the per-atom tallies");
+  NEED(!(eflag_atom && !eatom) && !(vflag_atom && !vatom), "b200md: null output for a requested per-atom tally");
+  CUDA_TRY(cudaSetDevice(c->device));
+  TRY(peratom_compute(c, eflag_atom, vflag_atom, which));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  const size_t n = (size_t)c->nlocal;
+  if (eflag_atom && n) CUDA_TRY(cudaMemcpy(eatom, c->peratom, sizeof(double) * n, cudaMemcpyDeviceToHost));
+  if (vflag_atom && n) {
+    std::vector<double> col(n);
+    for (int k = 0; k < 6; k++) {
+      CUDA_TRY(cudaMemcpy(col.data(), c->peratom + (size_t)(k + 1) * c->nmax, sizeof(double) * n, cudaMemcpyDeviceToHost));
+      for (size_t i = 0; i < n; i++) vatom[i * 6 + k] = col[i];
+    }
+  }
   return B200MD_OK;
 }
 

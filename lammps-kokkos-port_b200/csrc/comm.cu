@@ -697,6 +697,10 @@ int comm_reverse_force(b200md_ctx *c) {
 }
 int comm_reverse_scalar(b200md_ctx *c, double *arr) {
   if (c->list_kind == B200MD_LIST_FULL) return B200MD_OK;
+  return comm_reverse_column(c, arr);
+}
+// ghost rows of one per-atom column summed into their owners, whatever the list kind
+int comm_reverse_column(b200md_ctx *c, double *arr) {
   if (c->all_self) {
     if (c->nghost == 0) return B200MD_OK;
     k_reverse_flat<1><<<nblk(c->nghost), 256, 0, c->stream>>>(c->nghost, c->nlocal, c->nmax, arr, c->ghost_src);

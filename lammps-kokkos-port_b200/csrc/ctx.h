@@ -40,6 +40,14 @@ struct EamTables {
   double *scale = nullptr;  // [(ntypes+1)^2]
 };
 
+// kernel-argument view of EamTables (pair_eam.cu, peratom.cu)
+struct EamParams {
+  int ntypes, nrho, nr;
+  double rdr, rdrho, rhomax, cutforcesq, scale11;
+  const double *frho, *rhoA, *z2rV, *tabC, *scale;
+  const int *type2frho, *type2rhor, *type2z2r;
+};
+
 // molecular topology keyed by atom tag (bond.cu); CSR offsets are [natoms+2], row t = tag t
 struct Topology {
   bool molecular = false;
@@ -144,6 +152,8 @@ struct b200md_ctx {
   EamTables eam;
   Topology topo;
   double *rho = nullptr, *fp = nullptr;  // [nmax]
+  double *peratom = nullptr;             // [7][peratom_cap] eatom, vatom xx yy zz xy xz yz (peratom.cu; output steps only)
+  int peratom_cap = 0;
   // reductions
   double *partials = nullptr;  // device [npartial_blocks*8]
   int partial_cap = 0;
@@ -199,6 +209,7 @@ int comm_forward_scalar(b200md_ctx *c, double *arr);  // EAM fp
 int comm_reverse_force(b200md_ctx *c);
 int comm_reverse_scalar(b200md_ctx *c, double *arr);  // EAM rho (half lists)
 int comm_reverse_rho(b200md_ctx *c);
+int comm_reverse_column(b200md_ctx *c, double *arr);  // like _scalar, also on full lists (per-atom bond tallies)
 int comm_allreduce_sum(b200md_ctx *c, double *hostvals, int n);
 int comm_allreduce_max_int(b200md_ctx *c, int *hostval);
 void comm_free(b200md_ctx *c);
@@ -209,6 +220,10 @@ int pair_eam_launch(b200md_ctx *c, bool ev, int pass, const int *tiles, int ntl)
 int pair_eam_fp_comm(b200md_ctx *c);
 int pair_eam_embed(b200md_ctx *c, bool ev, double *e_embed);  // half-list path: F(rho), F'(rho) of owned atoms
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag);
+EamParams pair_eam_params(const b200md_ctx *c);
+// peratom.cu
+int peratom_compute(b200md_ctx *c, int eflag_atom, int vflag_atom, int which);
+void peratom_free(b200md_ctx *c);
 // bond.cu
 void topo_free(b200md_ctx *c);
 int topo_set(b200md_ctx *c, long long natoms, const int *bond_off, const int *bond_partner, const int *bond_type,

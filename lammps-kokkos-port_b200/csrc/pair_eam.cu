@@ -101,13 +101,6 @@ int pair_eam_config_impl(b200md_ctx *c, int ntypes, int nrho, int nr, double rdr
 
 constexpr int kRhoUnroll = EAM_RHO_UNROLL, kForceUnroll = EAM_FORCE_UNROLL;
 
-struct EamParams {
-  int ntypes, nrho, nr;
-  double rdr, rdrho, rhomax, cutforcesq, scale11;
-  const double *frho, *rhoA, *z2rV, *tabC, *scale;
-  const int *type2frho, *type2rhor, *type2z2r;
-};
-
 __device__ __forceinline__ double4 ld4(const double *p) {
 #if defined(B200MD_LD256)
   return ld_xq(reinterpret_cast<const double4 *>(p));   // one 256-bit load per 32-byte table row
@@ -440,6 +433,12 @@ static int launch_tpa(b200md_ctx *c, const EamLaunch &L, bool ev, int pass, cons
   return ev ? launch_mode<TPA, true>(c, L, pass, tiles, ntl) : launch_mode<TPA, false>(c, L, pass, tiles, ntl);
 }
 
+EamParams pair_eam_params(const b200md_ctx *c) {
+  const EamTables &e = c->eam;
+  return {e.ntypes, e.nrho, e.nr, e.rdr, e.rdrho, e.rhomax, e.cutforcesq, e.scale11, e.frho, e.rhoA, e.z2rV,
+          e.tabC, e.scale, e.type2frho, e.type2rhor, e.type2z2r};
+}
+
 static int eam_prepare(b200md_ctx *c, EamLaunch &L) {
   EamTables &e = c->eam;
   if (e.one && e.xfp_cap < c->nmax) {
@@ -447,8 +446,7 @@ static int eam_prepare(b200md_ctx *c, EamLaunch &L) {
     CUDA_TRY(cudaMalloc(&e.xfp, sizeof(double4) * (size_t)c->nmax));
     e.xfp_cap = c->nmax;
   }
-  L.P = {e.ntypes, e.nrho, e.nr, e.rdr, e.rdrho, e.rhomax, e.cutforcesq, e.scale11, e.frho, e.rhoA, e.z2rV,
-         e.tabC, e.scale, e.type2frho, e.type2rhor, e.type2z2r};
+  L.P = pair_eam_params(c);
   L.smem = (size_t)(e.nr + 1) * 8 * sizeof(double);
   // measured on B200 (2.05 M atoms, Cu_u3): tabC through L1 752 Matom-steps/s, staged in shared
   // memory 681 (bank conflicts on the random rows + lower occupancy) -> global is the default

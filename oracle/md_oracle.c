@@ -69,6 +69,9 @@ typedef struct {
   double *fene_k, *fene_r0, *fene_eps, *fene_sigma;
   double eng_bond, virial_bond[6];
   int bond_error;
+  /* per-atom tallies (Pair::ev_tally / Bond::ev_tally eflag_atom, vflag_atom branches) */
+  int eflag_atom, vflag_atom;
+  double *eatom, *vatom; /* [nmax], [nmax][6] pair + bond, as compute pe/atom / stress/atom sum them */
   long step;
 } ora_sim;
 
@@ -94,6 +97,8 @@ static void grow(ora_sim *s, int need) {
   s->firstoff = realloc(s->firstoff, sizeof(int) * n);
   s->rho = realloc(s->rho, sizeof(double) * n);
   s->fp = realloc(s->fp, sizeof(double) * n);
+  s->eatom = realloc(s->eatom, sizeof(double) * n);
+  s->vatom = realloc(s->vatom, sizeof(double) * 6 * n);
   s->nmax = n;
 }
 
@@ -120,7 +125,7 @@ ora_sim *ora_create(const double *boxlo, const double *boxhi, int n, const doubl
 void ora_destroy(ora_sim *s) {
   if (!s) return;
   free(s->x); free(s->v); free(s->f); free(s->xhold); free(s->type); free(s->tag); free(s->image); free(s->owner);
-  free(s->bins); free(s->atom2bin); free(s->numneigh); free(s->firstoff); free(s->rho); free(s->fp); free(s->mass);
+  free(s->bins); free(s->atom2bin); free(s->numneigh); free(s->firstoff); free(s->rho); free(s->fp); free(s->eatom); free(s->vatom); free(s->mass);
   free(s->cutneighsq); free(s->binhead); free(s->stencil); free(s->neigh);
   for (int k = 0; k < MAXSWAP; k++) free(s->sendlist[k]);
   free(s->cutsq); free(s->lj1); free(s->lj2); free(s->lj3); free(s->lj4); free(s->offset);
@@ -479,6 +484,18 @@ static void virial_fdotr(ora_sim *s) {
   }
 }
 
+/* eflag_atom / vflag_atom branches of Pair::ev_tally (pair.cpp:1036-1040, 1078-1097) and of
+ * Bond::ev_tally (bond.cpp:186-192, 234-251) with newton on: half of the pair's energy and of
+ * v = del (x) del * fpair to each of the two atoms, ghosts included (reverse-communicated later) */
+static void tally_atom(ora_sim *s, int i, int j, double e, double fpair, double delx, double dely, double delz) {
+  if (s->eflag_atom) { s->eatom[i] += 0.5 * e; s->eatom[j] += 0.5 * e; }
+  if (s->vflag_atom) {
+    double v[6] = {delx * delx * fpair, dely * dely * fpair, delz * delz * fpair,
+                   delx * dely * fpair, delx * delz * fpair, dely * delz * fpair};
+    for (int k = 0; k < 6; k++) { s->vatom[6 * i + k] += 0.5 * v[k]; s->vatom[6 * j + k] += 0.5 * v[k]; }
+  }
+}
+
 /* PairLJCut::compute (pair_lj_cut.cpp:69-137) on the half list with newton_pair on */
 static void compute_lj(ora_sim *s, int eflag, int vflag) {
   const int nt1 = s->ntypes + 1;
@@ -500,7 +517,9 @@ static void compute_lj(ora_sim *s, int eflag, int vflag) {
         double fpair = forcelj * r2inv;
         f[3 * i] += delx * fpair; f[3 * i + 1] += dely * fpair; f[3 * i + 2] += delz * fpair;
         f[3 * j] -= delx * fpair; f[3 * j + 1] -= dely * fpair; f[3 * j + 2] -= delz * fpair;
-        if (eflag) s->eng_vdwl += r6inv * (s->lj3[ij] * r6inv - s->lj4[ij]) - s->offset[ij];
+        double evdwl = r6inv * (s->lj3[ij] * r6inv - s->lj4[ij]) - s->offset[ij];
+        if (eflag) s->eng_vdwl += evdwl;
+        if (s->eflag_atom || s->vflag_atom) tally_atom(s, i, j, evdwl, fpair, delx, dely, delz);
       }
     }
   }
@@ -550,6 +569,7 @@ static void compute_eam(ora_sim *s, int eflag, int vflag) {
       if (rho[i] > s->rhomax) phi += fp[i] * (rho[i] - s->rhomax);
       phi *= s->scale[s->type[i] * nt1 + s->type[i]];
       s->eng_vdwl += phi;
+      if (s->eflag_atom) s->eatom[i] += phi; /* pair_eam.cpp:245 */
     }
   }
   forward_comm_scalar(s, fp); /* :251 */
@@ -584,6 +604,7 @@ static void compute_eam(ora_sim *s, int eflag, int vflag) {
         f[3 * i] += delx * fpair; f[3 * i + 1] += dely * fpair; f[3 * i + 2] += delz * fpair;
         f[3 * j] -= delx * fpair; f[3 * j + 1] -= dely * fpair; f[3 * j + 2] -= delz * fpair;
         if (eflag) s->eng_vdwl += s->scale[itype * nt1 + jtype] * phi;
+        if (s->eflag_atom || s->vflag_atom) tally_atom(s, i, j, s->scale[itype * nt1 + jtype] * phi, fpair, delx, dely, delz);
       }
     }
   }
@@ -677,6 +698,7 @@ static void compute_fene(ora_sim *s, int eflag, int vflag) {
     s->f[3 * i1] += delx * fbond; s->f[3 * i1 + 1] += dely * fbond; s->f[3 * i1 + 2] += delz * fbond;
     s->f[3 * i2] -= delx * fbond; s->f[3 * i2 + 1] -= dely * fbond; s->f[3 * i2 + 2] -= delz * fbond;
     if (eflag) s->eng_bond += ebond;
+    if (s->eflag_atom || s->vflag_atom) tally_atom(s, i1, i2, ebond, fbond, delx, dely, delz);
     if (vflag) {
       s->virial_bond[0] += delx * delx * fbond; s->virial_bond[1] += dely * dely * fbond; s->virial_bond[2] += delz * delz * fbond;
       s->virial_bond[3] += delx * dely * fbond; s->virial_bond[4] += delx * delz * fbond; s->virial_bond[5] += dely * delz * fbond;
@@ -696,6 +718,23 @@ int ora_compute(ora_sim *s, int eflag, int vflag) {
   reverse_comm_vec(s, s->f, 3);
   return s->bond_error ? -1 : 0;
 }
+
+/* what `compute pe/atom` and `compute stress/atom NULL virial` add up and reverse-communicate
+ * (compute_pe_atom.cpp:92-170, compute_stress_atom.cpp:140-240): pair + bond per-atom energy and
+ * virial of the current configuration.  vatom is the raw sum; stress/atom prints -nktv2p * it. */
+int ora_compute_peratom(ora_sim *s, int eflag_atom, int vflag_atom) {
+  int nall = s->nlocal + s->nghost;
+  memset(s->eatom, 0, sizeof(double) * nall);
+  memset(s->vatom, 0, sizeof(double) * 6 * nall);
+  s->eflag_atom = eflag_atom; s->vflag_atom = vflag_atom;
+  int r = ora_compute(s, 1, 1);
+  s->eflag_atom = s->vflag_atom = 0;
+  reverse_comm_vec(s, s->eatom, 1);
+  reverse_comm_vec(s, s->vatom, 6);
+  return r;
+}
+double *ora_eatom(ora_sim *s) { return s->eatom; }
+double *ora_vatom(ora_sim *s) { return s->vatom; }
 
 /* FixNVE::initial_integrate / final_integrate (fix_nve.cpp:64-141) */
 static void nve_initial(ora_sim *s, double dtv, double dtf) {

@@ -52,7 +52,7 @@ class Oracle:
             build_oracle()
         L = self.L = C.CDLL(ORACLE_SO)
         L.ora_create.restype = C.c_void_p
-        for fn in ("ora_x", "ora_v", "ora_f", "ora_tag", "ora_type", "ora_image", "ora_numneigh"):
+        for fn in ("ora_x", "ora_v", "ora_f", "ora_tag", "ora_type", "ora_image", "ora_numneigh", "ora_eatom", "ora_vatom"):
             getattr(L, fn).restype = C.c_void_p
         L.ora_neigh_total.restype = C.c_long
         x = _d(x); self.n = x.shape[0]
@@ -106,6 +106,14 @@ class Oracle:
     def compute(self, eflag=1, vflag=1):
         if self.L.ora_compute(self.h, eflag, vflag):
             raise RuntimeError("oracle: compute needs the half list and a pair style")
+
+    def peratom(self, eflag_atom=1, vflag_atom=1):
+        """(eatom[nlocal], vatom[nlocal,6]) pair + bond, local order (see atoms()["tag"]); vatom is the
+        raw virial sum: `compute stress/atom NULL virial` prints -nktv2p * vatom"""
+        if self.L.ora_compute_peratom(self.h, eflag_atom, vflag_atom):
+            raise RuntimeError("oracle: per-atom compute failed")
+        n = self.L.ora_nlocal(self.h)
+        return self._arr("ora_eatom", (n,), np.float64), self._arr("ora_vatom", (n, 6), np.float64)
 
     def setup(self):
         if self.L.ora_setup(self.h):
