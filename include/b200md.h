@@ -23,6 +23,7 @@
 
 #include <stddef.h>
 
+#include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -238,6 +239,52 @@ int b200md_bond_tallies(b200md_ctx *ctx, double *energy, double virial[6]);
  * eatom: host [nlocal] or NULL; vatom: host [nlocal][6] (xx yy zz xy xz yz) or NULL; rows in
  * the device's local order, the order b200md_get_atoms returns. */
 int b200md_peratom(b200md_ctx *ctx, int eflag_atom, int vflag_atom, int which, double *eatom, double *vatom);
+
+/* ---- fix langevin ---------------------------------------------------------------------- */
+
+/* `fix ID all langevin Tstart Tstop damp seed [scale type ratio ...]` (src/fix_langevin.cpp:60-150,
+ * defaults tally no / zero no / gjf no).  After every force evaluation — the set-up one included,
+ * FixLangevin::setup :360-361 — each owned atom gets f += gamma1 v + gamma2 (u - 0.5) with
+ * gamma1 = -m/damp/ftm2v/ratio, gamma2 = sqrt(m) sqrt(24 boltz/damp/dt/mvv2e)/ftm2v/sqrt(ratio)
+ * sqrt(T_target) (init :286-298, post_force_templated :636-713) and T_target ramped from Tstart
+ * to Tstop over the run (compute_target :773-787; the window is the nsteps of each b200md_run
+ * unless b200md_fix_langevin_window is used).  u are RanMars::uniform() draws
+ * (src/random_mars.cpp:78-95), three per atom in the HOST's local atom order: the order of the
+ * last b200md_set_atoms call, which a caller that wants the reference's numbers makes in
+ * Atom::sort order (b200md_atom_sort_order).  The device reproduces the serial stream exactly:
+ * each step's 3*nlocal draws are generated in parallel chunks by jump-ahead of the generator's
+ * linear recurrence.  One rank only (the reference seeds rank r with seed + r and draws in that
+ * rank's local order, which no other decomposition can replay); refused otherwise.
+ * ratio: [ntypes+1] or NULL (all 1); dt: the timestep of the set-up evaluation (update->dt at
+ * FixLangevin::init; b200md_run takes over its own dt like FixLangevin::reset_dt).
+ * Call after b200md_set_atoms and before b200md_setup. */
+int b200md_fix_langevin(b200md_ctx *ctx, double t_start, double t_stop, double t_period, int seed,
+                        const double *ratio, double dt);
+/* Update::beginstep / endstep of the enclosing `run` and the current timestep, for callers that
+ * split one run into several b200md_run calls (verlet/b200 stops at output steps).  endstep ==
+ * beginstep switches back to "every b200md_run is its own window". */
+int b200md_fix_langevin_window(b200md_ctx *ctx, long long ntimestep, long long beginstep, long long endstep);
+/* `unfix`: stop applying it. */
+int b200md_fix_langevin_off(b200md_ctx *ctx);
+
+/* ---- RanMars stream, Atom::sort order (host-side helpers, no GPU needed) ------------------ */
+
+#define B200MD_RANMARS_LAG 97
+/* State of RanMars(seed) right after construction (src/random_mars.cpp:30-72), in integer form:
+ * the 97 most recent lagged-Fibonacci values in units of 2^-24, oldest first. */
+int b200md_ranmars_state(int seed, uint32_t state[B200MD_RANMARS_LAG]);
+/* The state k draws later (x^k mod x^97 + x^64 - 1 over Z/2^24 applied to `state`). */
+int b200md_ranmars_jump(const uint32_t state[B200MD_RANMARS_LAG], long long k, uint32_t out[B200MD_RANMARS_LAG]);
+/* `count` consecutive RanMars::uniform() values from `state`; position = number of draws made
+ * before it (1 right after construction), needed for the generator's arithmetic sequence c. */
+int b200md_ranmars_draws(const uint32_t state[B200MD_RANMARS_LAG], long long position, int count, double *out);
+/* Device generator check: `fills` consecutive fills of n draws each, exactly as fix langevin
+ * requests them per force evaluation; out: host [fills*n]. */
+int b200md_ranmars_device_stream(b200md_ctx *ctx, int seed, int n, int fills, double *out);
+/* Atom::sort's permutation (src/atom.cpp:2246-2349, bins of cutneighmax/2 over the sub-box,
+ * stable): new atom I = old atom permute[I].  x: [n][3] wrapped positions. */
+int b200md_atom_sort_order(int n, const double *x, const double sublo[3], const double subhi[3],
+                           double cutneighmax, int *permute);
 
 /* ---- fix nve + thermo ---------------------------------------------------------------- */
 

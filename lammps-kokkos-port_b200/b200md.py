@@ -129,6 +129,35 @@ def comm_schedule(boxlo, boxhi, periodic, grid, myloc, cutghost):
     return s
 
 
+def atom_sort_order(x, sublo, subhi, cutneighmax):
+    """Atom::sort's permutation (src/atom.cpp:2246-2349): new atom I = old atom perm[I]"""
+    x = _d(x)
+    perm = np.empty(x.shape[0], np.int32)
+    _chk(lib().b200md_atom_sort_order(int(x.shape[0]), _p(x), _d3(sublo), _d3(subhi), C.c_double(cutneighmax), _p(perm)))
+    return perm
+
+
+def ranmars_state(seed):
+    """RanMars(seed) after construction, integer form (src/random_mars.cpp:30-72): uint32[97]"""
+    st = np.zeros(97, np.uint32)
+    _chk(lib().b200md_ranmars_state(int(seed), _p(st)))
+    return st
+
+
+def ranmars_jump(state, k):
+    st = np.ascontiguousarray(state, np.uint32)
+    out = np.zeros(97, np.uint32)
+    _chk(lib().b200md_ranmars_jump(_p(st), C.c_longlong(int(k)), _p(out)))
+    return out
+
+
+def ranmars_draws(state, position, count):
+    st = np.ascontiguousarray(state, np.uint32)
+    out = np.empty(count, np.float64)
+    _chk(lib().b200md_ranmars_draws(_p(st), C.c_longlong(int(position)), int(count), _p(out)))
+    return out
+
+
 def bin_setup(boxlo, boxhi, sublo, subhi, cutghost, cutneighmax):
     g = BinGeometry()
     _chk(lib().b200md_bin_setup(_d3(boxlo), _d3(boxhi), _d3(sublo), _d3(subhi), C.c_double(cutghost),
@@ -355,6 +384,25 @@ class Context:
         _chk(self.L.b200md_peratom(self.h, int(eflag_atom), int(vflag_atom), int(which),
                                    _p(e) if eflag_atom else None, _p(v) if vflag_atom else None))
         return e, v
+
+    def fix_langevin(self, t_start, t_stop, t_period, seed, dt, ratio=None):
+        """fix langevin Tstart Tstop damp seed [scale ...] (src/fix_langevin.cpp); call after set_atoms —
+        the RanMars draws follow the order of that call — and before setup"""
+        r = _d(ratio) if ratio is not None else None
+        _chk(self.L.b200md_fix_langevin(self.h, C.c_double(t_start), C.c_double(t_stop), C.c_double(t_period),
+                                        int(seed), _p(r), C.c_double(dt)))
+
+    def fix_langevin_window(self, ntimestep, beginstep, endstep):
+        _chk(self.L.b200md_fix_langevin_window(self.h, C.c_longlong(ntimestep), C.c_longlong(beginstep), C.c_longlong(endstep)))
+
+    def fix_langevin_off(self):
+        _chk(self.L.b200md_fix_langevin_off(self.h))
+
+    def ranmars_stream(self, seed, n, fills=1):
+        """`fills` consecutive device fills of n RanMars draws (the per-evaluation request of fix langevin)"""
+        out = np.empty(n * fills, np.float64)
+        _chk(self.L.b200md_ranmars_device_stream(self.h, int(seed), int(n), int(fills), _p(out)))
+        return out
 
     def stress_atom(self, ke=True, which=PERATOM_PAIR | PERATOM_BOND):
         """`compute stress/atom NULL [virial]` (src/compute_stress_atom.cpp:255-340): -(m v v + W) * nktv2p, tag order"""

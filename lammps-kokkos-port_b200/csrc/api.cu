@@ -88,6 +88,7 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
   pair_eam_free(c);
   topo_free(c);
   peratom_free(c);
+  langevin_free(c);
   void *ptrs[] = {c->xq, c->xq_tmp, c->cell_xq, c->v, c->v_tmp, c->f, c->xhold, c->tag, c->tag_tmp, c->image,
                   c->image_tmp, c->mass, c->cutneighsq, c->atom_bin, c->cell_count, c->cell_start, c->cell_fill,
                   c->cell_atoms, c->perm, c->scan_block, c->row_off, c->row_sx, c->row_flag, c->neigh, c->numneigh,
@@ -206,6 +207,8 @@ extern "C" int b200md_set_atoms(b200md_ctx *c, int nlocal, const double *x, cons
   TRY(comm_allreduce_sum(c, &nat, 1));
   c->natoms_global = nat;
   c->ago = 0; c->step = 0; c->ev_valid = false;
+  c->host_order = true;
+  if (c->lang.on) TRY(langevin_rank_from_host_order(c));   // the stream follows the new host order
   return B200MD_OK;
 }
 
@@ -366,6 +369,7 @@ extern "C" int b200md_neigh_build(b200md_ctx *c) {
   CUDA_TRY(cudaSetDevice(c->device));
   TRY(neigh_pbc(c));
   TRY(comm_exchange(c));
+  c->host_order = false;
   TRY(neigh_sort_owned(c));
   TRY(comm_borders(c));
   TRY(neigh_bin_all(c));
@@ -574,6 +578,35 @@ extern "C" int b200md_peratom(b200md_ctx *c, int eflag_atom, int vflag_atom, int
 }
 
 // ---------------------------------------------------------------------------------------
+// fix langevin (langevin.cu)
+// ---------------------------------------------------------------------------------------
+extern "C" int b200md_fix_langevin(b200md_ctx *c, double t_start, double t_stop, double t_period, int seed,
+                                   const double *ratio, double dt) {
+  NEED(c, "b200md: null context");
+  CUDA_TRY(cudaSetDevice(c->device));
+  return langevin_config(c, t_start, t_stop, t_period, seed, ratio, dt);
+}
+extern "C" int b200md_fix_langevin_window(b200md_ctx *c, long long ntimestep, long long beginstep, long long endstep) {
+  NEED(c && c->lang.on, "b200md: fix langevin is not set");
+  NEED(endstep >= beginstep && ntimestep >= beginstep && (ntimestep <= endstep || endstep == beginstep),
+       "b200md: bad fix langevin window");
+  Langevin &L = c->lang;
+  L.window = endstep > beginstep;
+  L.begin = beginstep; L.end = endstep; L.now = ntimestep;
+  return B200MD_OK;
+}
+extern "C" int b200md_fix_langevin_off(b200md_ctx *c) {
+  NEED(c, "b200md: null context");
+  c->lang.on = false;
+  return B200MD_OK;
+}
+extern "C" int b200md_ranmars_device_stream(b200md_ctx *c, int seed, int n, int fills, double *out) {
+  NEED(c && n >= 0 && fills >= 0 && (out || !n || !fills), "b200md: bad ranmars_device_stream arguments");
+  CUDA_TRY(cudaSetDevice(c->device));
+  return langevin_test_stream(c, seed, n, fills, out);
+}
+
+// ---------------------------------------------------------------------------------------
 // fix nve, thermo
 // ---------------------------------------------------------------------------------------
 extern "C" int b200md_nve_initial(b200md_ctx *c, double dtv, double dtf) {
@@ -623,6 +656,11 @@ extern "C" int b200md_setup(b200md_ctx *c) {
   TRY(b200md_pair_compute(c, 1, 1, nullptr, nullptr));
   TRY(bond_compute(c, 1, 1));
   TRY(b200md_reverse_comm(c));
+  if (c->lang.on) {   // Modify::setup -> FixLangevin::setup -> post_force on the set-up forces
+    Langevin &L = c->lang;
+    if (!L.window) L.begin = L.end = L.now = c->step;
+    TRY(langevin_post_force(c, false, 0.0));
+  }
   return B200MD_OK;
 }
 
@@ -733,9 +771,15 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
   PhaseTimer T{c, pt && pt[0] == '1', &ev_used};
   const long long launches0 = c->launches, pl0 = c->pair_launches, nb0 = c->nbuilds;
   PhaseTimer TT{c, true, &ev_used};
+  Langevin &LG = c->lang;
+  if (LG.on) {
+    TRY(langevin_set_dt(c, dt));   // FixLangevin::reset_dt
+    if (!LG.window) { LG.begin = first; LG.end = last; LG.now = first; }
+  }
   TT.begin(0);
   for (int i = 0; i < nsteps; i++) {
     c->step++;
+    LG.now++;
     // Integrate::ev_set: energy/virial only on thermo output steps
     const bool out_step = (thermo_every > 0 && (c->step - first) % thermo_every == 0) || c->step == last;
     const int ev = out_step ? 1 : 0;
@@ -750,7 +794,8 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
       T.begin(1); TRY(b200md_pair_compute(c, ev, ev, nullptr, nullptr)); TRY(bond_compute(c, ev, ev)); T.end();
       T.begin(3); TRY(comm_reverse_force(c)); T.end();
     }
-    T.begin(4); TRY(nve_final(c, dtf)); T.end();
+    // Modify::post_force (fix langevin) fused with FixNVE::final_integrate when the thermostat is on
+    T.begin(4); if (LG.on) TRY(langevin_post_force(c, true, dtf)); else TRY(nve_final(c, dtf)); T.end();
     if (out_step && thermo_out && nth < max_thermo) { TRY(b200md_thermo_compute(c, &thermo_out[nth])); nth++; }
   }
   TT.end();

@@ -62,6 +62,25 @@ struct Topology {
   double eng_bond = 0, virial_bond[6] = {0, 0, 0, 0, 0, 0};
 };
 
+// fix langevin + the device RanMars stream (langevin.cu)
+struct Langevin {
+  bool on = false;
+  double t_start = 0, t_stop = 0, t_period = 0, dt = 0;
+  std::vector<double> ratio;       // [ntypes+1]
+  bool window = false;             // begin/end/now set by the caller (b200md_fix_langevin_window)
+  long long begin = 0, end = 0, now = 0;
+  uint32_t *state[2] = {nullptr, nullptr};  // device [97]: generator state before / after a fill
+  int cur = 0;
+  long long position = 0;          // draws made so far
+  uint32_t *jumpT = nullptr;       // device [24][97][97] transposed jump tables
+  uint32_t *rnd = nullptr;         // device [rnd_cap] this evaluation's draws, 24-bit integers
+  int rnd_cap = 0;
+  int *rank_by_tag = nullptr;      // device [maxtag+1] host-order index of a tag
+  int nrank = 0;
+  double *gfac = nullptr;          // device [ntypes+1][2] gfactor1, gfactor2
+  int gfac_n = 0;
+};
+
 struct Swap {
   int dim, ineed, sendflag, sendproc, recvproc;
   int pbc[3];
@@ -151,6 +170,8 @@ struct b200md_ctx {
   double cutforcemax = 0;
   EamTables eam;
   Topology topo;
+  Langevin lang;
+  bool host_order = false;   // owned atoms are still in the order of the last b200md_set_atoms
   double *rho = nullptr, *fp = nullptr;  // [nmax]
   double *peratom = nullptr;             // [7][peratom_cap] eatom, vatom xx yy zz xy xz yz (peratom.cu; output steps only)
   int peratom_cap = 0;
@@ -232,6 +253,13 @@ int topo_set(b200md_ctx *c, long long natoms, const int *bond_off, const int *bo
 int bond_fene_set(b200md_ctx *c, int nbondtypes, const double *k, const double *r0, const double *eps, const double *sigma);
 int topo_build_map(b200md_ctx *c);
 int bond_compute(b200md_ctx *c, int eflag, int vflag);
+// langevin.cu
+int langevin_config(b200md_ctx *c, double t_start, double t_stop, double t_period, int seed, const double *ratio, double dt);
+int langevin_set_dt(b200md_ctx *c, double dt);
+int langevin_rank_from_host_order(b200md_ctx *c);
+int langevin_post_force(b200md_ctx *c, bool with_final, double dtf);
+int langevin_test_stream(b200md_ctx *c, int seed, int n, int fills, double *out);
+void langevin_free(b200md_ctx *c);
 // nve.cu
 int nve_initial(b200md_ctx *c, double dtv, double dtf, bool check_dist);
 int nve_final(b200md_ctx *c, double dtf);

@@ -10,8 +10,10 @@
 //   CreateAtoms::loop_lattice / Lattice::lattice2box create_atoms.cpp:1301-1370, lattice.cpp:469-486
 //   Velocity::create loop geom + RanPark             velocity.cpp:330-353, random_park.cpp:25-124
 #include <math.h>
+#include <stdint.h>
 #include <string.h>
 #include <string>
+#include <vector>
 #include "../../include/b200md.h"
 
 void b200md_set_error(const std::string &msg);
@@ -233,5 +235,159 @@ extern "C" int b200md_lattice_fcc(double scale, int nx, int ny, int nz, const do
         }
   if (n > 2147483647LL) { b200md_set_error("b200md: too many atoms for one rank"); return B200MD_ERR; }
   *natoms_out = (int)n;
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// Atom::sort — the local index order the reference's set-up leaves (atom.cpp:2246-2349 with
+// setup_sort_bins :2351-2410): bins of cutneighmax/2 over the (sub-)box, stable inside a bin.
+// The device keeps its own bin order; this order only matters to callers that must reproduce
+// order-dependent host semantics (fix langevin's RanMars draws, fix_langevin.cpp:636-662).
+// ---------------------------------------------------------------------------------------
+extern "C" int b200md_atom_sort_order(int n, const double *x, const double sublo[3], const double subhi[3],
+                                      double cutneighmax, int *permute) {
+  if (n < 0 || (n && (!x || !permute)) || !sublo || !subhi) { b200md_set_error("b200md: null argument"); return B200MD_ERR; }
+  const double binsize = 0.5 * cutneighmax;
+  int nb[3] = {1, 1, 1};
+  double binv[3] = {0, 0, 0};
+  if (binsize > 0.0) {
+    const double bininv = 1.0 / binsize;
+    for (int d = 0; d < 3; d++) {
+      nb[d] = static_cast<int>((subhi[d] - sublo[d]) * bininv);
+      if (nb[d] == 0) nb[d] = 1;
+      binv[d] = nb[d] / (subhi[d] - sublo[d]);
+    }
+  }
+  const long long nbins = (long long)nb[0] * nb[1] * nb[2];
+  if (binsize <= 0.0 || nbins == 1) {   // sorting disabled / single bin: order unchanged
+    for (int i = 0; i < n; i++) permute[i] = i;
+    return B200MD_OK;
+  }
+  std::vector<int> count(nbins + 1, 0), bin(n);
+  for (int i = 0; i < n; i++) {
+    int c[3];
+    for (int d = 0; d < 3; d++) {
+      c[d] = static_cast<int>((x[3 * (size_t)i + d] - sublo[d]) * binv[d]);
+      c[d] = c[d] < 0 ? 0 : c[d];
+      c[d] = c[d] > nb[d] - 1 ? nb[d] - 1 : c[d];
+    }
+    bin[i] = (c[2] * nb[1] + c[1]) * nb[0] + c[0];
+    count[bin[i] + 1]++;
+  }
+  for (long long b = 0; b < nbins; b++) count[b + 1] += count[b];
+  for (int i = 0; i < n; i++) permute[count[bin[i]]++] = i;   // new atom I = old atom permute[I]
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// RanMars in integer form (random_mars.cpp:30-95).  Every value the generator holds is a
+// multiple of 2^-24, so with L the lagged-Fibonacci sequence in units of 2^-24
+//     L[n+97] = L[n] - L[n+64]            (mod 2^24)         u[i97] - u[j97], lags 97 and 33
+//     c[n]    = (362436 - (n+1) 7654321)  (mod 16777213)     the arithmetic sequence `c`
+//     draw n  = ((L[n+97] - c[n]) mod 2^24) 2^-24            n = 0 is the constructor's own draw
+// The recurrence is linear, so the state k draws ahead is a polynomial in the shift operator:
+// x^k mod (x^97 + x^64 - 1) over Z/2^24 — computed here by square-and-multiply, applied on the
+// device by every block of the stream kernel to reach its own chunk (langevin.cu).
+// ---------------------------------------------------------------------------------------
+namespace {
+const int LAG = B200MD_RANMARS_LAG;
+typedef uint32_t u32;
+
+void poly_reduce(u32 *c, int top) {   // x^97 = 1 - x^64
+  for (int d = top; d >= LAG; d--) {
+    const u32 a = c[d];
+    if (!a) continue;
+    c[d] = 0;
+    c[d - LAG] += a;
+    c[d - 33] -= a;
+  }
+}
+void poly_mul(const u32 *a, const u32 *b, u32 *out) {
+  u32 c[2 * LAG];
+  memset(c, 0, sizeof(c));
+  for (int i = 0; i < LAG; i++) {
+    if (!a[i]) continue;
+    for (int j = 0; j < LAG; j++) c[i + j] += a[i] * b[j];
+  }
+  poly_reduce(c, 2 * LAG - 2);
+  memcpy(out, c, sizeof(u32) * LAG);
+}
+void poly_pow(long long k, u32 *out) {   // x^k mod P
+  u32 result[LAG], base[LAG];
+  memset(result, 0, sizeof(result)); memset(base, 0, sizeof(base));
+  result[0] = 1; base[1] = 1;
+  while (k > 0) {
+    if (k & 1) poly_mul(result, base, result);
+    k >>= 1;
+    if (k) poly_mul(base, base, base);
+  }
+  memcpy(out, result, sizeof(result));
+}
+}  // namespace
+
+// rows i = 0..96 of the jump-by-k matrix: coefficients of x^(k+i) mod P, so that
+// L[p+k+i] = sum_j M[i][j] L[p+j]  (mod 2^24; the arithmetic may run mod 2^32 and be masked at the end)
+void ranmars_jump_matrix(long long k, uint32_t *M) {
+  u32 row[LAG + 1];
+  poly_pow(k, row);
+  for (int i = 0; i < LAG; i++) {
+    memcpy(M + (size_t)i * LAG, row, sizeof(u32) * LAG);
+    // multiply by x
+    const u32 top = row[LAG - 1];
+    for (int j = LAG - 1; j > 0; j--) row[j] = row[j - 1];
+    row[0] = top;
+    row[64] -= top;
+  }
+}
+
+extern "C" int b200md_ranmars_state(int seed, uint32_t state[B200MD_RANMARS_LAG]) {
+  if (seed <= 0 || seed > 900000000) { b200md_set_error("Invalid seed for Marsaglia random # generator"); return B200MD_ERR; }
+  u32 u[LAG + 1];
+  int ij = (seed - 1) / 30082;
+  int kl = (seed - 1) - 30082 * ij;
+  int i = (ij / 177) % 177 + 2, j = ij % 177 + 2, k = (kl / 169) % 178 + 1, l = kl % 169;
+  for (int ii = 1; ii <= LAG; ii++) {
+    u32 s = 0;
+    for (int jj = 1; jj <= 24; jj++) {
+      const int m = ((i * j) % 179) * k % 179;
+      i = j; j = k; k = m;
+      l = (53 * l + 1) % 169;
+      if ((l * m) % 64 >= 32) s |= 1u << (24 - jj);   // s += 2^-jj
+    }
+    u[ii] = s;
+  }
+  // call n reads slot 97-n (n < 97): L[n] = u[97-n]; the constructor's draw moves the window to position 1
+  u32 L[LAG + 1];
+  for (int n = 0; n < LAG; n++) L[n] = u[LAG - n];
+  L[LAG] = (L[0] - L[64]) & 0xffffffu;
+  for (int n = 0; n < LAG; n++) state[n] = L[n + 1];
+  return B200MD_OK;
+}
+
+extern "C" int b200md_ranmars_jump(const uint32_t state[B200MD_RANMARS_LAG], long long k, uint32_t out[B200MD_RANMARS_LAG]) {
+  if (!state || !out || k < 0) { b200md_set_error("b200md: bad ranmars_jump arguments"); return B200MD_ERR; }
+  std::vector<u32> M((size_t)LAG * LAG);
+  ranmars_jump_matrix(k, M.data());
+  u32 r[LAG];
+  for (int i = 0; i < LAG; i++) {
+    u32 acc = 0;
+    for (int j = 0; j < LAG; j++) acc += M[(size_t)i * LAG + j] * state[j];
+    r[i] = acc & 0xffffffu;
+  }
+  memcpy(out, r, sizeof(r));
+  return B200MD_OK;
+}
+
+extern "C" int b200md_ranmars_draws(const uint32_t state[B200MD_RANMARS_LAG], long long position, int count, double *out) {
+  if (!state || position < 0 || count < 0 || (count && !out)) { b200md_set_error("b200md: bad ranmars_draws arguments"); return B200MD_ERR; }
+  std::vector<u32> L(state, state + LAG);
+  L.resize((size_t)LAG + count);
+  for (int k = 0; k < count; k++) {
+    const u32 w = (L[k] - L[k + 64]) & 0xffffffu;
+    L[(size_t)LAG + k] = w;
+    const long long n = position + k;
+    const long long cc = (362436LL + 16777213LL - ((((n + 1) % 16777213LL) * 7654321LL) % 16777213LL)) % 16777213LL;
+    out[k] = (double)((w - (u32)cc) & 0xffffffu) * (1.0 / 16777216.0);
+  }
   return B200MD_OK;
 }

@@ -1,0 +1,291 @@
+// langevin.cu — fix langevin on the device, with the reference's exact RanMars stream.
+//
+// Reference (/root/reference/src):
+//   FixLangevin::FixLangevin        fix_langevin.cpp:60-150   RanMars(seed + comm->me), ratio[]
+//   FixLangevin::init               fix_langevin.cpp:286-298  gfactor1 / gfactor2 per type
+//   FixLangevin::setup              fix_langevin.cpp:360-361  post_force on the set-up forces
+//   FixLangevin::compute_target     fix_langevin.cpp:773-787  T ramp over the run window
+//   post_force_templated<0,..,0>    fix_langevin.cpp:576-713  f += gamma1 v + gamma2 (u - 0.5),
+//                                   three draws per atom, atoms in local index order
+//   RanMars                         random_mars.cpp:30-95     lagged Fibonacci (97, 33) minus an
+//                                   arithmetic sequence, all in multiples of 2^-24
+//
+// B200 design.  The reference's thermostat is serial by construction: one generator, drawn
+// atom after atom.  Its recurrence is linear over Z/2^24, though (host.cpp, "RanMars in integer
+// form"), so the state k draws ahead is a fixed 97x97 integer matrix times the current state.
+// Each force evaluation needs the next 3*nlocal draws.  They are produced by one kernel:
+//   block m  -> start state = J^(m*CHUNK) state   (binary decomposition of m over precomputed
+//               J^(CHUNK*2^b) tables, <= 24 mat-vecs of 97x97 from L2-resident tables)
+//            -> CHUNK values in shared memory, 32 per warp iteration (lag 33 > 32, so a warp's
+//               lanes never depend on each other inside an iteration)
+//            -> subtracts c[n] in closed form and stores 24-bit integers
+//   the block that owns draw 3*nlocal also writes the generator state for the next evaluation.
+// The thermostat kernel then reads its three numbers at the atom's HOST rank (the local index
+// the reference would have drawn them at; rank_by_tag is built from the last b200md_set_atoms
+// order), so the device's own bin-sorted atom order does not matter.  In the step loop it is
+// fused with FixNVE::final_integrate: one pass over v and f instead of two.
+// Per atom-step: 12 B of random words written and read, 4 B tag, 4 B rank, plus the 96 B of the
+// v / f streams nve_final moves anyway; the generator itself is ~2 us per evaluation.
+#include "ctx.h"
+#include "util.cuh"
+
+#define RM_LAG B200MD_RANMARS_LAG
+#define RM_CHUNK 2048
+#define RM_LEVELS 24
+#define RM_THREADS 128
+#define RM_MASK 0xffffffu
+
+void ranmars_jump_matrix(long long k, uint32_t *M);   // host.cpp
+
+// c[n] of draw n (n = 0 is the constructor's own draw), in units of 2^-24
+__device__ __forceinline__ uint32_t mars_c(long long n) {
+  const long long CM = 16777213LL;
+  const long long t = (((n + 1) % CM) * 7654321LL) % CM;
+  return (uint32_t)((362436LL + CM - t) % CM);
+}
+
+// jumpT: [RM_LEVELS][97][97], level b = TRANSPOSE of the jump-by-(CHUNK*2^b) matrix, so thread i
+// reads element (j, i): consecutive threads, consecutive words
+__global__ void __launch_bounds__(RM_THREADS)
+k_ranmars_fill(const uint32_t *__restrict__ state_in, uint32_t *__restrict__ state_out,
+               const uint32_t *__restrict__ jumpT, long long position, int nnum, uint32_t *__restrict__ out) {
+  __shared__ uint32_t buf[RM_LAG + RM_CHUNK];
+  __shared__ uint32_t st[2][RM_LAG];
+  const int tid = threadIdx.x;
+  const int m = blockIdx.x;
+  int cur = 0;
+  if (tid < RM_LAG) st[0][tid] = state_in[tid];
+  __syncthreads();
+  for (int b = 0; b < RM_LEVELS; b++) {
+    if (!((m >> b) & 1)) continue;   // uniform across the block
+    if (tid < RM_LAG) {
+      const uint32_t *M = jumpT + (size_t)b * RM_LAG * RM_LAG;
+      uint32_t acc = 0;
+#pragma unroll 4
+      for (int j = 0; j < RM_LAG; j++) acc += M[j * RM_LAG + tid] * st[cur][j];
+      st[cur ^ 1][tid] = acc & RM_MASK;
+    }
+    __syncthreads();
+    cur ^= 1;
+  }
+  if (tid < RM_LAG) buf[tid] = st[cur][tid];
+  __syncthreads();
+  const int base = m * RM_CHUNK;                 // first draw of this chunk, relative to `position`
+  const int want = min(RM_CHUNK, nnum - base);   // > 0 by the grid size
+  if (tid < 32) {
+    const int iters = (want + 31) / 32;
+    for (int t = 0; t < iters; t++) {
+      const int k = 32 * t + tid;
+      buf[RM_LAG + k] = (buf[k] - buf[k + 64]) & RM_MASK;   // L[n+97] = L[n] - L[n+64]
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  for (int k = tid; k < want; k += RM_THREADS)
+    out[base + k] = (buf[RM_LAG + k] - mars_c(position + base + k)) & RM_MASK;
+  // generator state after draw position + nnum - 1
+  if (base + want == nnum && tid < RM_LAG) state_out[tid] = buf[want + tid];
+}
+
+// f += gamma1 v + gamma2 (u - 0.5)  [+ FixNVE::final_integrate when FINAL]
+template <bool FINAL>
+__global__ void k_langevin(int n, int nmax, const double4 *__restrict__ xq, double *__restrict__ v,
+                           double *__restrict__ f, const int *__restrict__ tag, const int *__restrict__ rank_by_tag,
+                           const uint32_t *__restrict__ rnd, const double *__restrict__ gfac /* [ntypes+1][2] */,
+                           const double *__restrict__ mass, double tsqrt, double dtf) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int type = xq_type(xq[i]);
+  const double gamma1 = gfac[2 * type], gamma2 = __dmul_rn(gfac[2 * type + 1], tsqrt);
+  const size_t r = (size_t)rank_by_tag[tag[i]] * 3;
+  const size_t s = (size_t)nmax;
+  double dtfm = 0.0;
+  if (FINAL) dtfm = dtf / mass[type];
+#pragma unroll
+  for (int d = 0; d < 3; d++) {
+    const double u = (double)rnd[r + d] * (1.0 / 16777216.0);
+    const double fran = __dmul_rn(gamma2, u - 0.5);
+    const double vv = v[i + d * s];
+    const double fdrag = __dmul_rn(gamma1, vv);
+    const double fn = __dadd_rn(f[i + d * s], __dadd_rn(fdrag, fran));
+    f[i + d * s] = fn;
+    if (FINAL) v[i + d * s] = __dadd_rn(vv, __dmul_rn(dtfm, fn));
+  }
+}
+
+void langevin_free(b200md_ctx *c) {
+  Langevin &L = c->lang;
+  if (L.state[0]) cudaFree(L.state[0]);
+  if (L.state[1]) cudaFree(L.state[1]);
+  if (L.jumpT) cudaFree(L.jumpT);
+  if (L.rnd) cudaFree(L.rnd);
+  if (L.rank_by_tag) cudaFree(L.rank_by_tag);
+  if (L.gfac) cudaFree(L.gfac);
+  L = Langevin();
+}
+
+static int ranmars_device_init(b200md_ctx *c, int seed) {
+  Langevin &L = c->lang;
+  uint32_t st[RM_LAG];
+  TRY(b200md_ranmars_state(seed, st));
+  if (!L.state[0]) {
+    CUDA_TRY(cudaMalloc(&L.state[0], sizeof(uint32_t) * RM_LAG));
+    CUDA_TRY(cudaMalloc(&L.state[1], sizeof(uint32_t) * RM_LAG));
+  }
+  if (!L.jumpT) {
+    // J^(CHUNK*2^b), b < LEVELS, transposed; 24 x 37 KB
+    std::vector<uint32_t> M((size_t)RM_LAG * RM_LAG), T((size_t)RM_LEVELS * RM_LAG * RM_LAG);
+    for (int b = 0; b < RM_LEVELS; b++) {
+      ranmars_jump_matrix((long long)RM_CHUNK << b, M.data());
+      uint32_t *Tb = T.data() + (size_t)b * RM_LAG * RM_LAG;
+      for (int i = 0; i < RM_LAG; i++)
+        for (int j = 0; j < RM_LAG; j++) Tb[j * RM_LAG + i] = M[(size_t)i * RM_LAG + j];
+    }
+    CUDA_TRY(cudaMalloc(&L.jumpT, sizeof(uint32_t) * T.size()));
+    CUDA_TRY(cudaMemcpy(L.jumpT, T.data(), sizeof(uint32_t) * T.size(), cudaMemcpyHostToDevice));
+  }
+  CUDA_TRY(cudaMemcpy(L.state[0], st, sizeof(st), cudaMemcpyHostToDevice));
+  L.cur = 0;
+  L.position = 1;   // the constructor drew once
+  return B200MD_OK;
+}
+
+// the next nnum draws of the stream into L.rnd (24-bit integers)
+static int ranmars_fill(b200md_ctx *c, int nnum) {
+  Langevin &L = c->lang;
+  if (nnum <= 0) return B200MD_OK;
+  if (L.rnd_cap < nnum) {
+    if (L.rnd) CUDA_TRY(cudaFree(L.rnd));
+    L.rnd_cap = nnum + nnum / 8 + 1024;
+    CUDA_TRY(cudaMalloc(&L.rnd, sizeof(uint32_t) * (size_t)L.rnd_cap));
+  }
+  const int nblocks = (nnum + RM_CHUNK - 1) / RM_CHUNK;
+  if (nblocks >= (1 << RM_LEVELS)) { b200md_set_error("b200md: fix langevin: too many atoms for one random stream"); return B200MD_ERR; }
+  k_ranmars_fill<<<nblocks, RM_THREADS, 0, c->stream>>>(L.state[L.cur], L.state[L.cur ^ 1], L.jumpT, L.position, nnum, L.rnd);
+  CUDA_TRY(cudaGetLastError());
+  c->launches++;
+  L.cur ^= 1;
+  L.position += nnum;
+  return B200MD_OK;
+}
+
+// rank_by_tag[tag] = index of the atom in the host's order (the order of the last set_atoms)
+int langevin_rank_from_host_order(b200md_ctx *c) {
+  Langevin &L = c->lang;
+  const int n = c->nlocal;
+  std::vector<int> tags(n);
+  if (n) CUDA_TRY(cudaMemcpy(tags.data(), c->tag, sizeof(int) * n, cudaMemcpyDeviceToHost));
+  int maxtag = 0;
+  for (int i = 0; i < n; i++) {
+    if (tags[i] < 1) { b200md_set_error("b200md: fix langevin requires atom IDs >= 1"); return B200MD_ERR; }
+    maxtag = tags[i] > maxtag ? tags[i] : maxtag;
+  }
+  std::vector<int> rank((size_t)maxtag + 1, -1);
+  for (int i = 0; i < n; i++) {
+    if (rank[tags[i]] >= 0) { b200md_set_error("b200md: fix langevin requires unique atom IDs"); return B200MD_ERR; }
+    rank[tags[i]] = i;
+  }
+  if (L.rank_by_tag) CUDA_TRY(cudaFree(L.rank_by_tag));
+  CUDA_TRY(cudaMalloc(&L.rank_by_tag, sizeof(int) * rank.size()));
+  CUDA_TRY(cudaMemcpy(L.rank_by_tag, rank.data(), sizeof(int) * rank.size(), cudaMemcpyHostToDevice));
+  L.nrank = n;
+  return B200MD_OK;
+}
+
+int langevin_config(b200md_ctx *c, double t_start, double t_stop, double t_period, int seed, const double *ratio, double dt) {
+  Langevin &L = c->lang;
+  if (c->nranks != 1) {
+    b200md_set_error("b200md: fix langevin runs on one rank (its random stream follows the host's local atom order)");
+    return B200MD_ERR;
+  }
+  if (!c->host_order) { b200md_set_error("b200md: fix langevin must be set after the atoms and before the set-up"); return B200MD_ERR; }
+  if (t_period <= 0.0) { b200md_set_error("Fix langevin period must be > 0.0"); return B200MD_ERR; }
+  if (dt <= 0.0) { b200md_set_error("b200md: fix langevin needs the timestep"); return B200MD_ERR; }
+  TRY(ranmars_device_init(c, seed));
+  TRY(langevin_rank_from_host_order(c));
+  L.t_start = t_start; L.t_stop = t_stop; L.t_period = t_period; L.dt = 0.0;
+  L.ratio.assign(c->ntypes + 1, 1.0);
+  if (ratio) for (int t = 1; t <= c->ntypes; t++) {
+    if (ratio[t] <= 0.0) { b200md_set_error("Illegal fix langevin command"); return B200MD_ERR; }
+    L.ratio[t] = ratio[t];
+  }
+  L.window = false;
+  L.begin = L.end = L.now = c->step;
+  L.on = true;
+  return langevin_set_dt(c, dt);
+}
+
+// FixLangevin::init / reset_dt: the per-type prefactors (same operation order)
+int langevin_set_dt(b200md_ctx *c, double dt) {
+  Langevin &L = c->lang;
+  if (dt == L.dt && L.gfac) return B200MD_OK;
+  std::vector<double> g(2 * ((size_t)c->ntypes + 1), 0.0);
+  for (int t = 1; t <= c->ntypes; t++) {
+    double g1 = -c->h_mass[t] / L.t_period / c->ftm2v;
+    double g2 = sqrt(c->h_mass[t]) / c->ftm2v;
+    g2 *= sqrt(24.0 * c->boltz / L.t_period / dt / c->mvv2e);
+    g1 *= 1.0 / L.ratio[t];
+    g2 *= 1.0 / sqrt(L.ratio[t]);
+    g[2 * t] = g1; g[2 * t + 1] = g2;
+  }
+  if (!L.gfac || L.gfac_n != (int)g.size()) {
+    if (L.gfac) CUDA_TRY(cudaFree(L.gfac));
+    CUDA_TRY(cudaMalloc(&L.gfac, sizeof(double) * g.size()));
+    L.gfac_n = (int)g.size();
+  }
+  // stream-ordered against kernels still reading the old values
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  CUDA_TRY(cudaMemcpy(L.gfac, g.data(), sizeof(double) * g.size(), cudaMemcpyHostToDevice));
+  L.dt = dt;
+  return B200MD_OK;
+}
+
+// Modify::post_force -> FixLangevin::post_force at timestep L.now; with_final also does
+// FixNVE::final_integrate in the same pass
+int langevin_post_force(b200md_ctx *c, bool with_final, double dtf) {
+  Langevin &L = c->lang;
+  const int n = c->nlocal;
+  if (n != L.nrank) {
+    b200md_set_error("b200md: fix langevin: the number of atoms changed since it was set");
+    return B200MD_ERR;
+  }
+  double delta = (double)(L.now - L.begin);
+  if (delta != 0.0) delta /= (double)(L.end - L.begin);
+  const double t_target = L.t_start + delta * (L.t_stop - L.t_start);
+  if (t_target < 0.0) { b200md_set_error("Fix langevin variable returned negative temperature"); return B200MD_ERR; }
+  const double tsqrt = sqrt(t_target);
+  TRY(ranmars_fill(c, 3 * n));
+  if (n == 0) return B200MD_OK;
+  const int nb = (n + 255) / 256;
+  if (with_final)
+    k_langevin<true><<<nb, 256, 0, c->stream>>>(n, c->nmax, c->xq, c->v, c->f, c->tag, L.rank_by_tag, L.rnd, L.gfac, c->mass, tsqrt, dtf);
+  else
+    k_langevin<false><<<nb, 256, 0, c->stream>>>(n, c->nmax, c->xq, c->v, c->f, c->tag, L.rank_by_tag, L.rnd, L.gfac, c->mass, tsqrt, dtf);
+  CUDA_TRY(cudaGetLastError());
+  c->launches++;
+  return B200MD_OK;
+}
+
+// b200md_ranmars_device_stream: `fills` consecutive fills of n draws, as doubles
+int langevin_test_stream(b200md_ctx *c, int seed, int n, int fills, double *out) {
+  Langevin saved = c->lang;
+  c->lang = Langevin();
+  int rc = ranmars_device_init(c, seed);
+  std::vector<uint32_t> h(n > 0 ? n : 1);
+  for (int k = 0; rc == B200MD_OK && k < fills; k++) {
+    rc = ranmars_fill(c, n);
+    if (rc != B200MD_OK) break;
+    if (cudaStreamSynchronize(c->stream) != cudaSuccess ||
+        (n && cudaMemcpy(h.data(), c->lang.rnd, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost) != cudaSuccess)) {
+      b200md_set_error("b200md: CUDA error in the RanMars stream kernel");
+      rc = B200MD_ERR;
+      break;
+    }
+    for (int i = 0; i < n; i++) out[(size_t)k * n + i] = (double)h[i] * (1.0 / 16777216.0);
+  }
+  Langevin tmp = c->lang;
+  c->lang = tmp;
+  langevin_free(c);
+  c->lang = saved;
+  return rc;
+}

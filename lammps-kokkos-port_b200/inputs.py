@@ -70,14 +70,21 @@ def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, 
     return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=50, units="metal")
 
 
-def in_chain(ctx, data_path, x=1, y=1, z=1, list_kind=B.LIST_HALF_NEWTON):
-    """bench/in.chain / in.chain.scaled (`replicate x y z`) WITHOUT `fix langevin`
+def atom_sort_order(x, sublo, subhi, cutneighmax):
+    """the local order Verlet::setup leaves (Atom::sort, src/atom.cpp:2246-2349, src/verlet.cpp:123)"""
+    return B.atom_sort_order(x, sublo, subhi, cutneighmax)
+
+
+def in_chain(ctx, data_path, x=1, y=1, z=1, list_kind=B.LIST_HALF_NEWTON, langevin=False):
+    """bench/in.chain / in.chain.scaled (`replicate x y z`)
     (/root/reference/bench/in.chain:1-28, in.chain.scaled:1-33): units lj;
     atom_style bond; special_bonds fene; read_data data.chain; neighbor 0.4 bin;
     neigh_modify every 1 delay 1; bond_style fene; bond_coeff 1 30.0 1.5 1.0 1.0;
     pair_style lj/cut 1.12; pair_modify shift yes; pair_coeff 1 1 1.0 1.0 1.12; fix 1 all nve;
-    timestep 0.012.  (fix langevin draws its RanMars numbers in the reference's local atom
-    order, src/fix_langevin.cpp:85 — not reproducible under another ordering)"""
+    timestep 0.012; and with langevin=True `fix 2 all langevin 1.0 1.0 10.0 904297`.
+    fix langevin draws its RanMars numbers in local atom order (src/fix_langevin.cpp:636-662), so
+    with langevin=True the atoms are uploaded in the order Atom::sort gives them at the reference's
+    set-up (one rank only)."""
     from . import molecule_host as M
     d = M.replicate(M.read_data(data_path), x, y, z)
     ctx.set_units("lj")
@@ -88,13 +95,18 @@ def in_chain(ctx, data_path, x=1, y=1, z=1, list_kind=B.LIST_HALF_NEWTON):
     own = np.ones(len(xs), bool)
     for k in range(3):
         own &= (xs[:, k] >= sublo[k]) & (xs[:, k] < subhi[k])
-    ctx.set_atoms(xs[own], d["v"][own], d["type"][own], d["tag"][own], d["mass"], image=d["image"][own])
+    T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 1.12)}, 1.12, shift=True)
+    skin = 0.4
+    cn, cmax = B.cutneighsq_table(1, T["cutsq"], skin)
+    sel = np.flatnonzero(own)
+    if langevin:
+        sel = sel[atom_sort_order(xs[sel], sublo, subhi, cmax)]
+    ctx.set_atoms(xs[sel], d["v"][sel], d["type"][sel], d["tag"][sel], d["mass"], image=d["image"][sel])
+    if langevin:
+        ctx.fix_langevin(1.0, 1.0, 10.0, 904297, 0.012)
     tp = M.build_topology(d["natoms"], d["bonds"])          # special_bonds fene: lj = coul = 0 1 1
     ctx.set_topology(tp)
     ctx.bond_fene_config([0.0, 30.0], [0.0, 1.5], [0.0, 1.0], [0.0, 1.0])
-    T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 1.12)}, 1.12, shift=True)
     ctx.pair_lj_cut_config(T["cutsq"], T["lj1"], T["lj2"], T["lj3"], T["lj4"], T["offset"])
-    skin = 0.4
-    cn, cmax = B.cutneighsq_table(1, T["cutsq"], skin)
     ctx.neigh_config(cn, cmax, skin, every=1, delay=1, check=1, list_kind=list_kind)
     return dict(natoms=d["natoms"], dt=0.012, thermo=100, units="lj", data=d, topology=tp, tables=T)

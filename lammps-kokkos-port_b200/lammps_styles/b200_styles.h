@@ -22,6 +22,14 @@ class B200BondStyle {
   virtual int b200_push_bond(b200md_ctx *ctx) = 0;
 };
 
+// a fix that acts inside the device step loop
+class B200FixStyle {
+ public:
+  virtual ~B200FixStyle() = default;
+  virtual int b200_push_fix(b200md_ctx *ctx) = 0;      // once the atoms are uploaded, before the set-up evaluation
+  virtual int b200_begin_chunk(b200md_ctx *ctx) = 0;   // before every b200md_run of a run
+};
+
 // the one device context of this LAMMPS instance (owned by VerletB200)
 struct B200Shared {
   static b200md_ctx *ctx;

@@ -82,10 +82,15 @@ void VerletB200::check_supported()
   // `run 0` (forces and tallies only) needs no integrator
   if (nintegrate > 1 || (nintegrate == 0 && update->nsteps > 0))
     error->all(FLERR, "Run style verlet/b200 requires exactly one fix nve/b200");
+  // fixes that act after the force evaluation: only those the device loop applies itself
+  int ndevice_post = 0;
+  for (const auto &fix : modify->get_fix_list())
+    if (dynamic_cast<B200FixStyle *>(fix)) ndevice_post++;
+  if (ndevice_post > 1) error->all(FLERR, "Run style verlet/b200 supports one fix langevin/b200");
   if (modify->n_initial_integrate != nintegrate || modify->n_final_integrate != nintegrate ||
       modify->n_post_integrate || modify->n_pre_exchange || modify->n_pre_neighbor ||
       modify->n_post_neighbor || modify->n_pre_force || modify->n_pre_reverse ||
-      modify->n_post_force_any || modify->n_end_of_step)
+      modify->n_post_force_any != ndevice_post || modify->n_end_of_step)
     error->all(FLERR, "Run style verlet/b200 does not support fixes that act during the step");
 }
 
@@ -124,6 +129,16 @@ void VerletB200::device_setup()
   domain->pbc();
   domain->reset_box();
   comm->setup();
+  // the local order Verlet::setup leaves (src/verlet.cpp:123): it decides which RanMars draws an
+  // atom gets from fix langevin; nothing else on the device depends on it
+  if (atom->sortfreq > 0 && comm->nprocs == 1) {
+    atom->nghost = 0;
+    atom->sort();
+    if (atom->map_style != Atom::MAP_NONE) {
+      atom->map_init();
+      atom->map_set();
+    }
+  }
 
   const int nlocal = atom->nlocal;
   const int *mask = atom->mask;
@@ -158,6 +173,13 @@ void VerletB200::device_setup()
     fail();
   if (dynamic_cast<B200PairStyle *>(force->pair)->b200_push(ctx)) fail();
   if (atom->molecular != Atom::ATOMIC) push_topology();
+  bool thermostat = false;
+  for (const auto &fix : modify->get_fix_list())
+    if (auto dev = dynamic_cast<B200FixStyle *>(fix)) {
+      if (dev->b200_push_fix(ctx)) fail();
+      thermostat = true;
+    }
+  if (!thermostat && b200md_fix_langevin_off(ctx)) fail();    // `unfix` between runs
   if (b200md_setup(ctx)) fail();
 
   long long nb = 0, nd = 0, tot = 0;
@@ -319,6 +341,9 @@ void VerletB200::run(int n)
     int chunk = n - done;
     if (togo > 0 && togo < (bigint) chunk) chunk = (int) togo;
 
+    for (const auto &fix : modify->get_fix_list())
+      if (auto dev = dynamic_cast<B200FixStyle *>(fix))
+        if (dev->b200_begin_chunk(ctx)) fail();
     timer->stamp();
     int nth = 0;
     if (b200md_run(ctx, chunk, update->dt, 0, nullptr, 0, &nth)) fail();

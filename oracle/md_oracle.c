@@ -73,6 +73,12 @@ typedef struct {
   int eflag_atom, vflag_atom;
   double *eatom, *vatom; /* [nmax], [nmax][6] pair + bond, as compute pe/atom / stress/atom sum them */
   long step;
+  /* fix langevin (fix_langevin.cpp) with its RanMars stream (random_mars.cpp) */
+  int langevin;
+  double lang_tstart, lang_tstop, lang_period, lang_dt, *lang_ratio;
+  long lang_begin, lang_end;
+  double mars_u[98], mars_c, mars_cd, mars_cm;
+  int mars_i97, mars_j97;
 } ora_sim;
 
 typedef struct {
@@ -130,7 +136,7 @@ void ora_destroy(ora_sim *s) {
   for (int k = 0; k < MAXSWAP; k++) free(s->sendlist[k]);
   free(s->cutsq); free(s->lj1); free(s->lj2); free(s->lj3); free(s->lj4); free(s->offset);
   free(s->frho_spline); free(s->rhor_spline); free(s->z2r_spline); free(s->scale);
-  free(s->type2frho); free(s->type2rhor); free(s->type2z2r);
+  free(s->type2frho); free(s->type2rhor); free(s->type2z2r); free(s->lang_ratio);
   free(s);
 }
 
@@ -765,10 +771,145 @@ void ora_thermo_compute(ora_sim *s, ora_thermo *t) {
   t->press = (dof * s->boltz * temp + t->virial[0] + t->virial[1] + t->virial[2]) / 3.0 * (1.0 / vol) * s->nktv2p;
 }
 
-/* Verlet::setup (verlet.cpp:93-162) */
+/* ---- Atom::sort (atom.cpp:2246-2349) with Atom::setup_sort_bins (atom.cpp:2351-2410) --------
+ * Spatial sort of the owned atoms, bins of 1/2 cutneighmax over the (sub-)box, stable inside a
+ * bin.  Verlet::setup calls it (verlet.cpp:123, sortfreq = 1000 by default) after Domain::pbc and
+ * before the borders, so it fixes the local index order — which is what the order of a half
+ * list's same-bin pairs and the RanMars draws of fix langevin follow. */
+void ora_atom_sort(ora_sim *s) {
+  pbc(s);
+  s->nghost = 0;
+  double binsize = 0.5 * s->cutneighmax;
+  if (binsize == 0.0) return;
+  double bininv = 1.0 / binsize;
+  int nb[3];
+  double binv[3];
+  for (int d = 0; d < 3; d++) {
+    nb[d] = (int)((s->boxhi[d] - s->boxlo[d]) * bininv);
+    if (nb[d] == 0) nb[d] = 1;
+    binv[d] = nb[d] / (s->boxhi[d] - s->boxlo[d]);
+  }
+  int nbins = nb[0] * nb[1] * nb[2], n = s->nlocal;
+  if (nbins == 1) return;
+  int *head = malloc(sizeof(int) * nbins), *next = malloc(sizeof(int) * (n + 1)), *permute = malloc(sizeof(int) * (n + 1));
+  for (int i = 0; i < nbins; i++) head[i] = -1;
+  for (int i = n - 1; i >= 0; i--) {
+    int c[3];
+    for (int d = 0; d < 3; d++) {
+      c[d] = (int)((s->x[3 * i + d] - s->boxlo[d]) * binv[d]);
+      c[d] = MAX(c[d], 0);
+      c[d] = MIN(c[d], nb[d] - 1);
+    }
+    int ibin = c[2] * nb[1] * nb[0] + c[1] * nb[0] + c[0];
+    next[i] = head[ibin];
+    head[ibin] = i;
+  }
+  int m = 0;
+  for (int b = 0; b < nbins; b++)
+    for (int i = head[b]; i >= 0; i = next[i]) permute[m++] = i;
+  /* new atom I = old atom permute[I] (the reference does it in place, cycle by cycle; same result) */
+  double *x = malloc(sizeof(double) * 3 * n), *v = malloc(sizeof(double) * 3 * n), *f = malloc(sizeof(double) * 3 * n);
+  int *type = malloc(sizeof(int) * n), *tag = malloc(sizeof(int) * n), *image = malloc(sizeof(int) * n);
+  for (int i = 0; i < n; i++) {
+    int j = permute[i];
+    for (int d = 0; d < 3; d++) { x[3 * i + d] = s->x[3 * j + d]; v[3 * i + d] = s->v[3 * j + d]; f[3 * i + d] = s->f[3 * j + d]; }
+    type[i] = s->type[j]; tag[i] = s->tag[j]; image[i] = s->image[j];
+  }
+  memcpy(s->x, x, sizeof(double) * 3 * n); memcpy(s->v, v, sizeof(double) * 3 * n); memcpy(s->f, f, sizeof(double) * 3 * n);
+  memcpy(s->type, type, sizeof(int) * n); memcpy(s->tag, tag, sizeof(int) * n); memcpy(s->image, image, sizeof(int) * n);
+  free(x); free(v); free(f); free(type); free(tag); free(image); free(head); free(next); free(permute);
+}
+
+/* ---- RanMars (random_mars.cpp:30-95): Marsaglia's lagged-Fibonacci generator --------------- */
+static double mars_uniform(ora_sim *s) {
+  double uni = s->mars_u[s->mars_i97] - s->mars_u[s->mars_j97];
+  if (uni < 0.0) uni += 1.0;
+  s->mars_u[s->mars_i97] = uni;
+  s->mars_i97--;
+  if (s->mars_i97 == 0) s->mars_i97 = 97;
+  s->mars_j97--;
+  if (s->mars_j97 == 0) s->mars_j97 = 97;
+  s->mars_c -= s->mars_cd;
+  if (s->mars_c < 0.0) s->mars_c += s->mars_cm;
+  uni -= s->mars_c;
+  if (uni < 0.0) uni += 1.0;
+  return uni;
+}
+static int mars_init(ora_sim *s, int seed) {
+  if (seed <= 0 || seed > 900000000) return -1; /* "Invalid seed for Marsaglia random # generator" */
+  memset(s->mars_u, 0, sizeof(s->mars_u));
+  int ij = (seed - 1) / 30082;
+  int kl = (seed - 1) - 30082 * ij;
+  int i = (ij / 177) % 177 + 2, j = ij % 177 + 2, k = (kl / 169) % 178 + 1, l = kl % 169;
+  for (int ii = 1; ii <= 97; ii++) {
+    double sum = 0.0, t = 0.5;
+    for (int jj = 1; jj <= 24; jj++) {
+      int m = ((i * j) % 179) * k % 179;
+      i = j; j = k; k = m;
+      l = (53 * l + 1) % 169;
+      if ((l * m) % 64 >= 32) sum = sum + t;
+      t = 0.5 * t;
+    }
+    s->mars_u[ii] = sum;
+  }
+  s->mars_c = 362436.0 / 16777216.0;
+  s->mars_cd = 7654321.0 / 16777216.0;
+  s->mars_cm = 16777213.0 / 16777216.0;
+  s->mars_i97 = 97;
+  s->mars_j97 = 33;
+  mars_uniform(s);
+  return 0;
+}
+/* the first n draws after construction (for checking the device generator) */
+int ora_ranmars_stream(int seed, long n, double *out) {
+  ora_sim *s = calloc(1, sizeof(ora_sim));
+  if (mars_init(s, seed)) { free(s); return -1; }
+  for (long k = 0; k < n; k++) out[k] = mars_uniform(s);
+  free(s);
+  return 0;
+}
+
+/* ---- fix langevin (fix_langevin.cpp): constructor :60-150 (seed + comm->me, ratio), init
+ * :286-298 (gfactor1/2), setup :360-361 (post_force once per run set-up), compute_target
+ * :773-787, post_force_templated<0,0,0,0,0,0> :576-713 — tally no, zero no, gjf no, per-type mass */
+int ora_fix_langevin(ora_sim *s, double t_start, double t_stop, double t_period, int seed, const double *ratio, double dt) {
+  if (t_period <= 0.0 || mars_init(s, seed)) return -1;
+  s->langevin = 1;
+  s->lang_tstart = t_start; s->lang_tstop = t_stop; s->lang_period = t_period; s->lang_dt = dt;
+  s->lang_ratio = realloc(s->lang_ratio, sizeof(double) * (s->ntypes + 1));
+  for (int t = 0; t <= s->ntypes; t++) s->lang_ratio[t] = ratio ? ratio[t] : 1.0;
+  s->lang_begin = s->lang_end = s->step;
+  return 0;
+}
+static void langevin_post_force(ora_sim *s) {
+  double delta = s->step - s->lang_begin;
+  if (delta != 0.0) delta /= s->lang_end - s->lang_begin;
+  double t_target = s->lang_tstart + delta * (s->lang_tstop - s->lang_tstart);
+  double tsqrt = sqrt(t_target);
+  for (int i = 0; i < s->nlocal; i++) {
+    int t = s->type[i];
+    double gfactor1 = -s->mass[t] / s->lang_period / s->ftm2v;
+    double gfactor2 = sqrt(s->mass[t]) / s->ftm2v;
+    gfactor2 *= sqrt(24.0 * s->boltz / s->lang_period / s->lang_dt / s->mvv2e);
+    gfactor1 *= 1.0 / s->lang_ratio[t];
+    gfactor2 *= 1.0 / sqrt(s->lang_ratio[t]);
+    double gamma1 = gfactor1, gamma2 = gfactor2 * tsqrt;
+    double fran[3], fdrag[3];
+    fran[0] = gamma2 * (mars_uniform(s) - 0.5);
+    fran[1] = gamma2 * (mars_uniform(s) - 0.5);
+    fran[2] = gamma2 * (mars_uniform(s) - 0.5);
+    for (int d = 0; d < 3; d++) fdrag[d] = gamma1 * s->v[3 * i + d];
+    for (int d = 0; d < 3; d++) s->f[3 * i + d] += fdrag[d] + fran[d];
+  }
+}
+
+/* Verlet::setup (verlet.cpp:93-162); Modify::setup -> FixLangevin::setup applies the thermostat
+ * to the set-up forces (delta = 0: Run::command sets beginstep = ntimestep before the set-up) */
 int ora_setup(ora_sim *s) {
   if (ora_neigh_build(s)) return -1;
-  return ora_compute(s, 1, 1);
+  if (ora_compute(s, 1, 1)) return -1;
+  if (s->langevin) { s->lang_begin = s->step; s->lang_end = s->step; langevin_post_force(s); }
+  return 0;
 }
 
 /* Verlet::run (verlet.cpp:229-360) with fix nve; thermo every `thermo_every` steps and at the end */
@@ -776,6 +917,7 @@ int ora_run(ora_sim *s, int nsteps, double dt, int thermo_every, ora_thermo *out
   double dtv = dt, dtf = 0.5 * dt * s->ftm2v;
   long first = s->step, last = s->step + nsteps;
   int nout = 0;
+  if (s->langevin) { s->lang_begin = first; s->lang_end = last; s->lang_dt = dt; }
   for (int i = 0; i < nsteps; i++) {
     s->step++;
     int out_step = (thermo_every > 0 && (s->step - first) % thermo_every == 0) || s->step == last;
@@ -783,6 +925,7 @@ int ora_run(ora_sim *s, int nsteps, double dt, int thermo_every, ora_thermo *out
     if (!decide(s)) forward_comm(s);
     else if (ora_neigh_build(s)) return -1;
     if (ora_compute(s, out_step, out_step)) return -1;
+    if (s->langevin) langevin_post_force(s); /* Modify::post_force (verlet.cpp:337) */
     nve_final(s, dtf);
     if (out_step && out && nout < max_out) ora_thermo_compute(s, &out[nout++]);
   }

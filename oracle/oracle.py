@@ -99,6 +99,16 @@ class Oracle:
         a = [_d(t) for t in (k, r0, epsilon, sigma)]
         self.L.ora_bond_fene(self.h, len(a[0]) - 1, *[_p(t) for t in a])
 
+    def atom_sort(self):
+        """Atom::sort as Verlet::setup calls it (after neigh_config, before setup)"""
+        self.L.ora_atom_sort(self.h)
+
+    def fix_langevin(self, t_start, t_stop, t_period, seed, dt, ratio=None):
+        r = _d(ratio) if ratio is not None else None
+        if self.L.ora_fix_langevin(self.h, C.c_double(t_start), C.c_double(t_stop), C.c_double(t_period), int(seed),
+                                   _p(r) if r is not None else None, C.c_double(dt)):
+            raise RuntimeError("oracle: fix langevin needs period > 0 and 0 < seed <= 900000000")
+
     def neigh_build(self):
         if self.L.ora_neigh_build(self.h):
             raise RuntimeError("oracle: neighbor build failed (too many ghost swaps)")
@@ -168,6 +178,17 @@ class Oracle:
         a = (C.c_int * 12)(); b = (C.c_double * 6)()
         self.L.ora_bin_geometry(self.h, a, b)
         return list(a), list(b)
+
+
+def ranmars_stream(seed, n):
+    """first n RanMars::uniform() draws after construction (src/random_mars.cpp), from the C oracle"""
+    if not os.path.exists(ORACLE_SO):
+        build_oracle()
+    L = C.CDLL(ORACLE_SO)
+    out = np.empty(n, np.float64)
+    if L.ora_ranmars_stream(int(seed), C.c_long(n), _p(out)):
+        raise RuntimeError("Invalid seed for Marsaglia random # generator")
+    return out
 
 
 class Reference:

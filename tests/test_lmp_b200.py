@@ -202,6 +202,41 @@ def test_in_chain_matches_reference_executable():
 
 
 @pytest.mark.gpu
+def test_in_chain_with_langevin_matches_reference_executable():
+    """bench/in.chain AS SHIPPED (fix nve + fix langevin 1.0 1.0 10.0 904297) with -sf b200:
+    fix langevin/b200 replays the reference's RanMars stream on the device in the reference's
+    local atom order (Atom::sort at set-up), so the thermo equals the reference executable's and
+    the published log (bench/log.6Oct16.chain.fixed.icc.1, step 100).  The second `run` checks
+    that the generator carries on across runs like the reference's (one RanMars per fix)."""
+    have_gpu_binary()
+    data = os.path.join(ROOT, "oracle", "_ref", "data", "data.chain")
+    if not (os.path.exists(LMP_REF) and os.path.exists(data)):
+        pytest.skip("oracle/_ref not built")
+    script = IN_CHAIN.format(data=data).replace(
+        "fix             1 all nve", "fix             1 all nve\nfix             2 all langevin 1.0 1.0 10.0 904297").replace(
+        "run             60", "run             100")
+    rc, out = run_lmp(LMP_B200, script, ("-sf", "b200"))
+    assert rc == 0, out[-2000:]
+    rc2, ref = run_lmp(LMP_REF, script)
+    assert rc2 == 0, ref[-2000:]
+    a, b = thermo_rows(out), thermo_rows(ref)
+    assert a.shape == b.shape == (8, 6)
+    np.testing.assert_allclose(a, b, rtol=1e-8, atol=1e-10)
+    np.testing.assert_allclose(a[5, 1:], [0.9729966, 0.4361122, 20.507698, 22.40326, 4.6548819], rtol=6e-8)
+    ma, mb = (re.findall(r"Neighbor list builds = (\d+)", t) for t in (out, ref))
+    assert ma == mb and len(ma) == 2
+
+
+@pytest.mark.gpu
+def test_langevin_options_the_device_does_not_cover_fail_loudly():
+    have_gpu_binary()
+    script = IN_LJ.format(n=5, thermo=100).replace(
+        "fix             1 all nve", "fix             1 all nve\nfix 2 all langevin 1.0 1.0 1.0 4711 zero yes")
+    rc, out = run_lmp(LMP_B200, script, ("-sf", "b200"))
+    assert rc != 0 and "langevin/b200" in out
+
+
+@pytest.mark.gpu
 def test_unsupported_setups_fail_loudly():
     """no silent host fallback: a fix the device loop does not cover is an error"""
     have_gpu_binary()
