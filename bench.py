@@ -28,7 +28,9 @@ BYTES_KERNEL = {"lj": 28 * 75.2 + 52, "eam": 64 * 75.5 + 104,    # LJ force pass
                 "chain": 28 * 9.74 + 52 + 1 * (8 + 24 + 24) + 52}  # + FENE: 0.99 bonds/atom x (tag,map + x_j + f_j RED) + own x,f
 # in.chain (SURVEY's method applied to C3, N=9.74, rebuild every ~4 steps): force passes 381 + NVE 192
 # + check_distance 48 + rebuild (4N list + 24 xhold + 176 sort + 28N candidates + 8 map)/4 = 128
-BYTES_STEP = {"lj": 2480.0, "eam": 5510.0, "chain": 750.0}
+# fix langevin adds 12 B written + 12 B read of random words, 4 B tag, 4 B rank per atom-step (its v/f
+# streams are the ones nve_final moves anyway: the two are one fused pass)
+BYTES_STEP = {"lj": 2480.0, "eam": 5510.0, "chain": 750.0, "chain+langevin": 782.0}
 # (the figures above are SURVEY 8(d)'s yardstick, defined on the full list; the half-list kernels do
 #  the same physical work -- every pair once instead of twice -- and are rated with the same figure)
 # measured choice by workload and world size (2 = "two or more"), profiles/r01_summary.md: in.lj at N>1
@@ -89,15 +91,16 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def ref_script(workload, xyz, warm, steps):
+def ref_script(workload, xyz, warm, steps, langevin=True):
     from oracle import oracle as O
     if workload == "lj":
         body = O.IN_LJ.format(nx=20 * xyz[0], ny=20 * xyz[1], nz=20 * xyz[2])
-    elif workload == "chain":   # bench/in.chain.scaled without fix langevin (what the B200 arm runs)
+    elif workload == "chain":   # bench/in.chain.scaled (what the B200 arm runs, thermostat included unless --no-langevin)
         body = ("units lj\natom_style bond\nspecial_bonds fene\nread_data %s\nreplicate %d %d %d\n"
                 "neighbor 0.4 bin\nneigh_modify every 1 delay 1\nbond_style fene\nbond_coeff 1 30.0 1.5 1.0 1.0\n"
                 "pair_style lj/cut 1.12\npair_modify shift yes\npair_coeff 1 1 1.0 1.0 1.12\nfix 1 all nve\n"
-                "timestep 0.012\n" % (os.path.join(os.path.dirname(O.POT_DIR), "data", "data.chain"), *xyz))
+                "%stimestep 0.012\n" % (os.path.join(os.path.dirname(O.POT_DIR), "data", "data.chain"), *xyz,
+                                       "fix 2 all langevin 1.0 1.0 10.0 904297\n" if langevin else ""))
     else:
         body = O.IN_EAM.format(nx=20 * xyz[0], ny=20 * xyz[1], nz=20 * xyz[2], style="eam",
                                coeff="1 1 " + os.path.join(O.POT_DIR, "Cu_u3.eam"))
@@ -105,12 +108,12 @@ def ref_script(workload, xyz, warm, steps):
     return body + ("run %d\n" % warm if warm > 0 else "") + "run %d\n" % steps
 
 
-def run_reference(workload, xyz, warm, steps, cores):
+def run_reference(workload, xyz, warm, steps, cores, langevin=True):
     """the reference's own CPU implementation (oracle/_ref/lmp, OPENMP package on all host cores)"""
     import re
     from oracle import oracle as O
     t0 = time.time()
-    _, atoms, nst, out = O.ref_exe_run(ref_script(workload, xyz, warm, steps), threads=cores, omp=True, timeout=3000)
+    _, atoms, nst, out = O.ref_exe_run(ref_script(workload, xyz, warm, steps, langevin), threads=cores, omp=True, timeout=3000)
     loops = re.findall(r"Loop time of ([0-9.eE+-]+) on \d+ procs for (\d+) steps with (\d+) atoms", out)
     lt, nst, atoms = float(loops[-1][0]), int(loops[-1][1]), int(loops[-1][2])
     return atoms * nst / lt, lt, atoms, time.time() - t0
@@ -127,6 +130,8 @@ def main():
     ap.add_argument("--list", default="auto", choices=["auto", "half", "full"],
                     help="half = half/bin/atomonly/newton (the input scripts' default, newton on); full = newton off")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-langevin", action="store_true",
+                    help="chain workload: leave `fix langevin` out (one GPU runs it by default, as bench/in.chain ships it)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -135,10 +140,14 @@ def main():
     xyz = SCALE.get(ngpus, (4 * ngpus, 4, 4))
     natoms = 4 * 8000 * xyz[0] * xyz[1] * xyz[2]
     wl = a.workload
+    # the thermostat's random stream follows one rank's local atom order (the reference seeds every rank
+    # separately): it is part of the chain workload on one GPU
+    langevin = wl == "chain" and not a.no_langevin and world == 1 and ngpus == 1
     desc = {"lj": "fcc lattice, lj/cut 2.5, neigh every 20", "eam": "fcc lattice, eam Cu_u3, neigh check yes",
-            "chain": "data.chain replicated, FENE bonds + lj/cut 1.12, special_bonds fene, fix langevin left out"}[wl]
-    config = {"workload": "bench/in.%s -var x %d -var y %d -var z %d (%d atoms, %s, NVE)" % (
-        wl + (".scaled" if wl == "chain" else ""), xyz[0], xyz[1], xyz[2], natoms, desc),
+            "chain": "data.chain replicated, FENE bonds + lj/cut 1.12, special_bonds fene, "
+                     + ("fix langevin 1.0 1.0 10.0 904297 (the reference's RanMars stream)" if langevin else "fix langevin left out")}[wl]
+    config = {"workload": "bench/in.%s -var x %d -var y %d -var z %d (%d atoms, %s)" % (
+        wl + (".scaled" if wl == "chain" else ""), xyz[0], xyz[1], xyz[2], natoms, desc + (", NVE" if not langevin else "")),
         "atoms_per_gpu": natoms // ngpus, "decomposition": None,
         "l2": "working set (neighbor list >= 1 GB/GPU) exceeds the 126 MB L2; no flush needed"}
     cores = os.cpu_count() or 1
@@ -146,7 +155,7 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return 0
-        val, lt, atoms, wall = run_reference(wl, xyz, a.warmup, a.steps, cores)
+        val, lt, atoms, wall = run_reference(wl, xyz, a.warmup, a.steps, cores, langevin)
         line = {"impl": "reference", "metric": "atom-steps/s", "value": val, "unit": "atom-steps/s", "n_gpus": ngpus,
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": lt / a.steps * 1e3, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
@@ -184,7 +193,8 @@ def main():
     if wl == "lj":
         cfg = P.inputs.in_lj(ctx, *xyz, list_kind=list_kind)
     elif wl == "chain":
-        cfg = P.inputs.in_chain(ctx, os.path.join(ROOT, "oracle", "_ref", "data", "data.chain"), *xyz, list_kind=list_kind)
+        cfg = P.inputs.in_chain(ctx, os.path.join(ROOT, "oracle", "_ref", "data", "data.chain"), *xyz, list_kind=list_kind,
+                                langevin=langevin)
     else:
         cfg = P.inputs.in_eam(ctx, *xyz, potential=os.path.join(ROOT, "oracle", "_ref", "potentials", "Cu_u3.eam"),
                               list_kind=list_kind)
@@ -230,12 +240,13 @@ def main():
     nloc = ctx.nlocal()[0]
     hbm, which = peaks()
     bytes_kernel = BYTES_KERNEL_HALF[wl] if lk == "half" else BYTES_KERNEL[wl]
+    bstep = BYTES_STEP["chain+langevin" if langevin else wl]
     achieved = bytes_kernel * nloc / (pair_ms / 1e3) / 1e9
     roofline = {"bound": "hbm", "kernel": ("k_lj" if wl == "lj" else "k_lj+k_bond_fene" if wl == "chain" else ("k_eam_rho_half+k_eam_embed+k_eam_force" if lk == "half" else "k_eam_rho_fp+k_eam_force")),
                 "list": lk, "achieved": achieved,
                 "peak": hbm, "peak_source": which, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
                 "kernel_ms": pair_ms, "bytes_per_atom_launch": bytes_kernel,
-                "step_achieved": BYTES_STEP[wl] * (value / ngpus) / 1e9, "step_frac": BYTES_STEP[wl] * (value / ngpus) / 1e9 / hbm,
+                "step_achieved": bstep * (value / ngpus) / 1e9, "step_frac": bstep * (value / ngpus) / 1e9 / hbm,
                 "phases_ms_per_step": {k: tp[k + "_ms"] / n_eval for k in ("pair", "neigh", "comm", "modify")}}
     tr = os.path.join(ROOT, "profiles", "traffic_%s_%s.json" % (wl, lk))
     if not os.path.exists(tr):
@@ -277,7 +288,7 @@ def main():
     if rank == 0 and not a.no_cpu_baseline and ngpus == 1:
         try:
             sample_steps = 20
-            val, lt, atoms, wall = run_reference(wl, xyz, 0, sample_steps, cores)
+            val, lt, atoms, wall = run_reference(wl, xyz, 0, sample_steps, cores, langevin)
             line["cpu_baseline"] = {"value": val, "unit": "atom-steps/s", "cores": cores, "kind": "reference",
                                     "sample": "same workload (%d atoms), %d steps, oracle/_ref/lmp -sf omp -pk omp %d, Loop time %.3f s"
                                               % (atoms, sample_steps, cores, lt)}

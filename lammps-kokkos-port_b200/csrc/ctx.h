@@ -69,10 +69,15 @@ struct Langevin {
   std::vector<double> ratio;       // [ntypes+1]
   bool window = false;             // begin/end/now set by the caller (b200md_fix_langevin_window)
   long long begin = 0, end = 0, now = 0;
-  uint32_t *state[2] = {nullptr, nullptr};  // device [97]: generator state before / after a fill
-  int cur = 0;
+  uint32_t *state[2] = {nullptr, nullptr};  // device [97]: generator state the chunk layout starts from
+  uint32_t h_state[B200MD_RANMARS_LAG];     // host copy of a known generator state ...
+  long long h_position = 0;                 // ... and the number of draws made before it
   long long position = 0;          // draws made so far
-  uint32_t *jumpT = nullptr;       // device [24][97][97] transposed jump tables
+  uint32_t *jumpT = nullptr;       // device [24][97][97] transposed jump tables (chunk layout)
+  uint32_t *stepT = nullptr;       // device [97][97] transposed jump by one evaluation's draws
+  uint32_t *chunk_state = nullptr; // device [chunk_cap][97] resident generator state of every chunk
+  int chunk_cap = 0, stride = 0;   // stride: draws per evaluation the layout was made for
+  long long nevals = 0;
   uint32_t *rnd = nullptr;         // device [rnd_cap] this evaluation's draws, 24-bit integers
   int rnd_cap = 0;
   int *rank_by_tag = nullptr;      // device [maxtag+1] host-order index of a tag

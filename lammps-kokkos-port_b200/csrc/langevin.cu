@@ -13,19 +13,23 @@
 // B200 design.  The reference's thermostat is serial by construction: one generator, drawn
 // atom after atom.  Its recurrence is linear over Z/2^24, though (host.cpp, "RanMars in integer
 // form"), so the state k draws ahead is a fixed 97x97 integer matrix times the current state.
-// Each force evaluation needs the next 3*nlocal draws.  They are produced by one kernel:
-//   block m  -> start state = J^(m*CHUNK) state   (binary decomposition of m over precomputed
-//               J^(CHUNK*2^b) tables, <= 24 mat-vecs of 97x97 from L2-resident tables)
+// Each force evaluation needs the next S = 3*nlocal draws, cut into chunks of CHUNK.  Chunk m of
+// every evaluation is served by block m, which keeps its OWN generator state resident in HBM:
+//   set-up (once, k_ranmars_chunk_states): state_m = J^(m*CHUNK) state, by binary decomposition
+//               of m over precomputed J^(CHUNK*2^b) tables (<= 24 mat-vecs of 97x97)
+//   every evaluation (k_ranmars_fill): block m
 //            -> CHUNK values in shared memory, 32 per warp iteration (lag 33 > 32, so a warp's
 //               lanes never depend on each other inside an iteration)
 //            -> subtracts c[n] in closed form and stores 24-bit integers
-//   the block that owns draw 3*nlocal also writes the generator state for the next evaluation.
+//            -> state_m = J^S state_m: ONE mat-vec with the one matrix every block shares
+//               (37 KB, L1/L2-resident), because the same chunk of the next evaluation starts
+//               exactly S draws later — no serial dependency between blocks, ever.
 // The thermostat kernel then reads its three numbers at the atom's HOST rank (the local index
 // the reference would have drawn them at; rank_by_tag is built from the last b200md_set_atoms
 // order), so the device's own bin-sorted atom order does not matter.  In the step loop it is
 // fused with FixNVE::final_integrate: one pass over v and f instead of two.
 // Per atom-step: 12 B of random words written and read, 4 B tag, 4 B rank, plus the 96 B of the
-// v / f streams nve_final moves anyway; the generator itself is ~2 us per evaluation.
+// v / f streams nve_final moves anyway.
 #include "ctx.h"
 #include "util.cuh"
 
@@ -44,12 +48,20 @@ __device__ __forceinline__ uint32_t mars_c(long long n) {
   return (uint32_t)((362436LL + CM - t) % CM);
 }
 
-// jumpT: [RM_LEVELS][97][97], level b = TRANSPOSE of the jump-by-(CHUNK*2^b) matrix, so thread i
-// reads element (j, i): consecutive threads, consecutive words
+// thread `tid` < 97 computes row tid of (matrix^T given transposed) x vector; MT[j*97 + tid] so
+// consecutive threads read consecutive words
+__device__ __forceinline__ uint32_t matvec_row(const uint32_t *__restrict__ MT, const uint32_t *v, int tid) {
+  uint32_t acc = 0;
+#pragma unroll 16
+  for (int j = 0; j < RM_LAG; j++) acc += __ldg(MT + j * RM_LAG + tid) * v[j];
+  return acc & RM_MASK;
+}
+
+// jumpT: [RM_LEVELS][97][97], level b = TRANSPOSE of the jump-by-(CHUNK*2^b) matrix.
+// chunk_state[m] = J^(m*CHUNK) state_in
 __global__ void __launch_bounds__(RM_THREADS)
-k_ranmars_fill(const uint32_t *__restrict__ state_in, uint32_t *__restrict__ state_out,
-               const uint32_t *__restrict__ jumpT, long long position, int nnum, uint32_t *__restrict__ out) {
-  __shared__ uint32_t buf[RM_LAG + RM_CHUNK];
+k_ranmars_chunk_states(const uint32_t *__restrict__ state_in, const uint32_t *__restrict__ jumpT,
+                       uint32_t *__restrict__ chunk_state) {
   __shared__ uint32_t st[2][RM_LAG];
   const int tid = threadIdx.x;
   const int m = blockIdx.x;
@@ -58,18 +70,27 @@ k_ranmars_fill(const uint32_t *__restrict__ state_in, uint32_t *__restrict__ sta
   __syncthreads();
   for (int b = 0; b < RM_LEVELS; b++) {
     if (!((m >> b) & 1)) continue;   // uniform across the block
-    if (tid < RM_LAG) {
-      const uint32_t *M = jumpT + (size_t)b * RM_LAG * RM_LAG;
-      uint32_t acc = 0;
-#pragma unroll 4
-      for (int j = 0; j < RM_LAG; j++) acc += M[j * RM_LAG + tid] * st[cur][j];
-      st[cur ^ 1][tid] = acc & RM_MASK;
-    }
+    if (tid < RM_LAG) st[cur ^ 1][tid] = matvec_row(jumpT + (size_t)b * RM_LAG * RM_LAG, st[cur], tid);
     __syncthreads();
     cur ^= 1;
   }
-  if (tid < RM_LAG) buf[tid] = st[cur][tid];
+  if (tid < RM_LAG) chunk_state[(size_t)m * RM_LAG + tid] = st[cur][tid];
+}
+
+// draws [position + m*CHUNK, ...) of this evaluation from block m's resident state, then
+// state_m <- J^S state_m (stepT = transposed jump-by-S matrix, S = draws per evaluation)
+__global__ void __launch_bounds__(RM_THREADS)
+k_ranmars_fill(uint32_t *__restrict__ chunk_state, const uint32_t *__restrict__ stepT, long long position, int nnum,
+               uint32_t *__restrict__ out) {
+  __shared__ uint32_t buf[RM_LAG + RM_CHUNK];
+  const int tid = threadIdx.x;
+  const int m = blockIdx.x;
+  uint32_t *mine = chunk_state + (size_t)m * RM_LAG;
+  if (tid < RM_LAG) buf[tid] = mine[tid];
   __syncthreads();
+  // the state hop does not depend on the generation: issue its loads first
+  uint32_t next = 0;
+  if (tid < RM_LAG) next = matvec_row(stepT, buf, tid);
   const int base = m * RM_CHUNK;                 // first draw of this chunk, relative to `position`
   const int want = min(RM_CHUNK, nnum - base);   // > 0 by the grid size
   if (tid < 32) {
@@ -83,8 +104,7 @@ k_ranmars_fill(const uint32_t *__restrict__ state_in, uint32_t *__restrict__ sta
   __syncthreads();
   for (int k = tid; k < want; k += RM_THREADS)
     out[base + k] = (buf[RM_LAG + k] - mars_c(position + base + k)) & RM_MASK;
-  // generator state after draw position + nnum - 1
-  if (base + want == nnum && tid < RM_LAG) state_out[tid] = buf[want + tid];
+  if (tid < RM_LAG) mine[tid] = next;
 }
 
 // f += gamma1 v + gamma2 (u - 0.5)  [+ FixNVE::final_integrate when FINAL]
@@ -118,6 +138,8 @@ void langevin_free(b200md_ctx *c) {
   if (L.state[0]) cudaFree(L.state[0]);
   if (L.state[1]) cudaFree(L.state[1]);
   if (L.jumpT) cudaFree(L.jumpT);
+  if (L.stepT) cudaFree(L.stepT);
+  if (L.chunk_state) cudaFree(L.chunk_state);
   if (L.rnd) cudaFree(L.rnd);
   if (L.rank_by_tag) cudaFree(L.rank_by_tag);
   if (L.gfac) cudaFree(L.gfac);
@@ -145,8 +167,42 @@ static int ranmars_device_init(b200md_ctx *c, int seed) {
     CUDA_TRY(cudaMemcpy(L.jumpT, T.data(), sizeof(uint32_t) * T.size(), cudaMemcpyHostToDevice));
   }
   CUDA_TRY(cudaMemcpy(L.state[0], st, sizeof(st), cudaMemcpyHostToDevice));
-  L.cur = 0;
+  memcpy(L.h_state, st, sizeof(st));
+  L.h_position = 1;
   L.position = 1;   // the constructor drew once
+  L.stride = 0;     // chunk states are laid out at the first fill
+  return B200MD_OK;
+}
+
+// resident chunk states for evaluations of `nnum` draws each, starting at the current position
+static int ranmars_layout(b200md_ctx *c, int nnum) {
+  Langevin &L = c->lang;
+  const int nblocks = (nnum + RM_CHUNK - 1) / RM_CHUNK;
+  if (nblocks >= (1 << RM_LEVELS)) { b200md_set_error("b200md: fix langevin: too many atoms for one random stream"); return B200MD_ERR; }
+  // generator state at L.position, from the last state the host knows (set-up time only)
+  uint32_t st[RM_LAG];
+  TRY(b200md_ranmars_jump(L.h_state, L.position - L.h_position, st));
+  memcpy(L.h_state, st, sizeof(st));
+  L.h_position = L.position;
+  CUDA_TRY(cudaMemcpyAsync(L.state[0], L.h_state, sizeof(st), cudaMemcpyHostToDevice, c->stream));
+  if (L.chunk_cap < nblocks) {
+    if (L.chunk_state) CUDA_TRY(cudaFree(L.chunk_state));
+    L.chunk_cap = nblocks + nblocks / 8 + 8;
+    CUDA_TRY(cudaMalloc(&L.chunk_state, sizeof(uint32_t) * RM_LAG * (size_t)L.chunk_cap));
+  }
+  k_ranmars_chunk_states<<<nblocks, RM_THREADS, 0, c->stream>>>(L.state[0], L.jumpT, L.chunk_state);
+  CUDA_TRY(cudaGetLastError());
+  c->launches++;
+  // the per-evaluation hop J^nnum, transposed
+  std::vector<uint32_t> M((size_t)RM_LAG * RM_LAG), T((size_t)RM_LAG * RM_LAG);
+  ranmars_jump_matrix(nnum, M.data());
+  for (int i = 0; i < RM_LAG; i++)
+    for (int j = 0; j < RM_LAG; j++) T[(size_t)j * RM_LAG + i] = M[(size_t)i * RM_LAG + j];
+  if (!L.stepT) CUDA_TRY(cudaMalloc(&L.stepT, sizeof(uint32_t) * T.size()));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));   // T is a local; also orders against earlier fills
+  CUDA_TRY(cudaMemcpy(L.stepT, T.data(), sizeof(uint32_t) * T.size(), cudaMemcpyHostToDevice));
+  L.stride = nnum;
+  L.nevals = 0;
   return B200MD_OK;
 }
 
@@ -159,13 +215,13 @@ static int ranmars_fill(b200md_ctx *c, int nnum) {
     L.rnd_cap = nnum + nnum / 8 + 1024;
     CUDA_TRY(cudaMalloc(&L.rnd, sizeof(uint32_t) * (size_t)L.rnd_cap));
   }
+  if (L.stride != nnum) TRY(ranmars_layout(c, nnum));   // first evaluation, or the atom count changed
   const int nblocks = (nnum + RM_CHUNK - 1) / RM_CHUNK;
-  if (nblocks >= (1 << RM_LEVELS)) { b200md_set_error("b200md: fix langevin: too many atoms for one random stream"); return B200MD_ERR; }
-  k_ranmars_fill<<<nblocks, RM_THREADS, 0, c->stream>>>(L.state[L.cur], L.state[L.cur ^ 1], L.jumpT, L.position, nnum, L.rnd);
+  k_ranmars_fill<<<nblocks, RM_THREADS, 0, c->stream>>>(L.chunk_state, L.stepT, L.position, nnum, L.rnd);
   CUDA_TRY(cudaGetLastError());
   c->launches++;
-  L.cur ^= 1;
   L.position += nnum;
+  L.nevals++;
   return B200MD_OK;
 }
 
@@ -283,8 +339,6 @@ int langevin_test_stream(b200md_ctx *c, int seed, int n, int fills, double *out)
     }
     for (int i = 0; i < n; i++) out[(size_t)k * n + i] = (double)h[i] * (1.0 / 16777216.0);
   }
-  Langevin tmp = c->lang;
-  c->lang = tmp;
   langevin_free(c);
   c->lang = saved;
   return rc;

@@ -100,6 +100,7 @@ def in_chain(ctx, data_path, x=1, y=1, z=1, list_kind=B.LIST_HALF_NEWTON, langev
     cn, cmax = B.cutneighsq_table(1, T["cutsq"], skin)
     sel = np.flatnonzero(own)
     if langevin:
+        sel = d["local_order"][own[d["local_order"]]]        # the reference's local order before its set-up
         sel = sel[atom_sort_order(xs[sel], sublo, subhi, cmax)]
     ctx.set_atoms(xs[sel], d["v"][sel], d["type"][sel], d["tag"][sel], d["mass"], image=d["image"][sel])
     if langevin:

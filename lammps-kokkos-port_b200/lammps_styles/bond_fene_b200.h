@@ -19,6 +19,7 @@ class BondFENEB200 : public BondFENE, public B200BondStyle {
   BondFENEB200(class LAMMPS *lmp) : BondFENE(lmp) {}
   void compute(int, int) override;
   int b200_push_bond(b200md_ctx *ctx) override;
+  int b200_peratom_bond(b200md_ctx *ctx, int eflag, int vflag, const int *rows, int n) override;
 };
 
 }    // namespace LAMMPS_NS

@@ -18,6 +18,13 @@ using namespace LAMMPS_NS;
   if (b200md_pair_compute(B200Shared::ctx, eflag, vflag, &eng_vdwl, virial))                         \
     error->one(FLERR, b200md_last_error())
 
+#define B200_EAM_PERATOM()                                                                          \
+  ev_init(eflag, vflag);                                                                             \
+  return b200_fetch_peratom(ctx, B200MD_PERATOM_PAIR, eflag_atom, vflag_atom, eatom, vatom, rows, n)
+
+int PairEAMB200::b200_peratom(b200md_ctx *ctx, int eflag, int vflag, const int *rows, int n) { B200_EAM_PERATOM(); }
+int PairEAMAlloyB200::b200_peratom(b200md_ctx *ctx, int eflag, int vflag, const int *rows, int n) { B200_EAM_PERATOM(); }
+int PairEAMFSB200::b200_peratom(b200md_ctx *ctx, int eflag, int vflag, const int *rows, int n) { B200_EAM_PERATOM(); }
 int PairEAMB200::b200_push(b200md_ctx *ctx) { return B200_EAM_PUSH(); }
 void PairEAMB200::compute(int eflag, int vflag) { B200_EAM_COMPUTE("eam/b200"); }
 int PairEAMAlloyB200::b200_push(b200md_ctx *ctx) { return B200_EAM_PUSH(); }

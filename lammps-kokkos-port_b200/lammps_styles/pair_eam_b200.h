@@ -23,6 +23,7 @@ class PairEAMB200 : public PairEAM, public B200PairStyle {
   PairEAMB200(class LAMMPS *lmp) : PairEAM(lmp) { no_virial_fdotr_compute = 1; }
   void compute(int, int) override;
   int b200_push(b200md_ctx *ctx) override;
+  int b200_peratom(b200md_ctx *ctx, int eflag, int vflag, const int *rows, int n) override;
 };
 
 class PairEAMAlloyB200 : public PairEAMAlloy, public B200PairStyle {
@@ -30,6 +31,7 @@ class PairEAMAlloyB200 : public PairEAMAlloy, public B200PairStyle {
   PairEAMAlloyB200(class LAMMPS *lmp) : PairEAM(lmp), PairEAMAlloy(lmp) { no_virial_fdotr_compute = 1; }
   void compute(int, int) override;
   int b200_push(b200md_ctx *ctx) override;
+  int b200_peratom(b200md_ctx *ctx, int eflag, int vflag, const int *rows, int n) override;
 };
 
 class PairEAMFSB200 : public PairEAMFS, public B200PairStyle {
@@ -37,6 +39,7 @@ class PairEAMFSB200 : public PairEAMFS, public B200PairStyle {
   PairEAMFSB200(class LAMMPS *lmp) : PairEAM(lmp), PairEAMFS(lmp) { no_virial_fdotr_compute = 1; }
   void compute(int, int) override;
   int b200_push(b200md_ctx *ctx) override;
+  int b200_peratom(b200md_ctx *ctx, int eflag, int vflag, const int *rows, int n) override;
 };
 
 }    // namespace LAMMPS_NS

@@ -26,3 +26,9 @@ void PairLJCutB200::compute(int eflag, int vflag)
   if (b200md_pair_compute(B200Shared::ctx, eflag, vflag, &eng_vdwl, virial))
     error->one(FLERR, b200md_last_error());
 }
+
+int PairLJCutB200::b200_peratom(b200md_ctx *ctx, int eflag, int vflag, const int *rows, int n)
+{
+  ev_init(eflag, vflag);    // allocates / clears eatom, vatom (owned + ghost rows)
+  return b200_fetch_peratom(ctx, B200MD_PERATOM_PAIR, eflag_atom, vflag_atom, eatom, vatom, rows, n);
+}

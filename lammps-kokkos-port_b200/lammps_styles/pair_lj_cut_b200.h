@@ -18,6 +18,7 @@ class PairLJCutB200 : public PairLJCut, public B200PairStyle {
   PairLJCutB200(class LAMMPS *lmp);
   void compute(int, int) override;
   int b200_push(b200md_ctx *ctx) override;
+  int b200_peratom(b200md_ctx *ctx, int eflag, int vflag, const int *rows, int n) override;
 };
 
 }    // namespace LAMMPS_NS

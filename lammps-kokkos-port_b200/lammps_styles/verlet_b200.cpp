@@ -191,9 +191,10 @@ void VerletB200::device_setup()
 
   force->setup();
   ev_set(update->ntimestep);
-  publish_tallies();
   host_stale = true;
   sync_host();
+  publish_peratom();    // clears the styles' global accumulators too (ev_setup): before the tallies
+  publish_tallies();
 }
 
 void VerletB200::setup(int flag)
@@ -233,6 +234,37 @@ void VerletB200::publish_tallies()
   if (force->bond && atom->molecular != Atom::ATOMIC) {
     if (b200md_bond_tallies(ctx, &force->bond->energy, force->bond->virial)) fail();
   }
+}
+
+/* ----------------------------------------------------------------------
+   Pair::eatom / vatom and Bond::eatom / vatom on steps where a compute asked for them
+   (Integrate::ev_set, src/integrate.cpp:131-183), read by compute pe/atom and stress/atom
+   (src/compute_pe_atom.cpp:92-170, src/compute_stress_atom.cpp:140-340).  The device returns
+   rows with the ghost contributions already summed into their owners; those computes still run
+   their own reverse_comm when newton is on, so the host gets a consistent ghost section
+   (Comm::borders: swap tables + ghost rows, which ev_setup leaves at zero).
+------------------------------------------------------------------------- */
+
+void VerletB200::publish_peratom()
+{
+  if (!(eflag & ENERGY_ATOM) && !(vflag & (VIRIAL_ATOM | VIRIAL_CENTROID))) return;
+  if (vflag & VIRIAL_CENTROID)
+    error->all(FLERR, "Run style verlet/b200 does not tally the centroid per-atom stress");
+  const int nlocal = atom->nlocal;
+  std::vector<int> rows(nlocal);
+  if (comm->nprocs == 1 && (int) host_index.size() == nlocal && (int) htag.size() == nlocal) {
+    for (int k = 0; k < nlocal; k++)
+      rows[k] = std::lower_bound(host_index.begin(), host_index.end(), std::make_pair(htag[k], 0))->second;
+  } else {
+    for (int k = 0; k < nlocal; k++) rows[k] = k;    // several ranks: the host arrays are in device order
+  }
+  if (force->newton) {
+    if (atom->map_style != Atom::MAP_NONE) atom->map_clear();
+    comm->borders();
+  }
+  if (dynamic_cast<B200PairStyle *>(force->pair)->b200_peratom(ctx, eflag, vflag, rows.data(), nlocal)) fail();
+  if (force->bond && atom->molecular != Atom::ATOMIC)
+    if (dynamic_cast<B200BondStyle *>(force->bond)->b200_peratom_bond(ctx, eflag, vflag, rows.data(), nlocal)) fail();
 }
 
 /* ----------------------------------------------------------------------
@@ -361,8 +393,9 @@ void VerletB200::run(int n)
     if (update->ntimestep == output->next) {
       // the last step of a chunk is evaluated with energy/virial tallies (Integrate::ev_set)
       ev_set(update->ntimestep);
-      publish_tallies();
       sync_host();
+      publish_peratom();
+      publish_tallies();
       timer->stamp();
       output->write(update->ntimestep);
       timer->stamp(Timer::OUTPUT);

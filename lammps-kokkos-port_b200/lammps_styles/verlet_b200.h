@@ -41,6 +41,7 @@ class VerletB200 : public Verlet {
   void device_setup();
   void push_topology();
   void publish_tallies();
+  void publish_peratom();
   void sync_host();
 };
 

@@ -70,9 +70,14 @@ def read_data(path):
 def replicate(d, nx, ny, nz):
     """`replicate nx ny nz` (src/replicate.cpp:146-150, 430-640): unmap by the image flags, copy
     into every replica cell (loops ix, iy, iz), remap into the enlarged box, tags / bond partners /
-    molecule ids offset by (iz*ny*nx + iy*nx + ix) * maxtag."""
+    molecule ids offset by (iz*ny*nx + iy*nx + ix) * maxtag.  Arrays come back sorted by tag;
+    `local_order` indexes them in the reference's local (creation) order — replica after replica,
+    the old atoms in their order inside each — which is what order-dependent host semantics
+    (Atom::sort's stable bins, hence fix langevin's draws) start from."""
     if (nx, ny, nz) == (1, 1, 1):
-        return d
+        out = dict(d)
+        out["local_order"] = np.arange(d["natoms"])
+        return out
     n = d["natoms"]
     prd = d["boxhi"] - d["boxlo"]
     img = d["image"]
@@ -105,7 +110,7 @@ def replicate(d, nx, ny, nz):
     out.update(natoms=n * nx * ny * nz, boxhi=newhi, x=np.concatenate(X)[o], v=np.concatenate(V)[o],
                type=np.concatenate(T)[o].astype(np.int32), tag=tag[o].astype(np.int32),
                molecule=np.concatenate(MOL)[o].astype(np.int32), image=np.concatenate(IMG)[o].astype(np.int32),
-               bonds=np.concatenate(BONDS))
+               bonds=np.concatenate(BONDS), local_order=np.argsort(o, kind="stable"))
     return out
 
 

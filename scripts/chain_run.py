@@ -1,4 +1,4 @@
-"""bench/in.chain without fix langevin on one GPU: thermo + timing.  python scripts/chain_run.py [steps] [half|full]"""
+"""bench/in.chain on one GPU: thermo + timing.  python scripts/chain_run.py [steps] [half|full|<replicate>] [langevin]"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import b200pkg
@@ -7,7 +7,7 @@ steps = int(sys.argv[1]) if len(sys.argv) > 1 else 100
 lk = B.LIST_FULL if (len(sys.argv) > 2 and sys.argv[2] == "full") else B.LIST_HALF_NEWTON
 rep = int(sys.argv[2]) if (len(sys.argv) > 2 and sys.argv[2].isdigit()) else 1
 ctx = B.Context(0)
-cfg = P.inputs.in_chain(ctx, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "data", "data.chain"), rep, rep, rep, list_kind=lk)
+cfg = P.inputs.in_chain(ctx, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "data", "data.chain"), rep, rep, rep, list_kind=lk, langevin="langevin" in sys.argv)
 ctx.setup()
 n = cfg["natoms"]
 t = ctx.thermo()

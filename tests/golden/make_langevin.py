@@ -5,6 +5,8 @@ chain_*  bench/in.chain exactly as the reference ships it (fix nve + fix langevi
          904297): forces after the set-up (`run 0`; they already hold the thermostat's drag and
          random force, FixLangevin::setup), thermo every 10 steps of the following 100
          (`run 10 pre no post no`, i.e. one uninterrupted run), x / v of every 8th tag at the end.
+rep212_* in.chain.scaled (replicate 2 1 2, 128 000 atoms) with the thermostat: thermo after `run 20`
+         (the draws follow the creation order `replicate` leaves, then Atom::sort).
 lj_*     the lj_n5 state with a temperature ramp and a scale factor
          (fix langevin 1.0 2.5 0.5 48271 scale 1 1.5), one `run 40`; x, v, f of all atoms.  The
          RanMars draws follow the reference's local atom order, so that order (tags) is stored.
@@ -44,6 +46,17 @@ def main():
     out["chain_series"] = np.array(series)
     out["chain_x_every8"] = R.gather("x", 3)[::8].copy()
     out["chain_v_every8"] = R.gather("v", 3)[::8].copy()
+    R.close()
+
+    # in.chain.scaled with -var x 2 -var y 1 -var z 2 (128 000 atoms) + the thermostat: thermo only
+    R = O.Reference(args=("-log", "none", "-echo", "none", "-nocite"))
+    R.command(IN_CHAIN.format(data=os.path.join(os.path.dirname(O.POT_DIR), "data", "data.chain")).replace(
+        "neighbor 0.4 bin", "replicate 2 1 2\nneighbor 0.4 bin"))
+    R.command(CHAIN_FIX)
+    R.command("thermo_style custom step temp pe ke press evdwl emol")
+    R.command("thermo_modify norm no")
+    R.command("run 20")
+    out["rep212_thermo20"] = np.array([R.thermo(k) for k in KW])
     R.close()
 
     R = O.Reference()

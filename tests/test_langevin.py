@@ -133,6 +133,29 @@ def test_oracle_chain_langevin(pkg, oracle_mod):
     o.close()
 
 
+def test_oracle_chain_replicated_langevin(pkg, oracle_mod):
+    """in.chain.scaled 2x1x2: `replicate` leaves the atoms in creation order (src/replicate.cpp:431-640),
+    Atom::sort is stable on top of it, and the draws follow"""
+    import test_chain as Tc
+    Tc.need_data()
+    G = golden()
+    M, B = pkg.molecule_host, pkg.b200md
+    d = M.replicate(M.read_data(Tc.DATA), 2, 1, 2)
+    lo = d["local_order"]
+    tp = M.build_topology(d["natoms"], d["bonds"])
+    o = oracle_mod.Oracle(d["boxlo"], d["boxhi"], d["x"][lo], d["v"][lo], d["type"][lo], d["tag"][lo], d["mass"], B.UNITS["lj"])
+    T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 1.12)}, 1.12, shift=True)
+    o.pair_lj(T); o.set_topology(tp)
+    o.bond_fene([0.0, 30.0], [0.0, 1.5], [0.0, 1.0], [0.0, 1.0])
+    cn, cmax = B.cutneighsq_table(1, T["cutsq"], 0.4)
+    o.neigh_config(cn, cmax, 0.4, 1, 1, 1, True)
+    o.atom_sort()
+    o.fix_langevin(1.0, 1.0, 10.0, 904297, 0.012)
+    o.setup()
+    close(tvec(o.run(20, 0.012, 0)[-1]), G["rep212_thermo20"], 1e-9)
+    o.close()
+
+
 def test_oracle_lj_langevin_ramp(pkg, oracle_mod):
     G = golden()
     B = pkg.b200md
@@ -197,6 +220,19 @@ def test_cuda_chain_langevin(pkg, half):
     series = [ctx.run(10, 0.012, 0)[-1] for _ in range(10)]
     a = ctx.get_atoms()
     check_chain(G, after, series, (a["tag"], a["x"], a["v"]))
+    ctx.close()
+
+
+@pytest.mark.gpu
+def test_cuda_chain_replicated_langevin(pkg):
+    import test_chain as Tc
+    Tc.need_data()
+    G = golden()
+    B = pkg.b200md
+    ctx = B.Context(0)
+    pkg.inputs.in_chain(ctx, Tc.DATA, 2, 1, 2, langevin=True)
+    ctx.setup()
+    close(tvec(ctx.run(20, 0.012, 0)[-1]), G["rep212_thermo20"], T_TOL)
     ctx.close()
 
 

@@ -236,6 +236,48 @@ def test_langevin_options_the_device_does_not_cover_fail_loudly():
     assert rc != 0 and "langevin/b200" in out
 
 
+PERATOM = """
+compute         pea all pe/atom
+compute         sta all stress/atom NULL
+compute         stv all stress/atom NULL virial
+variable        wpe atom c_pea*id
+variable        wxy atom c_sta[4]*id
+compute         r1 all reduce sum c_pea c_sta[1] c_sta[2] c_sta[3] c_stv[4] c_stv[5] c_stv[6] v_wpe v_wxy
+compute         r2 all reduce max c_pea c_sta[1] c_stv[6]
+compute         r3 all reduce min c_pea c_sta[1] c_stv[6]
+thermo_style    custom step temp pe press c_r1[*] c_r2[*] c_r3[*]
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["lj", "eam", "chain", "chain_newton_off"])
+def test_peratom_computes_match_reference_executable(case):
+    """compute pe/atom and stress/atom on top of the b200 styles (src/compute_pe_atom.cpp:92-170,
+    src/compute_stress_atom.cpp:140-340 read Pair::eatom/vatom and Bond::eatom/vatom): sums, extrema
+    and tag-weighted sums (which catch a permutation of the rows) against the reference executable."""
+    have_gpu_binary()
+    data = os.path.join(ROOT, "oracle", "_ref", "data", "data.chain")
+    if not (os.path.exists(LMP_REF) and os.path.exists(data)):
+        pytest.skip("oracle/_ref not built")
+    if case == "lj":
+        script = IN_LJ.format(n=6, thermo=20).replace("thermo_modify", PERATOM + "thermo_modify").replace("run             100", "run 40")
+    elif case == "eam":
+        script = IN_EAM.format(n=5, style="eam", coeff="1 1 %s/Cu_u3.eam" % POT).replace("thermo_modify", PERATOM + "thermo_modify").replace(
+            "thermo          50", "thermo 20").replace("run             100", "run 40")
+    else:
+        script = IN_CHAIN.format(data=data).replace("thermo_modify", PERATOM + "thermo_modify").replace(
+            "run             60", "run 40").replace("run             20\n", "")
+        if case == "chain_newton_off":
+            script = script.replace("special_bonds   fene", "special_bonds   fene\nnewton off on")
+    rc, out = run_lmp(LMP_B200, script, ("-sf", "b200"))
+    assert rc == 0, out[-2000:]
+    rc2, ref = run_lmp(LMP_REF, script)
+    assert rc2 == 0, ref[-2000:]
+    a, b = thermo_rows(out), thermo_rows(ref)
+    assert a.shape == b.shape == (3, 19)
+    np.testing.assert_allclose(a, b, rtol=2e-8, atol=1e-8 * np.abs(b).max())
+
+
 @pytest.mark.gpu
 def test_unsupported_setups_fail_loudly():
     """no silent host fallback: a fix the device loop does not cover is an error"""
