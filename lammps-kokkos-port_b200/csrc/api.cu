@@ -70,6 +70,7 @@ extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out)
   if (const char *sp = getenv("B200MD_SPLIT")) c->split = atof(sp);
   if (const char *bl = getenv("B200MD_BUILD_LANES")) { c->tpa_build = atoi(bl); c->tpa_build_user = true; }   // tuning
   { const char *ov = getenv("B200MD_OVERLAP"); c->overlap = !(ov && ov[0] == '0'); }
+  { const char *hl = getenv("B200MD_HALO"); c->direct.on = hl && !strcmp(hl, "direct") && nranks > 1; }
   CUDA_TRY(cudaMalloc(&c->d_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMallocHost(&c->h_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMalloc(&c->d_flags, 8 * sizeof(int)));
@@ -92,7 +93,7 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
   void *ptrs[] = {c->xq, c->xq_tmp, c->cell_xq, c->v, c->v_tmp, c->f, c->xhold, c->tag, c->tag_tmp, c->image,
                   c->image_tmp, c->mass, c->cutneighsq, c->atom_bin, c->cell_count, c->cell_start, c->cell_fill,
                   c->cell_atoms, c->perm, c->scan_block, c->row_off, c->row_sx, c->row_flag, c->neigh, c->numneigh,
-                  c->ghost_src, c->ghost_pbc, c->sendbuf, c->recvbuf, c->ljtab, c->rho, c->fp, c->partials,
+                  c->ghost_src, c->ghost_pbc, c->ghost_rank, c->sendbuf, c->recvbuf, c->ljtab, c->rho, c->fp, c->partials,
                   c->d_result, c->d_flags, c->stage, c->tile_ghost, c->tile_pos, c->tiles_int, c->tiles_bnd};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->h_result) cudaFreeHost(c->h_result);

@@ -13,6 +13,9 @@
 // grouped ncclSend/ncclRecv of packed double4 records over NVLink, received in place into
 // the ghost slots (ghosts of one swap are contiguous), both directions of a dimension in
 // one NCCL group.  One process per GPU; the unique id is distributed by the launcher.
+// B200MD_HALO=direct (opt-in): the staged borders additionally carry each ghost's owner (rank, index,
+// shift); per-step forward / reverse traffic then goes owner <-> holder directly in ONE NCCL group
+// (a message per peer rank) instead of three dependent stages — see "direct halo" below.
 #include <nccl.h>
 #include <algorithm>
 #include "ctx.h"
@@ -59,6 +62,15 @@ extern "C" int b200md_comm_init(b200md_ctx *c, const void *id128) {
 void comm_free(b200md_ctx *c) {
   for (auto &s : c->swaps) if (s.sendlist) cudaFree(s.sendlist);
   c->swaps.clear();
+  DirectHalo &D = c->direct;
+  if (D.req_idx) cudaFree(D.req_idx);
+  if (D.ghost_slot) cudaFree(D.ghost_slot);
+  if (D.serve_idx) cudaFree(D.serve_idx);
+  if (D.d_cnt) cudaFree(D.d_cnt);
+  if (D.h_cnt) cudaFreeHost(D.h_cnt);
+  D.req_idx = D.ghost_slot = D.serve_idx = D.d_cnt = D.h_cnt = nullptr;
+  D.req_cap = D.serve_cap = 0;
+  D.ready = false;
   if (c->nccl) {
     if (c->nccl->comm) ncclCommDestroy(c->nccl->comm);
     if (c->nccl->d_counts) cudaFree(c->nccl->d_counts);
@@ -139,7 +151,8 @@ __device__ __forceinline__ double shift_n(double x, int n, double prd) {
 // self swap of borders: append ghosts, record flattened source
 __global__ void k_self_border(int n, const int *__restrict__ list, int first, int nlocal, double4 *__restrict__ xq,
                               int *__restrict__ tag, int *__restrict__ ghost_src, int *__restrict__ ghost_pbc,
-                              int px, int py, int pz, double prdx, double prdy, double prdz) {
+                              int px, int py, int pz, double prdx, double prdy, double prdz,
+                              int *__restrict__ ghost_rank, int me) {
   int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
   const int j = list[k];
@@ -151,6 +164,19 @@ __global__ void k_self_border(int n, const int *__restrict__ list, int first, in
   if (j >= nlocal) { src = ghost_src[j]; code = ghost_pbc[j]; }
   ghost_src[first + k] = src;
   ghost_pbc[first + k] = pbc_code_add(code, px, py, pz);
+  if (ghost_rank) ghost_rank[first + k] = j >= nlocal ? ghost_rank[j] : me;   // direct halo: the owner's rank
+}
+// direct halo: owner (index on its rank, accumulated shift, rank) of every atom of a remote border swap
+__global__ void k_pack_border_owner(int n, const int *__restrict__ list, int nlocal, int me,
+                                    const int *__restrict__ ghost_src, const int *__restrict__ ghost_pbc,
+                                    const int *__restrict__ ghost_rank, int px, int py, int pz,
+                                    int *__restrict__ o_src, int *__restrict__ o_code, int *__restrict__ o_rank) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int j = list[k];
+  int src = j, code = PBC_ZERO, rk = me;
+  if (j >= nlocal) { src = ghost_src[j]; code = ghost_pbc[j]; rk = ghost_rank[j]; }
+  o_src[k] = src; o_code[k] = pbc_code_add(code, px, py, pz); o_rank[k] = rk;
 }
 // remote swap: packed records (positions with shift) + tags
 __global__ void k_pack_border(int n, const int *__restrict__ list, const double4 *__restrict__ xq,
@@ -209,6 +235,186 @@ static int ensure_buf(double *&p, size_t &cap, size_t need_doubles) {
 }
 
 static inline int nblk(int n) { return (n + 255) / 256; }
+
+// ---------------------------------------------------------------------------------------
+// direct halo (B200MD_HALO=direct)
+// The reference forwards ghosts dimension by dimension (x, then y including the x-ghosts, then z):
+// 3 dependent stages of 2 messages, which on NVLink cost latency, not bandwidth.  Once the staged
+// borders have run, each ghost's owner is known, so every later forward_comm / reverse_comm of the
+// same list goes owner <-> holder in one hop: ghosts are grouped by owner rank (request lists are
+// exchanged once per rebuild), and a step needs one pack kernel, ONE NCCL group with one send and
+// one receive per peer rank, and one unpack kernel that applies the accumulated periodic shift
+// exactly as the stages would have (one add of prd per crossed image and dimension).
+// ---------------------------------------------------------------------------------------
+__global__ void k_direct_count(int nghost, int nlocal, const int *__restrict__ ghost_rank, int *__restrict__ cnt) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= nghost) return;
+  atomicAdd(&cnt[ghost_rank[nlocal + g]], 1);
+}
+__global__ void k_direct_scatter(int nghost, int nlocal, const int *__restrict__ ghost_rank, const int *__restrict__ ghost_src,
+                                 int *__restrict__ cursor, int *__restrict__ req_idx, int *__restrict__ ghost_slot) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= nghost) return;
+  const int pos = atomicAdd(&cursor[ghost_rank[nlocal + g]], 1);
+  req_idx[pos] = ghost_src[nlocal + g];
+  ghost_slot[pos] = nlocal + g;
+}
+template <bool SCALAR>
+__global__ void k_direct_pack(int n, const int *__restrict__ serve_idx, const double4 *__restrict__ xq,
+                              const double *__restrict__ a, double *__restrict__ buf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  if (SCALAR) buf[k] = a[serve_idx[k]];
+  else reinterpret_cast<double4 *>(buf)[k] = xq[serve_idx[k]];
+}
+// requests [0, nremote) were answered through buf, [nremote, n) are images of my own atoms
+template <bool SCALAR>
+__global__ void k_direct_unpack(int n, int nremote, const int *__restrict__ ghost_slot, const int *__restrict__ req_idx,
+                                const double *__restrict__ buf, double4 *__restrict__ xq, double *__restrict__ a,
+                                const int *__restrict__ ghost_pbc, double prdx, double prdy, double prdz) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int g = ghost_slot[k];
+  if (SCALAR) { a[g] = k < nremote ? buf[k] : a[req_idx[k]]; return; }
+  double4 q = k < nremote ? reinterpret_cast<const double4 *>(buf)[k] : xq[req_idx[k]];
+  const int code = ghost_pbc[g];
+  q.x = shift_n(q.x, (code & 15) - 8, prdx);
+  q.y = shift_n(q.y, ((code >> 4) & 15) - 8, prdy);
+  q.z = shift_n(q.z, ((code >> 8) & 15) - 8, prdz);
+  xq[g] = q;
+}
+template <int NV>
+__global__ void k_direct_rev_pack(int n, int nremote, int nmax, const int *__restrict__ ghost_slot,
+                                  const int *__restrict__ req_idx, double *__restrict__ a, double *__restrict__ buf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int g = ghost_slot[k];
+#pragma unroll
+  for (int d = 0; d < NV; d++) {
+    const double v = a[g + d * (size_t)nmax];
+    if (k < nremote) buf[(size_t)k * NV + d] = v;
+    else atomicAdd(&a[req_idx[k] + d * (size_t)nmax], v);
+  }
+}
+template <int NV>
+__global__ void k_direct_rev_unpack(int n, int nmax, const int *__restrict__ serve_idx, double *__restrict__ a,
+                                    const double *__restrict__ buf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int j = serve_idx[k];
+#pragma unroll
+  for (int d = 0; d < NV; d++) atomicAdd(&a[j + d * (size_t)nmax], buf[(size_t)k * NV + d]);
+}
+
+static int direct_setup(b200md_ctx *c) {
+  DirectHalo &D = c->direct;
+  NcclState *nc = c->nccl;
+  if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
+  cudaStream_t st = c->stream;
+  const int nr = c->nranks, me = c->rank, ng = c->nghost;
+  if (!D.d_cnt) {
+    CUDA_TRY(cudaMalloc(&D.d_cnt, sizeof(int) * (2 * nr + (size_t)nr * nr)));
+    CUDA_TRY(cudaMallocHost(&D.h_cnt, sizeof(int) * (2 * nr + (size_t)nr * nr)));
+  }
+  int *d_row = D.d_cnt, *d_cursor = D.d_cnt + nr, *d_mat = D.d_cnt + 2 * nr;
+  int *h_row = D.h_cnt, *h_cursor = D.h_cnt + nr, *h_mat = D.h_cnt + 2 * nr;
+  // my requests per owner rank, and everybody's (row p of the matrix = rank p's requests)
+  CUDA_TRY(cudaMemsetAsync(d_row, 0, sizeof(int) * nr, st));
+  if (ng) k_direct_count<<<nblk(ng), 256, 0, st>>>(ng, c->nlocal, c->ghost_rank, d_row);
+  NCCL_TRY(ncclAllGather(d_row, d_mat, nr, ncclInt, nc->comm, st));
+  CUDA_TRY(cudaMemcpyAsync(h_row, d_row, sizeof(int) * nr, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaMemcpyAsync(h_mat, d_mat, sizeof(int) * (size_t)nr * nr, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  D.req_cnt.assign(h_row, h_row + nr);
+  D.req_off.assign(nr, 0); D.serve_cnt.assign(nr, 0); D.serve_off.assign(nr, 0);
+  int off = 0, soff = 0;
+  for (int p = 0; p < nr; p++) {
+    if (p == me) continue;
+    D.req_off[p] = off; off += D.req_cnt[p];
+    D.serve_cnt[p] = h_mat[(size_t)p * nr + me];
+    D.serve_off[p] = soff; soff += D.serve_cnt[p];
+  }
+  D.nreq_remote = off;
+  D.req_off[me] = off; off += D.req_cnt[me];   // images of my own atoms last
+  D.nreq = off;
+  D.nserve = soff;
+  if (D.nreq != ng) { b200md_set_error("b200md: direct halo: a ghost without a valid owner rank"); return B200MD_ERR; }
+  if (D.nreq > D.req_cap) {
+    if (D.req_idx) CUDA_TRY(cudaFree(D.req_idx));
+    if (D.ghost_slot) CUDA_TRY(cudaFree(D.ghost_slot));
+    D.req_cap = D.nreq + D.nreq / 4 + 1024;
+    CUDA_TRY(cudaMalloc(&D.req_idx, sizeof(int) * D.req_cap));
+    CUDA_TRY(cudaMalloc(&D.ghost_slot, sizeof(int) * D.req_cap));
+  }
+  if (D.nserve > D.serve_cap) {
+    if (D.serve_idx) CUDA_TRY(cudaFree(D.serve_idx));
+    D.serve_cap = D.nserve + D.nserve / 4 + 1024;
+    CUDA_TRY(cudaMalloc(&D.serve_idx, sizeof(int) * D.serve_cap));
+  }
+  for (int p = 0; p < nr; p++) h_cursor[p] = D.req_off[p];
+  CUDA_TRY(cudaMemcpyAsync(d_cursor, h_cursor, sizeof(int) * nr, cudaMemcpyHostToDevice, st));
+  if (ng) k_direct_scatter<<<nblk(ng), 256, 0, st>>>(ng, c->nlocal, c->ghost_rank, c->ghost_src, d_cursor, D.req_idx, D.ghost_slot);
+  c->launches += 2;
+  // the request lists travel to the owners once per rebuild
+  NCCL_TRY(ncclGroupStart());
+  for (int p = 0; p < nr; p++) {
+    if (p == me) continue;
+    if (D.req_cnt[p]) NCCL_TRY(ncclSend(D.req_idx + D.req_off[p], D.req_cnt[p], ncclInt, p, nc->comm, st));
+    if (D.serve_cnt[p]) NCCL_TRY(ncclRecv(D.serve_idx + D.serve_off[p], D.serve_cnt[p], ncclInt, p, nc->comm, st));
+  }
+  NCCL_TRY(ncclGroupEnd());
+  CUDA_TRY(cudaGetLastError());
+  D.ready = true;
+  return B200MD_OK;
+}
+
+// owners -> holders: positions (shift applied by the holder) or one per-atom scalar
+template <bool SCALAR>
+static int direct_forward(b200md_ctx *c, double *arr) {
+  DirectHalo &D = c->direct;
+  NcclState *nc = c->nccl;
+  cudaStream_t st = c->stream;
+  const int rec = SCALAR ? 1 : 4, nr = c->nranks, me = c->rank;
+  TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)D.nserve * rec + 8));
+  TRY(ensure_buf(c->recvbuf, c->recvcap, (size_t)D.nreq_remote * rec + 8));
+  if (D.nserve) { k_direct_pack<SCALAR><<<nblk(D.nserve), 256, 0, st>>>(D.nserve, D.serve_idx, c->xq, arr, c->sendbuf); c->launches++; }
+  NCCL_TRY(ncclGroupStart());
+  for (int p = 0; p < nr; p++) {
+    if (p == me) continue;
+    if (D.serve_cnt[p]) NCCL_TRY(ncclSend(c->sendbuf + (size_t)D.serve_off[p] * rec, (size_t)D.serve_cnt[p] * rec, ncclDouble, p, nc->comm, st));
+    if (D.req_cnt[p]) NCCL_TRY(ncclRecv(c->recvbuf + (size_t)D.req_off[p] * rec, (size_t)D.req_cnt[p] * rec, ncclDouble, p, nc->comm, st));
+  }
+  NCCL_TRY(ncclGroupEnd());
+  if (D.nreq) {
+    k_direct_unpack<SCALAR><<<nblk(D.nreq), 256, 0, st>>>(D.nreq, D.nreq_remote, D.ghost_slot, D.req_idx, c->recvbuf, c->xq, arr,
+                                                         c->ghost_pbc, c->prd[0], c->prd[1], c->prd[2]);
+    c->launches++;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
+// holders -> owners: every ghost copy adds its NV values straight into its owner (FP64 RED)
+template <int NV>
+static int direct_reverse(b200md_ctx *c, double *arr) {
+  DirectHalo &D = c->direct;
+  NcclState *nc = c->nccl;
+  cudaStream_t st = c->stream;
+  const int nr = c->nranks, me = c->rank;
+  TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)D.nreq_remote * NV + 8));
+  TRY(ensure_buf(c->recvbuf, c->recvcap, (size_t)D.nserve * NV + 8));
+  if (D.nreq) { k_direct_rev_pack<NV><<<nblk(D.nreq), 256, 0, st>>>(D.nreq, D.nreq_remote, c->nmax, D.ghost_slot, D.req_idx, arr, c->sendbuf); c->launches++; }
+  NCCL_TRY(ncclGroupStart());
+  for (int p = 0; p < nr; p++) {
+    if (p == me) continue;
+    if (D.req_cnt[p]) NCCL_TRY(ncclSend(c->sendbuf + (size_t)D.req_off[p] * NV, (size_t)D.req_cnt[p] * NV, ncclDouble, p, nc->comm, st));
+    if (D.serve_cnt[p]) NCCL_TRY(ncclRecv(c->recvbuf + (size_t)D.serve_off[p] * NV, (size_t)D.serve_cnt[p] * NV, ncclDouble, p, nc->comm, st));
+  }
+  NCCL_TRY(ncclGroupEnd());
+  if (D.nserve) { k_direct_rev_unpack<NV><<<nblk(D.nserve), 256, 0, st>>>(D.nserve, c->nmax, D.serve_idx, arr, c->recvbuf); c->launches++; }
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
 
 // ---------------------------------------------------------------------------------------
 // borders
@@ -374,25 +580,42 @@ int comm_borders(b200md_ctx *c) {
         if (self) {
           if (ns)
             k_self_border<<<nblk(ns), 256, 0, st>>>(ns, s.sendlist, first, c->nlocal, c->xq, c->tag, c->ghost_src,
-                                                   c->ghost_pbc, s.pbc[0], s.pbc[1], s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
+                                                   c->ghost_pbc, s.pbc[0], s.pbc[1], s.pbc[2], c->prd[0], c->prd[1], c->prd[2],
+                                                   c->direct.on ? c->ghost_rank : nullptr, c->rank);
           c->launches++;
         } else {
           NcclState *nc = c->nccl;
-          TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)ns * 5 + 8));
+          const bool owner = c->direct.on;
+          TRY(ensure_buf(c->sendbuf, c->sendcap, (size_t)ns * 7 + 16));
           double4 *buf = reinterpret_cast<double4 *>(c->sendbuf);
           int *tagbuf = reinterpret_cast<int *>(c->sendbuf + (size_t)ns * 4);
-          if (ns)
+          int *o_src = tagbuf + ns, *o_code = o_src + ns, *o_rank = o_code + ns;
+          if (ns) {
             k_pack_border<<<nblk(ns), 256, 0, st>>>(ns, s.sendlist, c->xq, c->tag, buf, tagbuf, s.pbc[0], s.pbc[1],
                                                    s.pbc[2], c->prd[0], c->prd[1], c->prd[2]);
+            if (owner)
+              k_pack_border_owner<<<nblk(ns), 256, 0, st>>>(ns, s.sendlist, c->nlocal, c->rank, c->ghost_src, c->ghost_pbc,
+                                                           c->ghost_rank, s.pbc[0], s.pbc[1], s.pbc[2], o_src, o_code, o_rank);
+          }
           c->launches++;
           NCCL_TRY(ncclGroupStart());
           if (ns) {
             NCCL_TRY(ncclSend(buf, (size_t)ns * 4, ncclDouble, s.sendproc, nc->comm, st));
             NCCL_TRY(ncclSend(tagbuf, ns, ncclInt, s.sendproc, nc->comm, st));
+            if (owner) {
+              NCCL_TRY(ncclSend(o_src, ns, ncclInt, s.sendproc, nc->comm, st));
+              NCCL_TRY(ncclSend(o_code, ns, ncclInt, s.sendproc, nc->comm, st));
+              NCCL_TRY(ncclSend(o_rank, ns, ncclInt, s.sendproc, nc->comm, st));
+            }
           }
           if (nrecv) {
             NCCL_TRY(ncclRecv(c->xq + first, (size_t)nrecv * 4, ncclDouble, s.recvproc, nc->comm, st));
             NCCL_TRY(ncclRecv(c->tag + first, nrecv, ncclInt, s.recvproc, nc->comm, st));
+            if (owner) {
+              NCCL_TRY(ncclRecv(c->ghost_src + first, nrecv, ncclInt, s.recvproc, nc->comm, st));
+              NCCL_TRY(ncclRecv(c->ghost_pbc + first, nrecv, ncclInt, s.recvproc, nc->comm, st));
+              NCCL_TRY(ncclRecv(c->ghost_rank + first, nrecv, ncclInt, s.recvproc, nc->comm, st));
+            }
           }
           NCCL_TRY(ncclGroupEnd());
         }
@@ -403,6 +626,8 @@ int comm_borders(b200md_ctx *c) {
     }
   }
   CUDA_TRY(cudaGetLastError());
+  c->direct.ready = false;
+  if (c->direct.on && !c->all_self) TRY(direct_setup(c));
   return B200MD_OK;
 }
 
@@ -473,6 +698,7 @@ int comm_forward(b200md_ctx *c) {
     CUDA_TRY(cudaGetLastError());
     return B200MD_OK;
   }
+  if (c->direct.ready) return direct_forward<false>(c, nullptr);
   return forward_staged<false>(c, nullptr);
 }
 
@@ -484,6 +710,7 @@ int comm_forward_scalar(b200md_ctx *c, double *arr) {
     CUDA_TRY(cudaGetLastError());
     return B200MD_OK;
   }
+  if (c->direct.ready) return direct_forward<true>(c, arr);
   return forward_staged<true>(c, arr);
 }
 
@@ -693,6 +920,7 @@ int comm_reverse_force(b200md_ctx *c) {
     CUDA_TRY(cudaGetLastError());
     return B200MD_OK;
   }
+  if (c->direct.ready) return direct_reverse<3>(c, c->f);
   return reverse_staged<3>(c, c->f);
 }
 int comm_reverse_scalar(b200md_ctx *c, double *arr) {
@@ -708,6 +936,7 @@ int comm_reverse_column(b200md_ctx *c, double *arr) {
     CUDA_TRY(cudaGetLastError());
     return B200MD_OK;
   }
+  if (c->direct.ready) return direct_reverse<1>(c, arr);
   return reverse_staged<1>(c, arr);
 }
 int comm_reverse_rho(b200md_ctx *c) { return comm_reverse_scalar(c, c->rho); }

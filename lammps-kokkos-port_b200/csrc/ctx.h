@@ -95,6 +95,22 @@ struct Swap {
   int sendcap = 0;
 };
 
+// "direct" halo (comm.cu, B200MD_HALO=direct): after the staged borders have placed the ghosts, every
+// ghost knows its OWNER (rank, index on that rank, accumulated periodic shift), so the per-step
+// traffic no longer has to be forwarded dimension by dimension: one pack, ONE NCCL group with a
+// message per peer rank, one unpack — instead of three dependent pack/group stages.
+struct DirectHalo {
+  bool on = false, ready = false;
+  int nreq = 0, nreq_remote = 0, nserve = 0;
+  std::vector<int> req_cnt, req_off, serve_cnt, serve_off;  // per rank; my requests to / the requests I serve for rank p
+  int *req_idx = nullptr;     // device [nreq]   index on the owner, grouped by owner rank (self last)
+  int *ghost_slot = nullptr;  // device [nreq]   my ghost that request fills
+  int *serve_idx = nullptr;   // device [nserve] my owned atoms other ranks asked for, grouped by asking rank
+  int req_cap = 0, serve_cap = 0;
+  int *d_cnt = nullptr;       // device [nranks] + [nranks] cursor + [nranks*nranks] gathered matrix
+  int *h_cnt = nullptr;       // pinned, same layout
+};
+
 struct b200md_ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
@@ -165,6 +181,8 @@ struct b200md_ctx {
   NcclState *nccl = nullptr;
   int *ghost_src = nullptr;       // single-rank fast path: flattened owner index per ghost
   int *ghost_pbc = nullptr;       // packed periodic-shift multiples (px+8)|(py+8)<<4|(pz+8)<<8
+  int *ghost_rank = nullptr;      // owner rank per ghost (direct halo)
+  DirectHalo direct;
   bool all_self = true;           // every swap partner is this rank -> flattened forward path
   double *sendbuf = nullptr, *recvbuf = nullptr;
   size_t sendcap = 0, recvcap = 0;

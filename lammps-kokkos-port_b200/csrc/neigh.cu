@@ -106,6 +106,7 @@ int neigh_grow_atoms(b200md_ctx *c, int need) {
   TRY(regrow(c->numneigh, 0, newcap, s));
   TRY(regrow(c->ghost_src, used, newcap, s));
   TRY(regrow(c->ghost_pbc, used, newcap, s));
+  TRY(regrow(c->ghost_rank, used, newcap, s));
   TRY(regrow(c->rho, 0, newcap, s));
   TRY(regrow(c->fp, 0, newcap, s));
   c->nmax = (int)newcap;

@@ -75,6 +75,132 @@ def _worker(rank, world, port, out):
     dist.destroy_process_group()
 
 
+def _xchg(payload, width, sendproc, recvproc, rank):
+    """one swap's message: to sendproc, from recvproc (self swaps are a copy)"""
+    payload = torch.from_numpy(np.ascontiguousarray(payload, dtype=np.float64).reshape(-1, width))
+    if sendproc == rank:
+        return payload.numpy().copy()
+    nsend = torch.tensor([payload.shape[0]]); nrecv = torch.zeros(1, dtype=torch.int64)
+    [r.wait() for r in (dist.isend(nsend, sendproc), dist.irecv(nrecv, recvproc))]
+    recv = torch.zeros((int(nrecv), width), dtype=torch.float64)
+    [r.wait() for r in (dist.isend(payload, sendproc), dist.irecv(recv, recvproc))]
+    return recv.numpy()
+
+
+def _worker_direct(rank, world, port, out):
+    """the direct halo of csrc/comm.cu (B200MD_HALO=direct) restated over gloo: the staged borders carry
+    every ghost's owner (rank, index, shift code); forward / reverse traffic then goes owner <-> holder in
+    one all-to-all and must reproduce the staged forward_comm bit for bit and the staged reverse_comm sums"""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import b200pkg
+    B = b200pkg.load().b200md
+    scale, n = 3.615, (8, 4, 4)
+    boxlo, boxhi = [0.0] * 3, [n[0] * scale, n[1] * scale, n[2] * scale]
+    prd = np.array(boxhi) - np.array(boxlo)
+    cut = 5.95
+    grid = B.procgrid(world, prd)
+    loc = B.rank2loc(rank, grid)
+    sublo, subhi = B.local_box(boxlo, boxhi, grid, loc)
+    x, v, tag = B.lattice_fcc(scale, *n, sublo, subhi, 376847, 63.55)
+    s = B.comm_schedule(boxlo, boxhi, [1, 1, 1], grid, loc, cut)
+    nlocal = len(tag)
+    X, T = x.copy(), tag.astype(np.int64)
+    own_rank = np.full(nlocal, rank, np.int64); own_idx = np.arange(nlocal, dtype=np.int64)
+    code = np.zeros((nlocal, 3), np.int64)
+    swaps = []
+    iswap = 0
+    for dim in range(3):
+        nlast = 0
+        for ineed in range(2 * s.maxneed[dim]):
+            if ineed % 2 == 0:
+                nfirst, nlast = nlast, len(T)
+            sel = np.nonzero((X[nfirst:nlast, dim] >= s.slablo[iswap]) & (X[nfirst:nlast, dim] <= s.slabhi[iswap]))[0] + nfirst \
+                if s.sendflag[iswap] else np.empty(0, np.int64)
+            pbc = np.array([s.pbc[iswap][d] for d in range(3)], np.int64)
+            buf = X[sel].copy()
+            for d in range(3):
+                buf[:, d] += pbc[d] * prd[d]
+            pay = np.concatenate([buf, T[sel, None], own_rank[sel, None], own_idx[sel, None], code[sel] + pbc], axis=1)
+            r = _xchg(pay, 9, s.sendproc[iswap], s.recvproc[iswap], rank)
+            swaps.append(dict(sendlist=sel, first=len(T), nrecv=len(r), sendproc=s.sendproc[iswap], recvproc=s.recvproc[iswap], pbc=pbc))
+            X = np.concatenate([X, r[:, :3]]); T = np.concatenate([T, r[:, 3].astype(np.int64)])
+            own_rank = np.concatenate([own_rank, r[:, 4].astype(np.int64)]); own_idx = np.concatenate([own_idx, r[:, 5].astype(np.int64)])
+            code = np.concatenate([code, r[:, 6:9].astype(np.int64)])
+            iswap += 1
+    nall = len(T)
+    # the owned atoms move (a deterministic function of the tag), ghosts are stale
+    rng_shift = lambda t: 0.05 * np.stack([np.sin(t * 0.37), np.cos(t * 0.11), np.sin(t * 0.23 + 1.0)], axis=1)
+    Xn = X.copy(); Xn[:nlocal] += rng_shift(T[:nlocal].astype(np.float64))
+    # --- staged forward_comm (comm_brick.cpp:538-591) ---
+    Xs = Xn.copy()
+    for sw in swaps:
+        buf = Xs[sw["sendlist"]].copy()
+        for d in range(3):
+            buf[:, d] += sw["pbc"][d] * prd[d]
+        r = _xchg(buf, 3, sw["sendproc"], sw["recvproc"], rank)
+        Xs[sw["first"]:sw["first"] + sw["nrecv"]] = r
+    # --- direct: requests grouped by owner rank, lists exchanged once, one all-to-all per step ---
+    g = np.arange(nlocal, nall)
+    req = {p: g[own_rank[g] == p] for p in range(world)}
+    serve = {}
+    for p in range(world):
+        if p == rank:
+            continue
+        cnt_out = torch.tensor([len(req[p])]); cnt_in = torch.zeros(1, dtype=torch.int64)
+        [r.wait() for r in (dist.isend(cnt_out, p), dist.irecv(cnt_in, p))]
+        lst = torch.zeros(int(cnt_in), dtype=torch.int64)
+        [r.wait() for r in (dist.isend(torch.from_numpy(own_idx[req[p]].copy()), p), dist.irecv(lst, p))]
+        serve[p] = lst.numpy()
+    Xd = Xn.copy()
+    for p in range(world):
+        if p == rank:
+            src = Xn[own_idx[req[p]]]
+        else:
+            recv = torch.zeros((len(req[p]), 3), dtype=torch.float64)
+            [r.wait() for r in (dist.isend(torch.from_numpy(Xn[serve[p]].copy()), p), dist.irecv(recv, p))]
+            src = recv.numpy()
+        q = src.copy()
+        for d in range(3):          # one add of prd per crossed image, like the stages (comm.cu shift_n)
+            c = code[req[p], d]
+            for k in range(1, int(np.abs(c).max(initial=0)) + 1):
+                q[:, d] = np.where(c >= k, q[:, d] + prd[d], np.where(-c >= k, q[:, d] - prd[d], q[:, d]))
+        Xd[req[p]] = q
+    same_forward = bool(np.array_equal(Xd, Xs))
+    # --- reverse: every copy holds a value; owners must receive the same sums either way ---
+    W = np.zeros(nall); W[nlocal:] = np.cos(T[nlocal:] * 0.7 + rank) + 0.1 * np.arange(nall - nlocal)
+    Ws = W.copy()
+    for sw in reversed(swaps):
+        r = _xchg(Ws[sw["first"]:sw["first"] + sw["nrecv"]], 1, sw["recvproc"], sw["sendproc"], rank)[:, 0]
+        np.add.at(Ws, sw["sendlist"], r)
+    Wd = W.copy()
+    for p in range(world):
+        if p == rank:
+            np.add.at(Wd, own_idx[req[p]], W[req[p]])
+        else:
+            recv = torch.zeros(len(serve[p]), dtype=torch.float64)
+            [r.wait() for r in (dist.isend(torch.from_numpy(W[req[p]].copy()), p), dist.irecv(recv, p))]
+            np.add.at(Wd, serve[p], recv.numpy())
+    rev_err = float(np.abs(Wd[:nlocal] - Ws[:nlocal]).max() / np.abs(Ws[:nlocal]).max())
+    out[rank] = (same_forward, rev_err, nall - nlocal, int(sum(len(v) for v in serve.values())), int((code != 0).any(axis=1).sum()))
+    dist.destroy_process_group()
+
+
+def test_two_rank_direct_halo_over_gloo():
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker_direct, args=(world, 29543, out), nprocs=world, join=True)
+    assert len(out) == 2
+    for r in range(world):
+        same_forward, rev_err, nghost, nserve, nshifted = out[r]
+        assert nghost > 0 and nserve > 0 and nshifted > 0
+        assert same_forward, r            # ghost positions bit-identical to the staged forward_comm
+        assert rev_err < 1e-12, (r, rev_err)
+
+
 def test_two_rank_borders_over_gloo():
     world = 2
     mgr = mp.Manager()
