@@ -33,9 +33,11 @@ BYTES_KERNEL = {"lj": 28 * 75.2 + 52, "eam": 64 * 75.5 + 104,    # LJ force pass
 BYTES_STEP = {"lj": 2480.0, "eam": 5510.0, "chain": 750.0, "chain+langevin": 782.0}
 # (the figures above are SURVEY 8(d)'s yardstick, defined on the full list; the half-list kernels do
 #  the same physical work -- every pair once instead of twice -- and are rated with the same figure)
-# measured choice by workload and world size (2 = "two or more"), profiles/r01_summary.md: in.lj at N>1
-# keeps the full list (halo overlapped with the interior tiles, no reverse_comm); eam is faster on
-# the half list everywhere
+# measured choice on ONE GPU (profiles/r01_summary.md): the half/newton list wins everywhere.  On several
+# GPUs the better list kind depends on how much of the halo the force kernel hides (full: no reverse pass;
+# half: half the pair work), so `--list auto` MEASURES it there: 20 untimed steps of each kind before the
+# warm-up, the faster one (max over ranks) runs the timed region.  The table's N>1 column is only the
+# order in which the candidates are tried.
 LIST_AUTO = {"lj": {1: "half", 2: "full"}, "eam": {1: "half", 2: "half"}, "chain": {1: "half", 2: "half"}}
 # algorithmic bytes of the half-list kernels per atom per step (N_h listed pairs per atom, each:
 # 4 index + 24 x_j [+ 8 fp_j] gathered, 24 f_j [8 rho_j] as RED payload; plus the per-atom terms)
@@ -199,6 +201,9 @@ def main():
         cfg = P.inputs.in_eam(ctx, *xyz, potential=os.path.join(ROOT, "oracle", "_ref", "potentials", "Cu_u3.eam"),
                               list_kind=list_kind)
     config["decomposition"] = "x".join(str(g) for g in B.procgrid(world, [20.0 * xyz[0], 20.0 * xyz[1], 20.0 * xyz[2]]))
+    config["halo"] = ("none (one rank)" if world == 1 else
+                      "staged (3 x 2 NCCL send/recv stages)" if os.environ.get("B200MD_HALO") == "staged" else
+                      "direct (owner <-> holder, one NCCL group per exchange)")
     ctx.setup()
 
     def barrier():
@@ -214,6 +219,25 @@ def main():
         t = torch.tensor([v], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
+
+    # ---- several ranks, --list auto: the list kind is chosen by measurement (untimed, before the warm-up) ----
+    if world > 1 and a.list == "auto" and wl != "chain":
+        trial = {}
+        for kind in ("full", "half"):
+            ctx.neigh_config(**cfg["neigh"], list_kind=B.LIST_HALF_NEWTON if kind == "half" else B.LIST_FULL)
+            ctx.setup()
+            ctx.run(5, cfg["dt"], 0)
+            barrier()
+            t0 = time.perf_counter()
+            ctx.run(20, cfg["dt"], 0)
+            barrier()
+            trial[kind] = maxr((time.perf_counter() - t0) * 1e3) / 20
+        lk = min(trial, key=trial.get)
+        list_kind = B.LIST_HALF_NEWTON if lk == "half" else B.LIST_FULL
+        ctx.neigh_config(**cfg["neigh"], list_kind=list_kind)
+        ctx.setup()
+        config["neighbor_list"] = "half/bin/atomonly/newton" if lk == "half" else "full/bin/atomonly (newton off)"
+        config["list_trial_ms_per_step"] = trial
 
     # ---- device-resident loop: W warm-up steps, K timed steps ----
     ctx.run(max(a.warmup, 3), cfg["dt"], 0)

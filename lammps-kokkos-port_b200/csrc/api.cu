@@ -70,7 +70,9 @@ extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out)
   if (const char *sp = getenv("B200MD_SPLIT")) c->split = atof(sp);
   if (const char *bl = getenv("B200MD_BUILD_LANES")) { c->tpa_build = atoi(bl); c->tpa_build_user = true; }   // tuning
   { const char *ov = getenv("B200MD_OVERLAP"); c->overlap = !(ov && ov[0] == '0'); }
-  { const char *hl = getenv("B200MD_HALO"); c->direct.on = hl && !strcmp(hl, "direct") && nranks > 1; }
+  // per-step halo: owner <-> holder in one NCCL group ("direct", default on several ranks) or the
+  // reference's three forwarding stages (B200MD_HALO=staged)
+  { const char *hl = getenv("B200MD_HALO"); c->direct.on = nranks > 1 && !(hl && !strcmp(hl, "staged")); }
   CUDA_TRY(cudaMalloc(&c->d_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMallocHost(&c->h_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMalloc(&c->d_flags, 8 * sizeof(int)));

@@ -37,7 +37,8 @@ def in_lj(ctx, x=1, y=1, z=1, list_kind=B.LIST_FULL, every=20, delay=0, check=0,
     skin = 0.3
     cn, cmax = B.cutneighsq_table(1, T["cutsq"], skin)
     ctx.neigh_config(cn, cmax, skin, every=every, delay=delay, check=check, list_kind=list_kind)
-    return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=0, units="lj")
+    return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=0, units="lj",
+                neigh=dict(cutneighsq=cn, cutneighmax=cmax, skin=skin, every=every, delay=delay, check=check))
 
 
 def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, seed=376847,
@@ -67,7 +68,8 @@ def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, 
     cutsq = np.zeros((2, 2)); cutsq[1, 1] = tb["cutforcesq"]
     cn, cmax = B.cutneighsq_table(1, cutsq, skin)
     ctx.neigh_config(cn, cmax, skin, every=1, delay=5, check=1, list_kind=list_kind)
-    return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=50, units="metal")
+    return dict(natoms=4 * nx * ny * nz, dt=0.005, thermo=50, units="metal",
+                neigh=dict(cutneighsq=cn, cutneighmax=cmax, skin=skin, every=1, delay=5, check=1))
 
 
 def atom_sort_order(x, sublo, subhi, cutneighmax):
@@ -110,4 +112,5 @@ def in_chain(ctx, data_path, x=1, y=1, z=1, list_kind=B.LIST_HALF_NEWTON, langev
     ctx.bond_fene_config([0.0, 30.0], [0.0, 1.5], [0.0, 1.0], [0.0, 1.0])
     ctx.pair_lj_cut_config(T["cutsq"], T["lj1"], T["lj2"], T["lj3"], T["lj4"], T["offset"])
     ctx.neigh_config(cn, cmax, skin, every=1, delay=1, check=1, list_kind=list_kind)
-    return dict(natoms=d["natoms"], dt=0.012, thermo=100, units="lj", data=d, topology=tp, tables=T)
+    return dict(natoms=d["natoms"], dt=0.012, thermo=100, units="lj", data=d, topology=tp, tables=T,
+                neigh=dict(cutneighsq=cn, cutneighmax=cmax, skin=skin, every=1, delay=1, check=1))

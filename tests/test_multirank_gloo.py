@@ -87,7 +87,7 @@ def _xchg(payload, width, sendproc, recvproc, rank):
     return recv.numpy()
 
 
-def _worker_direct(rank, world, port, out):
+def _worker_direct(rank, world, port, out, n=(8, 4, 4)):
     """the direct halo of csrc/comm.cu (B200MD_HALO=direct) restated over gloo: the staged borders carry
     every ghost's owner (rank, index, shift code); forward / reverse traffic then goes owner <-> holder in
     one all-to-all and must reproduce the staged forward_comm bit for bit and the staged reverse_comm sums"""
@@ -97,7 +97,7 @@ def _worker_direct(rank, world, port, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     import b200pkg
     B = b200pkg.load().b200md
-    scale, n = 3.615, (8, 4, 4)
+    scale = 3.615
     boxlo, boxhi = [0.0] * 3, [n[0] * scale, n[1] * scale, n[2] * scale]
     prd = np.array(boxhi) - np.array(boxlo)
     cut = 5.95
@@ -184,18 +184,24 @@ def _worker_direct(rank, world, port, out):
             [r.wait() for r in (dist.isend(torch.from_numpy(W[req[p]].copy()), p), dist.irecv(recv, p))]
             np.add.at(Wd, serve[p], recv.numpy())
     rev_err = float(np.abs(Wd[:nlocal] - Ws[:nlocal]).max() / np.abs(Ws[:nlocal]).max())
-    out[rank] = (same_forward, rev_err, nall - nlocal, int(sum(len(v) for v in serve.values())), int((code != 0).any(axis=1).sum()))
+    npeers = sum(1 for p in range(world) if p != rank and len(req[p]))
+    out[rank] = (same_forward, rev_err, nall - nlocal, int(sum(len(v) for v in serve.values())),
+                 int((code != 0).any(axis=1).sum()), npeers, list(grid))
     dist.destroy_process_group()
 
 
-def test_two_rank_direct_halo_over_gloo():
-    world = 2
+@pytest.mark.parametrize("world,n,grid,peers", [(2, (8, 4, 4), [2, 1, 1], 1), (4, (4, 4, 4), [1, 2, 2], 3),
+                                                (8, (4, 4, 4), [2, 2, 2], 7)])
+def test_direct_halo_over_gloo(world, n, grid, peers):
+    """2x1x1 (one peer, self swaps in y and z), 1x2x2 and 2x2x2 (the 8-GPU grid: 7 peers, ghosts of
+    ghosts owned by third ranks)"""
     mgr = mp.Manager()
     out = mgr.dict()
-    mp.spawn(_worker_direct, args=(world, 29543, out), nprocs=world, join=True)
-    assert len(out) == 2
+    mp.spawn(_worker_direct, args=(world, 29543 + world, out, n), nprocs=world, join=True)
+    assert len(out) == world
     for r in range(world):
-        same_forward, rev_err, nghost, nserve, nshifted = out[r]
+        same_forward, rev_err, nghost, nserve, nshifted, npeers, g = out[r]
+        assert g == grid and npeers == peers
         assert nghost > 0 and nserve > 0 and nshifted > 0
         assert same_forward, r            # ghost positions bit-identical to the staged forward_comm
         assert rev_err < 1e-12, (r, rev_err)
