@@ -272,3 +272,44 @@ def test_cuda_langevin_refusals(pkg):
     with pytest.raises(RuntimeError, match="seed"):
         ctx.fix_langevin(1.0, 1.0, 1.0, 0, 0.005)
     ctx.close()
+
+
+# ---- properties of the host-side stream helpers (no GPU) -----------------------------------------
+def test_ranmars_jump_properties(pkg, oracle_mod):
+    """random seeds and offsets: jump(k) then draw == the serial stream at offset k; jumps compose"""
+    B = pkg.b200md
+    rng = np.random.default_rng(20231105)
+    for _ in range(12):
+        seed = int(rng.integers(1, 900000001))
+        k1, k2 = int(rng.integers(0, 15000)), int(rng.integers(0, 15000))
+        u = oracle_mod.ranmars_stream(seed, k1 + k2 + 64)
+        st = B.ranmars_state(seed)
+        a = B.ranmars_jump(st, k1)
+        assert np.array_equal(B.ranmars_draws(a, 1 + k1, 64), u[k1:k1 + 64])
+        b = B.ranmars_jump(a, k2)
+        assert np.array_equal(b, B.ranmars_jump(st, k1 + k2))
+        assert np.array_equal(B.ranmars_draws(b, 1 + k1 + k2, 64), u[k1 + k2:k1 + k2 + 64])
+    with pytest.raises(B.B200MDError, match="Invalid seed"):
+        B.ranmars_state(0)
+    with pytest.raises(B.B200MDError, match="Invalid seed"):
+        B.ranmars_state(900000001)
+
+
+def test_atom_sort_order_properties(pkg):
+    """a permutation, stable inside a bin, bins ascending (x fastest), atoms outside the box clamped"""
+    B = pkg.b200md
+    rng = np.random.default_rng(7)
+    lo, hi = np.array([0.0, -1.0, 2.0]), np.array([9.0, 4.0, 7.5])
+    x = lo + (hi - lo) * rng.random((5000, 3))
+    x[:50] += 0.3 * (hi - lo) * rng.standard_normal((50, 3))        # some atoms outside the box
+    cmax = 2.8
+    perm = B.atom_sort_order(x, lo, hi, cmax)
+    assert np.array_equal(np.sort(perm), np.arange(len(x)))
+    nb = np.maximum(((hi - lo) / (0.5 * cmax)).astype(int), 1)
+    c = np.clip(((x - lo) * (nb / (hi - lo))).astype(int), 0, nb - 1)
+    bins = (c[:, 2] * nb[1] + c[:, 1]) * nb[0] + c[:, 0]
+    sb = bins[perm]
+    assert np.all(np.diff(sb) >= 0)
+    same = np.diff(sb) == 0
+    assert np.all(np.diff(perm)[same] > 0)                           # stable
+    assert np.array_equal(B.atom_sort_order(x, lo, hi, 0.0), np.arange(len(x)))   # sorting disabled
