@@ -70,6 +70,7 @@ extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out)
   if (const char *sp = getenv("B200MD_SPLIT")) c->split = atof(sp);
   if (const char *bl = getenv("B200MD_BUILD_LANES")) { c->tpa_build = atoi(bl); c->tpa_build_user = true; }   // tuning
   { const char *ov = getenv("B200MD_OVERLAP"); c->overlap = !(ov && ov[0] == '0'); }
+  { const char *fu = getenv("B200MD_FUSE_NVE"); c->fuse_nve = fu && fu[0] == '1'; }
   // per-step halo: owner <-> holder in one NCCL group ("direct", default on several ranks) or the
   // reference's three forwarding stages (B200MD_HALO=staged)
   { const char *hl = getenv("B200MD_HALO"); c->direct.on = nranks > 1 && !(hl && !strcmp(hl, "staged")); }
@@ -779,6 +780,7 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     TRY(langevin_set_dt(c, dt));   // FixLangevin::reset_dt
     if (!LG.window) { LG.begin = first; LG.end = last; LG.now = first; }
   }
+  bool initial_done = false;
   TT.begin(0);
   for (int i = 0; i < nsteps; i++) {
     c->step++;
@@ -786,7 +788,8 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     // Integrate::ev_set: energy/virial only on thermo output steps
     const bool out_step = (thermo_every > 0 && (c->step - first) % thermo_every == 0) || c->step == last;
     const int ev = out_step ? 1 : 0;
-    T.begin(4); TRY(b200md_nve_initial(c, dtv, dtf)); T.end();
+    if (initial_done) initial_done = false;   // this step's first half-kick + drift ran fused with the previous step's second one
+    else { T.begin(4); TRY(b200md_nve_initial(c, dtv, dtf)); T.end(); }
     int nflag = 0;
     TRY(b200md_neigh_decide(c, &nflag));
     if (!nflag && !ev && can_overlap(c)) {
@@ -798,7 +801,14 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
       T.begin(3); TRY(comm_reverse_force(c)); T.end();
     }
     // Modify::post_force (fix langevin) fused with FixNVE::final_integrate when the thermostat is on
-    T.begin(4); if (LG.on) TRY(langevin_post_force(c, true, dtf)); else TRY(nve_final(c, dtf)); T.end();
+    T.begin(4);
+    if (LG.on) TRY(langevin_post_force(c, true, dtf));
+    else if (c->fuse_nve && !out_step && i + 1 < nsteps) {
+      // the distance check belongs to the NEXT step's initial_integrate; ago only moves in decide / build
+      TRY(nve_final_initial(c, dtv, dtf, decide_will_check(c) && c->nbuilds > 0));
+      initial_done = true;
+    } else TRY(nve_final(c, dtf));
+    T.end();
     if (out_step && thermo_out && nth < max_thermo) { TRY(b200md_thermo_compute(c, &thermo_out[nth])); nth++; }
   }
   TT.end();

@@ -175,6 +175,7 @@ struct b200md_ctx {
   cudaEvent_t ev_bnd = nullptr, ev_rev = nullptr, ev_rb = nullptr, ev_rr = nullptr;  // half-list overlap
   double split = 0.5;  // share of the interior tiles evaluated before the boundary tiles (half-list overlap)
   bool overlap = true;
+  bool fuse_nve = false;  // B200MD_FUSE_NVE=1: final_integrate(n) + initial_integrate(n+1) in one pass (nve.cu)
   // comm
   b200md_swap_schedule sched;
   std::vector<Swap> swaps;
@@ -286,6 +287,7 @@ void langevin_free(b200md_ctx *c);
 // nve.cu
 int nve_initial(b200md_ctx *c, double dtv, double dtf, bool check_dist);
 int nve_final(b200md_ctx *c, double dtf);
+int nve_final_initial(b200md_ctx *c, double dtv, double dtf, bool check_dist);
 int thermo_ke(b200md_ctx *c, double *sum_mv2);
 int reduce_partials(b200md_ctx *c, int nblocks, int nvals, double *host_out);
 int ensure_partials(b200md_ctx *c, int nblocks);
