@@ -163,6 +163,12 @@ int bond_compute(b200md_ctx *c, int eflag, int vflag) {
   if (nblocks == 0) return B200MD_OK;
   const double3 prd = make_double3(c->prd[0], c->prd[1], c->prd[2]);
   const int3 per = make_int3(c->periodic[0], c->periodic[1], c->periodic[2]);
+  // several ranks: a bond partner can be a ghost, its share goes home with reverse_comm
+  // (newton_bond on).  The full-list pair kernels never touch ghost rows of f, so they are cleared
+  // here (half lists clear owned + ghost rows before the pair kernel, Verlet::force_clear).
+  if (c->list_kind == B200MD_LIST_FULL && !c->all_self && c->nghost)
+    for (int d = 0; d < 3; d++)
+      CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax + c->nlocal, 0, sizeof(double) * c->nghost, c->stream));
   if (ev) {
     TRY(ensure_partials(c, nblocks));
     k_bond_fene<true><<<nblocks, BOND_THREADS, 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->tag, t.bond_off, t.bond_partner,

@@ -912,7 +912,9 @@ __global__ void k_reverse_flat(int nghost, int nlocal, int nmax, double *__restr
 }
 
 int comm_reverse_force(b200md_ctx *c) {
-  if (c->list_kind == B200MD_LIST_FULL) return B200MD_OK;  // newton off: nothing on ghosts
+  // newton_pair off: nothing on ghosts — unless bonds (newton_bond on) put their partner's share there,
+  // which on one rank never happens (the tag map prefers the owned copy, bond.cu)
+  if (c->list_kind == B200MD_LIST_FULL && !(c->topo.molecular && c->topo.fene && !c->all_self)) return B200MD_OK;
   if (c->all_self) {
     if (c->nghost == 0) return B200MD_OK;
     k_reverse_flat<3><<<nblk(c->nghost), 256, 0, c->stream>>>(c->nghost, c->nlocal, c->nmax, c->f, c->ghost_src);

@@ -31,4 +31,23 @@ for wl in ("lj", "eam"):
             print("%s N=%d step %d T %.8g E_pair %.8g TotEng %.8g Press %.8g" % (wl, world, t["step"], t["temp"], t["pe"] / per, (t["pe"] + t["ke"]) / per, t["press"]), flush=True)
         print("   rank0 nlocal %d nghost %d loop %.2f ms builds %d" % (nl, ng, tm["total_ms"], tm["nbuilds"]), flush=True)
     ctx.close()
+# bench/in.chain without fix langevin (its stream is per rank): FENE bonds across sub-box faces, bond
+# shares of ghost partners returned by reverse_comm; must equal tests/golden/chain.npz (the 1-rank reference)
+if "chain" in sys.argv:
+    import numpy as np
+    g = np.load("tests/golden/chain.npz")
+    ctx = mk()
+    cfg = P.inputs.in_chain(ctx, "oracle/_ref/data/data.chain", list_kind=lk)
+    ctx.setup()
+    recs = [ctx.thermo()] + [ctx.run(10, cfg["dt"], 0)[-1] for _ in range(10)]
+    if rank == 0:
+        want = [g["thermo0"]] + list(g["thermo_series"])
+        worst = 0.0
+        for t, w in zip(recs, want):
+            got = [t["temp"], t["pe"], t["ke"], t["press"], t["pe"] - t["emol"], t["emol"]]
+            worst = max(worst, max(abs(a - b) / abs(b) for a, b in zip(got, w)))
+        t = recs[-1]
+        print("chain N=%d step %d T %.8g PE %.10g Press %.8g | worst relative deviation from the reference over 100 steps %.2e"
+              % (world, t["step"], t["temp"], t["pe"], t["press"], worst), flush=True)
+    ctx.close()
 dist.destroy_process_group()
