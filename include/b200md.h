@@ -264,6 +264,12 @@ int b200md_fix_langevin(b200md_ctx *ctx, double t_start, double t_stop, double t
  * split one run into several b200md_run calls (verlet/b200 stops at output steps).  endstep ==
  * beginstep switches back to "every b200md_run is its own window". */
 int b200md_fix_langevin_window(b200md_ctx *ctx, long long ntimestep, long long beginstep, long long endstep);
+/* Atom::sortfreq of the host (`atom_modify sort`, default 1000; 0 = never).  The reference re-sorts its
+ * atoms at the first reneighboring at or after every multiple of it (Verlet::run, src/verlet.cpp:285;
+ * Atom::sort sets nextsort, src/atom.cpp:2252), which changes the order the draws are handed out in; the
+ * device re-ranks its stream index the same way at that rebuild (stable by bin, previous rank inside a
+ * bin).  The host's own arrays are not re-ordered by this. */
+int b200md_fix_langevin_sort(b200md_ctx *ctx, int sortfreq);
 /* `unfix`: stop applying it. */
 int b200md_fix_langevin_off(b200md_ctx *ctx);
 

@@ -395,6 +395,10 @@ class Context:
     def fix_langevin_window(self, ntimestep, beginstep, endstep):
         _chk(self.L.b200md_fix_langevin_window(self.h, C.c_longlong(ntimestep), C.c_longlong(beginstep), C.c_longlong(endstep)))
 
+    def fix_langevin_sort(self, sortfreq):
+        """Atom::sortfreq of the host whose order the stream follows (default 1000, 0 = never re-sorted)"""
+        _chk(self.L.b200md_fix_langevin_sort(self.h, int(sortfreq)))
+
     def fix_langevin_off(self):
         _chk(self.L.b200md_fix_langevin_off(self.h))
 

@@ -373,6 +373,10 @@ extern "C" int b200md_neigh_build(b200md_ctx *c) {
   CUDA_TRY(cudaSetDevice(c->device));
   TRY(neigh_pbc(c));
   TRY(comm_exchange(c));
+  if (c->lang.on && c->lang.resort_pending) {   // Verlet::run's Atom::sort (verlet.cpp:285): the draws follow the new order
+    c->lang.resort_pending = false;
+    TRY(langevin_resort(c));
+  }
   c->host_order = false;
   TRY(neigh_sort_owned(c));
   TRY(comm_borders(c));
@@ -599,6 +603,12 @@ extern "C" int b200md_fix_langevin_window(b200md_ctx *c, long long ntimestep, lo
   L.begin = beginstep; L.end = endstep; L.now = ntimestep;
   return B200MD_OK;
 }
+extern "C" int b200md_fix_langevin_sort(b200md_ctx *c, int sortfreq) {
+  NEED(c && c->lang.on, "b200md: fix langevin is not set");
+  NEED(sortfreq >= 0, "Illegal atom_modify sort frequency");
+  c->lang.sortfreq = sortfreq;
+  return B200MD_OK;
+}
 extern "C" int b200md_fix_langevin_off(b200md_ctx *c) {
   NEED(c, "b200md: null context");
   c->lang.on = false;
@@ -663,6 +673,8 @@ extern "C" int b200md_setup(b200md_ctx *c) {
   if (c->lang.on) {   // Modify::setup -> FixLangevin::setup -> post_force on the set-up forces
     Langevin &L = c->lang;
     if (!L.window) L.begin = L.end = L.now = c->step;
+    // the host sorted at its set-up (Atom::sort sets nextsort from the current timestep, atom.cpp:2252)
+    if (L.sortfreq > 0) L.nextsort = (L.now / L.sortfreq) * L.sortfreq + L.sortfreq;
     TRY(langevin_post_force(c, false, 0.0));
   }
   return B200MD_OK;
@@ -796,7 +808,10 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
       T.begin(1); TRY(forces_overlapped(c)); T.end();   // includes reverse_comm on half lists
     } else {
       if (!nflag) { T.begin(3); TRY(comm_forward(c)); T.end(); }
-      else { T.begin(2); TRY(b200md_neigh_build(c)); T.end(); }
+      else {
+        if (LG.on && LG.sortfreq > 0 && LG.now >= LG.nextsort) LG.resort_pending = true;
+        T.begin(2); TRY(b200md_neigh_build(c)); T.end();
+      }
       T.begin(1); TRY(b200md_pair_compute(c, ev, ev, nullptr, nullptr)); TRY(bond_compute(c, ev, ev)); T.end();
       T.begin(3); TRY(comm_reverse_force(c)); T.end();
     }

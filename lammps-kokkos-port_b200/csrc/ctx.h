@@ -84,6 +84,9 @@ struct Langevin {
   int nrank = 0;
   double *gfac = nullptr;          // device [ntypes+1][2] gfactor1, gfactor2
   int gfac_n = 0;
+  // Atom::sort schedule of the host the stream order mirrors (atom.cpp:102-103, 2252; verlet.cpp:285)
+  long long sortfreq = 1000, nextsort = 0;
+  bool resort_pending = false;     // set by b200md_run for the rebuild that has to re-rank first
 };
 
 struct Swap {
@@ -282,6 +285,7 @@ int langevin_config(b200md_ctx *c, double t_start, double t_stop, double t_perio
 int langevin_set_dt(b200md_ctx *c, double dt);
 int langevin_rank_from_host_order(b200md_ctx *c);
 int langevin_post_force(b200md_ctx *c, bool with_final, double dtf);
+int langevin_resort(b200md_ctx *c);
 int langevin_test_stream(b200md_ctx *c, int seed, int n, int fills, double *out);
 void langevin_free(b200md_ctx *c);
 // nve.cu

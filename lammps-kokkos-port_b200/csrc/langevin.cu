@@ -30,6 +30,7 @@
 // fused with FixNVE::final_integrate: one pass over v and f instead of two.
 // Per atom-step: 12 B of random words written and read, 4 B tag, 4 B rank, plus the 96 B of the
 // v / f streams nve_final moves anyway.
+#include <cub/device/device_radix_sort.cuh>
 #include "ctx.h"
 #include "util.cuh"
 
@@ -245,6 +246,72 @@ int langevin_rank_from_host_order(b200md_ctx *c) {
   CUDA_TRY(cudaMalloc(&L.rank_by_tag, sizeof(int) * rank.size()));
   CUDA_TRY(cudaMemcpy(L.rank_by_tag, rank.data(), sizeof(int) * rank.size(), cudaMemcpyHostToDevice));
   L.nrank = n;
+  return B200MD_OK;
+}
+
+// ---- Atom::sort inside a run (verlet.cpp:285, atom.cpp:2246-2349) -------------------------------
+// The reference re-orders its atoms: bins of cutneighmax/2 over the sub-box, stable inside a bin.
+// Only the draw each atom gets depends on that order here, so the device re-ranks instead of moving
+// anything: key = (bin, previous rank), one radix sort, new rank = position in the sorted sequence.
+struct SortBins { double lo[3], binv[3]; int nb[3]; };
+
+__global__ void k_resort_keys(int n, const double4 *__restrict__ xq, const int *__restrict__ tag,
+                              const int *__restrict__ rank_by_tag, SortBins G, unsigned long long nrank,
+                              unsigned long long *__restrict__ keys, int *__restrict__ vals) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double4 q = xq[i];
+  int ix = (int)(__dmul_rn(q.x - G.lo[0], G.binv[0]));
+  int iy = (int)(__dmul_rn(q.y - G.lo[1], G.binv[1]));
+  int iz = (int)(__dmul_rn(q.z - G.lo[2], G.binv[2]));
+  ix = min(max(ix, 0), G.nb[0] - 1); iy = min(max(iy, 0), G.nb[1] - 1); iz = min(max(iz, 0), G.nb[2] - 1);
+  const unsigned long long bin = ((unsigned long long)iz * G.nb[1] + iy) * G.nb[0] + ix;
+  const int t = tag[i];
+  keys[i] = bin * nrank + (unsigned long long)rank_by_tag[t];
+  vals[i] = t;
+}
+__global__ void k_resort_assign(int n, const int *__restrict__ sorted_tag, int *__restrict__ rank_by_tag) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  rank_by_tag[sorted_tag[k]] = k;
+}
+
+int langevin_resort(b200md_ctx *c) {
+  Langevin &L = c->lang;
+  const int n = c->nlocal;
+  L.nextsort = (L.now / L.sortfreq) * L.sortfreq + L.sortfreq;   // atom.cpp:2252
+  if (n != L.nrank) { b200md_set_error("b200md: fix langevin: the number of atoms changed since it was set"); return B200MD_ERR; }
+  // Atom::setup_sort_bins (atom.cpp:2351-2410)
+  const double binsize = 0.5 * c->cutneighmax;
+  if (binsize <= 0.0 || n == 0) return B200MD_OK;
+  SortBins G;
+  const double bininv = 1.0 / binsize;
+  long long nbins = 1;
+  for (int d = 0; d < 3; d++) {
+    G.lo[d] = c->sublo[d];
+    G.nb[d] = static_cast<int>((c->subhi[d] - c->sublo[d]) * bininv);
+    if (G.nb[d] == 0) G.nb[d] = 1;
+    G.binv[d] = G.nb[d] / (c->subhi[d] - c->sublo[d]);
+    nbins *= G.nb[d];
+  }
+  if (nbins == 1) return B200MD_OK;   // Atom::sort returns before permuting anything
+  unsigned long long *keys = nullptr, *keys_out = nullptr;
+  int *vals = nullptr, *vals_out = nullptr;
+  void *tmp = nullptr;
+  size_t tmp_bytes = 0;
+  CUDA_TRY(cudaMalloc(&keys, sizeof(unsigned long long) * 2 * (size_t)n));
+  CUDA_TRY(cudaMalloc(&vals, sizeof(int) * 2 * (size_t)n));
+  keys_out = keys + n; vals_out = vals + n;
+  k_resort_keys<<<(n + 255) / 256, 256, 0, c->stream>>>(n, c->xq, c->tag, L.rank_by_tag, G, (unsigned long long)n, keys, vals);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys_out, vals, vals_out, n, 0, 64, c->stream));
+  CUDA_TRY(cudaMalloc(&tmp, tmp_bytes));
+  CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys_out, vals, vals_out, n, 0, 64, c->stream));
+  k_resort_assign<<<(n + 255) / 256, 256, 0, c->stream>>>(n, vals_out, L.rank_by_tag);
+  CUDA_TRY(cudaGetLastError());
+  c->launches += 3;
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  cudaFree(tmp); cudaFree(keys); cudaFree(vals);
   return B200MD_OK;
 }
 

@@ -56,6 +56,9 @@ int FixLangevinB200::b200_push_fix(b200md_ctx *ctx)
     if (b200md_fix_langevin(ctx, t_start, t_stop, t_period, seed + comm->me, r.data(), update->dt)) return 1;
     pushed_to = ctx;
   }
+  // Verlet::run re-sorts the atoms every atom->sortfreq steps (src/verlet.cpp:285); the device re-ranks
+  // its stream index at the same rebuild
+  if (b200md_fix_langevin_sort(ctx, atom->sortfreq)) return 1;
   return b200_begin_chunk(ctx);
 }
 

@@ -73,6 +73,9 @@ typedef struct {
   int eflag_atom, vflag_atom;
   double *eatom, *vatom; /* [nmax], [nmax][6] pair + bond, as compute pe/atom / stress/atom sum them */
   long step;
+  /* Atom::sort schedule (atom.cpp:102-103, 2252): 0 = the caller never sorted, sorting stays off */
+  long sortfreq, nextsort;
+  int in_run;
   /* fix langevin (fix_langevin.cpp) with its RanMars stream (random_mars.cpp) */
   int langevin;
   double lang_tstart, lang_tstop, lang_period, lang_dt, *lang_ratio;
@@ -423,9 +426,11 @@ void ora_neigh_config(ora_sim *s, const double *cutneighsq, double cutneighmax, 
 
 static void map_set(ora_sim *s);
 static int bond_list_build(ora_sim *s);
+static void atom_sort(ora_sim *s);
 /* the reneighbor branch of Verlet::run (verlet.cpp:289-307) + Neighbor::build (neighbor.cpp:2398-2492) */
 int ora_neigh_build(ora_sim *s) {
   pbc(s);
+  if (s->in_run && s->sortfreq > 0 && s->step >= s->nextsort) atom_sort(s); /* verlet.cpp:285 */
   if (borders(s)) return -1;
   for (int i = 0; i < 3 * s->nlocal; i++) s->xhold[i] = s->x[i];
   bin_atoms(s);
@@ -776,8 +781,9 @@ void ora_thermo_compute(ora_sim *s, ora_thermo *t) {
  * bin.  Verlet::setup calls it (verlet.cpp:123, sortfreq = 1000 by default) after Domain::pbc and
  * before the borders, so it fixes the local index order — which is what the order of a half
  * list's same-bin pairs and the RanMars draws of fix langevin follow. */
-void ora_atom_sort(ora_sim *s) {
-  pbc(s);
+static void atom_sort(ora_sim *s) {
+  if (s->sortfreq <= 0) s->sortfreq = 1000;
+  s->nextsort = (s->step / s->sortfreq) * s->sortfreq + s->sortfreq;
   s->nghost = 0;
   double binsize = 0.5 * s->cutneighmax;
   if (binsize == 0.0) return;
@@ -819,6 +825,14 @@ void ora_atom_sort(ora_sim *s) {
   memcpy(s->type, type, sizeof(int) * n); memcpy(s->tag, tag, sizeof(int) * n); memcpy(s->image, image, sizeof(int) * n);
   free(x); free(v); free(f); free(type); free(tag); free(image); free(head); free(next); free(permute);
 }
+
+/* Verlet::setup's sort (verlet.cpp:123); it also switches on the in-run re-sort of Verlet::run
+ * (verlet.cpp:285: at the first reneighboring with ntimestep >= nextsort) */
+void ora_atom_sort(ora_sim *s) {
+  pbc(s);
+  atom_sort(s);
+}
+void ora_set_sortfreq(ora_sim *s, long sortfreq) { s->sortfreq = sortfreq; }
 
 /* ---- RanMars (random_mars.cpp:30-95): Marsaglia's lagged-Fibonacci generator --------------- */
 static double mars_uniform(ora_sim *s) {
@@ -923,7 +937,12 @@ int ora_run(ora_sim *s, int nsteps, double dt, int thermo_every, ora_thermo *out
     int out_step = (thermo_every > 0 && (s->step - first) % thermo_every == 0) || s->step == last;
     nve_initial(s, dtv, dtf);
     if (!decide(s)) forward_comm(s);
-    else if (ora_neigh_build(s)) return -1;
+    else {
+      s->in_run = 1;
+      int rc = ora_neigh_build(s);
+      s->in_run = 0;
+      if (rc) return -1;
+    }
     if (ora_compute(s, out_step, out_step)) return -1;
     if (s->langevin) langevin_post_force(s); /* Modify::post_force (verlet.cpp:337) */
     nve_final(s, dtf);

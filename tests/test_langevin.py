@@ -174,6 +174,48 @@ def test_oracle_lj_langevin_ramp(pkg, oracle_mod):
     o.close()
 
 
+def ljsort_inputs(pkg, G):
+    order = G["ljsort_local_tags"].astype(np.int64) - 1
+    s = Cm.lj_system(pkg, 1)
+    scale = (4.0 / 0.8442) ** (1.0 / 3.0)
+    s["boxlo"], s["boxhi"] = [0.0] * 3, [5 * scale] * 3
+    s.update(x=G["ljsort_x0"][order], v=G["ljsort_v0"][order], tag=(order + 1).astype(np.int32),
+             type=np.ones(len(order), np.int32))
+    return s
+
+
+def check_ljsort(G, s, tag, x, v, thermo, xtol, ttol):
+    o = np.argsort(tag)
+    prd = np.array(s["boxhi"]) - np.array(s["boxlo"])
+    d = x[o] - G["ljsort_x"]
+    d -= prd * np.round(d / prd)
+    assert np.abs(d).max() <= xtol * prd[0]
+    assert np.abs(v[o] - G["ljsort_v"]).max() <= xtol * np.abs(G["ljsort_v"]).max()
+    close(tvec(thermo), G["ljsort_thermo"], ttol, 4)
+
+
+def test_oracle_langevin_across_resort(pkg, oracle_mod):
+    """ONE run of 1100 steps: at the first reneighboring at or after step 1000 the reference re-sorts
+    its atoms (Atom::sort, src/verlet.cpp:285) and the draws follow the new order.  A stream handed out
+    in the old order shows up as O(1e-2) in the thermo; the restatement stays at rounding level."""
+    G = golden()
+    B = pkg.b200md
+    s = ljsort_inputs(pkg, G)
+    o = oracle_mod.Oracle(s["boxlo"], s["boxhi"], s["x"], s["v"], s["type"], s["tag"], s["mass"], s["units"])
+    T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 2.5)}, 2.5)
+    o.pair_lj(T)
+    cn, cmax = B.cutneighsq_table(1, T["cutsq"], 0.3)
+    o.neigh_config(cn, cmax, 0.3, 20, 0, 0, True)
+    o.atom_sort()
+    o.fix_langevin(1.0, 1.0, 1.0, 7771, 0.005)
+    o.setup()
+    t = o.run(1100, 0.005, 0)[-1]
+    a = o.atoms()
+    check_ljsort(G, s, a["tag"], a["x"], a["v"], t, 1e-7, 1e-7)
+    assert np.array_equal(a["tag"], G["ljsort_local_tags_end"])       # the reference's local order after its re-sort
+    o.close()
+
+
 def test_host_atom_sort_matches_oracle(pkg, oracle_mod):
     """the host mirror of Atom::sort (what the Python driver applies before the upload) gives the
     oracle's order"""

@@ -50,3 +50,32 @@ def test_fused_nve_is_bit_identical(pkg, oracle_mod, name, kind):
         for k in ("temp", "pe", "ke", "press"):
             assert a[k] == b[k], (k, a[k], b[k])
     assert l1 < l0                            # one launch fewer per fused step pair
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("half", [True, False])
+def test_cuda_langevin_across_resort(pkg, half):
+    """fix langevin over ONE run of 1100 steps: at the first rebuild at or after step 1000 the reference
+    re-sorts its atoms (Atom::sort, src/verlet.cpp:285) and hands out the RanMars draws in the new order;
+    the device re-ranks its stream index at the same rebuild (csrc/langevin.cu: langevin_resort).
+    Golden: tests/golden/langevin.npz ljsort_* from the unmodified reference.  Rounding differences
+    grow over 1100 steps (5.5 tau) of a melt, hence 2e-4; a stream left in the old order is off by 3e-3 .. 8e-2
+    (measured with the oracle)."""
+    import test_langevin as TL
+    G = TL.golden()
+    B = pkg.b200md
+    s = TL.ljsort_inputs(pkg, G)
+    T = B.lj_cut_tables(1, {(1, 1): (1.0, 1.0, 2.5)}, 2.5)
+    cn, cmax = B.cutneighsq_table(1, T["cutsq"], 0.3)
+    perm = pkg.inputs.atom_sort_order(s["x"], s["boxlo"], s["boxhi"], cmax)
+    ctx = B.Context(0)
+    ctx.set_units("lj"); ctx.set_box(s["boxlo"], s["boxhi"])
+    ctx.set_atoms(s["x"][perm], s["v"][perm], s["type"][perm], s["tag"][perm], s["mass"])
+    ctx.pair_lj_cut_config(*[T[k] for k in ("cutsq", "lj1", "lj2", "lj3", "lj4", "offset")])
+    ctx.neigh_config(cn, cmax, 0.3, every=20, delay=0, check=0, list_kind=B.LIST_HALF_NEWTON if half else B.LIST_FULL)
+    ctx.fix_langevin(1.0, 1.0, 1.0, 7771, 0.005)
+    ctx.setup()
+    t = ctx.run(1100, 0.005, 0)[-1]
+    a = ctx.get_atoms(("x", "v", "tag"))
+    TL.check_ljsort(G, s, a["tag"], a["x"], a["v"], t, 2e-4, 2e-4)
+    ctx.close()
