@@ -2,12 +2,23 @@
 """bench.py — atom-steps/s of the short-range MD hot path (neighbor build -> lj/cut | eam -> fix nve)
 on N B200s of one node, measured on the reference's own bench inputs.
 
-  python bench.py --gpus N --steps K --warmup W [--workload lj|eam] [--impl reference]
+  python bench.py --gpus N --steps K --warmup W [--impl reference]
 
 A "step" is one MD timestep of the workload (Verlet::run body, /root/reference/src/verlet.cpp:246-359)
-including the neighbor rebuilds that fall inside the K steps.  Workload at N GPUs: bench/in.lj scaled to
-2 048 000 atoms per GPU (-var x/y/z = 4,4,4 / 8,4,4 / 8,8,4 / 8,8,8), weak scaling, one process per GPU,
-spatial decomposition with NCCL halo exchange.  One JSON line on rank 0.
+including the neighbor rebuilds that fall inside the K steps.  One JSON line on rank 0:
+
+  value / e2e / roofline   bench/in.lj scaled to 2 048 000 atoms per GPU (-var x/y/z = 4,4,4 / 8,4,4 / 8,8,4 /
+                           8,8,8: config C4, weak scaling), one process per GPU, spatial decomposition
+  parity_check             BEFORE anything is timed: bench/in.lj and bench/in.eam at 32 000 atoms, 100 steps on
+                           the same N ranks with the halo mode and list kind of the timed regions; thermo at steps
+                           0/50/100 must equal the reference's own logs (bench/log.6Oct16.{lj,eam}.fixed.icc.1) in
+                           all 8 printed digits.  A mismatch prints the offending line and exits non-zero.
+  secondary.eam            bench/in.eam (Cu_u3) at 2 048 000 atoms per GPU (weak), with its own roofline
+  secondary.eam_alloy_strong   config C5: in.eam with eam/alloy Cu_mishin1, 4 000 000 atoms in TOTAL on the N ranks
+                           (strong scaling, atom migration at every rebuild); its thermo at steps 0/50/100 is checked
+                           against tests/golden/c5_thermo.json (the unmodified reference, 4 M atoms)
+  secondary.lj_32k / eam_32k   the 32 000-atom configs C1 / C2 as shipped (latency regime)
+  cpu_baseline (N=1)       the reference's own CPU implementation on this box's host cores, bounded sample
 """
 import argparse
 import json
@@ -22,34 +33,27 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 SCALE = {1: (4, 4, 4), 2: (8, 4, 4), 4: (8, 8, 4), 8: (8, 8, 8)}
-# algorithmic bytes: force pass per atom per launch, and whole step per atom-step
-N_FULL = {"lj": 75.2, "eam": 75.5, "chain": 9.74}
-BYTES_KERNEL = {"lj": 28 * 75.2 + 52, "eam": 64 * 75.5 + 104,    # LJ force pass; EAM rho+fp and force passes
-                "chain": 28 * 9.74 + 52 + 1 * (8 + 24 + 24) + 52}  # + FENE: 0.99 bonds/atom x (tag,map + x_j + f_j RED) + own x,f
-# in.chain (SURVEY's method applied to C3, N=9.74, rebuild every ~4 steps): force passes 381 + NVE 192
-# + check_distance 48 + rebuild (4N list + 24 xhold + 176 sort + 28N candidates + 8 map)/4 = 128
-# fix langevin adds 12 B written + 12 B read of random words, 4 B tag, 4 B rank per atom-step (its v/f
-# streams are the ones nve_final moves anyway: the two are one fused pass)
-BYTES_STEP = {"lj": 2480.0, "eam": 5510.0, "chain": 750.0, "chain+langevin": 782.0}
-# (the figures above are SURVEY 8(d)'s yardstick, defined on the full list; the half-list kernels do
-#  the same physical work -- every pair once instead of twice -- and are rated with the same figure)
-# measured choice on ONE GPU (profiles/r01_summary.md): the half/newton list wins everywhere.  On several
-# GPUs the better list kind depends on how much of the halo the force kernel hides (full: no reverse pass;
-# half: half the pair work), so `--list auto` MEASURES it there: 20 untimed steps of each kind before the
-# warm-up, the faster one (max over ranks) runs the timed region.  The table's N>1 column is only the
-# order in which the candidates are tried.
-LIST_AUTO = {"lj": {1: "half", 2: "full"}, "eam": {1: "half", 2: "half"}, "chain": {1: "half", 2: "half"}}
-# algorithmic bytes of the half-list kernels per atom per step (N_h listed pairs per atom, each:
-# 4 index + 24 x_j [+ 8 fp_j] gathered, 24 f_j [8 rho_j] as RED payload; plus the per-atom terms)
-N_HALF = {"lj": 37.6, "eam": 37.75, "chain": 4.87}
-BYTES_KERNEL_HALF = {"lj": 52 * 37.6 + 52, "eam": (36 + 60) * 37.75 + 104, "chain": 52 * 4.87 + 52 + 56 + 52}
+# algorithmic bytes: force pass(es) per owned atom per step, and whole step per atom-step.
+# N = full-list length, N_h = N/2.  full list: LJ 28N+52, EAM 64N+104; half list: LJ 52 N_h + 52 (4 index + 24 x_j
+# gathered + 24 f_j RED payload per listed pair), EAM 96 N_h + 104.
+N_FULL = {"lj": 75.2, "eam": 75.5, "c5": 88.8}
+BYTES_KERNEL = {k: {"full": (28 if k == "lj" else 64) * n + (52 if k == "lj" else 104),
+                    "half": (52 if k == "lj" else 96) * n / 2 + (52 if k == "lj" else 104)} for k, n in N_FULL.items()}
+BYTES_STEP = {"lj": 2480.0, "eam": 5510.0, "c5": 6420.0}
+KERNELS = {("lj", "half"): "k_lj<half>", ("lj", "full"): "k_lj<full>",
+           ("eam", "half"): "k_eam_rho_half+k_eam_embed+k_eam_force<half>", ("eam", "full"): "k_eam_rho_fp+k_eam_force",
+           ("c5", "half"): "k_eam_rho_half+k_eam_embed+k_eam_force<half>", ("c5", "full"): "k_eam_rho_fp+k_eam_force"}
+# thermo printed by the reference's own logs (bench/log.6Oct16.{lj,eam}.fixed.icc.1): T, E_pair, TotEng, Press
+LOG = {"lj": {0: (1.44, -6.7733681, -4.6134356, -5.0197073), 100: (0.7574531, -5.7585055, -4.6223613, 0.20726105)},
+       "eam": {0: (1600.0, -113280.0, -106662.09, 18703.573), 50: (781.69049, -109873.35, -106640.13, 52273.088),
+               100: (801.832, -109957.3, -106640.77, 51322.821)}}
 
 
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
-        return float(json.load(open(p))["hbm_gbs"]), "measured"
-    return 6650.0, "fallback"
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler(threading.Thread):
@@ -93,32 +97,177 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def ref_script(workload, xyz, warm, steps, langevin=True):
+# ------------------------------------------------------------------------------------------------------------
+# workloads
+# ------------------------------------------------------------------------------------------------------------
+def workload_xyz(wl, ngpus):
+    if wl in ("lj", "eam"):
+        return SCALE.get(ngpus, (4 * ngpus, 4, 4))
+    if wl == "c5":
+        return (5, 5, 5)
+    return (1, 1, 1)       # lj_32k, eam_32k
+
+
+def workload_desc(wl, ngpus):
+    xyz = workload_xyz(wl, ngpus)
+    natoms = 4 * 8000 * xyz[0] * xyz[1] * xyz[2]
+    kind = {"lj": "lj", "lj_32k": "lj", "eam": "eam", "eam_32k": "eam", "c5": "c5"}[wl]
+    text = {"lj": "bench/in.lj -var x %d -var y %d -var z %d (%d atoms, fcc lattice, lj/cut 2.5, neigh every 20, NVE)",
+            "eam": "bench/in.eam -var x %d -var y %d -var z %d (%d atoms, fcc lattice, eam Cu_u3, neigh check yes, NVE)",
+            "c5": "bench/in.eam with pair_style eam/alloy Cu_mishin1 -var x %d -var y %d -var z %d (%d atoms in total, "
+                  "strong scaling, neigh check yes, NVE)"}[kind] % (xyz[0], xyz[1], xyz[2], natoms)
+    return kind, xyz, natoms, text
+
+
+def ref_script(kind, xyz, warm, steps, thermo=0):
     from oracle import oracle as O
-    if workload == "lj":
+    if kind == "lj":
         body = O.IN_LJ.format(nx=20 * xyz[0], ny=20 * xyz[1], nz=20 * xyz[2])
-    elif workload == "chain":   # bench/in.chain.scaled (what the B200 arm runs, thermostat included unless --no-langevin)
-        body = ("units lj\natom_style bond\nspecial_bonds fene\nread_data %s\nreplicate %d %d %d\n"
-                "neighbor 0.4 bin\nneigh_modify every 1 delay 1\nbond_style fene\nbond_coeff 1 30.0 1.5 1.0 1.0\n"
-                "pair_style lj/cut 1.12\npair_modify shift yes\npair_coeff 1 1 1.0 1.0 1.12\nfix 1 all nve\n"
-                "%stimestep 0.012\n" % (os.path.join(os.path.dirname(O.POT_DIR), "data", "data.chain"), *xyz,
-                                       "fix 2 all langevin 1.0 1.0 10.0 904297\n" if langevin else ""))
-    else:
+    elif kind == "eam":
         body = O.IN_EAM.format(nx=20 * xyz[0], ny=20 * xyz[1], nz=20 * xyz[2], style="eam",
                                coeff="1 1 " + os.path.join(O.POT_DIR, "Cu_u3.eam"))
+    else:
+        body = O.IN_EAM.format(nx=20 * xyz[0], ny=20 * xyz[1], nz=20 * xyz[2], style="eam/alloy",
+                               coeff="* * " + os.path.join(O.POT_DIR, "Cu_mishin1.eam.alloy") + " Cu")
     body = body.replace("atom_modify map array\n", "")
+    if thermo:
+        body += "thermo %d\n" % thermo
     return body + ("run %d\n" % warm if warm > 0 else "") + "run %d\n" % steps
 
 
-def run_reference(workload, xyz, warm, steps, cores, langevin=True):
+def run_reference(kind, xyz, warm, steps, cores):
     """the reference's own CPU implementation (oracle/_ref/lmp, OPENMP package on all host cores)"""
     import re
     from oracle import oracle as O
-    t0 = time.time()
-    _, atoms, nst, out = O.ref_exe_run(ref_script(workload, xyz, warm, steps, langevin), threads=cores, omp=True, timeout=3000)
+    _, atoms, nst, out = O.ref_exe_run(ref_script(kind, xyz, warm, steps), threads=cores, omp=True, timeout=3000)
     loops = re.findall(r"Loop time of ([0-9.eE+-]+) on \d+ procs for (\d+) steps with (\d+) atoms", out)
     lt, nst, atoms = float(loops[-1][0]), int(loops[-1][1]), int(loops[-1][2])
-    return atoms * nst / lt, lt, atoms, time.time() - t0
+    return atoms * nst / lt, lt, atoms
+
+
+def fmt8(v):
+    return float("%.8g" % v)
+
+
+def thermo_mismatch(recs, want, per):
+    """recs: {step: thermo dict}; want: {step: (T, E_pair, TotEng, Press)} printed with 8 digits"""
+    for step, w in want.items():
+        t = recs.get(step)
+        if t is None:
+            return "no thermo record at step %d" % step
+        got = (t["temp"], t["pe"] / per, (t["pe"] + t["ke"]) / per, t["press"])
+        for name, a, b in zip(("T", "E_pair", "TotEng", "Press"), got, w):
+            if abs(fmt8(a) - b) > 2e-8 * abs(b):
+                return "step %d %s: got %.10g, the reference prints %.8g" % (step, name, a, b)
+    return None
+
+
+class Job:
+    """one process per GPU; NCCL id shipped over torch.distributed"""
+
+    def __init__(self):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        import b200pkg
+        self.P = b200pkg.load()
+        self.B = self.P.b200md
+        if self.world > 1:
+            import torch
+            import torch.distributed as dist
+            torch.cuda.set_device(self.local_rank)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+            self.dist = dist
+
+    def open(self, options=()):
+        B = self.B
+        ctx = B.Context(self.local_rank, self.rank, self.world)
+        if self.world > 1:
+            import torch
+            idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if self.rank == 0:
+                idt = torch.frombuffer(bytearray(B.Context.unique_id()), dtype=torch.uint8).cuda()
+            self.dist.broadcast(idt, 0)
+            ctx.comm_init(bytes(idt.cpu().numpy().tobytes()))
+        for k, v in options:
+            ctx.set_option(k, v)
+        return ctx
+
+    def barrier(self):
+        if self.dist is not None:
+            import torch
+            self.dist.barrier()
+            torch.cuda.synchronize()
+
+    def maxr(self, v):
+        if self.dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def configure(self, ctx, kind, xyz, lk):
+        B, P = self.B, self.P
+        list_kind = B.LIST_HALF_NEWTON if lk == "half" else B.LIST_FULL
+        if kind == "lj":
+            return P.inputs.in_lj(ctx, *xyz, list_kind=list_kind)
+        if kind == "eam":
+            return P.inputs.in_eam(ctx, *xyz, list_kind=list_kind)
+        return P.inputs.in_eam(ctx, *xyz, style="eam/alloy", list_kind=list_kind)
+
+
+def measure(job, ctx, cfg, natoms, steps, warmup, sampler=None):
+    """W warm-up steps, then K steps timed on the device (CUDA events on the context's stream around the K steps,
+    max over ranks) between barriers; then 20 more steps with per-phase events for the kernel figures"""
+    ctx.run(max(warmup, 3), cfg["dt"], 0)
+    if sampler:
+        sampler.start()
+    job.barrier()
+    t0 = time.perf_counter()
+    ctx.run(steps, cfg["dt"], 0)
+    job.barrier()
+    wall_ms = job.maxr((time.perf_counter() - t0) * 1e3)
+    tm = ctx.timing()
+    clocks = sampler.result() if sampler else None
+    dev_ms = job.maxr(tm["total_ms"])
+    ctx.set_option("phase_timing", "on")
+    ctx.run(20, cfg["dt"], 0)
+    ctx.set_option("phase_timing", "off")
+    tp = ctx.timing()
+    phases = {k: job.maxr(tp[k + "_ms"]) / 20 for k in ("pair", "neigh", "comm", "modify")}
+    return dict(value=natoms * steps / (dev_ms / 1e3), ms_per_step=dev_ms / steps, device_ms=dev_ms, wall_ms=wall_ms,
+                launches=int(tm["launches"]), rebuilds=int(tm["nbuilds"]), phases=phases, clocks=clocks)
+
+
+def roofline_of(kind, lk, m, nloc, ngpus):
+    hbm, which = peaks()
+    bk = BYTES_KERNEL[kind][lk]
+    pair_ms = m["phases"]["pair"]
+    achieved = bk * nloc / (pair_ms / 1e3) / 1e9
+    r = {"bound": "hbm", "kernel": KERNELS[(kind, lk)], "list": lk, "achieved": achieved, "peak": hbm, "peak_source": which,
+         "unit": "GB/s", "frac": achieved / hbm, "traffic": None, "kernel_ms": pair_ms, "bytes_per_atom_launch": bk,
+         "step_achieved": BYTES_STEP[kind] * (m["value"] / ngpus) / 1e9,
+         "step_frac": BYTES_STEP[kind] * (m["value"] / ngpus) / 1e9 / hbm,
+         "phases_ms_per_step": m["phases"],
+         "note": "algorithmic gather bytes (every listed neighbor record counted as an HBM read) over the measured copy "
+                 "bandwidth; atoms are bin-sorted, so most gathers hit L1/L2 and the unit that binds is the L1 LSU data "
+                 "pipe, see binding_unit / DESIGN.md §3"}
+    # DRAM traffic and the binding unit of THIS kernel variant from its `ncu --set full` capture (profiles/), if one is
+    # committed for exactly this kernel name
+    tr = os.path.join(ROOT, "profiles", "traffic_%s_%s.json" % ("eam" if kind == "c5" else kind, lk))
+    if os.path.exists(tr):
+        t = json.load(open(tr))
+        if t.get("kernel_variant") == kernel_variant():
+            r["traffic"] = t.get("dram_bytes_per_launch")
+            r["binding_unit"] = t.get("binding_unit")
+    return r
+
+
+def kernel_variant():
+    p = os.path.join(ROOT, "profiles", "KERNEL_VARIANT")
+    return open(p).read().strip() if os.path.exists(p) else None
 
 
 def main():
@@ -126,202 +275,210 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--workload", default="lj", choices=["lj", "eam", "chain"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="lj", choices=["lj", "eam", "c5"],
+                    help="the workload reported as `value` (default lj = config C4; the others are always under `secondary`)")
     ap.add_argument("--lanes", type=int, default=0)
     ap.add_argument("--list", default="auto", choices=["auto", "half", "full"],
                     help="half = half/bin/atomonly/newton (the input scripts' default, newton on); full = newton off")
+    ap.add_argument("--option", action="append", default=[], metavar="KEY=VALUE", help="b200md_set_option, e.g. halo=staged")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-langevin", action="store_true",
-                    help="chain workload: leave `fix langevin` out (one GPU runs it by default, as bench/in.chain ships it)")
+    ap.add_argument("--no-secondary", action="store_true", help="skip secondary.* (development runs)")
+    ap.add_argument("--no-parity", action="store_true", help="skip parity_check (development runs)")
+    ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     ngpus = a.gpus
-    xyz = SCALE.get(ngpus, (4 * ngpus, 4, 4))
-    natoms = 4 * 8000 * xyz[0] * xyz[1] * xyz[2]
-    wl = a.workload
-    # the thermostat's random stream follows one rank's local atom order (the reference seeds every rank
-    # separately): it is part of the chain workload on one GPU
-    langevin = wl == "chain" and not a.no_langevin and world == 1 and ngpus == 1
-    desc = {"lj": "fcc lattice, lj/cut 2.5, neigh every 20", "eam": "fcc lattice, eam Cu_u3, neigh check yes",
-            "chain": "data.chain replicated, FENE bonds + lj/cut 1.12, special_bonds fene, "
-                     + ("fix langevin 1.0 1.0 10.0 904297 (the reference's RanMars stream)" if langevin else "fix langevin left out")}[wl]
-    config = {"workload": "bench/in.%s -var x %d -var y %d -var z %d (%d atoms, %s)" % (
-        wl + (".scaled" if wl == "chain" else ""), xyz[0], xyz[1], xyz[2], natoms, desc + (", NVE" if not langevin else "")),
-        "atoms_per_gpu": natoms // ngpus, "decomposition": None,
-        "l2": "working set (neighbor list >= 1 GB/GPU) exceeds the 126 MB L2; no flush needed"}
     cores = os.cpu_count() or 1
+    kind, xyz, natoms, text = workload_desc(a.workload, ngpus)
+    # `config` is the same object in both arms (the driver compares them); run-specific details go to `run`
+    config = {"workload": text, "atoms_per_gpu": natoms // ngpus,
+              "l2": "working set (neighbor list >= 0.5 GB/GPU) exceeds the 126 MB L2; no flush needed"}
 
     if a.impl == "reference":
-        if rank != 0:
+        if int(os.environ.get("RANK", "0")) != 0:
             return 0
-        val, lt, atoms, wall = run_reference(wl, xyz, a.warmup, a.steps, cores, langevin)
+        val, lt, atoms = run_reference(kind, xyz, a.warmup, a.steps, cores)
         line = {"impl": "reference", "metric": "atom-steps/s", "value": val, "unit": "atom-steps/s", "n_gpus": ngpus,
                 "steps": a.steps, "warmup": a.warmup, "ms_per_step": lt / a.steps * 1e3, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": val, "unit": "atom-steps/s", "cores": cores, "kind": "reference",
                                  "sample": "full workload, %d steps, oracle/_ref/lmp -sf omp -pk omp %d" % (a.steps, cores)},
                 "e2e": {"value": val, "unit": "atom-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        if not a.no_secondary:
+            sec = {}
+            for name, wl in (("eam", "eam"), ("eam_alloy_strong", "c5")):
+                k2, xyz2, n2, text2 = workload_desc(wl, ngpus)
+                sample = min(a.steps, 20)
+                try:
+                    v2, lt2, at2 = run_reference(k2, xyz2, 0, sample, cores)
+                    sec[name] = {"value": v2, "unit": "atom-steps/s", "ms_per_step": lt2 / sample * 1e3, "workload": text2,
+                                 "sample": "%d steps, oracle/_ref/lmp -sf omp -pk omp %d" % (sample, cores)}
+                except Exception as e:
+                    sec[name] = {"value": None, "unavailable": str(e)[:200]}
+            line["secondary"] = sec
         print(json.dumps(line))
         return 0
 
-    import b200pkg
-    P = b200pkg.load()
-    B = P.b200md
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    ctx = B.Context(local_rank, rank, world)
-    if world > 1:
-        import torch
-        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            idt = torch.frombuffer(bytearray(B.Context.unique_id()), dtype=torch.uint8).cuda()
-        dist.broadcast(idt, 0)
-        ctx.comm_init(bytes(idt.cpu().numpy().tobytes()))
+    job = Job()
+    B, rank, world = job.B, job.rank, job.world
+    options = [tuple(o.split("=", 1)) for o in a.option]
     if a.lanes:
-        ctx.set_lanes_per_atom(a.lanes)
-    # list kind: the scripts run with `newton on` -> half list (f_j, rho_j by FP64 RED + reverse_comm);
-    # measured on B200 (profiles/): half wins on one GPU; with several ranks the full list lets the
-    # force kernel overlap the halo and needs no reverse_comm
-    lk = a.list if a.list != "auto" else LIST_AUTO[wl][min(world, 2)]
-    list_kind = B.LIST_HALF_NEWTON if lk == "half" else B.LIST_FULL
-    config["neighbor_list"] = "half/bin/atomonly/newton" if lk == "half" else "full/bin/atomonly (newton off)"
-    if wl == "lj":
-        cfg = P.inputs.in_lj(ctx, *xyz, list_kind=list_kind)
-    elif wl == "chain":
-        cfg = P.inputs.in_chain(ctx, os.path.join(ROOT, "oracle", "_ref", "data", "data.chain"), *xyz, list_kind=list_kind,
-                                langevin=langevin)
-    else:
-        cfg = P.inputs.in_eam(ctx, *xyz, potential=os.path.join(ROOT, "oracle", "_ref", "potentials", "Cu_u3.eam"),
-                              list_kind=list_kind)
-    config["decomposition"] = "x".join(str(g) for g in B.procgrid(world, [20.0 * xyz[0], 20.0 * xyz[1], 20.0 * xyz[2]]))
-    config["halo"] = ("none (one rank)" if world == 1 else
-                      "staged (3 x 2 NCCL send/recv stages)" if os.environ.get("B200MD_HALO") == "staged" else
-                      "direct (owner <-> holder, one NCCL group per exchange)")
+        options.append(("lanes", str(a.lanes)))
+    run_info = {"decomposition": "x".join(str(g) for g in B.procgrid(world, [20.0 * xyz[0], 20.0 * xyz[1], 20.0 * xyz[2]]))}
+
+    # ---- list kind.  The scripts run with `newton on` -> half list (f_j, rho_j by FP64 RED + reverse_comm); measured on
+    # B200 (profiles/) the half list wins on one GPU.  On several ranks `--list auto` MEASURES it for in.lj (20 untimed
+    # steps of each kind) and uses half for eam ----
+    lk_main = a.list if a.list != "auto" else "half"
+    ctx = job.open(options)
+    run_info["halo"] = ctx.get_option("halo")
+    cfg = job.configure(ctx, kind, xyz, lk_main)
     ctx.setup()
-
-    def barrier():
-        if dist is not None:
-            import torch
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    def maxr(v):
-        if dist is None:
-            return v
-        import torch
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    # ---- several ranks, --list auto: the list kind is chosen by measurement (untimed, before the warm-up) ----
-    if world > 1 and a.list == "auto" and wl != "chain":
+    if world > 1 and a.list == "auto" and kind == "lj":
         trial = {}
-        for kind in ("full", "half"):
-            ctx.neigh_config(**cfg["neigh"], list_kind=B.LIST_HALF_NEWTON if kind == "half" else B.LIST_FULL)
+        for k2 in ("full", "half"):
+            ctx.neigh_config(**cfg["neigh"], list_kind=B.LIST_HALF_NEWTON if k2 == "half" else B.LIST_FULL)
             ctx.setup()
             ctx.run(5, cfg["dt"], 0)
-            barrier()
+            job.barrier()
             ctx.run(20, cfg["dt"], 0)
-            trial[kind] = maxr(ctx.timing()["total_ms"]) / 20     # CUDA events on the context's stream, max over ranks
-        lk = min(trial, key=trial.get)
-        list_kind = B.LIST_HALF_NEWTON if lk == "half" else B.LIST_FULL
-        ctx.neigh_config(**cfg["neigh"], list_kind=list_kind)
-        ctx.setup()
-        config["neighbor_list"] = "half/bin/atomonly/newton" if lk == "half" else "full/bin/atomonly (newton off)"
-        config["list_trial_ms_per_step"] = trial
+            trial[k2] = job.maxr(ctx.timing()["total_ms"]) / 20     # CUDA events on the context's stream, max over ranks
+        lk_main = min(trial, key=trial.get)
+        run_info["list_trial_ms_per_step"] = trial
+    ctx.close()
+    run_info["neighbor_list"] = "half/bin/atomonly/newton" if lk_main == "half" else "full/bin/atomonly (newton off)"
+    lk_sec = a.list if a.list != "auto" else "half"
 
-    # ---- device-resident loop: W warm-up steps, K timed steps ----
-    ctx.run(max(a.warmup, 3), cfg["dt"], 0)
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    barrier()
-    t0 = time.perf_counter()
-    ctx.run(a.steps, cfg["dt"], 0)
-    barrier()
-    wall_ms = (time.perf_counter() - t0) * 1e3
-    tm = ctx.timing()
-    clocks = sampler.result()
-    dev_ms = maxr(tm["total_ms"])
-    ms = dev_ms   # device time (CUDA events around the K steps on the context's stream), max over ranks; wall_ms is reported beside it
-    value = natoms * a.steps / (ms / 1e3)
+    # ---- parity check on the N ranks, before anything is timed ----
+    parity = {"nranks": world, "halo": run_info["halo"], "lists": {"lj": lk_main, "eam": lk_sec}}
+    small = {}
+    if not a.no_parity:
+        for wl, lk in (("lj", lk_main), ("eam", lk_sec)):
+            ctx = job.open(options)
+            cfg = job.configure(ctx, wl, (1, 1, 1), lk)
+            ctx.setup()
+            recs = {0: ctx.thermo()}
+            for t in ctx.run(100, cfg["dt"], 50):
+                recs[t["step"]] = t
+            bad = thermo_mismatch(recs, LOG[wl], 32000.0 if wl == "lj" else 1.0)
+            parity[wl] = "ok" if bad is None else "MISMATCH " + bad
+            # the 32 000-atom configs as shipped (C1, C2): 100 more steps, timed on the device
+            job.barrier()
+            ctx.run(100, cfg["dt"], 50 if wl == "eam" else 0)
+            tm = ctx.timing()
+            ms = job.maxr(tm["total_ms"])
+            small[wl + "_32k"] = {"value": 32000 * 100 / (ms / 1e3), "unit": "atom-steps/s", "ms_per_step": ms / 100,
+                                  "launches": int(tm["launches"]), "rebuilds": int(tm["nbuilds"]), "list": lk,
+                                  "workload": "bench/in.%s as shipped (32 000 atoms)" % wl}
+            ctx.close()
+        if any(str(parity[w]).startswith("MISMATCH") for w in ("lj", "eam")):
+            if rank == 0:
+                print(json.dumps({"parity_check": parity, "error": "thermo differs from the reference logs"}))
+            return 2
 
-    # ---- dominant kernel: pair force kernel(s), CUDA events around each launch on its stream ----
-    os.environ["B200MD_PHASE_TIMING"] = "1"
-    ctx.run(20, cfg["dt"], 0)
-    os.environ["B200MD_PHASE_TIMING"] = "0"
-    tp = ctx.timing()
-    n_eval = 20
-    pair_ms = tp["pair_ms"] / n_eval  # per timestep (LJ: one launch; EAM: rho+fp, fp halo, force)
+    # ---- the workload reported as `value`: device-resident loop ----
+    ctx = job.open(options)
+    cfg = job.configure(ctx, kind, xyz, lk_main)
+    ctx.setup()
+    m = measure(job, ctx, cfg, natoms, a.steps, a.warmup, ClockSampler(job.local_rank))
     nloc = ctx.nlocal()[0]
-    hbm, which = peaks()
-    bytes_kernel = BYTES_KERNEL_HALF[wl] if lk == "half" else BYTES_KERNEL[wl]
-    bstep = BYTES_STEP["chain+langevin" if langevin else wl]
-    achieved = bytes_kernel * nloc / (pair_ms / 1e3) / 1e9
-    roofline = {"bound": "hbm", "kernel": ("k_lj" if wl == "lj" else "k_lj+k_bond_fene" if wl == "chain" else ("k_eam_rho_half+k_eam_embed+k_eam_force" if lk == "half" else "k_eam_rho_fp+k_eam_force")),
-                "list": lk, "achieved": achieved,
-                "peak": hbm, "peak_source": which, "unit": "GB/s", "frac": achieved / hbm, "traffic": None,
-                "kernel_ms": pair_ms, "bytes_per_atom_launch": bytes_kernel,
-                "step_achieved": bstep * (value / ngpus) / 1e9, "step_frac": bstep * (value / ngpus) / 1e9 / hbm,
-                "phases_ms_per_step": {k: tp[k + "_ms"] / n_eval for k in ("pair", "neigh", "comm", "modify")}}
-    tr = os.path.join(ROOT, "profiles", "traffic_%s_%s.json" % (wl, lk))
-    if not os.path.exists(tr):
-        tr = os.path.join(ROOT, "profiles", "traffic_%s.json" % wl)
-    if os.path.exists(tr):
-        roofline["traffic"] = json.load(open(tr)).get("dram_bytes_per_launch")
+    roofline = roofline_of(kind, lk_main, m, nloc, ngpus)
 
-    # ---- end to end through the C ABI with HOST buffers: every step uploads x,v (pinned) and
-    # downloads x,v,f,tag of the step's result ----
-    n = ctx.nlocal()[0]
-    cap = int(n * 1.05) + 1024
-    hx, hv, hf = B.pinned_empty((cap, 3)), B.pinned_empty((cap, 3)), B.pinned_empty((cap, 3))
-    htag = B.pinned_empty((cap,), np.int32)
-    ctx.get_atoms_into(hx, hv, hf, htag)
-    e2e_steps = a.steps
-    for _ in range(3):
-        ctx.put_atoms(hx, hv); ctx.run(1, cfg["dt"], 0); ctx.get_atoms_into(hx, hv, hf, htag)
-    barrier()
-    t0 = time.perf_counter()
-    h2d = d2h = 0
-    for _ in range(e2e_steps):
+    # ---- end to end through the C ABI with HOST buffers (pinned): every step uploads the step's inputs and downloads
+    # its result.  "full_state": x,v up and x,v,f,tag down (a host that owns the whole state); "offload": x up and f down,
+    # the per-step boundary of the reference's own GPU package (src/GPU/pair_lj_cut_gpu.cpp:98-102) ----
+    e2e = None
+    if not a.no_e2e:
         n = ctx.nlocal()[0]
-        ctx.put_atoms(hx, hv)
-        ctx.run(1, cfg["dt"], 0)
-        n = ctx.nlocal()[0]
+        cap = int(n * 1.05) + 1024
+        hx, hv, hf = B.pinned_empty((cap, 3)), B.pinned_empty((cap, 3)), B.pinned_empty((cap, 3))
+        htag = B.pinned_empty((cap,), np.int32)
         ctx.get_atoms_into(hx, hv, hf, htag)
-        h2d += 48 * n; d2h += 76 * n
-    barrier()
-    e2e_ms = maxr((time.perf_counter() - t0) * 1e3)
-    e2e = {"value": natoms * e2e_steps / (e2e_ms / 1e3), "unit": "atom-steps/s", "h2d_bytes_per_step": h2d // e2e_steps,
-           "d2h_bytes_per_step": d2h // e2e_steps, "ms_per_step": e2e_ms / e2e_steps,
-           "api": "b200md_put_atoms(x,v) + b200md_run(1) + b200md_get_atoms(x,v,f,tag), pinned host buffers"}
+        variants = {}
+        for name in ("full_state", "offload"):
+            full = name == "full_state"
+            for _ in range(3):
+                ctx.put_atoms(hx, hv if full else None); ctx.run(1, cfg["dt"], 0)
+                ctx.get_atoms_into(hx if full else None, hv if full else None, hf, htag if full else None)
+            job.barrier()
+            t0 = time.perf_counter()
+            h2d = d2h = 0
+            for _ in range(a.steps):
+                n = ctx.nlocal()[0]
+                ctx.put_atoms(hx, hv if full else None)
+                ctx.run(1, cfg["dt"], 0)
+                n2 = ctx.nlocal()[0]
+                ctx.get_atoms_into(hx if full else None, hv if full else None, hf, htag if full else None)
+                h2d += (48 if full else 24) * n; d2h += (76 if full else 24) * n2
+            job.barrier()
+            ms = job.maxr((time.perf_counter() - t0) * 1e3)
+            variants[name] = {"value": natoms * a.steps / (ms / 1e3), "ms_per_step": ms / a.steps,
+                              "h2d_bytes_per_step": h2d // a.steps, "d2h_bytes_per_step": d2h // a.steps}
+            if not full:   # the host keeps integrating its own copy in a real offload; here x is refreshed for the next step
+                ctx.get_atoms_into(hx, hv, hf, htag)
+        e2e = dict(variants["full_state"], unit="atom-steps/s",
+                   api="b200md_put_atoms(x,v) + b200md_run(1) + b200md_get_atoms(x,v,f,tag), pinned host buffers, every step",
+                   offload=dict(variants["offload"], api="b200md_put_atoms(x) + b200md_run(1) + b200md_get_atoms(f)"))
+    ctx.close()
 
-    line = {"metric": "atom-steps/s", "value": value, "unit": "atom-steps/s", "n_gpus": ngpus, "steps": a.steps,
-            "warmup": max(a.warmup, 3), "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config, "roofline": roofline, "e2e": e2e,
-            "gpu_launches": int(tm["launches"]), "clocks": clocks, "device_ms": dev_ms, "wall_ms": maxr(wall_ms),
-            "rebuilds_in_timed_region": int(tm["nbuilds"])}
+    # ---- secondary workloads (same JSON line: the driver only ever runs `bench.py --gpus N`) ----
+    secondary = dict(small)
+    if not a.no_secondary:
+        for name, wl in (("eam", "eam"), ("eam_alloy_strong", "c5")):
+            if wl == a.workload:
+                continue
+            k2, xyz2, n2, text2 = workload_desc(wl, ngpus)
+            ctx = job.open(options)
+            cfg2 = job.configure(ctx, k2, xyz2, lk_sec)
+            ctx.setup()
+            entry = {"unit": "atom-steps/s", "workload": text2, "list": lk_sec,
+                     "scaling": "strong" if wl == "c5" else "weak"}
+            if wl == "c5" and not a.no_parity:
+                # parity of the strong-scaling config from the run itself: 100 steps from the set-up, thermo 50
+                gold = json.load(open(os.path.join(ROOT, "tests", "golden", "c5_thermo.json")))
+                recs = {0: ctx.thermo()}
+                for t in ctx.run(100, cfg2["dt"], 50):
+                    recs[t["step"]] = t
+                bad = None
+                for step in ("0", "50", "100"):
+                    for key in ("temp", "pe", "ke", "press"):
+                        got, want = recs[int(step)][key], gold["thermo"][step][key]
+                        if abs(got - want) > 1e-8 * abs(want) and bad is None:
+                            bad = "step %s %s: got %.12g, reference %.12g" % (step, key, got, want)
+                parity["eam_alloy_4M"] = "ok" if bad is None else "MISMATCH " + bad
+                entry["rebuilds_first_100_steps"] = int(ctx.timing()["nbuilds"])
+                entry["reference_rebuilds_first_100_steps"] = gold["neighbor_list_builds"]
+            m2 = measure(job, ctx, cfg2, n2, a.steps, a.warmup)
+            entry.update(value=m2["value"], ms_per_step=m2["ms_per_step"], launches=m2["launches"], rebuilds=m2["rebuilds"],
+                         roofline=roofline_of(k2, lk_sec, m2, ctx.nlocal()[0], ngpus))
+            ctx.close()
+            secondary[name] = entry
+        if str(parity.get("eam_alloy_4M", "ok")).startswith("MISMATCH"):
+            if rank == 0:
+                print(json.dumps({"parity_check": parity, "error": "eam/alloy 4M thermo differs from the reference"}))
+            return 2
+
+    line = {"metric": "atom-steps/s", "value": m["value"], "unit": "atom-steps/s", "n_gpus": ngpus, "steps": a.steps,
+            "warmup": max(a.warmup, 3), "ms_per_step": m["ms_per_step"], "higher_is_better": True,
+            "scaling": "strong" if a.workload == "c5" else "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config, "run": run_info,
+            "parity_check": parity, "roofline": roofline, "e2e": e2e, "secondary": secondary,
+            "gpu_launches": m["launches"], "clocks": m["clocks"], "device_ms": m["device_ms"], "wall_ms": m["wall_ms"],
+            "rebuilds_in_timed_region": m["rebuilds"]}
     if rank == 0 and not a.no_cpu_baseline and ngpus == 1:
         try:
             sample_steps = 20
-            val, lt, atoms, wall = run_reference(wl, xyz, 0, sample_steps, cores, langevin)
+            val, lt, atoms = run_reference(kind, xyz, 0, sample_steps, cores)
             line["cpu_baseline"] = {"value": val, "unit": "atom-steps/s", "cores": cores, "kind": "reference",
                                     "sample": "same workload (%d atoms), %d steps, oracle/_ref/lmp -sf omp -pk omp %d, Loop time %.3f s"
                                               % (atoms, sample_steps, cores, lt)}
         except Exception as e:  # the checker is optional for the measurement itself
             line["cpu_baseline"] = {"value": None, "unit": "atom-steps/s", "cores": cores, "kind": "reference",
                                     "sample": "unavailable: %s" % str(e)[:200]}
-    ctx.close()
     if rank == 0:
         print(json.dumps(line))
-    if dist is not None:
-        dist.destroy_process_group()
+    if job.dist is not None:
+        job.dist.destroy_process_group()
     return 0
 
 

@@ -332,6 +332,23 @@ int b200md_get_timing(b200md_ctx *ctx, b200md_timing *out);
 /* tuning knob: lanes cooperating on one atom in the pair kernels (1,2,4,8,16,32); the list
  * build has its own lane count (default 1). Call before b200md_setup. */
 int b200md_set_lanes_per_atom(b200md_ctx *ctx, int lanes);
+/* Runtime options, the role the reference gives its `package <accelerator> <keyword> <value>`
+ * command (Input::package src/input.cpp -> KokkosLMP::accelerator src/KOKKOS/kokkos.cpp:300-560,
+ * FixGPU src/GPU/fix_gpu.cpp:90-230): `package b200 <keyword> <value>` in verlet/b200.  The library
+ * reads NO environment variables.  Keywords (value as text):
+ *   halo         direct | staged   per-step ghost traffic owner<->holder in one exchange, or the
+ *                                  reference's three forwarding stages (several ranks only)
+ *   overlap      on | off          compute / halo overlap on several ranks
+ *   split        0..1              share of the interior tiles evaluated before the boundary tiles
+ *   fuse_nve     on | off          final_integrate(n) + initial_integrate(n+1) in one pass (default on)
+ *   eam_smem     on | off          one-element EAM tables staged in shared memory (default off)
+ *   phase_timing on | off          per-phase CUDA events in b200md_run (b200md_get_timing)
+ *   lanes        1,2,...,32        = b200md_set_lanes_per_atom
+ *   build_lanes  1,2,...,32        lanes per atom in the list build
+ *   graph        on | off          small-system mode: non-rebuild steps replayed as a CUDA graph
+ * Unknown keywords and bad values fail with "Illegal package b200 command: ...". */
+int b200md_set_option(b200md_ctx *ctx, const char *key, const char *value);
+int b200md_get_option(b200md_ctx *ctx, const char *key, char *value, int len);
 /* cudaStream_t of the context (as void*), for callers that time with their own events. */
 int b200md_get_stream(b200md_ctx *ctx, void **stream);
 

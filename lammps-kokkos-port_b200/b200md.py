@@ -19,6 +19,7 @@ LIB_PATH = os.environ.get("B200MD_LIB", os.path.join(_HERE, "libb200md.so"))
 LIST_FULL, LIST_HALF_NEWTON = 0, 1
 PERATOM_PAIR, PERATOM_BOND = 1, 2
 MAXSWAP = 64
+OPTION_KEYS = ("halo", "overlap", "split", "fuse_nve", "eam_smem", "phase_timing", "lanes", "build_lanes", "graph")
 
 
 class B200MDError(RuntimeError):
@@ -206,6 +207,22 @@ class Context:
         _chk(self.L.b200md_create(int(device), int(rank), int(nranks), C.byref(self.h)))
         self.rank, self.nranks = rank, nranks
         self.ntypes = 0
+        # developer convenience of THIS driver (the library itself reads no environment): B200MD_<KEY>=value
+        for key in OPTION_KEYS:
+            v = os.environ.get("B200MD_" + key.upper())
+            if v is not None:
+                self.set_option(key, v)
+
+    def set_option(self, key, value):
+        """`package b200 <key> <value>` (include/b200md.h: b200md_set_option)"""
+        if isinstance(value, bool):
+            value = "on" if value else "off"
+        _chk(self.L.b200md_set_option(self.h, str(key).encode(), str(value).encode()))
+
+    def get_option(self, key):
+        buf = C.create_string_buffer(64)
+        _chk(self.L.b200md_get_option(self.h, str(key).encode(), buf, 64))
+        return buf.value.decode()
 
     def close(self):
         if self.h:
@@ -476,7 +493,9 @@ def lj_cut_tables(ntypes, coeffs, cut_global, mix="geometric", shift=False):
                     eps[i, j] = math.sqrt(eps[i, i] * eps[j, j]); sig[i, j] = 0.5 * (sig[i, i] + sig[j, j])
                 else:
                     raise B200MDError("unsupported pair_modify mix " + mix)
-                cut[i, j] = max(cut[i, i], cut[j, j])
+                # PairLJCut::init_one: cut[i][j] = mix_distance(cut[i][i], cut[j][j]) (src/pair_lj_cut.cpp:506,
+                # Pair::mix_distance src/pair.cpp:722-733) -- the same rule as sigma
+                cut[i, j] = math.sqrt(cut[i, i] * cut[j, j]) if mix == "geometric" else 0.5 * (cut[i, i] + cut[j, j])
             e, s, c = eps[i, j], sig[i, j], cut[i, j]
             v = dict(cutsq=c * c, lj1=48.0 * e * s ** 12, lj2=24.0 * e * s ** 6, lj3=4.0 * e * s ** 12,
                      lj4=4.0 * e * s ** 6, offset=0.0)

@@ -6,6 +6,8 @@
 // (:229-360); the rebuild decision follows Neighbor::decide/check_distance
 // (src/neighbor.cpp:2309-2390).
 #include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include "ctx.h"
 
@@ -67,13 +69,10 @@ extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out)
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rev, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rb, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rr, cudaEventDisableTiming));
-  if (const char *sp = getenv("B200MD_SPLIT")) c->split = atof(sp);
-  if (const char *bl = getenv("B200MD_BUILD_LANES")) { c->tpa_build = atoi(bl); c->tpa_build_user = true; }   // tuning
-  { const char *ov = getenv("B200MD_OVERLAP"); c->overlap = !(ov && ov[0] == '0'); }
-  { const char *fu = getenv("B200MD_FUSE_NVE"); c->fuse_nve = fu && fu[0] == '1'; }
-  // per-step halo: owner <-> holder in one NCCL group ("direct", default on several ranks) or the
-  // reference's three forwarding stages (B200MD_HALO=staged)
-  { const char *hl = getenv("B200MD_HALO"); c->direct.on = nranks > 1 && !(hl && !strcmp(hl, "staged")); }
+  // runtime knobs are set through b200md_set_option (the library reads no environment variables);
+  // per-step halo: owner <-> holder in one exchange ("direct", default on several ranks) or the
+  // reference's three forwarding stages ("staged")
+  c->direct.on = nranks > 1;
   CUDA_TRY(cudaMalloc(&c->d_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMallocHost(&c->h_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMalloc(&c->d_flags, 8 * sizeof(int)));
@@ -469,6 +468,72 @@ extern "C" int b200md_get_stream(b200md_ctx *c, void **stream) {
 }
 
 // ---------------------------------------------------------------------------------------
+// runtime options: what the reference's accelerator packages take through the `package` command
+// (src/input.cpp Input::package -> FixGPU / KokkosLMP::accelerator, src/KOKKOS/kokkos.cpp:300-560)
+// ---------------------------------------------------------------------------------------
+static bool opt_bool(const char *v, bool *out) {
+  if (!strcmp(v, "1") || !strcmp(v, "on") || !strcmp(v, "yes")) { *out = true; return true; }
+  if (!strcmp(v, "0") || !strcmp(v, "off") || !strcmp(v, "no")) { *out = false; return true; }
+  return false;
+}
+static bool lanes_ok(int l) { return l == 1 || l == 2 || l == 4 || l == 8 || l == 16 || l == 32; }
+
+extern "C" int b200md_set_option(b200md_ctx *c, const char *key, const char *value) {
+  NEED(c && key && value, "b200md: null argument");
+  const std::string k(key);
+  bool b = false;
+  if (k == "halo") {
+    if (!strcmp(value, "direct")) c->direct.on = c->nranks > 1;
+    else if (!strcmp(value, "staged")) c->direct.on = false;
+    else { b200md_set_error("Illegal package b200 command: halo must be direct or staged"); return B200MD_ERR; }
+    c->direct.ready = false;
+  } else if (k == "overlap") {
+    NEED(opt_bool(value, &b), "Illegal package b200 command: overlap must be on or off");
+    c->overlap = b;
+  } else if (k == "split") {
+    const double s = atof(value);
+    NEED(s >= 0.0 && s <= 1.0, "Illegal package b200 command: split must be in [0,1]");
+    c->split = s;
+  } else if (k == "fuse_nve") {
+    NEED(opt_bool(value, &b), "Illegal package b200 command: fuse_nve must be on or off");
+    c->fuse_nve = b;
+  } else if (k == "eam_smem") {
+    NEED(opt_bool(value, &b), "Illegal package b200 command: eam_smem must be on or off");
+    c->eam_smem = b;
+  } else if (k == "phase_timing") {
+    NEED(opt_bool(value, &b), "Illegal package b200 command: phase_timing must be on or off");
+    c->phase_timing = b;
+  } else if (k == "build_lanes") {
+    const int l = atoi(value);
+    NEED(lanes_ok(l), "Illegal package b200 command: build_lanes must be 1, 2, 4, 8, 16 or 32");
+    c->tpa_build = l; c->tpa_build_user = true;
+  } else if (k == "lanes") {
+    return b200md_set_lanes_per_atom(c, atoi(value));
+  } else {
+    b200md_set_error("Illegal package b200 command: unknown keyword " + k);
+    return B200MD_ERR;
+  }
+  return B200MD_OK;
+}
+
+extern "C" int b200md_get_option(b200md_ctx *c, const char *key, char *value, int len) {
+  NEED(c && key && value && len > 0, "b200md: null argument");
+  const std::string k(key);
+  std::string v;
+  if (k == "halo") v = c->nranks == 1 ? "none" : (c->direct.on ? "direct" : "staged");
+  else if (k == "overlap") v = c->overlap ? "on" : "off";
+  else if (k == "split") v = std::to_string(c->split);
+  else if (k == "fuse_nve") v = c->fuse_nve ? "on" : "off";
+  else if (k == "eam_smem") v = c->eam_smem ? "on" : "off";
+  else if (k == "phase_timing") v = c->phase_timing ? "on" : "off";
+  else if (k == "build_lanes") v = std::to_string(c->tpa_build);
+  else if (k == "lanes") v = std::to_string(c->tpa);
+  else { b200md_set_error("Illegal package b200 command: unknown keyword " + k); return B200MD_ERR; }
+  snprintf(value, len, "%s", v.c_str());
+  return B200MD_OK;
+}
+
+// ---------------------------------------------------------------------------------------
 // pair
 // ---------------------------------------------------------------------------------------
 extern "C" int b200md_pair_lj_cut_config(b200md_ctx *c, int ntypes, const double *cutsq, const double *lj1,
@@ -782,9 +847,8 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
   const double dtv = dt, dtf = 0.5 * dt * c->ftm2v;  // FixNVE::init (src/fix_nve.cpp:51-58)
   const long long first = c->step, last = c->step + nsteps;
   int nth = 0;
-  const char *pt = getenv("B200MD_PHASE_TIMING");
   size_t ev_used = 0;
-  PhaseTimer T{c, pt && pt[0] == '1', &ev_used};
+  PhaseTimer T{c, c->phase_timing, &ev_used};
   const long long launches0 = c->launches, pl0 = c->pair_launches, nb0 = c->nbuilds;
   PhaseTimer TT{c, true, &ev_used};
   Langevin &LG = c->lang;
@@ -827,7 +891,14 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     if (out_step && thermo_out && nth < max_thermo) { TRY(b200md_thermo_compute(c, &thermo_out[nth])); nth++; }
   }
   TT.end();
+  if (c->topo.molecular) CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4, c->d_flags + 4, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
+  if (c->topo.molecular && c->h_flags[4]) {   // bond kernel flags, at least once per run (bond.cu)
+    const int fl = c->h_flags[4];
+    CUDA_TRY(cudaMemsetAsync(c->d_flags + 4, 0, sizeof(int), c->stream));
+    if (fl & 1) { b200md_set_error("Bond atoms missing"); return B200MD_ERR; }
+    if (fl & 4) { b200md_set_error("Bad FENE bond"); return B200MD_ERR; }
+  }
   if (n_thermo) *n_thermo = nth;
   float ms = 0;
   cudaEventElapsedTime(&ms, TT.spans[0].second.first, TT.spans[0].second.second);

@@ -187,6 +187,7 @@ int bond_compute(b200md_ctx *c, int eflag, int vflag) {
     // the reduction synchronised the stream: the error flags of this evaluation are final
     int fl = 0;
     CUDA_TRY(cudaMemcpy(&fl, c->d_flags + 4, sizeof(int), cudaMemcpyDeviceToHost));
+    if (fl) CUDA_TRY(cudaMemsetAsync(c->d_flags + 4, 0, sizeof(int), c->stream));   // read -> cleared
     if (fl & 1) { b200md_set_error("Bond atoms missing"); return B200MD_ERR; }
     if (fl & 4) { b200md_set_error("Bad FENE bond"); return B200MD_ERR; }
   }

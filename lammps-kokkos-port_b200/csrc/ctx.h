@@ -87,6 +87,11 @@ struct Langevin {
   // Atom::sort schedule of the host the stream order mirrors (atom.cpp:102-103, 2252; verlet.cpp:285)
   long long sortfreq = 1000, nextsort = 0;
   bool resort_pending = false;     // set by b200md_run for the rebuild that has to re-rank first
+  unsigned long long *sort_keys = nullptr;   // langevin_resort scratch: [2][sort_cap] keys, values, radix-sort workspace
+  int *sort_vals = nullptr;
+  void *sort_tmp = nullptr;
+  int sort_cap = 0;
+  size_t sort_tmp_bytes = 0;
 };
 
 struct Swap {
@@ -178,7 +183,9 @@ struct b200md_ctx {
   cudaEvent_t ev_bnd = nullptr, ev_rev = nullptr, ev_rb = nullptr, ev_rr = nullptr;  // half-list overlap
   double split = 0.5;  // share of the interior tiles evaluated before the boundary tiles (half-list overlap)
   bool overlap = true;
-  bool fuse_nve = false;  // B200MD_FUSE_NVE=1: final_integrate(n) + initial_integrate(n+1) in one pass (nve.cu)
+  bool fuse_nve = true;   // option fuse_nve: final_integrate(n) + initial_integrate(n+1) in one pass (nve.cu), bit-identical
+  bool eam_smem = false;  // option eam_smem: one-element EAM tables staged in shared memory (measured slower on B200)
+  bool phase_timing = false;  // option phase_timing: per-phase CUDA events in b200md_run
   // comm
   b200md_swap_schedule sched;
   std::vector<Swap> swaps;

@@ -144,6 +144,9 @@ void langevin_free(b200md_ctx *c) {
   if (L.rnd) cudaFree(L.rnd);
   if (L.rank_by_tag) cudaFree(L.rank_by_tag);
   if (L.gfac) cudaFree(L.gfac);
+  if (L.sort_keys) cudaFree(L.sort_keys);
+  if (L.sort_vals) cudaFree(L.sort_vals);
+  if (L.sort_tmp) cudaFree(L.sort_tmp);
   L = Langevin();
 }
 
@@ -295,24 +298,38 @@ int langevin_resort(b200md_ctx *c) {
     nbins *= G.nb[d];
   }
   if (nbins == 1) return B200MD_OK;   // Atom::sort returns before permuting anything
-  unsigned long long *keys = nullptr, *keys_out = nullptr;
-  int *vals = nullptr, *vals_out = nullptr;
-  void *tmp = nullptr;
+  // scratch kept in the Langevin struct (grown on demand, freed by langevin_free): nothing is allocated, freed
+  // or leaked per call, and no error path can drop it
+  if (n > L.sort_cap) {
+    if (L.sort_keys) CUDA_TRY(cudaFree(L.sort_keys));
+    if (L.sort_vals) CUDA_TRY(cudaFree(L.sort_vals));
+    L.sort_keys = nullptr; L.sort_vals = nullptr; L.sort_cap = 0;
+    const size_t cap = (size_t)n + (size_t)n / 8 + 1024;
+    CUDA_TRY(cudaMalloc(&L.sort_keys, sizeof(unsigned long long) * 2 * cap));
+    CUDA_TRY(cudaMalloc(&L.sort_vals, sizeof(int) * 2 * cap));
+    L.sort_cap = (int)cap;
+  }
+  unsigned long long *keys = L.sort_keys, *keys_out = L.sort_keys + L.sort_cap;
+  int *vals = L.sort_vals, *vals_out = L.sort_vals + L.sort_cap;
+  // only the bits the keys use: key < nbins * n
+  int end_bit = 1;
+  while (end_bit < 64 && ((unsigned long long)nbins * (unsigned long long)n) >> end_bit) end_bit++;
   size_t tmp_bytes = 0;
-  CUDA_TRY(cudaMalloc(&keys, sizeof(unsigned long long) * 2 * (size_t)n));
-  CUDA_TRY(cudaMalloc(&vals, sizeof(int) * 2 * (size_t)n));
-  keys_out = keys + n; vals_out = vals + n;
+  CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys_out, vals, vals_out, n, 0, end_bit, c->stream));
+  if (tmp_bytes > L.sort_tmp_bytes) {
+    if (L.sort_tmp) CUDA_TRY(cudaFree(L.sort_tmp));
+    L.sort_tmp = nullptr; L.sort_tmp_bytes = 0;
+    CUDA_TRY(cudaMalloc(&L.sort_tmp, tmp_bytes + tmp_bytes / 8));
+    L.sort_tmp_bytes = tmp_bytes + tmp_bytes / 8;
+  }
   k_resort_keys<<<(n + 255) / 256, 256, 0, c->stream>>>(n, c->xq, c->tag, L.rank_by_tag, G, (unsigned long long)n, keys, vals);
   CUDA_TRY(cudaGetLastError());
-  CUDA_TRY(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys_out, vals, vals_out, n, 0, 64, c->stream));
-  CUDA_TRY(cudaMalloc(&tmp, tmp_bytes));
-  CUDA_TRY(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys_out, vals, vals_out, n, 0, 64, c->stream));
+  tmp_bytes = L.sort_tmp_bytes;
+  CUDA_TRY(cub::DeviceRadixSort::SortPairs(L.sort_tmp, tmp_bytes, keys, keys_out, vals, vals_out, n, 0, end_bit, c->stream));
   k_resort_assign<<<(n + 255) / 256, 256, 0, c->stream>>>(n, vals_out, L.rank_by_tag);
   CUDA_TRY(cudaGetLastError());
   c->launches += 3;
-  CUDA_TRY(cudaStreamSynchronize(c->stream));
-  cudaFree(tmp); cudaFree(keys); cudaFree(vals);
-  return B200MD_OK;
+  return B200MD_OK;   // stream-ordered: the thermostat kernel that reads rank_by_tag follows on the same stream
 }
 
 int langevin_config(b200md_ctx *c, double t_start, double t_stop, double t_period, int seed, const double *ratio, double dt) {

@@ -635,9 +635,14 @@ int neigh_build_list(b200md_ctx *c) {
     }
     c->launches++;
     CUDA_TRY(cudaGetLastError());
-    CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 4 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 5 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     if (c->h_flags[2]) { b200md_set_error("Non-numeric positions - simulation unstable"); return B200MD_ERR; }
+    // bond kernel flags of the steps since the last rebuild (bond.cu): the reference stops at the rebuild
+    // (NTopoBondAll::build, src/ntopo_bond_all.cpp:37-80) or at the step itself (BondFENE::compute)
+    if (c->h_flags[4] & 1) { b200md_set_error("Bond atoms missing"); return B200MD_ERR; }
+    if (c->h_flags[4] & 4) { b200md_set_error("Bad FENE bond"); return B200MD_ERR; }
+    if (c->h_flags[4]) CUDA_TRY(cudaMemsetAsync(c->d_flags + 4, 0, sizeof(int), c->stream));   // warning bit: reported once
     if (c->h_flags[1] == 0) return neigh_split_tiles(c);
     // overflow: regrow the pitch like the reference's Kokkos path (npair_kokkos.cpp:302-316)
     int p = (int)(c->h_flags[1] * 1.2) + 8;

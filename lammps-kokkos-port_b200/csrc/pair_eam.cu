@@ -450,9 +450,8 @@ static int eam_prepare(b200md_ctx *c, EamLaunch &L) {
   L.smem = (size_t)(e.nr + 1) * 8 * sizeof(double);
   // measured on B200 (2.05 M atoms, Cu_u3): tabC through L1 752 Matom-steps/s, staged in shared
   // memory 681 (bank conflicts on the random rows + lower occupancy) -> global is the default
-  const char *sm = getenv("B200MD_EAM_SMEM");
   L.mode = 0;
-  if (e.one) L.mode = (L.smem <= 64 * 1024 && sm && sm[0] == '1') ? 2 : 1;
+  if (e.one) L.mode = (L.smem <= 64 * 1024 && c->eam_smem) ? 2 : 1;
   return B200MD_OK;
 }
 

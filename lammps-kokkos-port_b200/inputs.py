@@ -3,10 +3,23 @@
 -var x/y/z like the originals.  Synthetic fcc lattice data, no files except the EAM potential.
 """
 import math
+import os
 
 import numpy as np
 
 from . import b200md as B  # noqa: F401  (package import)
+
+
+DATA_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "data")
+
+
+def data_file(name):
+    """input data the bench configs name (Cu_u3.eam, Cu_mishin1.eam.alloy, data.chain): data/<name>, put there by
+    __graft_entry__.build() from the reference tree (bench/, potentials/)"""
+    p = os.path.join(DATA_DIR, name)
+    if not os.path.exists(p):
+        raise B.B200MDError("input data file %s is missing; run __graft_entry__.build() where the reference tree exists" % p)
+    return p
 
 
 def _decompose(ctx, boxlo, boxhi):
@@ -55,6 +68,8 @@ def in_eam(ctx, x=1, y=1, z=1, potential=None, style="eam", temperature=1600.0, 
     boxhi = [nx * scale, ny * scale, nz * scale]
     _decompose(ctx, boxlo, boxhi)
     sublo, subhi = ctx.subbox()
+    if potential is None:
+        potential = data_file("Cu_u3.eam" if style == "eam" else "Cu_mishin1.eam.alloy")
     if style == "eam":
         tb = eam_host.tables_from_funcfl([potential])
     else:
@@ -77,7 +92,7 @@ def atom_sort_order(x, sublo, subhi, cutneighmax):
     return B.atom_sort_order(x, sublo, subhi, cutneighmax)
 
 
-def in_chain(ctx, data_path, x=1, y=1, z=1, list_kind=B.LIST_HALF_NEWTON, langevin=False):
+def in_chain(ctx, data_path=None, x=1, y=1, z=1, list_kind=B.LIST_HALF_NEWTON, langevin=False):
     """bench/in.chain / in.chain.scaled (`replicate x y z`)
     (/root/reference/bench/in.chain:1-28, in.chain.scaled:1-33): units lj;
     atom_style bond; special_bonds fene; read_data data.chain; neighbor 0.4 bin;
@@ -88,6 +103,8 @@ def in_chain(ctx, data_path, x=1, y=1, z=1, list_kind=B.LIST_HALF_NEWTON, langev
     with langevin=True the atoms are uploaded in the order Atom::sort gives them at the reference's
     set-up (one rank only)."""
     from . import molecule_host as M
+    if data_path is None:
+        data_path = data_file("data.chain")
     d = M.replicate(M.read_data(data_path), x, y, z)
     ctx.set_units("lj")
     boxlo, boxhi = list(d["boxlo"]), list(d["boxhi"])

@@ -29,8 +29,14 @@ b200md_ctx *B200Shared::ctx = nullptr;
 /* ---------------------------------------------------------------------- */
 
 VerletB200::VerletB200(LAMMPS *lmp, int narg, char **arg) :
-    Verlet(lmp, narg, arg), ctx(nullptr), host_stale(false), builds_at_setup(0)
+    Verlet(lmp, narg, arg), ctx(nullptr), host_stale(false), builds_at_setup(0), danger_at_setup(0)
 {
+  // run_style verlet/b200 [keyword value ...]: the runtime options of the device library, the role
+  // `package gpu|kokkos <keyword> <value>` plays for the reference's accelerator packages (an unmodified
+  // Input::package knows only its own package names, src/input.cpp).  Keywords: include/b200md.h,
+  // b200md_set_option (halo, overlap, split, fuse_nve, eam_smem, lanes, build_lanes, graph).
+  if (narg % 2) error->all(FLERR, "Illegal run_style verlet/b200 command: keyword without a value");
+  for (int i = 0; i + 1 < narg; i += 2) options.emplace_back(arg[i], arg[i + 1]);
 }
 
 VerletB200::~VerletB200()
@@ -113,6 +119,8 @@ void VerletB200::init()
       if (b200md_comm_init(ctx, id)) fail();
     }
     B200Shared::ctx = ctx;
+    for (const auto &kv : options)
+      if (b200md_set_option(ctx, kv.first.c_str(), kv.second.c_str())) fail();
   }
   if (b200md_set_units(ctx, force->boltz, force->mvv2e, force->ftm2v, force->nktv2p)) fail();
   if (b200md_set_box(ctx, domain->boxlo, domain->boxhi, domain->periodicity, comm->procgrid)) fail();
@@ -182,10 +190,10 @@ void VerletB200::device_setup()
   if (!thermostat && b200md_fix_langevin_off(ctx)) fail();    // `unfix` between runs
   if (b200md_setup(ctx)) fail();
 
-  long long nb = 0, nd = 0, tot = 0;
-  int pitch = 0;
-  b200md_neigh_stats(ctx, &nb, &nd, &tot, &pitch);
+  long long nb = 0, nd = 0;
+  b200md_neigh_stats(ctx, &nb, &nd, nullptr, nullptr);
   builds_at_setup = nb;
+  danger_at_setup = nd;
   neighbor->ncalls = 0;
   neighbor->ndanger = 0;
 
@@ -384,11 +392,10 @@ void VerletB200::run(int n)
     done += chunk;
     host_stale = true;
 
-    long long nb = 0, nd = 0, tot = 0;
-    int pitch = 0;
-    b200md_neigh_stats(ctx, &nb, &nd, &tot, &pitch);
+    long long nb = 0, nd = 0;
+    b200md_neigh_stats(ctx, &nb, &nd, nullptr, nullptr);    // counters only: no list download
     neighbor->ncalls = (bigint) (nb - builds_at_setup);
-    neighbor->ndanger = (bigint) nd;
+    neighbor->ndanger = (bigint) (nd - danger_at_setup);
 
     if (update->ntimestep == output->next) {
       // the last step of a chunk is evaluated with energy/virial tallies (Integrate::ev_set)

@@ -9,6 +9,7 @@ IntegrateStyle(verlet/b200,VerletB200);
 #include "b200_styles.h"
 #include "verlet.h"
 
+#include <string>
 #include <utility>
 #include <vector>
 
@@ -30,7 +31,8 @@ class VerletB200 : public Verlet {
  private:
   b200md_ctx *ctx;
   bool host_stale;
-  long long builds_at_setup;
+  long long builds_at_setup, danger_at_setup;
+  std::vector<std::pair<std::string, std::string>> options;    // run_style verlet/b200 keyword value ...
   std::vector<std::pair<int, int>> mask_by_tag;    // several ranks: only when group masks are not uniform
   std::vector<std::pair<int, int>> host_index;     // one rank: (tag, host index), sorted; host order is kept
   std::vector<double> hx, hv, hf;                   // staging for the order-preserving sync

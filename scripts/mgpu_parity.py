@@ -21,7 +21,7 @@ ok = True
 for wl in ("lj", "eam"):
     ctx = mk()
     if wl == "lj": cfg = P.inputs.in_lj(ctx, x, x, x, list_kind=lk); per = cfg["natoms"]
-    else: cfg = P.inputs.in_eam(ctx, x, x, x, potential="oracle/_ref/potentials/Cu_u3.eam", list_kind=lk); per = 1.0
+    else: cfg = P.inputs.in_eam(ctx, x, x, x, list_kind=lk); per = 1.0
     ctx.setup()
     recs = [ctx.thermo()] + ctx.run(100, cfg["dt"], 50)
     nl, ng = ctx.nlocal()
@@ -37,7 +37,7 @@ if "chain" in sys.argv:
     import numpy as np
     g = np.load("tests/golden/chain.npz")
     ctx = mk()
-    cfg = P.inputs.in_chain(ctx, "oracle/_ref/data/data.chain", list_kind=lk)
+    cfg = P.inputs.in_chain(ctx, list_kind=lk)
     ctx.setup()
     recs = [ctx.thermo()]
     for _ in range(10):       # every `run 10` of the golden run starts with a set-up (tests/test_chain.py)

@@ -17,7 +17,7 @@ if world > 1:
     dist.broadcast(idt, 0)
     ctx.comm_init(bytes(idt.cpu().numpy().tobytes()))
 lk = B.LIST_HALF_NEWTON if (len(sys.argv) > 2 and sys.argv[2] == "half") else B.LIST_FULL
-cfg = P.inputs.in_eam(ctx, x, x, x, potential="oracle/_ref/potentials/Cu_mishin1.eam.alloy", style="eam/alloy", list_kind=lk)
+cfg = P.inputs.in_eam(ctx, x, x, x, style="eam/alloy", list_kind=lk)
 ctx.setup()
 t0 = ctx.thermo()
 ctx.run(10, cfg["dt"], 0)

@@ -134,7 +134,59 @@ def make_chain():
     print("chain", out["natoms"], out["npairs"], out["pair_digest"], out["thermo0"], out["thermo_series"][-1])
 
 
+IN_LJMIX = """
+units lj
+atom_style atomic
+atom_modify map array
+lattice fcc 0.8442
+region box block 0 4 0 4 0 4
+create_box 2 box
+create_atoms 1 box
+region left block 0 2 INF INF INF INF
+set region left type 2
+mass 1 1.0
+mass 2 1.5
+velocity all create 1.44 87287 loop geom
+pair_style lj/cut 2.5
+pair_modify mix {mix}
+pair_coeff 1 1 1.0 1.0 2.5
+pair_coeff 2 2 0.5 0.9 2.0
+neighbor 0.3 bin
+neigh_modify delay 0 every 20 check no
+fix 1 all nve
+"""
+
+
+def make_ljmix():
+    """two atom types with DIFFERENT per-type cutoffs and no explicit 1-2 coefficients: epsilon, sigma and
+    the cutoff of the mixed pair come from Pair::mix_energy / mix_distance (PairLJCut::init_one,
+    src/pair_lj_cut.cpp:501-556), for `pair_modify mix geometric` and `arithmetic`."""
+    out = {}
+    for mix in ("geometric", "arithmetic"):
+        R = O.Reference()
+        R.command(IN_LJMIX.format(mix=mix))
+        R.command("thermo_style custom step temp pe ke press")
+        R.command("thermo_modify norm no")
+        R.command("run 25")
+        R.command("run 0")
+        out[mix + "_x"] = R.gather("x", 3); out[mix + "_v"] = R.gather("v", 3); out[mix + "_f"] = R.gather("f", 3)
+        out[mix + "_type"] = R.gather("type", 1, np.int32)
+        out[mix + "_thermo0"] = np.array([R.thermo(k) for k in KW])
+        i, j = keys(R.neighlist_by_tag("lj/cut"))
+        lo, hi = np.minimum(i, j), np.maximum(i, j)
+        o = np.lexsort((hi, lo))
+        out[mix + "_half_lo"] = lo[o].astype(np.int32); out[mix + "_half_hi"] = hi[o].astype(np.int32)
+        R.command("run 20")
+        out[mix + "_thermo20"] = np.array([R.thermo(k) for k in KW])
+        R.close()
+        print("ljmix", mix, len(lo), out[mix + "_thermo0"], out[mix + "_thermo20"])
+    np.savez_compressed(os.path.join(HERE, "ljmix.npz"), **out)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "ljmix":
+        make_ljmix()
+        sys.exit(0)
     if len(sys.argv) > 1 and sys.argv[1] == "chain":
         make_chain()
         sys.exit(0)

@@ -201,3 +201,34 @@ def test_full_size_properties(pkg):
     assert abs(e1 - e0) <= 5e-3 * abs(e0)
     assert ctx.neigh_stats()["nbuilds"] == 6  # setup + every 20 steps
     ctx.close()
+
+
+@pytest.mark.parametrize("list_kind", ["half", "full"])
+@pytest.mark.parametrize("mix", ["geometric", "arithmetic"])
+def test_lj_mixed_cutoffs_gpu(pkg, mix, list_kind):
+    """two types with different per-type cutoffs, the 1-2 cutoff mixed like PairLJCut::init_one
+    (tests/golden/ljmix.npz, from the unmodified reference)"""
+    from test_oracle_golden import ljmix_case
+    B = pkg.b200md
+    g, T, s, cn, cmax = ljmix_case(pkg, mix)
+    ctx = B.Context(0)
+    ctx.set_units("lj"); ctx.set_box(s["boxlo"], s["boxhi"])
+    ctx.set_atoms(s["x"], s["v"], s["type"], s["tag"], s["mass"])
+    ctx.pair_lj_cut_config(*[T[k] for k in ("cutsq", "lj1", "lj2", "lj3", "lj4", "offset")])
+    ctx.neigh_config(cn, cmax, 0.3, every=20, delay=0, check=0,
+                     list_kind=B.LIST_HALF_NEWTON if list_kind == "half" else B.LIST_FULL)
+    ctx.setup()
+    a = ctx.get_atoms()
+    if list_kind == "half":
+        nn, flat = ctx.neigh_export(by_tag=True)
+        want = np.sort(g[mix + "_half_lo"].astype(np.int64) * (1 << 32) + g[mix + "_half_hi"].astype(np.int64))
+        assert np.array_equal(Cm.pairs_from_lists(a["tag"], nn, flat), want)
+    f = a["f"][np.argsort(a["tag"])]
+    assert np.abs(f - g[mix + "_f"]).max() <= F_TOL * np.abs(g[mix + "_f"]).max()
+    t = ctx.thermo()
+    for k, key in enumerate(KEYS):
+        assert abs(t[key] - g[mix + "_thermo0"][k]) <= T_TOL * abs(g[mix + "_thermo0"][k]), key
+    t = ctx.run(20, 0.005, 0)[-1]
+    for k, key in enumerate(KEYS):
+        assert abs(t[key] - g[mix + "_thermo20"][k]) <= T_TOL * abs(g[mix + "_thermo20"][k]), key
+    ctx.close()

@@ -88,3 +88,42 @@ def test_full_list(pkg, oracle_mod, name, kind):
     want = np.sort(g["full_i"].astype(np.int64) * (1 << 32) + g["full_j"].astype(np.int64))
     assert np.array_equal(got, want)
     o.close()
+
+
+def ljmix_case(pkg, mix):
+    """tests/golden/ljmix.npz (make_golden.py ljmix): two types, per-type cutoffs 2.5 / 2.0, the 1-2 pair mixed by
+    PairLJCut::init_one (src/pair_lj_cut.cpp:501-556) -> epsilon, sigma AND cutoff from Pair::mix_*"""
+    B = pkg.b200md
+    g = np.load(os.path.join(Cm.GOLDEN, "ljmix.npz"))
+    T = B.lj_cut_tables(2, {(1, 1): (1.0, 1.0, 2.5), (2, 2): (0.5, 0.9, 2.0)}, 2.5, mix=mix)
+    scale = (4.0 / 0.8442) ** (1.0 / 3.0)
+    nat = len(g[mix + "_type"])
+    s = dict(boxlo=[0.0] * 3, boxhi=[4 * scale] * 3, x=g[mix + "_x"], v=g[mix + "_v"], type=g[mix + "_type"],
+             tag=np.arange(1, nat + 1, dtype=np.int32), mass=np.array([0.0, 1.0, 1.5]), units=B.UNITS["lj"],
+             dt=0.005, skin=0.3)
+    cn, cmax = B.cutneighsq_table(2, T["cutsq"], 0.3)
+    return g, T, s, cn, cmax
+
+
+@pytest.mark.parametrize("mix", ["geometric", "arithmetic"])
+def test_lj_mixed_cutoffs(pkg, oracle_mod, mix):
+    g, T, s, cn, cmax = ljmix_case(pkg, mix)
+    c12 = np.sqrt(2.5 * 2.0) if mix == "geometric" else 2.25
+    assert T["cutsq"][1, 2] == pytest.approx(c12 * c12, rel=1e-15)
+    o = oracle_mod.Oracle(s["boxlo"], s["boxhi"], s["x"], s["v"], s["type"], s["tag"], s["mass"], s["units"])
+    o.pair_lj(T)
+    o.neigh_config(cn, cmax, 0.3, 20, 0, 0, True)
+    o.setup()
+    a = o.atoms()
+    nn, flat = o.neigh_tags()
+    want = np.sort(g[mix + "_half_lo"].astype(np.int64) * (1 << 32) + g[mix + "_half_hi"].astype(np.int64))
+    assert np.array_equal(Cm.pairs_from_lists(a["tag"], nn, flat), want)
+    f = a["f"][np.argsort(a["tag"])]
+    assert np.abs(f - g[mix + "_f"]).max() <= 1e-12 * np.abs(g[mix + "_f"]).max()
+    t = o.thermo()
+    for k, key in enumerate(("temp", "pe", "ke", "press")):
+        assert abs(t[key] - g[mix + "_thermo0"][k]) <= 1e-11 * abs(g[mix + "_thermo0"][k])
+    t = o.run(20, 0.005, 0)[-1]
+    for k, key in enumerate(("temp", "pe", "ke", "press")):
+        assert abs(t[key] - g[mix + "_thermo20"][k]) <= 1e-9 * abs(g[mix + "_thermo20"][k])
+    o.close()
