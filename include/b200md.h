@@ -345,6 +345,9 @@ int b200md_set_lanes_per_atom(b200md_ctx *ctx, int lanes);
  *   phase_timing on | off          per-phase CUDA events in b200md_run (b200md_get_timing)
  *   lanes        1,2,...,32        = b200md_set_lanes_per_atom
  *   build_lanes  1,2,...,32        lanes per atom in the list build
+ *   cluster      on | off | auto   cluster-pair neighbor list for atomic systems: 4 consecutive atoms of the bin-sorted
+ *                                  order share one j-list whose entries carry a 4-bit pair mask (auto, the default:
+ *                                  lj/cut yes, eam no)
  *   graph        on | off          small-system mode: non-rebuild steps replayed as a CUDA graph
  * Unknown keywords and bad values fail with "Illegal package b200 command: ...". */
 int b200md_set_option(b200md_ctx *ctx, const char *key, const char *value);

@@ -10,6 +10,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include "ctx.h"
+#include "util.cuh"
 
 int vel_adjust(b200md_ctx *c, double sx, double sy, double sz, double factor);  // nve.cu
 int pair_eam_config_impl(b200md_ctx *c, int ntypes, int nrho, int nr, double rdr, double rdrho, double rhomax,
@@ -413,13 +414,47 @@ __global__ void k_export_list(int nlocal, int tpa, int pitch, const int *__restr
   }
 }
 
+// cluster-pair list -> the exact per-atom lists: atom k of a cluster owns the entries whose mask has bit k
+__global__ void k_cluster_count(int nlocal, int tpa, int pitch, const int *__restrict__ neigh, const int *__restrict__ numneigh,
+                                int *__restrict__ count) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const int c = i / CL, k = i % CL, C = 32 / tpa;
+  const int *nb = neigh + (size_t)(c / C) * pitch * C + (c % C) * tpa;
+  const int n = numneigh[c];
+  int cnt = 0;
+  for (int s = 0; s < n; s++) cnt += ((unsigned)nb[(s / tpa) * 32 + (s % tpa)] >> (CL_SHIFT + k)) & 1u;
+  count[i] = cnt;
+}
+__global__ void k_export_cluster(int nlocal, int tpa, int pitch, const int *__restrict__ neigh, const int *__restrict__ numneigh,
+                                 const long long *__restrict__ offs, const int *__restrict__ tag, int by_tag, int *__restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlocal) return;
+  const int c = i / CL, k = i % CL, C = 32 / tpa;
+  const int *nb = neigh + (size_t)(c / C) * pitch * C + (c % C) * tpa;
+  const int n = numneigh[c];
+  int *o = out + offs[i];
+  int w = 0;
+  for (int s = 0; s < n; s++) {
+    const unsigned e = (unsigned)nb[(s / tpa) * 32 + (s % tpa)];
+    if ((e >> (CL_SHIFT + k)) & 1u) { const int j = (int)(e & CL_JMASK); o[w++] = by_tag ? tag[j] : j; }
+  }
+}
+
 extern "C" int b200md_neigh_export(b200md_ctx *c, int by_tag, int *numneigh, int *neigh_flat, long long *total) {
   NEED(c && c->neigh && c->nbuilds > 0, "b200md: no neighbor list built");
   CUDA_TRY(cudaSetDevice(c->device));
   const int n = c->nlocal;
   std::vector<int> nn(n);
-  CUDA_TRY(cudaMemcpyAsync(nn.data(), c->numneigh, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
+  int *d_count = nullptr;
+  if (c->cluster && n) {
+    CUDA_TRY(cudaMalloc(&d_count, sizeof(int) * n));
+    k_cluster_count<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->tpa, c->pitch, c->neigh, c->numneigh, d_count);
+    CUDA_TRY(cudaGetLastError());
+  }
+  CUDA_TRY(cudaMemcpyAsync(nn.data(), c->cluster ? d_count : c->numneigh, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
+  if (d_count) cudaFree(d_count);
   std::vector<long long> offs(n + 1);
   long long t = 0;
   for (int i = 0; i < n; i++) { offs[i] = t; t += nn[i]; }
@@ -431,7 +466,10 @@ extern "C" int b200md_neigh_export(b200md_ctx *c, int by_tag, int *numneigh, int
     CUDA_TRY(cudaMalloc(&d_offs, sizeof(long long) * (n + 1)));
     CUDA_TRY(cudaMalloc(&d_out, sizeof(int) * t));
     CUDA_TRY(cudaMemcpy(d_offs, offs.data(), sizeof(long long) * (n + 1), cudaMemcpyHostToDevice));
-    k_export_list<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->tpa, c->pitch, c->neigh, c->numneigh, d_offs, c->tag, by_tag, d_out);
+    if (c->cluster)
+      k_export_cluster<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->tpa, c->pitch, c->neigh, c->numneigh, d_offs, c->tag, by_tag, d_out);
+    else
+      k_export_list<<<(n + 127) / 128, 128, 0, c->stream>>>(n, c->tpa, c->pitch, c->neigh, c->numneigh, d_offs, c->tag, by_tag, d_out);
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaMemcpyAsync(neigh_flat, d_out, sizeof(int) * t, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
@@ -500,6 +538,12 @@ extern "C" int b200md_set_option(b200md_ctx *c, const char *key, const char *val
   } else if (k == "eam_smem") {
     NEED(opt_bool(value, &b), "Illegal package b200 command: eam_smem must be on or off");
     c->eam_smem = b;
+  } else if (k == "cluster") {
+    if (!strcmp(value, "auto")) c->use_cluster = -1;
+    else {
+      NEED(opt_bool(value, &b), "Illegal package b200 command: cluster must be on, off or auto");
+      c->use_cluster = b ? 1 : 0;
+    }
   } else if (k == "phase_timing") {
     NEED(opt_bool(value, &b), "Illegal package b200 command: phase_timing must be on or off");
     c->phase_timing = b;
@@ -525,6 +569,7 @@ extern "C" int b200md_get_option(b200md_ctx *c, const char *key, char *value, in
   else if (k == "split") v = std::to_string(c->split);
   else if (k == "fuse_nve") v = c->fuse_nve ? "on" : "off";
   else if (k == "eam_smem") v = c->eam_smem ? "on" : "off";
+  else if (k == "cluster") v = c->use_cluster < 0 ? "auto" : (c->use_cluster ? "on" : "off");
   else if (k == "phase_timing") v = c->phase_timing ? "on" : "off";
   else if (k == "build_lanes") v = std::to_string(c->tpa_build);
   else if (k == "lanes") v = std::to_string(c->tpa);
@@ -571,7 +616,6 @@ extern "C" int b200md_pair_eam_config(b200md_ctx *c, int ntypes, int nrho, int n
                            rhor_spline, nz2r, z2r_spline, type2frho, type2rhor, type2z2r, scale));
   c->cutforcemax = sqrt(cutforcesq);
   c->pair_style = B200MD_PAIR_EAM;
-  if (!c->tpa_user) c->tpa = 1;   // measured: one lane per atom is best for the eam passes
   return B200MD_OK;
 }
 

@@ -171,7 +171,10 @@ struct b200md_ctx {
   int tpa_build = 1;  // lanes per atom in the list build (1..32); measured best on B200 for lj, eam and chain
   bool tpa_build_user = false;
   bool tpa_user = false;  // set by b200md_set_lanes_per_atom; otherwise the pair style picks (lj 2, eam 1)
-  int pitch = 0;  // max neighbors per atom (multiple of tpa)
+  int use_cluster = -1;     // option cluster: on (1) / off (0) / auto (-1: lj/cut yes; eam no, its table look-ups are
+                            // per pair either way and the masked-out slots of a cluster would fetch rows for nothing)
+  bool cluster = false;     // layout of the current list: units are clusters of 4 atoms, entries carry a 4-bit pair mask
+  int pitch = 0;  // max neighbors per list unit (atom or cluster; multiple of 32)
   int *neigh = nullptr;
   size_t neigh_cap = 0;
   int *numneigh = nullptr;  // [nmax]
@@ -244,6 +247,10 @@ void b200md_set_error(const std::string &msg);
     int _r = (call);                   \
     if (_r != B200MD_OK) return _r;    \
   } while (0)
+
+// list units: what a group of `tpa` lanes works on — an atom, or a cluster of 4 atoms (neigh.cu)
+static inline int list_units(const b200md_ctx *c) { return c->cluster ? (c->nlocal + 3) / 4 : c->nlocal; }
+static inline int list_tiles(const b200md_ctx *c) { const int A = 32 / c->tpa; return (list_units(c) + A - 1) / A; }
 
 // ---- kernels' host launchers ----
 // neigh.cu

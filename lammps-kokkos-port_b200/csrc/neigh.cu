@@ -541,6 +541,126 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
   if (tile_ghost && has_ghost) tile_ghost[i / AF] = 1;
 }
 
+
+// ---------------------------------------------------------------------------------------
+// cluster-pair list (atomic systems): CL = 4 consecutive owned atoms of the bin-sorted order form an
+// i-cluster with ONE j-list; entry = j | mask << 28, bit k of the mask set iff (i0+k, j) is a pair of the
+// reference's exact per-atom list (rsq <= cutneighsq[itype][jtype] and the full / half-newton membership
+// rule).  The force kernels gather each j once per cluster, evaluate up to four pairs from registers and
+// issue one RED triple per (cluster, j) instead of one per pair; the exact per-atom lists are recovered
+// from the masks (b200md_neigh_export).  The union of the four stencils is scanned once: the atoms are
+// bin-sorted, so their stencil rows overlap and (same bin row) merge into one contiguous range of
+// cell_xq.  Membership in atom k's stencil needs no test of its own: a candidate outside it is farther
+// than cutneighmax (NStencil keeps every bin closer than that, nstencil_full_bin_3d.cpp:35).
+// Half/newton rule (npair_half_bin_atomonly_newton.cpp:55-104) in the device's order — owned atoms sorted
+// by bin, ascending inside a bin, ghosts after the owned atoms of a cell:
+//   owned j : j in a later bin, or in i's bin behind i            <=>  j > i
+//   ghost j : j in a later bin (cell position >= end of i's bin), or in i's bin and not below i in
+//             (z, y, x) order
+// ---------------------------------------------------------------------------------------
+template <bool HALF, bool ONETYPE>
+__global__ void __launch_bounds__(BUILD_THREADS)
+k_build_cluster(int nlocal, int ncl, const double4 *__restrict__ xq, const int *__restrict__ atom_bin,
+                const int *__restrict__ cell_start, const int *__restrict__ cell_atoms,
+                const double4 *__restrict__ cell_xq, int nrows, const int *__restrict__ row_off,
+                const int *__restrict__ row_sx, const int *__restrict__ row_flag,
+                const double *__restrict__ cutneighsq, int ntypes, int mbinx, int *__restrict__ neigh,
+                int *__restrict__ numneigh, int pitch, int *flags, int *__restrict__ tile_ghost, int L) {
+  __shared__ int s_off[MAX_ROWS], s_sx[MAX_ROWS], s_flag[MAX_ROWS];
+  __shared__ double s_cut[(MAX_TYPES_SMEM + 1) * (MAX_TYPES_SMEM + 1)];
+  for (int r = threadIdx.x; r < nrows; r += blockDim.x) { s_off[r] = row_off[r]; s_sx[r] = row_sx[r]; s_flag[r] = row_flag[r]; }
+  const int nt1 = ntypes + 1;
+  const bool cut_smem = ntypes <= MAX_TYPES_SMEM;
+  if (cut_smem) for (int r = threadIdx.x; r < nt1 * nt1; r += blockDim.x) s_cut[r] = cutneighsq[r];
+  __syncthreads();
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncl) return;
+  const int C = 32 / L;
+  int *out = neigh + (size_t)(c / C) * pitch * C + (c % C) * L;
+  const int i0 = c * CL;
+  const int ni = min(CL, nlocal - i0);
+  double xi[CL], yi[CL], zi[CL];
+  int bi[CL], own_lo[CL], own_hi[CL];
+  const double *cutrow[CL];
+  const double cut1 = ONETYPE ? cutneighsq[nt1 + 1] : 0.0;
+#pragma unroll
+  for (int k = 0; k < CL; k++) {
+    const int i = i0 + min(k, ni - 1);
+    const double4 q = xq[i];
+    // an absent atom of the last cluster sits far away: no candidate is ever within its cutoff
+    xi[k] = k < ni ? q.x : 1e150; yi[k] = q.y; zi[k] = q.z;
+    bi[k] = atom_bin[i];
+    own_lo[k] = cell_start[bi[k]]; own_hi[k] = cell_start[bi[k] + 1];
+    const int it = xq_type(q);
+    cutrow[k] = cut_smem ? &s_cut[it * nt1] : &cutneighsq[it * nt1];
+  }
+  int cnt = 0;
+  bool has_ghost = false;
+  // The atoms of a cluster are consecutive in bin order, so they normally sit in one row of bins (same iy, iz) and
+  // the union of their stencil rows is one contiguous range per (dy,dz).  A cluster that straddles the end of a bin
+  // row is handled as several groups, one per bin row, each scanning for its own atoms only: a j reached from two
+  // groups then appears in two entries with disjoint masks, never as a duplicate pair.
+  for (int g0 = 0; g0 < CL;) {
+    int g1 = g0 + 1;
+    while (g1 < CL && bi[g1] / mbinx == bi[g0] / mbinx) g1++;    // bins ascend with k
+    const unsigned gmask = ((1u << g1) - 1u) & ~((1u << g0) - 1u);
+    const int bmin = bi[g0], bmax = bi[g1 - 1];
+    for (int r = 0; r < nrows; r++) {
+      const int off = s_off[r], sx = s_sx[r];
+      const int back = (HALF && s_flag[r] == 2) ? 0 : sx;        // own row of the half stencil: own bin and dx > 0
+      const int lo = cell_start[bmin + off - back], hi = cell_start[bmax + off + sx + 1];
+      if (lo >= hi) continue;
+      // the thread walks its candidates one by one; the next record is in flight while this one is tested
+      double4 qj = ld_xq(&cell_xq[lo]);
+      int j = __ldg(&cell_atoms[lo]);
+      for (int cidx = lo; cidx < hi; cidx++) {
+        const int nx = min(cidx + 1, hi - 1);
+        const double4 qn = ld_xq(&cell_xq[nx]);
+        const int jn = __ldg(&cell_atoms[nx]);
+        const int jt = ONETYPE ? 1 : xq_type(qj);
+        unsigned m = 0;
+#pragma unroll
+        for (int a = 0; a < CL; a++) {
+          const double dx = xi[a] - qj.x, dy = yi[a] - qj.y, dz = zi[a] - qj.z;
+          m |= (rsq_nofma(dx, dy, dz) <= (ONETYPE ? cut1 : cutrow[a][jt]) ? 1u : 0u) << a;
+        }
+        m &= gmask;
+        if (m) {
+          const int d = j - i0;
+          if (HALF) {
+            if (j < nlocal) m &= d <= 0 ? 0u : (d >= CL ? 0xfu : (1u << d) - 1u);   // owned j pairs with the atoms before it
+            else {
+#pragma unroll
+              for (int a = 0; a < CL; a++) {
+                bool keep = true;
+                if (cidx < own_hi[a]) {          // not in a later bin than atom a's
+                  if (cidx < own_lo[a]) keep = false;
+                  else if (qj.z < zi[a]) keep = false;
+                  else if (qj.z == zi[a]) {
+                    if (qj.y < yi[a]) keep = false;
+                    else if (qj.y == yi[a] && qj.x < xi[a]) keep = false;
+                  }
+                }
+                if (!keep) m &= ~(1u << a);
+              }
+            }
+          } else if (d >= 0 && d < CL) m &= ~(1u << d);
+          if (m) {
+            if (cnt < pitch) out[(cnt / L) * 32 + (cnt % L)] = (int)((unsigned)j | (m << CL_SHIFT));
+            cnt++;
+            has_ghost |= (j >= nlocal);
+          }
+        }
+        qj = qn; j = jn;
+      }
+    }
+    g0 = g1;
+  }
+  numneigh[c] = cnt;
+  if (cnt > pitch) atomicMax(&flags[1], cnt);
+  if (tile_ghost && has_ghost) tile_ghost[c / C] = 1;
+}
+
 template <int TPA, bool HALF, bool MOL>
 static void launch_build3(b200md_ctx *c, int nblocks, const MolParams &M) {
   k_build<TPA, HALF, MOL><<<nblocks, BUILD_THREADS, 0, c->stream>>>(
@@ -565,7 +685,7 @@ static void launch_build(b200md_ctx *c) {
 
 static int ensure_neigh_storage(b200md_ctx *c) {
   const int A = 32 / c->tpa;
-  const size_t ntiles = (size_t)(c->nlocal + A - 1) / A + 1;
+  const size_t ntiles = (size_t)(list_units(c) + A - 1) / A + 1;
   const size_t need = ntiles * (size_t)c->pitch * A;
   if (need > c->neigh_cap) {
     if (c->neigh) CUDA_TRY(cudaFree(c->neigh));
@@ -595,8 +715,7 @@ __global__ void k_split_tiles(int ntiles, const int *__restrict__ flag, const in
 static int neigh_split_tiles(b200md_ctx *c) {
   c->n_tiles_int = c->n_tiles_bnd = 0;
   if (c->all_self || c->nlocal == 0) return B200MD_OK;
-  const int A = 32 / c->tpa;
-  const int ntiles = (c->nlocal + A - 1) / A;
+  const int ntiles = list_tiles(c);
   CUDA_TRY(cudaMemsetAsync(c->tile_ghost + ntiles, 0, sizeof(int), c->stream));
   TRY(dev_exclusive_scan(c, c->tile_ghost, c->tile_pos, ntiles + 1));
   k_split_tiles<<<(ntiles + 255) / 256, 256, 0, c->stream>>>(ntiles, c->tile_ghost, c->tile_pos, c->tiles_int, c->tiles_bnd);
@@ -610,12 +729,20 @@ static int neigh_split_tiles(b200md_ctx *c) {
 
 int neigh_build_list(b200md_ctx *c) {
   if (c->nrows > MAX_ROWS) { b200md_set_error("b200md: stencil has too many rows"); return B200MD_ERR; }
+  // atomic systems use the cluster-pair list; molecular ones (special-bond exclusions, short lists) the per-atom list
+  const bool cluster = !c->topo.molecular && (c->use_cluster < 0 ? c->pair_style == B200MD_PAIR_LJ_CUT : c->use_cluster != 0);
+  if (cluster != c->cluster) { c->cluster = cluster; c->pitch = 0; }
+  // lanes per list unit, measured on B200 (profiles/): lj/cut 4 per cluster, 2 per atom on the per-atom list; eam 1 per atom
+  if (!c->tpa_user) c->tpa = cluster ? 4 : (c->pair_style == B200MD_PAIR_EAM ? 1 : 2);
+  if (cluster && c->nlocal + c->nghost > CL_JMASK) { b200md_set_error("b200md: more than 2^28 atoms on one rank"); return B200MD_ERR; }
   if (c->pitch == 0) {
-    // first guess from the number density: full sphere of cutneighmax, +35 % slack
+    // first guess from the number density: full sphere of cutneighmax, +35 % slack; a cluster's j-list is the union
+    // of four such spheres around atoms about one bin apart (measured 1.7-1.9 x one sphere)
     double vol = (c->subhi[0] - c->sublo[0]) * (c->subhi[1] - c->sublo[1]) * (c->subhi[2] - c->sublo[2]);
     double dens = vol > 0 ? c->nlocal / vol : 1.0;
     double est = 4.18879 * c->cutneighmax * c->cutneighmax * c->cutneighmax * dens;
     if (c->list_kind == B200MD_LIST_HALF_NEWTON) est *= 0.5;
+    if (cluster) est *= 2.0;
     int p = (int)(est * 1.35) + 16;
     c->pitch = (p + 31) / 32 * 32;
   }
@@ -623,7 +750,21 @@ int neigh_build_list(b200md_ctx *c) {
     TRY(ensure_neigh_storage(c));
     c->h_flags[1] = 0;
     CUDA_TRY(cudaMemsetAsync(c->d_flags + 1, 0, sizeof(int), c->stream));
-    CUDA_TRY(cudaMemsetAsync(c->tile_ghost, 0, sizeof(int) * ((c->nlocal + 32 / c->tpa - 1) / (32 / c->tpa) + 1), c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->tile_ghost, 0, sizeof(int) * (list_tiles(c) + 1), c->stream));
+    if (cluster) {
+      const int ncl = list_units(c);
+      if (ncl) {
+        const int nb = (ncl + BUILD_THREADS - 1) / BUILD_THREADS;
+        const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON, one = c->ntypes == 1;
+#define B200_LAUNCH_BUILD_CL(H, O)                                                                                             \
+  k_build_cluster<H, O><<<nb, BUILD_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, \
+      c->cell_xq, c->nrows, c->row_off, c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->bin.mbinx, c->neigh, c->numneigh,  \
+      c->pitch, c->d_flags, c->tile_ghost, c->tpa)
+        if (half) { if (one) B200_LAUNCH_BUILD_CL(true, true); else B200_LAUNCH_BUILD_CL(true, false); }
+        else { if (one) B200_LAUNCH_BUILD_CL(false, true); else B200_LAUNCH_BUILD_CL(false, false); }
+#undef B200_LAUNCH_BUILD_CL
+      }
+    } else
     switch (c->tpa_build) {
       case 1: launch_build<1>(c); break;
       case 2: launch_build<2>(c); break;

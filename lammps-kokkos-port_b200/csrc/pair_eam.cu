@@ -433,6 +433,278 @@ static int launch_tpa(b200md_ctx *c, const EamLaunch &L, bool ev, int pass, cons
   return ev ? launch_mode<TPA, true>(c, L, pass, tiles, ntl) : launch_mode<TPA, false>(c, L, pass, tiles, ntl);
 }
 
+
+// =============================================================================================
+// cluster-pair list variants (atomic systems; neigh.cu k_build_cluster, pair_lj.cu k_lj_cl): L lanes share an
+// i-cluster of CL = 4 atoms kept in registers, each j record is gathered once per cluster, and rho_j / f_j leave
+// with one RED (triple) per (cluster, j).  Table rows are still fetched per evaluated pair.
+// =============================================================================================
+#ifndef EAM_CL_MINBLOCKS
+#define EAM_CL_MINBLOCKS 2
+#endif
+
+// pass 1.  HALF: rho_i and rho_j of every listed pair (RED), embedding done by k_eam_embed after the reverse_comm.
+// Full list: rho_i only, then the embedding of the cluster's atoms (the reference Kokkos port's KernelAB).
+template <int L, bool EV, bool ONE, bool HALF>
+__global__ void __launch_bounds__(EAM_THREADS, EAM_CL_MINBLOCKS)
+k_eam_rho_cl(int nlocal, int ncl, const double4 *__restrict__ xq, const int *__restrict__ neigh, const int *__restrict__ numneigh,
+             int pitch, EamParams P, double *__restrict__ rho, double *__restrict__ fp, double4 *__restrict__ xfp,
+             double *__restrict__ partials, const int *__restrict__ tile_list, int ntile_list) {
+  constexpr int C = 32 / L;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / L, l = lane % L;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const bool in_list = !tile_list || w < ntile_list;
+  const int tile = tile_list ? (in_list ? tile_list[w] : 0) : w;
+  const int c = tile * C + sub;
+  const bool active = in_list && c < ncl;
+  const int i0 = c * CL;
+  const int nt1 = P.ntypes + 1;
+  double xi[CL], yi[CL], zi[CL], ri[CL];
+  int ti[CL];
+#pragma unroll
+  for (int k = 0; k < CL; k++) { xi[k] = yi[k] = zi[k] = ri[k] = 0; ti[k] = 1; }
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < CL; k++) {
+      const double4 q = xq[min(i0 + k, nlocal - 1)];
+      xi[k] = q.x; yi[k] = q.y; zi[k] = q.z;
+      if (!ONE) ti[k] = xq_type(q);
+    }
+    const int n = numneigh[c];
+    const int *nb = neigh + (size_t)tile * pitch * C + sub * L + l;
+    const int niter = (n + L - 1) / L;
+    // software pipeline as in k_lj_cl: entry it+2 and record it+1 in flight while slot it is evaluated; the four pairs
+    // of a slot are evaluated branch-free (a miss runs at r = 1 with weight 0) so their table loads and FP64 chains overlap
+    unsigned e0 = (0 * L + l < n) ? (unsigned)__ldg(nb) : 0u;
+    unsigned e1 = (1 * L + l < n) ? (unsigned)__ldg(nb + 32) : 0u;
+    double4 q0 = ld_xq(&xq[e0 & CL_JMASK]);
+    for (int it = 0; it < niter; it++) {
+      const unsigned e2 = ((it + 2) * L + l < n) ? (unsigned)__ldg(nb + (it + 2) * 32) : 0u;
+      const double4 q1 = ld_xq(&xq[e1 & CL_JMASK]);
+      {
+        const int j = (int)(e0 & CL_JMASK);
+        const unsigned m4 = e0 >> CL_SHIFT;
+        const double4 qj = q0;
+        const int tj = ONE ? 1 : xq_type(qj);
+        double g = 0;
+#pragma unroll
+        for (int k = 0; k < CL; k++) {
+          const double dx = xi[k] - qj.x, dy = yi[k] - qj.y, dz = zi[k] - qj.z;
+          const double rsq = fma(dz, dz, fma(dy, dy, dx * dx));
+          const bool hit = ((m4 >> k) & 1u) && rsq < P.cutforcesq;
+          const double rs = hit ? rsq : 1.0;
+          double p = rs * rsqrt_nr(rs) * P.rdr + 1.0;
+          int m = (int)p;
+          m = min(m, P.nr - 1);
+          p -= m;
+          p = fmin(p, 1.0);
+          if (ONE) {
+            const double4 cf = ld4(P.tabC + (size_t)m * 8);
+            const double d = hit ? ((cf.x * p + cf.y) * p + cf.z) * p + cf.w : 0.0;
+            ri[k] += d;
+            if (HALF) g += d;
+          } else {
+            const int tji = P.type2rhor[tj * nt1 + ti[k]], tij = P.type2rhor[ti[k] * nt1 + tj];
+            const double4 cf = ld4(P.rhoA + ((size_t)tji * (P.nr + 1) + m) * 4);
+            const double di = hit ? ((cf.x * p + cf.y) * p + cf.z) * p + cf.w : 0.0;
+            ri[k] += di;
+            if (HALF) {
+              double dj = di;
+              if (tij != tji) {
+                const double4 cg = ld4(P.rhoA + ((size_t)tij * (P.nr + 1) + m) * 4);
+                dj = hit ? ((cg.x * p + cg.y) * p + cg.z) * p + cg.w : 0.0;
+              }
+              g += dj;
+            }
+          }
+        }
+        if (HALF && g != 0.0) atomicAdd(&rho[j], g);
+      }
+      e0 = e1; e1 = e2; q0 = q1;
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < CL; k++) ri[k] = group_sum<L>(ri[k]);
+  double ev[1] = {0};
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < CL; k++) {
+      if (l == (L >= CL ? k : 0) && i0 + k < nlocal) {
+        const int i = i0 + k;
+        if (HALF) atomicAdd(&rho[i], ri[k]);
+        else {
+          const double r = ri[k];
+          rho[i] = r;
+          double p = r * P.rdrho + 1.0;
+          int m = (int)p;
+          m = max(1, min(m, P.nrho - 1));
+          p -= m;
+          p = fmin(p, 1.0);
+          const double *cf = P.frho + ((size_t)P.type2frho[ti[k]] * (P.nrho + 1) + m) * 8;
+          const double fpi = (cf[0] * p + cf[1]) * p + cf[2];
+          fp[i] = fpi;
+          if (ONE) xfp[i] = make_double4(xi[k], yi[k], zi[k], fpi);
+          if (EV) {
+            double phi = ((cf[3] * p + cf[4]) * p + cf[5]) * p + cf[6];
+            if (r > P.rhomax) phi += fpi * (r - P.rhomax);
+            ev[0] += phi * P.scale[ti[k] * nt1 + ti[k]];
+          }
+        }
+      }
+    }
+  }
+  if (EV && !HALF) block_reduce_store<1>(ev, partials);
+}
+
+// pass 3: forces
+template <int L, bool EV, bool ONE, bool HALF>
+__global__ void __launch_bounds__(EAM_THREADS, EAM_CL_MINBLOCKS)
+k_eam_force_cl(int nlocal, int ncl, int nmax, const double4 *__restrict__ xq, const double4 *__restrict__ xfp,
+               const int *__restrict__ neigh, const int *__restrict__ numneigh, int pitch, EamParams P,
+               const double *__restrict__ fp, double *__restrict__ f, double *__restrict__ partials,
+               const int *__restrict__ tile_list, int ntile_list) {
+  constexpr int C = 32 / L;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / L, l = lane % L;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const bool in_list = !tile_list || w < ntile_list;
+  const int tile = tile_list ? (in_list ? tile_list[w] : 0) : w;
+  const int c = tile * C + sub;
+  const bool active = in_list && c < ncl;
+  const int i0 = c * CL;
+  const int nt1 = P.ntypes + 1;
+  double xi[CL], yi[CL], zi[CL], fpi[CL], fx[CL], fy[CL], fz[CL];
+  int ti[CL];
+  double ev[7] = {0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+  for (int k = 0; k < CL; k++) { xi[k] = yi[k] = zi[k] = fpi[k] = fx[k] = fy[k] = fz[k] = 0; ti[k] = 1; }
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < CL; k++) {
+      const int i = min(i0 + k, nlocal - 1);
+      const double4 q = ONE ? xfp[i] : xq[i];
+      xi[k] = q.x; yi[k] = q.y; zi[k] = q.z;
+      if (ONE) fpi[k] = q.w; else { ti[k] = xq_type(q); fpi[k] = fp[i]; }
+    }
+    const int n = numneigh[c];
+    const int *nb = neigh + (size_t)tile * pitch * C + sub * L + l;
+    const int niter = (n + L - 1) / L;
+    const double4 *rec = ONE ? xfp : xq;
+    unsigned e0 = (0 * L + l < n) ? (unsigned)__ldg(nb) : 0u;
+    unsigned e1 = (1 * L + l < n) ? (unsigned)__ldg(nb + 32) : 0u;
+    double4 q0 = ld_xq(&rec[e0 & CL_JMASK]);
+    for (int it = 0; it < niter; it++) {
+      const unsigned e2 = ((it + 2) * L + l < n) ? (unsigned)__ldg(nb + (it + 2) * 32) : 0u;
+      const double4 q1 = ld_xq(&rec[e1 & CL_JMASK]);
+      {
+        const int j = (int)(e0 & CL_JMASK);
+        const unsigned m4 = e0 >> CL_SHIFT;
+        const double4 qj = q0;
+        const int tj = ONE ? 1 : xq_type(qj);
+        const double fpj = ONE ? qj.w : __ldg(&fp[j]);
+        double gx = 0, gy = 0, gz = 0;
+#pragma unroll
+        for (int k = 0; k < CL; k++) {
+          const double dx = xi[k] - qj.x, dy = yi[k] - qj.y, dz = zi[k] - qj.z;
+          const double rsq = fma(dz, dz, fma(dy, dy, dx * dx));
+          const bool hit = ((m4 >> k) & 1u) && rsq < P.cutforcesq;
+          const double rs = hit ? rsq : 1.0;
+          const double recip = rsqrt_nr(rs);
+          const double r = rs * recip;
+          double p = r * P.rdr + 1.0;
+          int m = (int)p;
+          m = min(m, P.nr - 1);
+          p -= m;
+          p = fmin(p, 1.0);
+          double rhoip, rhojp, scl;
+          double4 z;
+          if (ONE) {
+            const double4 a = ld4(P.tabC + (size_t)m * 8);
+            z = ld4(P.tabC + (size_t)m * 8 + 4);
+            rhoip = rhojp = ((3.0 * a.x * p + 2.0 * a.y) * p + a.z) * P.rdr;
+            scl = P.scale11;
+          } else {
+            const int tij = P.type2rhor[ti[k] * nt1 + tj], tji = P.type2rhor[tj * nt1 + ti[k]];
+            const double4 a = ld4(P.rhoA + ((size_t)tij * (P.nr + 1) + m) * 4);
+            rhoip = ((3.0 * a.x * p + 2.0 * a.y) * p + a.z) * P.rdr;
+            if (tji == tij) rhojp = rhoip;
+            else {
+              const double4 b = ld4(P.rhoA + ((size_t)tji * (P.nr + 1) + m) * 4);
+              rhojp = ((3.0 * b.x * p + 2.0 * b.y) * p + b.z) * P.rdr;
+            }
+            z = ld4(P.z2rV + ((size_t)P.type2z2r[ti[k] * nt1 + tj] * (P.nr + 1) + m) * 4);
+            scl = P.scale[ti[k] * nt1 + tj];
+          }
+          const double z2p = ((3.0 * z.x * p + 2.0 * z.y) * p + z.z) * P.rdr;
+          const double z2 = ((z.x * p + z.y) * p + z.z) * p + z.w;
+          const double phi = z2 * recip;
+          const double phip = z2p * recip - phi * recip;
+          const double psip = fpi[k] * rhojp + fpj * rhoip + phip;
+          const double fpair = hit ? -scl * psip * recip : 0.0;
+          fx[k] = fma(dx, fpair, fx[k]); fy[k] = fma(dy, fpair, fy[k]); fz[k] = fma(dz, fpair, fz[k]);
+          if (HALF) { gx = fma(dx, fpair, gx); gy = fma(dy, fpair, gy); gz = fma(dz, fpair, gz); }
+          if (EV) {
+            const double px = dx * fpair, py = dy * fpair, pz = dz * fpair;
+            ev[0] += hit ? scl * phi : 0.0;
+            ev[1] += dx * px; ev[2] += dy * py; ev[3] += dz * pz;
+            ev[4] += dx * py; ev[5] += dx * pz; ev[6] += dy * pz;
+          }
+        }
+        if (HALF && m4 && (gx != 0.0 || gy != 0.0 || gz != 0.0)) {
+          atomicAdd(&f[j], -gx);
+          atomicAdd(&f[j + nmax], -gy);
+          atomicAdd(&f[j + 2 * (size_t)nmax], -gz);
+        }
+      }
+      e0 = e1; e1 = e2; q0 = q1;
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < CL; k++) { fx[k] = group_sum<L>(fx[k]); fy[k] = group_sum<L>(fy[k]); fz[k] = group_sum<L>(fz[k]); }
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < CL; k++) {
+      if (l == (L >= CL ? k : 0) && i0 + k < nlocal) {
+        const int i = i0 + k;
+        if (HALF) { atomicAdd(&f[i], fx[k]); atomicAdd(&f[i + nmax], fy[k]); atomicAdd(&f[i + 2 * (size_t)nmax], fz[k]); }
+        else { f[i] = fx[k]; f[i + nmax] = fy[k]; f[i + 2 * (size_t)nmax] = fz[k]; }
+      }
+    }
+  }
+  if (EV) block_reduce_store<7>(ev, partials);
+}
+
+template <int L, bool EV, bool ONE>
+static int launch_pass_cl(b200md_ctx *c, const EamParams &P, int pass, const int *tiles, int ntl) {
+  const int ncl = list_units(c);
+  const int ntiles = tiles ? ntl : list_tiles(c);
+  const int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
+  if (nblocks == 0) return B200MD_OK;
+  if (pass == 0)
+    k_eam_rho_cl<L, EV, ONE, false><<<nblocks, EAM_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->xq, c->neigh, c->numneigh, c->pitch, P,
+                                                                          c->rho, c->fp, c->eam.xfp, c->partials, tiles, ntl);
+  else if (pass == 1)
+    k_eam_force_cl<L, EV, ONE, false><<<nblocks, EAM_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->nmax, c->xq, c->eam.xfp, c->neigh,
+                                                                            c->numneigh, c->pitch, P, c->fp, c->f, c->partials, tiles, ntl);
+  else if (pass == 2)
+    k_eam_rho_cl<L, false, ONE, true><<<nblocks, EAM_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->xq, c->neigh, c->numneigh, c->pitch, P,
+                                                                            c->rho, c->fp, c->eam.xfp, c->partials, tiles, ntl);
+  else
+    k_eam_force_cl<L, EV, ONE, true><<<nblocks, EAM_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->nmax, c->xq, c->eam.xfp, c->neigh,
+                                                                           c->numneigh, c->pitch, P, c->fp, c->f, c->partials, tiles, ntl);
+  c->launches++; c->pair_launches++;
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+template <int L>
+static int launch_cl(b200md_ctx *c, const EamLaunch &Ln, bool ev, int pass, const int *tiles, int ntl) {
+  if (Ln.mode) return ev ? launch_pass_cl<L, true, true>(c, Ln.P, pass, tiles, ntl) : launch_pass_cl<L, false, true>(c, Ln.P, pass, tiles, ntl);
+  return ev ? launch_pass_cl<L, true, false>(c, Ln.P, pass, tiles, ntl) : launch_pass_cl<L, false, false>(c, Ln.P, pass, tiles, ntl);
+}
+
 EamParams pair_eam_params(const b200md_ctx *c) {
   const EamTables &e = c->eam;
   return {e.ntypes, e.nrho, e.nr, e.rdr, e.rdrho, e.rhomax, e.cutforcesq, e.scale11, e.frho, e.rhoA, e.z2rV,
@@ -459,7 +731,15 @@ static int eam_prepare(b200md_ctx *c, EamLaunch &L) {
 int pair_eam_launch(b200md_ctx *c, bool ev, int pass, const int *tiles, int ntl) {
   EamLaunch L;
   TRY(eam_prepare(c, L));
-  switch (c->tpa) {
+  if (c->cluster) switch (c->tpa) {
+    case 1: return launch_cl<1>(c, L, ev, pass, tiles, ntl);
+    case 2: return launch_cl<2>(c, L, ev, pass, tiles, ntl);
+    case 4: return launch_cl<4>(c, L, ev, pass, tiles, ntl);
+    case 8: return launch_cl<8>(c, L, ev, pass, tiles, ntl);
+    case 16: return launch_cl<16>(c, L, ev, pass, tiles, ntl);
+    case 32: return launch_cl<32>(c, L, ev, pass, tiles, ntl);
+  }
+  else switch (c->tpa) {
     case 1: return launch_tpa<1>(c, L, ev, pass, tiles, ntl);
     case 2: return launch_tpa<2>(c, L, ev, pass, tiles, ntl);
     case 4: return launch_tpa<4>(c, L, ev, pass, tiles, ntl);
@@ -501,8 +781,7 @@ int pair_eam_embed(b200md_ctx *c, bool ev, double *e_embed) {
 // half list / newton on: PairEAM::compute with its reverse_comm(rho) and, via the caller,
 // Comm::reverse_comm of the forces
 static int pair_eam_compute_half(b200md_ctx *c, bool ev) {
-  const int A = 32 / c->tpa;
-  const int ntiles = (c->nlocal + A - 1) / A;
+  const int ntiles = list_tiles(c);
   const int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
   const int nall = c->nlocal + c->nghost;
   const int nb_atoms = (c->nlocal + EAM_THREADS - 1) / EAM_THREADS;
@@ -532,8 +811,7 @@ static int pair_eam_compute_half(b200md_ctx *c, bool ev) {
 int pair_eam_compute(b200md_ctx *c, int eflag, int vflag) {
   if (c->list_kind == B200MD_LIST_HALF_NEWTON) return pair_eam_compute_half(c, eflag || vflag);
   const bool ev = eflag || vflag;
-  const int A = 32 / c->tpa;
-  const int ntiles = (c->nlocal + A - 1) / A;
+  const int ntiles = list_tiles(c);
   const int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
   c->ev_valid = false;
   if (ev && nblocks) TRY(ensure_partials(c, nblocks));

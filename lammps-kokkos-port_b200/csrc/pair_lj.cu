@@ -125,10 +125,143 @@ static void launch_lj(b200md_ctx *c, int nblocks, bool ev, const LJOne &one, con
   else { if (half) launch_lj2<TPA, false, true>(c, nblocks, one, tiles, ntl); else launch_lj2<TPA, false, false>(c, nblocks, one, tiles, ntl); }
 }
 
+
+// ---- cluster-pair list (atomic systems; neigh.cu k_build_cluster) ---------------------------------------
+// L lanes share one i-cluster of CL = 4 owned atoms whose positions and force accumulators live in
+// registers; each lane takes every L-th entry of the cluster's j-list, gathers x_j ONCE, evaluates the pairs
+// its 4-bit mask names, and (half list) returns the summed f_j with ONE RED triple.  Against the per-atom
+// list this cuts the gathers and REDs per atom ~2.2x (the L1 data pipe is what binds these kernels) at
+// the price of distance tests on masked-out slots (FP64 pipe was at 26 %).
+#ifndef LJ_CL_MINBLOCKS
+#define LJ_CL_MINBLOCKS 2
+#endif
+template <int L, bool EV, bool HALF, bool ONETYPE>
+__global__ void __launch_bounds__(PAIR_THREADS, EV ? 2 : LJ_CL_MINBLOCKS)
+k_lj_cl(int nlocal, int ncl, int nmax, const double4 *__restrict__ xq, const int *__restrict__ neigh,
+        const int *__restrict__ numneigh, int pitch, LJOne one, const double *__restrict__ ljtab, int ntypes,
+        double *__restrict__ f, double *__restrict__ partials, const int *__restrict__ tile_list, int ntile_list) {
+  constexpr int C = 32 / L;
+  __shared__ double s_tab[ONETYPE ? 1 : (LJ_MAX_TYPES_SMEM + 1) * (LJ_MAX_TYPES_SMEM + 1) * 6];
+  const int nt1 = ntypes + 1;
+  if (!ONETYPE) {
+    for (int r = threadIdx.x; r < nt1 * nt1; r += blockDim.x)
+#pragma unroll
+      for (int k = 0; k < 6; k++) s_tab[r * 6 + k] = ljtab[r * 8 + k];
+    __syncthreads();
+  }
+  const int lane = threadIdx.x & 31;
+  const int sub = lane / L, l = lane % L;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const bool in_list = !tile_list || w < ntile_list;
+  const int tile = tile_list ? (in_list ? tile_list[w] : 0) : w;
+  const int c = tile * C + sub;
+  const bool active = in_list && c < ncl;
+  const int i0 = c * CL;
+
+  double xi[CL], yi[CL], zi[CL], fx[CL], fy[CL], fz[CL];
+  int ti[CL];
+  double ev[7] = {0, 0, 0, 0, 0, 0, 0};  // evdwl, vxx, vyy, vzz, vxy, vxz, vyz
+#pragma unroll
+  for (int k = 0; k < CL; k++) { fx[k] = fy[k] = fz[k] = 0; xi[k] = yi[k] = zi[k] = 0; ti[k] = 1; }
+  if (active) {
+#pragma unroll
+    for (int k = 0; k < CL; k++) {
+      const double4 q = xq[min(i0 + k, nlocal - 1)];   // absent atoms of the last cluster never appear in a mask
+      xi[k] = q.x; yi[k] = q.y; zi[k] = q.z;
+      if (!ONETYPE) ti[k] = xq_type(q);
+    }
+    const int n = numneigh[c];
+    const int *nb = neigh + (size_t)tile * pitch * C + sub * L + l;
+    const int niter = (n + L - 1) / L;
+    // software pipeline (the kernel is latency-bound: ncu long-scoreboard stalls): the entry of iteration it+2 and
+    // the x_j record of iteration it+1 are in flight while iteration it is evaluated.  Slots past the end of the
+    // list read entry 0 of the padded row with an empty mask.
+    unsigned e0 = (0 * L + l < n) ? (unsigned)__ldg(nb) : 0u;
+    unsigned e1 = (1 * L + l < n) ? (unsigned)__ldg(nb + 32) : 0u;
+    double4 q0 = ld_xq(&xq[e0 & CL_JMASK]);
+    for (int it = 0; it < niter; it++) {
+      const unsigned e2 = ((it + 2) * L + l < n) ? (unsigned)__ldg(nb + (it + 2) * 32) : 0u;
+      const double4 q1 = ld_xq(&xq[e1 & CL_JMASK]);
+      {
+        const int j = (int)(e0 & CL_JMASK);
+        const unsigned m = e0 >> CL_SHIFT;
+        const double4 qj = q0;
+        const int tj = ONETYPE ? 1 : xq_type(qj);
+        double gx = 0, gy = 0, gz = 0;
+#pragma unroll
+        for (int k = 0; k < CL; k++) {
+          const double dx = xi[k] - qj.x, dy = yi[k] - qj.y, dz = zi[k] - qj.z;
+          // list membership is exact in the mask (k_build_cluster tests rsq without FMA like the reference); the force
+          // cutoff test and the force itself use the fused form (the FP64 pipe is this kernel's top unit)
+          const double rsq = fma(dz, dz, fma(dy, dy, dx * dx));
+          double cutsq, lj1, lj2, lj3, lj4, offset;
+          if (ONETYPE) { cutsq = one.cutsq; lj1 = one.lj1; lj2 = one.lj2; lj3 = one.lj3; lj4 = one.lj4; offset = one.offset; }
+          else {
+            const double *t = &s_tab[(ti[k] * nt1 + tj) * 6];
+            cutsq = t[0]; lj1 = t[1]; lj2 = t[2]; lj3 = t[3]; lj4 = t[4]; offset = t[5];
+          }
+          // branch-free: the four pair evaluations of a slot interleave; a masked-out pair is evaluated at rsq = 1
+          // and multiplied by zero
+          const bool hit = ((m >> k) & 1u) && rsq < cutsq;
+          const double r2inv = rcp_nr(hit ? rsq : 1.0);
+          const double r6inv = r2inv * r2inv * r2inv;
+          const double forcelj = r6inv * (lj1 * r6inv - lj2);
+          const double fpair = hit ? forcelj * r2inv : 0.0;
+          fx[k] = fma(dx, fpair, fx[k]); fy[k] = fma(dy, fpair, fy[k]); fz[k] = fma(dz, fpair, fz[k]);
+          if (HALF) { gx = fma(dx, fpair, gx); gy = fma(dy, fpair, gy); gz = fma(dz, fpair, gz); }
+          if (EV) {
+            const double px = dx * fpair, py = dy * fpair, pz = dz * fpair;
+            ev[0] += hit ? r6inv * (lj3 * r6inv - lj4) - offset : 0.0;
+            ev[1] += dx * px; ev[2] += dy * py; ev[3] += dz * pz;
+            ev[4] += dx * py; ev[5] += dx * pz; ev[6] += dy * pz;
+          }
+        }
+        if (HALF && m && (gx != 0.0 || gy != 0.0 || gz != 0.0)) {
+          atomicAdd(&f[j], -gx);
+          atomicAdd(&f[j + nmax], -gy);
+          atomicAdd(&f[j + 2 * (size_t)nmax], -gz);
+        }
+      }
+      e0 = e1; e1 = e2; q0 = q1;
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < CL; k++) { fx[k] = group_sum<L>(fx[k]); fy[k] = group_sum<L>(fy[k]); fz[k] = group_sum<L>(fz[k]); }
+  if (active) {
+    // lane k of the group stores atom k (L >= 4), or lane 0 all of them
+#pragma unroll
+    for (int k = 0; k < CL; k++) {
+      if (l == (L >= CL ? k : 0) && i0 + k < nlocal) {
+        const int i = i0 + k;
+        if (HALF) { atomicAdd(&f[i], fx[k]); atomicAdd(&f[i + nmax], fy[k]); atomicAdd(&f[i + 2 * (size_t)nmax], fz[k]); }
+        else { f[i] = fx[k]; f[i + nmax] = fy[k]; f[i + 2 * (size_t)nmax] = fz[k]; }
+      }
+    }
+  }
+  if (EV) block_reduce_store<7>(ev, partials);
+}
+
+template <int L, bool EV, bool HALF>
+static void launch_lj_cl2(b200md_ctx *c, int nblocks, const LJOne &one, const int *tiles, int ntl) {
+  const int ncl = list_units(c);
+  if (c->ntypes == 1)
+    k_lj_cl<L, EV, HALF, true><<<nblocks, PAIR_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->nmax, c->xq, c->neigh, c->numneigh,
+                                                                      c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials, tiles, ntl);
+  else
+    k_lj_cl<L, EV, HALF, false><<<nblocks, PAIR_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->nmax, c->xq, c->neigh, c->numneigh,
+                                                                       c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials, tiles, ntl);
+}
+template <int L>
+static void launch_lj_cl(b200md_ctx *c, int nblocks, bool ev, const LJOne &one, const int *tiles, int ntl) {
+  const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON;
+  if (ev) { if (half) launch_lj_cl2<L, true, true>(c, nblocks, one, tiles, ntl); else launch_lj_cl2<L, true, false>(c, nblocks, one, tiles, ntl); }
+  else { if (half) launch_lj_cl2<L, false, true>(c, nblocks, one, tiles, ntl); else launch_lj_cl2<L, false, false>(c, nblocks, one, tiles, ntl); }
+}
+
 // one launch over all tiles (tiles == nullptr) or over a tile list (interior / boundary split)
 int pair_lj_launch(b200md_ctx *c, bool ev, const int *tiles, int ntl) {
-  const int A = 32 / c->tpa;
-  const int ntiles = tiles ? ntl : (c->nlocal + A - 1) / A;
+  const int ntiles = tiles ? ntl : list_tiles(c);
   const int nblocks = (ntiles + PAIR_THREADS / 32 - 1) / (PAIR_THREADS / 32);
   if (nblocks == 0) return B200MD_OK;
   LJOne one = {0, 0, 0, 0, 0, 0};
@@ -136,7 +269,16 @@ int pair_lj_launch(b200md_ctx *c, bool ev, const int *tiles, int ntl) {
     const double *t = &c->h_ljtab[((size_t)1 * 2 + 1) * 8];  // row (1,1)
     one = {t[0], t[1], t[2], t[3], t[4], t[5]};
   }
-  switch (c->tpa) {
+  if (c->cluster) switch (c->tpa) {
+    case 1: launch_lj_cl<1>(c, nblocks, ev, one, tiles, ntl); break;
+    case 2: launch_lj_cl<2>(c, nblocks, ev, one, tiles, ntl); break;
+    case 4: launch_lj_cl<4>(c, nblocks, ev, one, tiles, ntl); break;
+    case 8: launch_lj_cl<8>(c, nblocks, ev, one, tiles, ntl); break;
+    case 16: launch_lj_cl<16>(c, nblocks, ev, one, tiles, ntl); break;
+    case 32: launch_lj_cl<32>(c, nblocks, ev, one, tiles, ntl); break;
+    default: b200md_set_error("b200md: lanes per atom must be 1, 2, 4, 8, 16 or 32"); return B200MD_ERR;
+  }
+  else switch (c->tpa) {
     case 1: launch_lj<1>(c, nblocks, ev, one, tiles, ntl); break;
     case 2: launch_lj<2>(c, nblocks, ev, one, tiles, ntl); break;
     case 4: launch_lj<4>(c, nblocks, ev, one, tiles, ntl); break;
@@ -154,8 +296,7 @@ int pair_lj_launch(b200md_ctx *c, bool ev, const int *tiles, int ntl) {
 int pair_lj_compute(b200md_ctx *c, int eflag, int vflag) {
   if (c->ntypes > LJ_MAX_TYPES_SMEM) { b200md_set_error("b200md: lj/cut supports at most 8 atom types"); return B200MD_ERR; }
   const bool ev = eflag || vflag;
-  const int A = 32 / c->tpa;
-  const int ntiles = (c->nlocal + A - 1) / A;
+  const int ntiles = list_tiles(c);
   const int nblocks = (ntiles + PAIR_THREADS / 32 - 1) / (PAIR_THREADS / 32);
   const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON;
   if (half)  // Verlet::force_clear over owned + ghost (src/verlet.cpp:376-421)

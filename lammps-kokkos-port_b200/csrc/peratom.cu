@@ -70,18 +70,24 @@ __device__ __forceinline__ void tally_store(const Tally &t, double *__restrict__
 template <bool HALF>
 __global__ void __launch_bounds__(PA_THREADS)
 k_lj_atom(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict__ neigh,
-          const int *__restrict__ numneigh, int pitch, int F, const double *__restrict__ ljtab, int ntypes,
+          const int *__restrict__ numneigh, int pitch, int F, int cl, const double *__restrict__ ljtab, int ntypes,
           double *__restrict__ pa, int do_e, int do_v) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nlocal) return;
   const int nt1 = ntypes + 1;
   const double4 qi = xq[i];
   const int itype = xq_type(qi);
-  const int n = numneigh[i];
-  const int *base = list_base(neigh, pitch, F, i);
+  // cluster-pair list (cl): the list unit is the cluster i / CL, atom i owns the entries with bit i % CL of the mask
+  const int unit = cl ? i / CL : i;
+  const int n = numneigh[unit];
+  const int *base = list_base(neigh, pitch, F, unit);
   Tally t; t.clear();
   for (int k = 0; k < n; k++) {
-    const int j = list_at(base, F, k);
+    int j = list_at(base, F, k);
+    if (cl) {
+      if (!(((unsigned)j >> (CL_SHIFT + i % CL)) & 1u)) continue;
+      j &= CL_JMASK;
+    }
     const double4 qj = xq[j];
     const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
     const double rsq = rsq_nofma(dx, dy, dz);
@@ -101,7 +107,7 @@ k_lj_atom(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__res
 template <bool HALF>
 __global__ void __launch_bounds__(PA_THREADS)
 k_eam_atom(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__restrict__ neigh,
-           const int *__restrict__ numneigh, int pitch, int F, EamParams P, const double *__restrict__ rho,
+           const int *__restrict__ numneigh, int pitch, int F, int cl, EamParams P, const double *__restrict__ rho,
            const double *__restrict__ fp, double *__restrict__ pa, int do_e, int do_v) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nlocal) return;
@@ -109,8 +115,10 @@ k_eam_atom(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__re
   const double4 qi = xq[i];
   const int itype = xq_type(qi);
   const double fpi = fp[i];
-  const int n = numneigh[i];
-  const int *base = list_base(neigh, pitch, F, i);
+  // cluster-pair list (cl): the list unit is the cluster i / CL, atom i owns the entries with bit i % CL of the mask
+  const int unit = cl ? i / CL : i;
+  const int n = numneigh[unit];
+  const int *base = list_base(neigh, pitch, F, unit);
   const size_t rows = (size_t)P.nr + 1;
   Tally t; t.clear();
   if (do_e) {   // embedding energy of atom i
@@ -126,7 +134,11 @@ k_eam_atom(int nlocal, int nmax, const double4 *__restrict__ xq, const int *__re
     t.e += phi * P.scale[itype * nt1 + itype];
   }
   for (int k = 0; k < n; k++) {
-    const int j = list_at(base, F, k);
+    int j = list_at(base, F, k);
+    if (cl) {
+      if (!(((unsigned)j >> (CL_SHIFT + i % CL)) & 1u)) continue;
+      j &= CL_JMASK;
+    }
     const double4 qj = xq[j];
     const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
     const double rsq = rsq_nofma(dx, dy, dz);
@@ -211,15 +223,15 @@ int peratom_compute(b200md_ctx *c, int eflag_atom, int vflag_atom, int which) {
   bool ghost_rows = false;
   if (nblocks && (which & B200MD_PERATOM_PAIR)) {
     if (c->pair_style == B200MD_PAIR_LJ_CUT) {
-      if (half) k_lj_atom<true><<<nblocks, PA_THREADS, 0, c->stream>>>(c->nlocal, nmax, c->xq, c->neigh, c->numneigh, c->pitch, c->tpa,
+      if (half) k_lj_atom<true><<<nblocks, PA_THREADS, 0, c->stream>>>(c->nlocal, nmax, c->xq, c->neigh, c->numneigh, c->pitch, c->tpa, c->cluster ? 1 : 0,
                                                                       c->ljtab, c->ntypes, pa, eflag_atom, vflag_atom);
-      else k_lj_atom<false><<<nblocks, PA_THREADS, 0, c->stream>>>(c->nlocal, nmax, c->xq, c->neigh, c->numneigh, c->pitch, c->tpa,
+      else k_lj_atom<false><<<nblocks, PA_THREADS, 0, c->stream>>>(c->nlocal, nmax, c->xq, c->neigh, c->numneigh, c->pitch, c->tpa, c->cluster ? 1 : 0,
                                                                   c->ljtab, c->ntypes, pa, eflag_atom, vflag_atom);
     } else if (c->pair_style == B200MD_PAIR_EAM) {
       const EamParams P = pair_eam_params(c);
-      if (half) k_eam_atom<true><<<nblocks, PA_THREADS, 0, c->stream>>>(c->nlocal, nmax, c->xq, c->neigh, c->numneigh, c->pitch, c->tpa,
+      if (half) k_eam_atom<true><<<nblocks, PA_THREADS, 0, c->stream>>>(c->nlocal, nmax, c->xq, c->neigh, c->numneigh, c->pitch, c->tpa, c->cluster ? 1 : 0,
                                                                        P, c->rho, c->fp, pa, eflag_atom, vflag_atom);
-      else k_eam_atom<false><<<nblocks, PA_THREADS, 0, c->stream>>>(c->nlocal, nmax, c->xq, c->neigh, c->numneigh, c->pitch, c->tpa,
+      else k_eam_atom<false><<<nblocks, PA_THREADS, 0, c->stream>>>(c->nlocal, nmax, c->xq, c->neigh, c->numneigh, c->pitch, c->tpa, c->cluster ? 1 : 0,
                                                                    P, c->rho, c->fp, pa, eflag_atom, vflag_atom);
     } else {
       b200md_set_error("All pair coeffs are not set");

@@ -60,3 +60,30 @@ __device__ __forceinline__ void block_reduce_store(double (&val)[NV], double *ou
     }
   }
 }
+
+// cluster-pair list (neigh.cu): CL owned atoms share one j-list, entry = j | mask << CL_SHIFT
+#define CL 4
+#define CL_SHIFT 28
+#define CL_JMASK 0x0fffffff
+
+// 1/x to FP64 rounding error (not correctly rounded): MUFU.RCP64H seed (2^-23) + two Newton steps.
+// x is a squared pair distance (normal, positive); 5 instructions instead of the ~12 of the IEEE division.
+__device__ __forceinline__ double rcp_nr(double x) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double t = fma(-x, y, 1.0);
+  y = fma(y, t, y);
+  t = fma(-x, y, 1.0);
+  return fma(y, t, y);
+}
+
+// 1/sqrt(x) to FP64 rounding error (not correctly rounded): MUFU.RSQ64H seed + two Newton steps
+__device__ __forceinline__ double rsqrt_nr(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double xh = 0.5 * x;
+  double e = fma(-xh * y, y, 0.5);
+  y = fma(y, e, y);
+  e = fma(-xh * y, y, 0.5);
+  return fma(y, e, y);
+}

@@ -232,3 +232,37 @@ def test_lj_mixed_cutoffs_gpu(pkg, mix, list_kind):
     for k, key in enumerate(KEYS):
         assert abs(t[key] - g[mix + "_thermo20"][k]) <= T_TOL * abs(g[mix + "_thermo20"][k]), key
     ctx.close()
+
+
+@pytest.mark.parametrize("cluster", ["on", "off"])
+@pytest.mark.parametrize("half", [True, False])
+@pytest.mark.parametrize("name,kind", CASES)
+def test_golden_both_list_layouts(pkg, oracle_mod, name, kind, half, cluster):
+    """the cluster-pair list (4 atoms share one j-list, 4-bit pair masks; default for lj/cut) and the per-atom list
+    (default for eam and molecular systems) must give the same exact per-atom lists, forces and thermo for every
+    pair style: option `cluster` forces either layout"""
+    B = pkg.b200md
+    g = np.load(os.path.join(Cm.GOLDEN, name + ".npz"))
+    ctx, s = make_ctx(pkg, oracle_mod, g, kind, B.LIST_HALF_NEWTON if half else B.LIST_FULL, 4)
+    ctx.set_option("cluster", cluster)
+    assert ctx.get_option("cluster") == cluster
+    ctx.setup()
+    a = ctx.get_atoms()
+    nn, flat = ctx.neigh_export(by_tag=True)
+    if half:
+        want = np.sort(g["half_lo"].astype(np.int64) * (1 << 32) + g["half_hi"].astype(np.int64))
+        assert np.array_equal(Cm.pairs_from_lists(a["tag"], nn, flat), want)
+    else:
+        want = np.sort(g["full_i"].astype(np.int64) * (1 << 32) + g["full_j"].astype(np.int64))
+        assert np.array_equal(Cm.full_sets(a["tag"], nn, flat), want)
+    order = np.argsort(a["tag"])
+    assert np.abs(a["f"][order] - g["f"]).max() <= F_TOL * np.abs(g["f"]).max()
+    t = ctx.thermo()
+    for k, key in enumerate(KEYS):
+        assert abs(t[key] - g["thermo0"][k]) <= T_TOL * abs(g["thermo0"][k]), key
+    for row in g["thermo_series"][:3]:
+        ctx.setup()
+        t = ctx.run(10, s["dt"], 0)[-1]
+        for k, key in enumerate(KEYS):
+            assert abs(t[key] - row[k]) <= T_TOL * abs(row[k]), (key, t[key], row[k])
+    ctx.close()

@@ -81,7 +81,7 @@ def test_lj_tables(pkg):
     B = pkg.b200md
     T = B.lj_cut_tables(2, {(1, 1): (1.0, 1.0), (2, 2): (0.5, 1.2, 3.0)}, 2.5, mix="arithmetic", shift=True)
     assert T["lj1"][1, 1] == 48.0 and T["lj2"][1, 1] == 24.0 and T["cutsq"][1, 1] == 6.25
-    e, s, c = math.sqrt(0.5), 1.1, 3.0
+    e, s, c = math.sqrt(0.5), 1.1, 2.75   # cutoff mixed like sigma: mix_distance(2.5, 3.0), src/pair_lj_cut.cpp:506
     assert T["lj3"][1, 2] == pytest.approx(4 * e * s ** 12) and T["lj3"][2, 1] == T["lj3"][1, 2]
     assert T["offset"][1, 2] == pytest.approx(4 * e * ((s / c) ** 12 - (s / c) ** 6))
     with pytest.raises(B.B200MDError, match="All pair coeffs are not set"):
