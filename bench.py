@@ -145,6 +145,15 @@ def run_reference(kind, xyz, warm, steps, cores):
     return atoms * nst / lt, lt, atoms
 
 
+T_START = time.time()
+
+
+def progress(msg):
+    """phase markers on stderr (rank 0), so a run that stalls says where"""
+    if int(os.environ.get("RANK", "0")) == 0:
+        print("[bench %6.1fs] %s" % (time.time() - T_START, msg), file=sys.stderr, flush=True)
+
+
 def fmt8(v):
     return float("%.8g" % v)
 
@@ -271,6 +280,10 @@ def kernel_variant():
 
 
 def main():
+    wd = int(os.environ.get("B200MD_BENCH_WATCHDOG", "1500"))
+    if wd > 0:      # a rank that fails leaves its peers waiting in NCCL: dump the Python stacks and exit instead of hanging
+        import faulthandler
+        faulthandler.dump_traceback_later(wd, exit=True)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
@@ -330,6 +343,7 @@ def main():
     # B200 (profiles/) the half list wins on one GPU.  On several ranks `--list auto` MEASURES it for in.lj (20 untimed
     # steps of each kind) and uses half for eam ----
     lk_main = a.list if a.list != "auto" else "half"
+    progress("start: %d rank(s), workload %s" % (world, a.workload))
     ctx = job.open(options)
     run_info["halo"] = ctx.get_option("halo")
     cfg = job.configure(ctx, kind, xyz, lk_main)
@@ -337,6 +351,7 @@ def main():
     if world > 1 and a.list == "auto" and kind == "lj":
         trial = {}
         for k2 in ("full", "half"):
+            progress("list trial " + k2)
             ctx.neigh_config(**cfg["neigh"], list_kind=B.LIST_HALF_NEWTON if k2 == "half" else B.LIST_FULL)
             ctx.setup()
             ctx.run(5, cfg["dt"], 0)
@@ -354,6 +369,7 @@ def main():
     small = {}
     if not a.no_parity:
         for wl, lk in (("lj", lk_main), ("eam", lk_sec)):
+            progress("parity check " + wl + " 32k, list " + lk)
             ctx = job.open(options)
             cfg = job.configure(ctx, wl, (1, 1, 1), lk)
             ctx.setup()
@@ -377,6 +393,7 @@ def main():
             return 2
 
     # ---- the workload reported as `value`: device-resident loop ----
+    progress("main workload, list " + lk_main)
     ctx = job.open(options)
     cfg = job.configure(ctx, kind, xyz, lk_main)
     ctx.setup()
@@ -388,6 +405,7 @@ def main():
     # its result.  "full_state": x,v up and x,v,f,tag down (a host that owns the whole state); "offload": x up and f down,
     # the per-step boundary of the reference's own GPU package (src/GPU/pair_lj_cut_gpu.cpp:98-102) ----
     e2e = None
+    progress("main workload measured: %.4f ms/step; e2e" % m["ms_per_step"])
     if not a.no_e2e:
         n = ctx.nlocal()[0]
         cap = int(n * 1.05) + 1024
@@ -397,28 +415,29 @@ def main():
         variants = {}
         for name in ("full_state", "offload"):
             full = name == "full_state"
+            # the device integrates, so the host needs the new positions back before it can upload them again:
+            # offload = x up, x and f down
+            def step():
+                ctx.put_atoms(hx, hv if full else None)
+                ctx.run(1, cfg["dt"], 0)
+                ctx.get_atoms_into(hx, hv if full else None, hf, htag if full else None)
             for _ in range(3):
-                ctx.put_atoms(hx, hv if full else None); ctx.run(1, cfg["dt"], 0)
-                ctx.get_atoms_into(hx if full else None, hv if full else None, hf, htag if full else None)
+                step()
             job.barrier()
             t0 = time.perf_counter()
             h2d = d2h = 0
-            for _ in range(a.steps):
+            for it in range(a.steps):
                 n = ctx.nlocal()[0]
-                ctx.put_atoms(hx, hv if full else None)
-                ctx.run(1, cfg["dt"], 0)
+                step()
                 n2 = ctx.nlocal()[0]
-                ctx.get_atoms_into(hx if full else None, hv if full else None, hf, htag if full else None)
-                h2d += (48 if full else 24) * n; d2h += (76 if full else 24) * n2
+                h2d += (48 if full else 24) * n; d2h += (76 if full else 48) * n2
             job.barrier()
             ms = job.maxr((time.perf_counter() - t0) * 1e3)
             variants[name] = {"value": natoms * a.steps / (ms / 1e3), "ms_per_step": ms / a.steps,
                               "h2d_bytes_per_step": h2d // a.steps, "d2h_bytes_per_step": d2h // a.steps}
-            if not full:   # the host keeps integrating its own copy in a real offload; here x is refreshed for the next step
-                ctx.get_atoms_into(hx, hv, hf, htag)
         e2e = dict(variants["full_state"], unit="atom-steps/s",
                    api="b200md_put_atoms(x,v) + b200md_run(1) + b200md_get_atoms(x,v,f,tag), pinned host buffers, every step",
-                   offload=dict(variants["offload"], api="b200md_put_atoms(x) + b200md_run(1) + b200md_get_atoms(f)"))
+                   offload=dict(variants["offload"], api="b200md_put_atoms(x) + b200md_run(1) + b200md_get_atoms(x,f)"))
     ctx.close()
 
     # ---- secondary workloads (same JSON line: the driver only ever runs `bench.py --gpus N`) ----
@@ -428,6 +447,7 @@ def main():
             if wl == a.workload:
                 continue
             k2, xyz2, n2, text2 = workload_desc(wl, ngpus)
+            progress("secondary " + name)
             ctx = job.open(options)
             cfg2 = job.configure(ctx, k2, xyz2, lk_sec)
             ctx.setup()
@@ -465,6 +485,7 @@ def main():
             "parity_check": parity, "roofline": roofline, "e2e": e2e, "secondary": secondary,
             "gpu_launches": m["launches"], "clocks": m["clocks"], "device_ms": m["device_ms"], "wall_ms": m["wall_ms"],
             "rebuilds_in_timed_region": m["rebuilds"]}
+    progress("done with the GPU part")
     if rank == 0 and not a.no_cpu_baseline and ngpus == 1:
         try:
             sample_steps = 20

@@ -75,6 +75,15 @@ int b200md_comm_schedule(const double boxlo[3], const double boxhi[3], const int
                          const int procgrid[3], const int myloc[3], double cutghost,
                          b200md_swap_schedule *out);
 
+/* Direct halo tables (csrc/halo26.cu): the staged ghost set of CommBrick::borders (src/comm_brick.cpp:771-979) is the
+ * product set over the dimensions of the per-dimension send slabs, so an owned atom can be classified once by the up
+ * to 26 directions (dx,dy,dz), index (dx+1)+3(dy+1)+9(dz+1), it is a ghost in.  Per direction: the rank a copy lands
+ * on (-1 = no neighbour), the periodic shift multiples (CommBrick::setup pbc flags); per dimension the slab bounds.
+ * usable = 0 when some dimension needs more than one ghost layer (then the staged path runs). */
+int b200md_halo_directions(const double boxlo[3], const double boxhi[3], const int periodic[3],
+                           const int procgrid[3], const int myloc[3], double cutghost, int peer[27],
+                           int shift[27][3], double slabhi_left[3], double slablo_right[3], int *usable);
+
 /* NBinStandard::setup_bins (src/nbin_standard.cpp:82-214) + NStencil::create_setup
  * (src/nstencil.cpp:213-247): the reference's bin geometry for a sub-box. */
 typedef struct b200md_bin_geometry {

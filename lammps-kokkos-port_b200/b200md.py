@@ -19,7 +19,7 @@ LIB_PATH = os.environ.get("B200MD_LIB", os.path.join(_HERE, "libb200md.so"))
 LIST_FULL, LIST_HALF_NEWTON = 0, 1
 PERATOM_PAIR, PERATOM_BOND = 1, 2
 MAXSWAP = 64
-OPTION_KEYS = ("halo", "overlap", "split", "fuse_nve", "eam_smem", "phase_timing", "lanes", "build_lanes", "graph", "cluster")
+OPTION_KEYS = ("halo", "overlap", "split", "fuse_nve", "eam_smem", "phase_timing", "lanes", "build_lanes", "graph", "cluster", "trace")
 
 
 class B200MDError(RuntimeError):
@@ -128,6 +128,16 @@ def comm_schedule(boxlo, boxhi, periodic, grid, myloc, cutghost):
     _chk(lib().b200md_comm_schedule(_d3(boxlo), _d3(boxhi), _i3(periodic), _i3(grid), _i3(myloc),
                                     C.c_double(cutghost), C.byref(s)))
     return s
+
+
+def halo_directions(boxlo, boxhi, periodic, grid, myloc, cutghost):
+    """direct-halo tables (csrc/halo26.cu): peer[27], shift[27][3], slabhi_left[3], slablo_right[3], usable"""
+    peer = (C.c_int * 27)(); shift = ((C.c_int * 3) * 27)()
+    shl, slr = (C.c_double * 3)(), (C.c_double * 3)()
+    ok = C.c_int()
+    _chk(lib().b200md_halo_directions(_d3(boxlo), _d3(boxhi), _i3(periodic), _i3(grid), _i3(myloc), C.c_double(cutghost),
+                                      peer, shift, shl, slr, C.byref(ok)))
+    return list(peer), [list(r) for r in shift], list(shl), list(slr), bool(ok.value)
 
 
 def atom_sort_order(x, sublo, subhi, cutneighmax):

@@ -73,7 +73,7 @@ extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out)
   // runtime knobs are set through b200md_set_option (the library reads no environment variables);
   // per-step halo: owner <-> holder in one exchange ("direct", default on several ranks) or the
   // reference's three forwarding stages ("staged")
-  c->direct.on = nranks > 1;
+  c->halo_mode = 2;
   CUDA_TRY(cudaMalloc(&c->d_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMallocHost(&c->h_result, 16 * sizeof(double)));
   CUDA_TRY(cudaMalloc(&c->d_flags, 8 * sizeof(int)));
@@ -521,10 +521,11 @@ extern "C" int b200md_set_option(b200md_ctx *c, const char *key, const char *val
   const std::string k(key);
   bool b = false;
   if (k == "halo") {
-    if (!strcmp(value, "direct")) c->direct.on = c->nranks > 1;
-    else if (!strcmp(value, "staged")) c->direct.on = false;
-    else { b200md_set_error("Illegal package b200 command: halo must be direct or staged"); return B200MD_ERR; }
-    c->direct.ready = false;
+    if (!strcmp(value, "direct")) c->halo_mode = 2;
+    else if (!strcmp(value, "owner")) c->halo_mode = 1;
+    else if (!strcmp(value, "staged")) c->halo_mode = 0;
+    else { b200md_set_error("Illegal package b200 command: halo must be direct, owner or staged"); return B200MD_ERR; }
+    if (c->neigh_configured) TRY(comm_setup(c));
   } else if (k == "overlap") {
     NEED(opt_bool(value, &b), "Illegal package b200 command: overlap must be on or off");
     c->overlap = b;
@@ -544,6 +545,9 @@ extern "C" int b200md_set_option(b200md_ctx *c, const char *key, const char *val
       NEED(opt_bool(value, &b), "Illegal package b200 command: cluster must be on, off or auto");
       c->use_cluster = b ? 1 : 0;
     }
+  } else if (k == "trace") {
+    NEED(opt_bool(value, &b), "Illegal package b200 command: trace must be on or off");
+    c->trace = b;
   } else if (k == "phase_timing") {
     NEED(opt_bool(value, &b), "Illegal package b200 command: phase_timing must be on or off");
     c->phase_timing = b;
@@ -564,7 +568,7 @@ extern "C" int b200md_get_option(b200md_ctx *c, const char *key, char *value, in
   NEED(c && key && value && len > 0, "b200md: null argument");
   const std::string k(key);
   std::string v;
-  if (k == "halo") v = c->nranks == 1 ? "none" : (c->direct.on ? "direct" : "staged");
+  if (k == "halo") v = c->nranks == 1 ? "none" : (c->h26.on || (!c->neigh_configured && c->halo_mode == 2) ? "direct" : (c->direct.on || c->halo_mode == 1 ? "owner" : "staged"));
   else if (k == "overlap") v = c->overlap ? "on" : "off";
   else if (k == "split") v = std::to_string(c->split);
   else if (k == "fuse_nve") v = c->fuse_nve ? "on" : "off";
@@ -789,6 +793,25 @@ extern "C" int b200md_setup(b200md_ctx *c) {
   return B200MD_OK;
 }
 
+// option trace: a timed event on stream `s` under a label (development aid: what the two streams overlap)
+static void trace_mark(b200md_ctx *c, const char *label, cudaStream_t s) {
+  if (!c->trace) return;
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  cudaEventRecord(e, s);
+  c->trace_ev.emplace_back(label, e);
+}
+static void trace_dump(b200md_ctx *c) {
+  if (!c->trace || c->trace_ev.empty()) return;
+  for (auto &le : c->trace_ev) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->trace_ev[0].second, le.second);
+    fprintf(stderr, "[trace rank %d] %9.1f us  %s\n", c->rank, ms * 1e3, le.first.c_str());
+    }
+  for (auto &le : c->trace_ev) cudaEventDestroy(le.second);
+  c->trace_ev.clear();
+}
+
 // Non-rebuild, non-thermo step on several ranks: the forward halo (and EAM's fp halo) runs on the
 // comm stream while the tiles without ghost neighbors are evaluated; boundary tiles follow.
 // Same kernels, same per-atom arithmetic and order as the unsplit launch -> identical results.
@@ -813,35 +836,48 @@ static int forces_overlapped_half(b200md_ctx *c) {
   const bool eam = c->pair_style == B200MD_PAIR_EAM;
   for (int d = 0; d < 3; d++) CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax, 0, sizeof(double) * nall, s));
   if (eam) CUDA_TRY(cudaMemsetAsync(c->rho, 0, sizeof(double) * nall, s));
+  trace_mark(c, "main: f cleared", s);
   if (!eam) {
     TRY(pair_lj_launch(c, false, int1, n1));
+    trace_mark(c, "main: lj interior part 1 done", s);
     CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
     TRY(pair_lj_launch(c, false, c->tiles_bnd, c->n_tiles_bnd));
+    trace_mark(c, "main: lj boundary tiles done", s);
   } else {
     TRY(pair_eam_launch(c, false, 2, int1, n1));
+    trace_mark(c, "main: rho interior part 1 done", s);
     CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
     TRY(pair_eam_launch(c, false, 2, c->tiles_bnd, c->n_tiles_bnd));
+    trace_mark(c, "main: rho boundary done", s);
     CUDA_TRY(cudaEventRecord(c->ev_rb, s));              // ghost rho complete
     CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_rb, 0));
     TRY(on_comm_stream(c, comm_reverse_rho));
+    trace_mark(c, "comm: rho reverse done", cs);
     CUDA_TRY(cudaEventRecord(c->ev_rr, cs));
     TRY(pair_eam_launch(c, false, 2, int2, n2));
+    trace_mark(c, "main: rho interior part 2 done", s);
     CUDA_TRY(cudaStreamWaitEvent(s, c->ev_rr, 0));
     TRY(pair_eam_embed(c, false, nullptr));
+    trace_mark(c, "main: embed done", s);
     CUDA_TRY(cudaEventRecord(c->ev_fp, s));
     CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_fp, 0));
     TRY(on_comm_stream(c, pair_eam_fp_comm));
+    trace_mark(c, "comm: fp forward done", cs);
     CUDA_TRY(cudaEventRecord(c->ev_fphalo, cs));
     TRY(pair_eam_launch(c, false, 3, int1, n1));
+    trace_mark(c, "main: force interior part 1 done", s);
     CUDA_TRY(cudaStreamWaitEvent(s, c->ev_fphalo, 0));
     TRY(pair_eam_launch(c, false, 3, c->tiles_bnd, c->n_tiles_bnd));
+    trace_mark(c, "main: force boundary done", s);
   }
   CUDA_TRY(cudaEventRecord(c->ev_bnd, s));               // ghost forces complete
   CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_bnd, 0));
   TRY(on_comm_stream(c, comm_reverse_force));
+  trace_mark(c, "comm: f reverse done", cs);
   CUDA_TRY(cudaEventRecord(c->ev_rev, cs));
   if (!eam) TRY(pair_lj_launch(c, false, int2, n2));
   else TRY(pair_eam_launch(c, false, 3, int2, n2));
+  trace_mark(c, "main: interior part 2 done", s);
   CUDA_TRY(cudaStreamWaitEvent(s, c->ev_rev, 0));
   return B200MD_OK;
 }
@@ -849,9 +885,11 @@ static int forces_overlapped_half(b200md_ctx *c) {
 // non-rebuild, non-tally step on several ranks; on return f is complete (reverse_comm included)
 static int forces_overlapped(b200md_ctx *c) {
   cudaStream_t s = c->stream, cs = c->comm_stream;
+  trace_mark(c, "main: step start (x integrated)", s);
   CUDA_TRY(cudaEventRecord(c->ev_x, s));               // positions integrated
   CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_x, 0));
   TRY(on_comm_stream(c, comm_forward));                // x halo on the comm stream
+  trace_mark(c, "comm: x forward done", cs);
   CUDA_TRY(cudaEventRecord(c->ev_halo, cs));
   c->ev_valid = false;
   if (c->list_kind == B200MD_LIST_HALF_NEWTON) return forces_overlapped_half(c);
@@ -935,6 +973,7 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     if (out_step && thermo_out && nth < max_thermo) { TRY(b200md_thermo_compute(c, &thermo_out[nth])); nth++; }
   }
   TT.end();
+  trace_mark(c, "main: run end", c->stream);
   if (c->topo.molecular) CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4, c->d_flags + 4, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
   CUDA_TRY(cudaStreamSynchronize(c->stream));
   if (c->topo.molecular && c->h_flags[4]) {   // bond kernel flags, at least once per run (bond.cu)
@@ -944,6 +983,7 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     if (fl & 4) { b200md_set_error("Bad FENE bond"); return B200MD_ERR; }
   }
   if (n_thermo) *n_thermo = nth;
+  trace_dump(c);
   float ms = 0;
   cudaEventElapsedTime(&ms, TT.spans[0].second.first, TT.spans[0].second.second);
   c->timing.total_ms = ms;

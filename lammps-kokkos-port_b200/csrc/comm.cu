@@ -16,27 +16,7 @@
 // B200MD_HALO=direct (opt-in): the staged borders additionally carry each ghost's owner (rank, index,
 // shift); per-step forward / reverse traffic then goes owner <-> holder directly in ONE NCCL group
 // (a message per peer rank) instead of three dependent stages — see "direct halo" below.
-#include <nccl.h>
-#include <algorithm>
-#include "ctx.h"
-#include "util.cuh"
-
-struct NcclState {
-  ncclComm_t comm = nullptr;
-  int *d_counts = nullptr;  // [4] scratch for count exchange
-  int *h_counts = nullptr;  // pinned [4]
-  double *d_red = nullptr;  // [16] allreduce scratch
-};
-
-#define NCCL_TRY(call)                                                                    \
-  do {                                                                                    \
-    ncclResult_t _r = (call);                                                             \
-    if (_r != ncclSuccess) {                                                              \
-      b200md_set_error(std::string("b200md: NCCL error: ") + ncclGetErrorString(_r) +     \
-                       " at " + __FILE__ + ":" + std::to_string(__LINE__));               \
-      return B200MD_ERR;                                                                  \
-    }                                                                                     \
-  } while (0)
+#include "comm.h"
 
 extern "C" int b200md_comm_unique_id(void *id128) {
   static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
@@ -60,6 +40,7 @@ extern "C" int b200md_comm_init(b200md_ctx *c, const void *id128) {
 }
 
 void comm_free(b200md_ctx *c) {
+  h26_free(c);
   for (auto &s : c->swaps) if (s.sendlist) cudaFree(s.sendlist);
   c->swaps.clear();
   DirectHalo &D = c->direct;
@@ -112,6 +93,11 @@ int comm_setup(b200md_ctx *c) {
     for (int d = 0; d < 3; d++) s.pbc[d] = c->sched.pbc[i][d];
     s.slablo = c->sched.slablo[i]; s.slabhi = c->sched.slabhi[i];
   }
+  // halo mode on several ranks: direct (halo26.cu) when every dimension needs one ghost layer, else the owner-tracking
+  // variant of the staged borders; "staged" keeps the reference's forwarding stages for the per-step traffic too
+  TRY(h26_setup(c, c->halo_mode == 2));
+  c->direct.on = c->nranks > 1 && (c->halo_mode == 1 || (c->halo_mode == 2 && !c->h26.on));
+  c->direct.ready = false;
   return B200MD_OK;
 }
 
@@ -141,12 +127,6 @@ __device__ __forceinline__ int pbc_code_add(int code, int px, int py, int pz) {
 }
 #define PBC_ZERO (8 | (8 << 4) | (8 << 8))
 
-__device__ __forceinline__ double shift_n(double x, int n, double prd) {
-  // x + pbc*prd once per swap like AtomVec::pack_comm/pack_border (atom_vec.cpp:349-378, 794-830)
-  for (; n > 0; n--) x = __dadd_rn(x, prd);
-  for (; n < 0; n++) x = __dsub_rn(x, prd);
-  return x;
-}
 
 // self swap of borders: append ghosts, record flattened source
 __global__ void k_self_border(int n, const int *__restrict__ list, int first, int nlocal, double4 *__restrict__ xq,
@@ -226,15 +206,6 @@ __global__ void k_scalar_pack(int n, const int *__restrict__ list, const double 
   buf[k] = a[list[k]];
 }
 
-static int ensure_buf(double *&p, size_t &cap, size_t need_doubles) {
-  if (need_doubles <= cap) return B200MD_OK;
-  if (p) CUDA_TRY(cudaFree(p));
-  cap = need_doubles + need_doubles / 4 + 1024;
-  CUDA_TRY(cudaMalloc(&p, cap * sizeof(double)));
-  return B200MD_OK;
-}
-
-static inline int nblk(int n) { return (n + 255) / 256; }
 
 // ---------------------------------------------------------------------------------------
 // direct halo (B200MD_HALO=direct)
@@ -520,6 +491,7 @@ static int grow_sendlist(Swap &s, int nsend) {
 }
 
 int comm_borders(b200md_ctx *c) {
+  if (c->h26.on) return h26_borders(c);
   cudaStream_t st = c->stream;
   c->nghost = 0;
   c->all_self = true;
@@ -698,6 +670,7 @@ int comm_forward(b200md_ctx *c) {
     CUDA_TRY(cudaGetLastError());
     return B200MD_OK;
   }
+  if (c->h26.ready) return h26_forward(c, nullptr);
   if (c->direct.ready) return direct_forward<false>(c, nullptr);
   return forward_staged<false>(c, nullptr);
 }
@@ -710,6 +683,7 @@ int comm_forward_scalar(b200md_ctx *c, double *arr) {
     CUDA_TRY(cudaGetLastError());
     return B200MD_OK;
   }
+  if (c->h26.ready) return h26_forward(c, arr);
   if (c->direct.ready) return direct_forward<true>(c, arr);
   return forward_staged<true>(c, arr);
 }
@@ -767,6 +741,7 @@ __global__ void k_exch_unpack(const double *__restrict__ buf, int n, const int *
 int comm_exchange(b200md_ctx *c) {
   c->nghost = 0;  // ghosts are discarded (comm_brick.cpp:672-676)
   if (c->nranks == 1) return B200MD_OK;
+  if (c->h26.on) return h26_exchange(c);
   cudaStream_t st = c->stream;
   NcclState *nc = c->nccl;
   if (!nc) { b200md_set_error("b200md: comm not initialised (b200md_comm_init)"); return B200MD_ERR; }
@@ -922,6 +897,7 @@ int comm_reverse_force(b200md_ctx *c) {
     CUDA_TRY(cudaGetLastError());
     return B200MD_OK;
   }
+  if (c->h26.ready) return h26_reverse3(c, c->f);
   if (c->direct.ready) return direct_reverse<3>(c, c->f);
   return reverse_staged<3>(c, c->f);
 }
@@ -938,6 +914,7 @@ int comm_reverse_column(b200md_ctx *c, double *arr) {
     CUDA_TRY(cudaGetLastError());
     return B200MD_OK;
   }
+  if (c->h26.ready) return h26_reverse1(c, arr);
   if (c->direct.ready) return direct_reverse<1>(c, arr);
   return reverse_staged<1>(c, arr);
 }

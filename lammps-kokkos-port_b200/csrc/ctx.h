@@ -119,6 +119,46 @@ struct DirectHalo {
   int *h_cnt = nullptr;       // pinned, same layout
 };
 
+// "direct" halo on several ranks (comm.cu, option halo=direct, the default): every owned atom is classified ONCE per
+// rebuild by the up to 26 directions (dx,dy,dz) it has to appear in as a ghost, and by the one direction it migrates
+// in; a direction maps to one peer rank and one periodic shift.  Owner and holder then talk directly: one message per
+// peer rank per exchange, no forwarding stages, no owner bookkeeping, no all-gather.  Rebuild-time messages have a
+// capacity both sides derive from the previous rebuild's counts and carry their true counts in a header, so a
+// rebuild costs one NCCL group + one host sync for the migration and one + one for the ghosts.
+#define H26_NDIR 27
+#define H26_HDR 32   // ints per message header
+struct Halo26 {
+  bool on = false, ready = false;
+  int peer[H26_NDIR];           // rank a copy sent in direction d lands on; -1 = direction unused
+  int shift[H26_NDIR][3];       // periodic shift multiples applied by the sender
+  int npeers = 0;               // distinct REMOTE peers
+  std::vector<int> peers;       // ascending rank
+  std::vector<std::vector<int>> dirs_to, dirs_from;   // per remote peer: directions I send in / receive in, ascending
+  std::vector<int> dirs_self;   // directions that land on this rank (a dimension with one rank)
+  int cap_b[H26_NDIR], cap_m[H26_NDIR];     // capacities (atoms) of my outgoing border / migrant segments
+  int capin_b[H26_NDIR], capin_m[H26_NDIR]; // ... of the incoming ones (= the sender's cap for that direction)
+  int prev_b[H26_NDIR], prevb_in[H26_NDIR]; // counts of the previous rebuild (what the next capacities derive from)
+  bool have_prev = false;
+  int *d_cnt = nullptr;         // device [64]: border counters [0,27), migrant counters [32,59)
+  int *h_cnt = nullptr;         // pinned [64]
+  int *d_hdr_send = nullptr, *d_hdr_recv = nullptr;   // device [npeers][H26_HDR]
+  int *h_hdr = nullptr;         // pinned [npeers][H26_HDR]
+  int *list = nullptr;          // device: border candidates of direction d at [lo_b[d], lo_b[d] + cap_b[d])
+  int list_cap = 0;
+  int lo_b[H26_NDIR + 1];
+  int *dead = nullptr;          // device [nmax]: 1 = atom left this rank (dropped by the next sort)
+  int dead_cap = 0;
+  int *send_idx = nullptr;      // device [nsend]: owned atom of every outgoing ghost copy, remote peers first (by peer,
+  int *send_dir = nullptr;      //   direction), then the copies that stay on this rank; its direction
+  int send_cap = 0;
+  int nsend = 0, nsend_remote = 0, nghost_remote = 0;
+  std::vector<int> send_off, send_cnt, recv_off, recv_cnt;   // per remote peer, in atoms (per-step message sizes)
+  char *sbuf = nullptr, *rbuf = nullptr;   // rebuild-time message regions
+  size_t sbuf_cap = 0, rbuf_cap = 0;
+  int ndead = 0;                // leavers of the last exchange, not yet dropped
+  long long nredo = 0;          // rebuilds that had to repeat an exchange because a capacity was exceeded
+};
+
 struct b200md_ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
@@ -189,6 +229,8 @@ struct b200md_ctx {
   bool fuse_nve = true;   // option fuse_nve: final_integrate(n) + initial_integrate(n+1) in one pass (nve.cu), bit-identical
   bool eam_smem = false;  // option eam_smem: one-element EAM tables staged in shared memory (measured slower on B200)
   bool phase_timing = false;  // option phase_timing: per-phase CUDA events in b200md_run
+  bool trace = false;         // option trace: timestamps of both streams' milestones of every step, printed to stderr after b200md_run
+  std::vector<std::pair<std::string, cudaEvent_t>> trace_ev;
   // comm
   b200md_swap_schedule sched;
   std::vector<Swap> swaps;
@@ -197,6 +239,8 @@ struct b200md_ctx {
   int *ghost_pbc = nullptr;       // packed periodic-shift multiples (px+8)|(py+8)<<4|(pz+8)<<8
   int *ghost_rank = nullptr;      // owner rank per ghost (direct halo)
   DirectHalo direct;
+  Halo26 h26;
+  int halo_mode = 2;              // option halo: 0 staged, 1 owner (staged borders that track owners), 2 direct (halo26.cu)
   bool all_self = true;           // every swap partner is this rank -> flattened forward path
   double *sendbuf = nullptr, *recvbuf = nullptr;
   size_t sendcap = 0, recvcap = 0;

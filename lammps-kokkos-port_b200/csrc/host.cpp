@@ -123,6 +123,40 @@ extern "C" int b200md_comm_schedule(const double boxlo[3], const double boxhi[3]
   return B200MD_OK;
 }
 
+// Direct halo (halo26.cu): the 26 directions (dx,dy,dz), index (dx+1) + 3(dy+1) + 9(dz+1), an owned atom can be a
+// ghost in / migrate in.  For each: the rank a copy sent that way lands on (-1: no neighbour there, a non-periodic
+// edge), the periodic shift multiples the sender applies (CommBrick::setup pbc flags, comm_brick.cpp:432-470), and
+// per dimension the send slab bounds of the first swap (x <= slabhi_left sends left, x >= slablo_right sends right,
+// comm_brick.cpp:407-428, 838).  usable = 0 when a dimension needs more than one ghost layer (maxneed > 1).
+extern "C" int b200md_halo_directions(const double boxlo[3], const double boxhi[3], const int periodic[3],
+                                      const int procgrid[3], const int myloc[3], double cutghost, int peer[27],
+                                      int shift[27][3], double slabhi_left[3], double slablo_right[3], int *usable) {
+  b200md_swap_schedule sch;
+  if (b200md_comm_schedule(boxlo, boxhi, periodic, procgrid, myloc, cutghost, &sch)) return B200MD_ERR;
+  *usable = (sch.maxneed[0] == 1 && sch.maxneed[1] == 1 && sch.maxneed[2] == 1) ? 1 : 0;
+  for (int d = 0; d < 27; d++) { peer[d] = -1; shift[d][0] = shift[d][1] = shift[d][2] = 0; }
+  if (!*usable) return B200MD_OK;
+  for (int k = 0; k < 3; k++) { slabhi_left[k] = sch.slabhi[2 * k]; slablo_right[k] = sch.slablo[2 * k + 1]; }
+  for (int d = 0; d < 27; d++) {
+    if (d == 13) continue;
+    const int comp[3] = {d % 3 - 1, (d / 3) % 3 - 1, d / 9 - 1};
+    int loc[3] = {myloc[0], myloc[1], myloc[2]};
+    bool ok = true;
+    for (int k = 0; k < 3 && ok; k++) {
+      if (!comp[k]) continue;
+      const int sw = 2 * k + (comp[k] < 0 ? 0 : 1);   // maxneed == 1: swap 2k sends left, 2k+1 right
+      if (!sch.sendflag[sw]) { ok = false; break; }
+      loc[k] += comp[k];
+      if (loc[k] < 0) loc[k] = procgrid[k] - 1;
+      if (loc[k] >= procgrid[k]) loc[k] = 0;
+      shift[d][k] = sch.pbc[sw][k];
+    }
+    if (ok) peer[d] = loc2rank(loc, procgrid);
+    else shift[d][0] = shift[d][1] = shift[d][2] = 0;
+  }
+  return B200MD_OK;
+}
+
 extern "C" int b200md_bin_setup(const double boxlo[3], const double boxhi[3], const double sublo[3],
                                 const double subhi[3], double cutghost, double cutneighmax,
                                 b200md_bin_geometry *g) {

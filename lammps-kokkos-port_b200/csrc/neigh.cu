@@ -310,12 +310,13 @@ int neigh_pbc(b200md_ctx *c) {
 }
 
 __global__ void k_bin_count(const double4 *__restrict__ xq, int n, BinParams p, int *__restrict__ atom_bin,
-                            int *__restrict__ cell_count, int *flags) {
+                            int *__restrict__ cell_count, int *flags, const int *__restrict__ dead, int dead_bin) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   bool ok;
   int b = coord2bin(xq[i], p, ok);
-  if (!ok) { flags[2] = 1; b = 0; }
+  if (dead && dead[i]) b = dead_bin;   // migrated away (halo26.cu): parked behind the last bin, dropped by the permutation
+  else if (!ok) { flags[2] = 1; b = 0; }
   atom_bin[i] = b;
   atomicAdd(&cell_count[b], 1);
 }
@@ -327,29 +328,49 @@ __global__ void k_bin_scatter(const int *__restrict__ atom_bin, int n, const int
   int pos = cell_start[b] + atomicAdd(&cell_fill[b], 1);
   cell_atoms[pos] = i;
 }
-// make the within-cell order deterministic: ascending atom index = the order of the
-// reference's linked lists (nbin_standard.cpp:252-257: owned ascending, ghosts last)
-__global__ void k_cell_sort(const int *__restrict__ cell_start, int *__restrict__ cell_atoms, int mbins) {
+// make the within-cell order deterministic.  BYTAG = false: ascending atom index = the order of the reference's
+// linked lists (nbin_standard.cpp:252-257: owned ascending, ghosts last).  BYTAG = true (direct halo on several
+// ranks, where arrivals and ghosts are placed through atomic slot counters): owned atoms by tag, then ghosts by
+// (tag, z, y, x) — independent of the order the messages were filled in, and of the decomposition.
+template <bool BYTAG>
+__device__ __forceinline__ bool cell_before(int a, int b, int nlocal, const int *__restrict__ tag, const double4 *__restrict__ xq) {
+  if (!BYTAG) return a < b;
+  const bool ga = a >= nlocal, gb = b >= nlocal;
+  if (ga != gb) return gb;
+  const int ta = tag[a], tb = tag[b];
+  if (ta != tb) return ta < tb;
+  if (!ga) return a < b;
+  const double4 qa = xq[a], qb = xq[b];
+  if (qa.z != qb.z) return qa.z < qb.z;
+  if (qa.y != qb.y) return qa.y < qb.y;
+  return qa.x < qb.x;
+}
+template <bool BYTAG>
+__global__ void k_cell_sort(const int *__restrict__ cell_start, int *__restrict__ cell_atoms, int mbins, int nlocal,
+                            const int *__restrict__ tag, const double4 *__restrict__ xq) {
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= mbins) return;
   int s = cell_start[b], e = cell_start[b + 1];
   for (int a = s + 1; a < e; a++) {
     int key = cell_atoms[a], k = a - 1;
-    while (k >= s && cell_atoms[k] > key) { cell_atoms[k + 1] = cell_atoms[k]; k--; }
+    while (k >= s && cell_before<BYTAG>(key, cell_atoms[k], nlocal, tag, xq)) { cell_atoms[k + 1] = cell_atoms[k]; k--; }
     cell_atoms[k + 1] = key;
   }
 }
 
-static int bin_range(b200md_ctx *c, int n) {
-  // counting sort of atoms [0,n) into cells; leaves atom_bin, cell_start[0..mbins], cell_atoms
+// counting sort of atoms [0,n) into cells; leaves atom_bin, cell_start[0..mbins(+1)], cell_atoms.  nown: atoms below
+// it are owned (in-cell order key).  dead != nullptr: flagged atoms go to an extra bin behind the last one.
+static int bin_range(b200md_ctx *c, int n, int nown, const int *dead) {
   cudaStream_t s = c->stream;
-  CUDA_TRY(cudaMemsetAsync(c->cell_count, 0, sizeof(int) * (c->mbins + 1), s));
-  CUDA_TRY(cudaMemsetAsync(c->cell_fill, 0, sizeof(int) * (c->mbins + 1), s));
+  const int nb = c->mbins + (dead ? 1 : 0);
+  CUDA_TRY(cudaMemsetAsync(c->cell_count, 0, sizeof(int) * (nb + 1), s));
+  CUDA_TRY(cudaMemsetAsync(c->cell_fill, 0, sizeof(int) * (nb + 1), s));
   BinParams p = make_bin_params(c);
-  if (n > 0) k_bin_count<<<(n + 255) / 256, 256, 0, s>>>(c->xq, n, p, c->atom_bin, c->cell_count, c->d_flags);
-  TRY(dev_exclusive_scan(c, c->cell_count, c->cell_start, c->mbins + 1));
+  if (n > 0) k_bin_count<<<(n + 255) / 256, 256, 0, s>>>(c->xq, n, p, c->atom_bin, c->cell_count, c->d_flags, dead, c->mbins);
+  TRY(dev_exclusive_scan(c, c->cell_count, c->cell_start, nb + 1));
   if (n > 0) k_bin_scatter<<<(n + 255) / 256, 256, 0, s>>>(c->atom_bin, n, c->cell_start, c->cell_fill, c->cell_atoms);
-  k_cell_sort<<<(c->mbins + 255) / 256, 256, 0, s>>>(c->cell_start, c->cell_atoms, c->mbins);
+  if (c->h26.on) k_cell_sort<true><<<(c->mbins + 255) / 256, 256, 0, s>>>(c->cell_start, c->cell_atoms, c->mbins, nown, c->tag, c->xq);
+  else k_cell_sort<false><<<(c->mbins + 255) / 256, 256, 0, s>>>(c->cell_start, c->cell_atoms, c->mbins, nown, c->tag, c->xq);
   c->launches += 3;
   CUDA_TRY(cudaGetLastError());
   return B200MD_OK;
@@ -371,8 +392,13 @@ __global__ void k_permute_owned(int n, int nmax, const int *__restrict__ perm, c
 }
 
 int neigh_sort_owned(b200md_ctx *c) {
-  const int n = c->nlocal;
-  TRY(bin_range(c, n));
+  // after a migration of the direct halo c->nlocal still counts the atoms that left: they are flagged dead, sorted
+  // behind the last bin and dropped here
+  const bool drop = c->h26.on && c->h26.dead;
+  const int ntot = c->nlocal;
+  TRY(bin_range(c, ntot, ntot, drop ? c->h26.dead : nullptr));
+  const int n = drop ? ntot - c->h26.ndead : ntot;
+  if (drop) { c->nlocal = n; c->h26.ndead = 0; }
   if (n == 0) return B200MD_OK;
   k_permute_owned<<<(n + 255) / 256, 256, 0, c->stream>>>(n, c->nmax, c->cell_atoms, c->xq, c->xq_tmp, c->v,
                                                          c->v_tmp, c->tag, c->tag_tmp, c->image, c->image_tmp);
@@ -394,7 +420,7 @@ __global__ void k_gather_cell_xq(int n, const int *__restrict__ cell_atoms, cons
 
 int neigh_bin_all(b200md_ctx *c) {
   const int n = c->nlocal + c->nghost;
-  TRY(bin_range(c, n));
+  TRY(bin_range(c, n, c->nlocal, nullptr));
   if (n > 0) {
     k_gather_cell_xq<<<(n + 255) / 256, 256, 0, c->stream>>>(n, c->cell_atoms, c->xq, c->cell_xq);
     c->launches++;

@@ -26,6 +26,7 @@ ap.add_argument("--list", default="half", choices=["half", "full"])
 ap.add_argument("--lanes", type=int, default=0)
 ap.add_argument("--langevin", action="store_true")
 ap.add_argument("--phases", action="store_true")
+ap.add_argument("--trace", type=int, default=0, help="after the run: N more steps with both streams' milestones printed (option trace)")
 ap.add_argument("--option", action="append", default=[])
 a = ap.parse_args()
 P = b200pkg.load(); B = P.b200md
@@ -75,6 +76,9 @@ if rank == 0:
     print("%s %s list, %d atoms on %d GPU(s): %.4f ms/step, %.1f Matom-steps/s, %d rebuilds, %d launches | step 0 T %.8g PE %.10g P %.8g | step %d T %.8g PE %.10g P %.8g"
           % (a.workload, a.list, n, world, ms / a.steps, n * a.steps / ms / 1e3, tm["nbuilds"], tm["launches"], t0["temp"], t0["pe"], t0["press"],
              th["step"], th["temp"], th["pe"], th["press"]), flush=True)
+if a.trace:
+    ctx.set_option("trace", "on")
+    ctx.run(a.trace + 1, cfg["dt"], 0)
 ctx.close()
 if dist is not None:
     dist.destroy_process_group()
