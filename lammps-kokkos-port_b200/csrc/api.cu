@@ -61,12 +61,14 @@ extern "C" int b200md_create(int device, int rank, int nranks, b200md_ctx **out)
     int lo = 0, hi = 0;
     CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CUDA_TRY(cudaStreamCreateWithPriority(&c->comm_stream, cudaStreamNonBlocking, hi));
+    CUDA_TRY(cudaStreamCreateWithPriority(&c->bnd_stream, cudaStreamNonBlocking, hi));   // boundary tiles: ahead of the interior kernel
   }
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_x, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_fp, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_fphalo, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_bnd, cudaEventDisableTiming));
+  CUDA_TRY(cudaEventCreateWithFlags(&c->ev_clr, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rev, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rb, cudaEventDisableTiming));
   CUDA_TRY(cudaEventCreateWithFlags(&c->ev_rr, cudaEventDisableTiming));
@@ -102,9 +104,10 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
   if (c->h_result) cudaFreeHost(c->h_result);
   if (c->h_flags) cudaFreeHost(c->h_flags);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
-  cudaEvent_t evs[] = {c->ev_x, c->ev_halo, c->ev_fp, c->ev_fphalo, c->ev_bnd, c->ev_rev, c->ev_rb, c->ev_rr};
+  cudaEvent_t evs[] = {c->ev_x, c->ev_halo, c->ev_fp, c->ev_fphalo, c->ev_bnd, c->ev_rev, c->ev_rb, c->ev_rr, c->ev_clr};
   for (auto e : evs) if (e) cudaEventDestroy(e);
   if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
+  if (c->bnd_stream) cudaStreamDestroy(c->bnd_stream);
   cudaStreamDestroy(c->stream);
   delete c;
   return B200MD_OK;
@@ -825,66 +828,29 @@ static int on_comm_stream(b200md_ctx *c, int (*fn)(b200md_ctx *)) {
   c->stream = saved;
   return r;
 }
-// Half/newton list with compute/halo overlap.  Interior tiles (no ghost neighbor) are split in two
-// parts: part 1 runs while the forward halo is in flight, then the boundary tiles, then part 2 runs
-// while the ghost contributions travel back (reverse_comm on the comm stream, RED into f / rho).
-static int forces_overlapped_half(b200md_ctx *c) {
-  cudaStream_t s = c->stream, cs = c->comm_stream;
-  const int nall = c->nlocal + c->nghost;
-  const int n1 = (int)(c->n_tiles_int * c->split), n2 = c->n_tiles_int - n1;
-  const int *int1 = c->tiles_int, *int2 = c->tiles_int + n1;
-  const bool eam = c->pair_style == B200MD_PAIR_EAM;
-  for (int d = 0; d < 3; d++) CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax, 0, sizeof(double) * nall, s));
-  if (eam) CUDA_TRY(cudaMemsetAsync(c->rho, 0, sizeof(double) * nall, s));
-  trace_mark(c, "main: f cleared", s);
-  if (!eam) {
-    TRY(pair_lj_launch(c, false, int1, n1));
-    trace_mark(c, "main: lj interior part 1 done", s);
-    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
-    TRY(pair_lj_launch(c, false, c->tiles_bnd, c->n_tiles_bnd));
-    trace_mark(c, "main: lj boundary tiles done", s);
-  } else {
-    TRY(pair_eam_launch(c, false, 2, int1, n1));
-    trace_mark(c, "main: rho interior part 1 done", s);
-    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
-    TRY(pair_eam_launch(c, false, 2, c->tiles_bnd, c->n_tiles_bnd));
-    trace_mark(c, "main: rho boundary done", s);
-    CUDA_TRY(cudaEventRecord(c->ev_rb, s));              // ghost rho complete
-    CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_rb, 0));
-    TRY(on_comm_stream(c, comm_reverse_rho));
-    trace_mark(c, "comm: rho reverse done", cs);
-    CUDA_TRY(cudaEventRecord(c->ev_rr, cs));
-    TRY(pair_eam_launch(c, false, 2, int2, n2));
-    trace_mark(c, "main: rho interior part 2 done", s);
-    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_rr, 0));
-    TRY(pair_eam_embed(c, false, nullptr));
-    trace_mark(c, "main: embed done", s);
-    CUDA_TRY(cudaEventRecord(c->ev_fp, s));
-    CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_fp, 0));
-    TRY(on_comm_stream(c, pair_eam_fp_comm));
-    trace_mark(c, "comm: fp forward done", cs);
-    CUDA_TRY(cudaEventRecord(c->ev_fphalo, cs));
-    TRY(pair_eam_launch(c, false, 3, int1, n1));
-    trace_mark(c, "main: force interior part 1 done", s);
-    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_fphalo, 0));
-    TRY(pair_eam_launch(c, false, 3, c->tiles_bnd, c->n_tiles_bnd));
-    trace_mark(c, "main: force boundary done", s);
-  }
-  CUDA_TRY(cudaEventRecord(c->ev_bnd, s));               // ghost forces complete
-  CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_bnd, 0));
-  TRY(on_comm_stream(c, comm_reverse_force));
-  trace_mark(c, "comm: f reverse done", cs);
-  CUDA_TRY(cudaEventRecord(c->ev_rev, cs));
-  if (!eam) TRY(pair_lj_launch(c, false, int2, n2));
-  else TRY(pair_eam_launch(c, false, 3, int2, n2));
-  trace_mark(c, "main: interior part 2 done", s);
-  CUDA_TRY(cudaStreamWaitEvent(s, c->ev_rev, 0));
-  return B200MD_OK;
+// Compute / halo overlap on several ranks (non-rebuild, non-tally steps).  Tiles whose atoms have no ghost neighbour
+// ("interior", ~85-90 % at 2 M atoms per GPU) are ONE launch on the main stream.  The boundary tiles are a second
+// launch on a high-priority stream that waits for the forward halo: their blocks are dispatched ahead of the interior
+// kernel's remaining blocks as soon as the ghosts have landed, so the reverse pass (comm stream, FP64 RED into f / rho)
+// is in flight while most of the interior work is still running, and neither kernel leaves a tail of idle SMs for
+// the other to wait behind.  Same kernels, same per-atom arithmetic as the unsplit launch.
+static int on_stream(b200md_ctx *c, cudaStream_t st, int (*fn)(b200md_ctx *, bool, int, const int *, int), bool ev, int pass,
+                     const int *tiles, int ntl) {
+  cudaStream_t saved = c->stream;
+  c->stream = st;
+  int r = fn(c, ev, pass, tiles, ntl);
+  c->stream = saved;
+  return r;
 }
+static int lj_pass(b200md_ctx *c, bool ev, int, const int *tiles, int ntl) { return pair_lj_launch(c, ev, tiles, ntl); }
 
 // non-rebuild, non-tally step on several ranks; on return f is complete (reverse_comm included)
 static int forces_overlapped(b200md_ctx *c) {
-  cudaStream_t s = c->stream, cs = c->comm_stream;
+  cudaStream_t s = c->stream, cs = c->comm_stream, bs = c->bnd_stream;
+  const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON, eam = c->pair_style == B200MD_PAIR_EAM;
+  const int nall = c->nlocal + c->nghost;
+  const int *ti = c->tiles_int, *tb = c->tiles_bnd;
+  const int ni = c->n_tiles_int, nb = c->n_tiles_bnd;
   trace_mark(c, "main: step start (x integrated)", s);
   CUDA_TRY(cudaEventRecord(c->ev_x, s));               // positions integrated
   CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_x, 0));
@@ -892,23 +858,55 @@ static int forces_overlapped(b200md_ctx *c) {
   trace_mark(c, "comm: x forward done", cs);
   CUDA_TRY(cudaEventRecord(c->ev_halo, cs));
   c->ev_valid = false;
-  if (c->list_kind == B200MD_LIST_HALF_NEWTON) return forces_overlapped_half(c);
-  if (c->pair_style == B200MD_PAIR_LJ_CUT) {
-    TRY(pair_lj_launch(c, false, c->tiles_int, c->n_tiles_int));
-    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
-    TRY(pair_lj_launch(c, false, c->tiles_bnd, c->n_tiles_bnd));
-  } else {
-    TRY(pair_eam_launch(c, false, 0, c->tiles_int, c->n_tiles_int));
-    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_halo, 0));
-    TRY(pair_eam_launch(c, false, 0, c->tiles_bnd, c->n_tiles_bnd));
-    CUDA_TRY(cudaEventRecord(c->ev_fp, s));            // fp of every owned atom is final
-    CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_fp, 0));
-    TRY(on_comm_stream(c, pair_eam_fp_comm));          // fp halo on the comm stream
-    CUDA_TRY(cudaEventRecord(c->ev_fphalo, cs));
-    TRY(pair_eam_launch(c, false, 1, c->tiles_int, c->n_tiles_int));
-    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_fphalo, 0));
-    TRY(pair_eam_launch(c, false, 1, c->tiles_bnd, c->n_tiles_bnd));
+  if (half) {   // Verlet::force_clear over owned + ghost rows
+    for (int d = 0; d < 3; d++) CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax, 0, sizeof(double) * nall, s));
+    if (eam) CUDA_TRY(cudaMemsetAsync(c->rho, 0, sizeof(double) * nall, s));
   }
+  CUDA_TRY(cudaEventRecord(c->ev_clr, s));
+  CUDA_TRY(cudaStreamWaitEvent(bs, c->ev_clr, 0));
+  CUDA_TRY(cudaStreamWaitEvent(bs, c->ev_halo, 0));
+  if (!eam) {
+    TRY(lj_pass(c, false, 0, ti, ni));
+    trace_mark(c, "main: lj interior done", s);
+    TRY(on_stream(c, bs, lj_pass, false, 0, tb, nb));
+    trace_mark(c, "bnd : lj boundary done", bs);
+  } else {
+    // pass 1 (density).  half: rho of both atoms of a pair, ghost rho returned, then the embedding; full: rho + fp fused
+    const int p1 = half ? 2 : 0, p3 = half ? 3 : 1;
+    TRY(pair_eam_launch(c, false, p1, ti, ni));
+    trace_mark(c, "main: rho interior done", s);
+    TRY(on_stream(c, bs, pair_eam_launch, false, p1, tb, nb));
+    trace_mark(c, "bnd : rho boundary done", bs);
+    CUDA_TRY(cudaEventRecord(c->ev_rb, bs));
+    if (half) {
+      CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_rb, 0));
+      TRY(on_comm_stream(c, comm_reverse_rho));
+      trace_mark(c, "comm: rho reverse done", cs);
+      CUDA_TRY(cudaEventRecord(c->ev_rr, cs));
+      CUDA_TRY(cudaStreamWaitEvent(s, c->ev_rr, 0));
+    }
+    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_rb, 0));
+    if (half) { TRY(pair_eam_embed(c, false, nullptr)); trace_mark(c, "main: embed done", s); }
+    CUDA_TRY(cudaEventRecord(c->ev_fp, s));              // fp of every owned atom is final
+    CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_fp, 0));
+    TRY(on_comm_stream(c, pair_eam_fp_comm));            // fp halo on the comm stream
+    trace_mark(c, "comm: fp forward done", cs);
+    CUDA_TRY(cudaEventRecord(c->ev_fphalo, cs));
+    TRY(pair_eam_launch(c, false, p3, ti, ni));
+    trace_mark(c, "main: force interior done", s);
+    CUDA_TRY(cudaStreamWaitEvent(bs, c->ev_fphalo, 0));
+    TRY(on_stream(c, bs, pair_eam_launch, false, p3, tb, nb));
+    trace_mark(c, "bnd : force boundary done", bs);
+  }
+  CUDA_TRY(cudaEventRecord(c->ev_bnd, bs));              // boundary tiles done: ghost rows of f complete
+  if (half) {
+    CUDA_TRY(cudaStreamWaitEvent(cs, c->ev_bnd, 0));
+    TRY(on_comm_stream(c, comm_reverse_force));
+    trace_mark(c, "comm: f reverse done", cs);
+    CUDA_TRY(cudaEventRecord(c->ev_rev, cs));
+    CUDA_TRY(cudaStreamWaitEvent(s, c->ev_rev, 0));
+  }
+  CUDA_TRY(cudaStreamWaitEvent(s, c->ev_bnd, 0));
   return B200MD_OK;
 }
 

@@ -221,9 +221,9 @@ struct b200md_ctx {
   // tiles (warps) split by 'has a ghost neighbor' for compute/halo overlap
   int *tile_ghost = nullptr, *tile_pos = nullptr, *tiles_int = nullptr, *tiles_bnd = nullptr;
   int tile_cap = 0, n_tiles_int = 0, n_tiles_bnd = 0;
-  cudaStream_t comm_stream = nullptr;
+  cudaStream_t comm_stream = nullptr, bnd_stream = nullptr;
   cudaEvent_t ev_x = nullptr, ev_halo = nullptr, ev_fp = nullptr, ev_fphalo = nullptr;
-  cudaEvent_t ev_bnd = nullptr, ev_rev = nullptr, ev_rb = nullptr, ev_rr = nullptr;  // half-list overlap
+  cudaEvent_t ev_bnd = nullptr, ev_rev = nullptr, ev_rb = nullptr, ev_rr = nullptr, ev_clr = nullptr;  // half-list overlap
   double split = 0.5;  // share of the interior tiles evaluated before the boundary tiles (half-list overlap)
   bool overlap = true;
   bool fuse_nve = true;   // option fuse_nve: final_integrate(n) + initial_integrate(n+1) in one pass (nve.cu), bit-identical
