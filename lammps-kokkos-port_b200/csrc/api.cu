@@ -90,6 +90,10 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
   if (!c) return B200MD_OK;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  if (c->sg.exec) cudaGraphExecDestroy(c->sg.exec);
+  if (c->sg.graph) cudaGraphDestroy(c->sg.graph);
+  if (c->sg.d_loop) cudaFree(c->sg.d_loop);
+  if (c->sg.h_loop) cudaFreeHost(c->sg.h_loop);
   comm_free(c);
   pair_eam_free(c);
   topo_free(c);
@@ -548,6 +552,12 @@ extern "C" int b200md_set_option(b200md_ctx *c, const char *key, const char *val
       NEED(opt_bool(value, &b), "Illegal package b200 command: cluster must be on, off or auto");
       c->use_cluster = b ? 1 : 0;
     }
+  } else if (k == "graph") {
+    if (!strcmp(value, "auto")) c->sg.mode = -1;
+    else {
+      NEED(opt_bool(value, &b), "Illegal package b200 command: graph must be on, off or auto");
+      c->sg.mode = b ? 1 : 0;
+    }
   } else if (k == "trace") {
     NEED(opt_bool(value, &b), "Illegal package b200 command: trace must be on or off");
     c->trace = b;
@@ -576,6 +586,7 @@ extern "C" int b200md_get_option(b200md_ctx *c, const char *key, char *value, in
   else if (k == "split") v = std::to_string(c->split);
   else if (k == "fuse_nve") v = c->fuse_nve ? "on" : "off";
   else if (k == "eam_smem") v = c->eam_smem ? "on" : "off";
+  else if (k == "graph") v = c->sg.mode < 0 ? "auto" : (c->sg.mode ? "on" : "off");
   else if (k == "cluster") v = c->use_cluster < 0 ? "auto" : (c->use_cluster ? "on" : "off");
   else if (k == "phase_timing") v = c->phase_timing ? "on" : "off";
   else if (k == "build_lanes") v = std::to_string(c->tpa_build);
@@ -859,7 +870,7 @@ static int forces_overlapped(b200md_ctx *c) {
   CUDA_TRY(cudaEventRecord(c->ev_halo, cs));
   c->ev_valid = false;
   if (half) {   // Verlet::force_clear over owned + ghost rows
-    for (int d = 0; d < 3; d++) CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax, 0, sizeof(double) * nall, s));
+    CUDA_TRY(cudaMemset2DAsync(c->f, sizeof(double) * (size_t)c->nmax, 0, sizeof(double) * nall, 3, s));   // 3 rows, one launch
     if (eam) CUDA_TRY(cudaMemsetAsync(c->rho, 0, sizeof(double) * nall, s));
   }
   CUDA_TRY(cudaEventRecord(c->ev_clr, s));
@@ -910,6 +921,105 @@ static int forces_overlapped(b200md_ctx *c) {
   return B200MD_OK;
 }
 
+// ---------------------------------------------------------------------------------------
+// option graph: small systems are launch-bound (7-13 launches of a few microseconds per step, and with `check yes` a
+// host round trip for the rebuild decision on every step).  The steps between two list builds run as ONE graph
+// launch: a WHILE conditional node whose body is a complete non-rebuild timestep
+//     forward_comm -> pair -> reverse_comm -> final_integrate(n) + initial_integrate(n+1) with the distance test
+// followed by a one-thread kernel that evaluates Neighbor::decide for step n+1 (src/neighbor.cpp:2309-2324: ago++,
+// ago >= delay && ago % every == 0, then check_distance's flag) and sets the loop condition.  The loop leaves exactly
+// on the step the reference rebuilds on — its first half-kick and drift already applied, like Verlet::run has them
+// when it calls Neighbor::decide — and the host does the rebuild.  Reference counterpart to beat:
+// verlet_kokkos.cpp:287-524 (resident loop, but a host decision per step).
+// ---------------------------------------------------------------------------------------
+__global__ void k_loop_cond(cudaGraphConditionalHandle handle, int *__restrict__ loop, int *__restrict__ flags, int every,
+                            int delay, int check) {
+  const int left = loop[0] - 1, ago = loop[1] + 1;
+  const bool due = ago >= delay && ago % every == 0;
+  const int rebuild = (due && (!check || flags[0])) ? 1 : 0;
+  if (!rebuild) flags[0] = 0;     // the test of a step that is not due does not count (check_distance runs on due steps only)
+  loop[0] = left; loop[1] = ago; loop[2] += 1; loop[3] = rebuild;
+  cudaGraphSetConditional(handle, (left > 0 && !rebuild) ? 1u : 0u);
+}
+
+static void step_graph_free(b200md_ctx *c) {
+  StepGraph &G = c->sg;
+  if (G.exec) cudaGraphExecDestroy(G.exec);
+  if (G.graph) cudaGraphDestroy(G.graph);
+  G.exec = nullptr; G.graph = nullptr; G.built_for = -1;
+}
+
+static bool step_graph_usable(const b200md_ctx *c) {
+  const StepGraph &G = c->sg;
+  if (G.mode == 0 || c->nranks != 1 || c->lang.on || c->topo.molecular || !c->fuse_nve || c->phase_timing || c->trace) return false;
+  if (G.mode < 0) return false;   // auto = off: measured on B200 the 32 000-atom steps are bound by the chain of small dependent
+                                  // kernels on the GPU, not by host launches (in.lj 62 us/step host-driven, 68 us as a graph)
+  return c->nlocal > 0;
+}
+
+static int step_graph_build(b200md_ctx *c, double dtv, double dtf) {
+  StepGraph &G = c->sg;
+  if (G.exec && G.built_for == c->nbuilds && G.dtv == dtv && G.dtf == dtf) return B200MD_OK;
+  step_graph_free(c);
+  if (!G.d_loop) {
+    CUDA_TRY(cudaMalloc(&G.d_loop, 4 * sizeof(int)));
+    CUDA_TRY(cudaMallocHost(&G.h_loop, 4 * sizeof(int)));
+  }
+  CUDA_TRY(cudaGraphCreate(&G.graph, 0));
+  cudaGraphConditionalHandle handle;
+  CUDA_TRY(cudaGraphConditionalHandleCreate(&handle, G.graph, 1, cudaGraphCondAssignDefault));
+  cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
+  np.conditional.handle = handle;
+  np.conditional.type = cudaGraphCondTypeWhile;
+  np.conditional.size = 1;
+  cudaGraphNode_t node;
+  CUDA_TRY(cudaGraphAddNode(&node, G.graph, nullptr, 0, &np));
+  cudaGraph_t body = np.conditional.phGraph_out[0];
+  const long long l0 = c->launches, p0 = c->pair_launches;
+  CUDA_TRY(cudaStreamBeginCaptureToGraph(c->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+  int rc = comm_forward(c);
+  if (rc == B200MD_OK) rc = b200md_pair_compute(c, 0, 0, nullptr, nullptr);
+  if (rc == B200MD_OK) rc = comm_reverse_force(c);
+  if (rc == B200MD_OK) rc = nve_final_initial(c, dtv, dtf, c->check != 0);
+  if (rc == B200MD_OK) k_loop_cond<<<1, 1, 0, c->stream>>>(handle, G.d_loop, c->d_flags, c->every, c->delay, c->check);
+  cudaGraph_t captured = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture(c->stream, &captured);
+  G.launches_per_body = (int)(c->launches - l0) + 1;
+  G.pair_launches_per_body = (int)(c->pair_launches - p0);
+  c->launches = l0; c->pair_launches = p0;
+  if (rc != B200MD_OK) { step_graph_free(c); return rc; }
+  if (ce != cudaSuccess) {
+    step_graph_free(c);
+    b200md_set_error(std::string("b200md: CUDA graph capture failed: ") + cudaGetErrorString(ce));
+    return B200MD_ERR;
+  }
+  CUDA_TRY(cudaGraphInstantiate(&G.exec, G.graph, 0));
+  G.built_for = c->nbuilds; G.dtv = dtv; G.dtf = dtf;
+  return B200MD_OK;
+}
+
+// run up to `nbody` consecutive non-rebuild, non-tally steps; the first one has had its initial_integrate and its
+// Neighbor::decide.  On return: *done steps are complete, the following step is pre-integrated and *rebuild holds its
+// decision (c->ago already counts it).
+static int step_graph_run(b200md_ctx *c, int nbody, double dtv, double dtf, int *done, int *rebuild) {
+  StepGraph &G = c->sg;
+  TRY(step_graph_build(c, dtv, dtf));
+  G.h_loop[0] = nbody; G.h_loop[1] = c->ago; G.h_loop[2] = 0; G.h_loop[3] = 0;
+  CUDA_TRY(cudaMemcpyAsync(G.d_loop, G.h_loop, 4 * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  CUDA_TRY(cudaGraphLaunch(G.exec, c->stream));
+  CUDA_TRY(cudaMemcpyAsync(G.h_loop, G.d_loop, 4 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CUDA_TRY(cudaStreamSynchronize(c->stream));
+  *done = G.h_loop[2];
+  *rebuild = G.h_loop[3];
+  c->ago = G.h_loop[1];
+  c->ev_valid = false;
+  c->launches += (long long)*done * G.launches_per_body;
+  c->pair_launches += (long long)*done * G.pair_launches_per_body;
+  G.nlaunch++; G.nsteps += *done;
+  if (*rebuild && c->check && c->ago == (c->every > c->delay ? c->every : c->delay)) c->ndanger++;
+  return B200MD_OK;
+}
+
 struct PhaseTimer {
   b200md_ctx *c; bool on; size_t *used; std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> spans;
   cudaEvent_t get() {
@@ -936,7 +1046,8 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     TRY(langevin_set_dt(c, dt));   // FixLangevin::reset_dt
     if (!LG.window) { LG.begin = first; LG.end = last; LG.now = first; }
   }
-  bool initial_done = false;
+  bool initial_done = false, predecided = false;
+  int pre_flag = 0;
   TT.begin(0);
   for (int i = 0; i < nsteps; i++) {
     c->step++;
@@ -947,7 +1058,24 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     if (initial_done) initial_done = false;   // this step's first half-kick + drift ran fused with the previous step's second one
     else { T.begin(4); TRY(b200md_nve_initial(c, dtv, dtf)); T.end(); }
     int nflag = 0;
-    TRY(b200md_neigh_decide(c, &nflag));
+    if (predecided) { nflag = pre_flag; predecided = false; }   // Neighbor::decide of this step ran on the device (option graph)
+    else TRY(b200md_neigh_decide(c, &nflag));
+    if (!nflag && !ev && i + 1 < nsteps && step_graph_usable(c)) {
+      // steps i .. i+m-1 are non-output steps that have a successor in this run: one graph launch
+      int m = 0;
+      for (int j = i; j + 1 < nsteps; j++) {
+        const long long stepj = first + j + 1;
+        if ((thermo_every > 0 && (stepj - first) % thermo_every == 0) || stepj == last) break;
+        m++;
+      }
+      int done = 0;
+      TRY(step_graph_run(c, m, dtv, dtf, &done, &pre_flag));
+      c->step += done - 1;
+      i += done - 1;
+      initial_done = true;
+      predecided = true;
+      continue;
+    }
     if (!nflag && !ev && can_overlap(c)) {
       T.begin(1); TRY(forces_overlapped(c)); T.end();   // includes reverse_comm on half lists
     } else {

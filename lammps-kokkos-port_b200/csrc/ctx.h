@@ -159,6 +159,19 @@ struct Halo26 {
   long long nredo = 0;          // rebuilds that had to repeat an exchange because a capacity was exceeded
 };
 
+// option graph (api.cu): the non-rebuild steps between two neighbor-list builds replayed as ONE CUDA graph launch — a
+// WHILE conditional node whose body is a whole timestep and whose condition is Neighbor::decide evaluated on the device
+struct StepGraph {
+  int mode = -1;                 // -1 auto (one rank, small systems), 0 off, 1 on
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  long long built_for = -1;      // c->nbuilds the body was captured for (its kernel arguments change with every list)
+  double dtv = 0, dtf = 0;
+  int launches_per_body = 0, pair_launches_per_body = 0;
+  int *d_loop = nullptr, *h_loop = nullptr;   // [0] bodies left, [1] ago, [2] bodies done, [3] rebuild decided for the next step
+  long long nlaunch = 0, nsteps = 0;
+};
+
 struct b200md_ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
@@ -240,6 +253,7 @@ struct b200md_ctx {
   int *ghost_rank = nullptr;      // owner rank per ghost (direct halo)
   DirectHalo direct;
   Halo26 h26;
+  StepGraph sg;
   int halo_mode = 2;              // option halo: 0 staged, 1 owner (staged borders that track owners), 2 direct (halo26.cu)
   bool all_self = true;           // every swap partner is this rank -> flattened forward path
   double *sendbuf = nullptr, *recvbuf = nullptr;

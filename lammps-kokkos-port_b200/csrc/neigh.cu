@@ -687,6 +687,114 @@ k_build_cluster(int nlocal, int ncl, const double4 *__restrict__ xq, const int *
   if (tile_ghost && has_ghost) tile_ghost[c / C] = 1;
 }
 
+// Small systems: the same cluster build with T lanes per cluster (one thread per cluster leaves most SMs empty below
+// ~10^5 atoms and walks ~200 candidates serially).  The T lanes stride over each candidate range; kept entries are
+// compacted with a ballot over the group's lanes, so the entry order (ascending candidates) is the same as with T = 1.
+template <bool HALF, bool ONETYPE, int T>
+__global__ void __launch_bounds__(BUILD_THREADS)
+k_build_cluster_mt(int nlocal, int ncl, const double4 *__restrict__ xq, const int *__restrict__ atom_bin,
+                   const int *__restrict__ cell_start, const int *__restrict__ cell_atoms,
+                   const double4 *__restrict__ cell_xq, int nrows, const int *__restrict__ row_off,
+                   const int *__restrict__ row_sx, const int *__restrict__ row_flag,
+                   const double *__restrict__ cutneighsq, int ntypes, int mbinx, int *__restrict__ neigh,
+                   int *__restrict__ numneigh, int pitch, int *flags, int *__restrict__ tile_ghost, int L) {
+  __shared__ int s_off[MAX_ROWS], s_sx[MAX_ROWS], s_flag[MAX_ROWS];
+  __shared__ double s_cut[(MAX_TYPES_SMEM + 1) * (MAX_TYPES_SMEM + 1)];
+  for (int r = threadIdx.x; r < nrows; r += blockDim.x) { s_off[r] = row_off[r]; s_sx[r] = row_sx[r]; s_flag[r] = row_flag[r]; }
+  const int nt1 = ntypes + 1;
+  const bool cut_smem = ntypes <= MAX_TYPES_SMEM;
+  if (cut_smem) for (int r = threadIdx.x; r < nt1 * nt1; r += blockDim.x) s_cut[r] = cutneighsq[r];
+  __syncthreads();
+  const int gt = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = gt / T, l = gt % T;
+  if (c >= ncl) return;                     // whole groups leave together
+  const int lane = threadIdx.x & 31;
+  const unsigned gmask_lanes = (T == 32) ? 0xffffffffu : (((1u << T) - 1u) << (lane - l));
+  const unsigned below = gmask_lanes & ((1u << lane) - 1u);
+  const int C = 32 / L;
+  int *out = neigh + (size_t)(c / C) * pitch * C + (c % C) * L;
+  const int i0 = c * CL;
+  const int ni = min(CL, nlocal - i0);
+  double xi[CL], yi[CL], zi[CL];
+  int bi[CL], own_lo[CL], own_hi[CL];
+  const double *cutrow[CL];
+  const double cut1 = ONETYPE ? cutneighsq[nt1 + 1] : 0.0;
+#pragma unroll
+  for (int k = 0; k < CL; k++) {
+    const int i = i0 + min(k, ni - 1);
+    const double4 q = xq[i];
+    xi[k] = k < ni ? q.x : 1e150; yi[k] = q.y; zi[k] = q.z;
+    bi[k] = atom_bin[i];
+    own_lo[k] = cell_start[bi[k]]; own_hi[k] = cell_start[bi[k] + 1];
+    const int it = xq_type(q);
+    cutrow[k] = cut_smem ? &s_cut[it * nt1] : &cutneighsq[it * nt1];
+  }
+  int cnt = 0;
+  bool has_ghost = false;
+  for (int g0 = 0; g0 < CL;) {
+    int g1 = g0 + 1;
+    while (g1 < CL && bi[g1] / mbinx == bi[g0] / mbinx) g1++;
+    const unsigned gmask = ((1u << g1) - 1u) & ~((1u << g0) - 1u);
+    const int bmin = bi[g0], bmax = bi[g1 - 1];
+    for (int r = 0; r < nrows; r++) {
+      const int off = s_off[r], sx = s_sx[r];
+      const int back = (HALF && s_flag[r] == 2) ? 0 : sx;
+      const int lo = cell_start[bmin + off - back], hi = cell_start[bmax + off + sx + 1];
+      for (int base = lo; base < hi; base += T) {
+        const int cidx = base + l;
+        unsigned m = 0;
+        int j = 0;
+        if (cidx < hi) {
+          const double4 qj = ld_xq(&cell_xq[cidx]);
+          j = __ldg(&cell_atoms[cidx]);
+          const int jt = ONETYPE ? 1 : xq_type(qj);
+#pragma unroll
+          for (int a = 0; a < CL; a++) {
+            const double dx = xi[a] - qj.x, dy = yi[a] - qj.y, dz = zi[a] - qj.z;
+            m |= (rsq_nofma(dx, dy, dz) <= (ONETYPE ? cut1 : cutrow[a][jt]) ? 1u : 0u) << a;
+          }
+          m &= gmask;
+          if (m) {
+            const int d = j - i0;
+            if (HALF) {
+              if (j < nlocal) m &= d <= 0 ? 0u : (d >= CL ? 0xfu : (1u << d) - 1u);
+              else {
+#pragma unroll
+                for (int a = 0; a < CL; a++) {
+                  bool keep = true;
+                  if (cidx < own_hi[a]) {
+                    if (cidx < own_lo[a]) keep = false;
+                    else if (qj.z < zi[a]) keep = false;
+                    else if (qj.z == zi[a]) {
+                      if (qj.y < yi[a]) keep = false;
+                      else if (qj.y == yi[a] && qj.x < xi[a]) keep = false;
+                    }
+                  }
+                  if (!keep) m &= ~(1u << a);
+                }
+              }
+            } else if (d >= 0 && d < CL) m &= ~(1u << d);
+          }
+        }
+        const unsigned kept = __ballot_sync(gmask_lanes, m != 0) & gmask_lanes;
+        if (m) {
+          const int k = cnt + __popc(kept & below);
+          if (k < pitch) out[(k / L) * 32 + (k % L)] = (int)((unsigned)j | (m << CL_SHIFT));
+          has_ghost |= (j >= nlocal);
+        }
+        cnt += __popc(kept);
+      }
+    }
+    g0 = g1;
+  }
+  has_ghost = __any_sync(gmask_lanes, has_ghost);
+  if (l == 0) {
+    numneigh[c] = cnt;
+    if (cnt > pitch) atomicMax(&flags[1], cnt);
+    if (tile_ghost && has_ghost) tile_ghost[c / C] = 1;
+  }
+}
+
 template <int TPA, bool HALF, bool MOL>
 static void launch_build3(b200md_ctx *c, int nblocks, const MolParams &M) {
   k_build<TPA, HALF, MOL><<<nblocks, BUILD_THREADS, 0, c->stream>>>(
@@ -759,7 +867,10 @@ int neigh_build_list(b200md_ctx *c) {
   const bool cluster = !c->topo.molecular && (c->use_cluster < 0 ? c->pair_style == B200MD_PAIR_LJ_CUT : c->use_cluster != 0);
   if (cluster != c->cluster) { c->cluster = cluster; c->pitch = 0; }
   // lanes per list unit, measured on B200 (profiles/): lj/cut 4 per cluster, 2 per atom on the per-atom list; eam 1 per atom
-  if (!c->tpa_user) c->tpa = cluster ? 4 : (c->pair_style == B200MD_PAIR_EAM ? 1 : 2);
+  // small systems (fewer lanes than the SMs can hold) are latency-bound: more lanes per unit shorten the serial chains
+  const bool small = c->nlocal < 300000;
+  if (!c->tpa_user) c->tpa = cluster ? (small ? 8 : 4) : (c->pair_style == B200MD_PAIR_EAM ? (small ? 4 : 1) : 2);
+  if (!c->tpa_build_user) c->tpa_build = (small && c->pair_style == B200MD_PAIR_EAM) ? 8 : 1;
   if (cluster && c->nlocal + c->nghost > CL_JMASK) { b200md_set_error("b200md: more than 2^28 atoms on one rank"); return B200MD_ERR; }
   if (c->pitch == 0) {
     // first guess from the number density: full sphere of cutneighmax, +35 % slack; a cluster's j-list is the union
@@ -786,9 +897,18 @@ int neigh_build_list(b200md_ctx *c) {
   k_build_cluster<H, O><<<nb, BUILD_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, \
       c->cell_xq, c->nrows, c->row_off, c->row_sx, c->row_flag, c->cutneighsq, c->ntypes, c->bin.mbinx, c->neigh, c->numneigh,  \
       c->pitch, c->d_flags, c->tile_ghost, c->tpa)
-        if (half) { if (one) B200_LAUNCH_BUILD_CL(true, true); else B200_LAUNCH_BUILD_CL(true, false); }
+#define B200_LAUNCH_BUILD_CL_MT(H, O)                                                                                          \
+  k_build_cluster_mt<H, O, 8><<<(ncl * 8 + BUILD_THREADS - 1) / BUILD_THREADS, BUILD_THREADS, 0, c->stream>>>(                    \
+      c->nlocal, ncl, c->xq, c->atom_bin, c->cell_start, c->cell_atoms, c->cell_xq, c->nrows, c->row_off, c->row_sx, c->row_flag, \
+      c->cutneighsq, c->ntypes, c->bin.mbinx, c->neigh, c->numneigh, c->pitch, c->d_flags, c->tile_ghost, c->tpa)
+        const bool mt = c->tpa_build_user ? c->tpa_build > 1 : small;   // 8 lanes per cluster below ~3 10^5 atoms
+        if (mt) {
+          if (half) { if (one) B200_LAUNCH_BUILD_CL_MT(true, true); else B200_LAUNCH_BUILD_CL_MT(true, false); }
+          else { if (one) B200_LAUNCH_BUILD_CL_MT(false, true); else B200_LAUNCH_BUILD_CL_MT(false, false); }
+        } else if (half) { if (one) B200_LAUNCH_BUILD_CL(true, true); else B200_LAUNCH_BUILD_CL(true, false); }
         else { if (one) B200_LAUNCH_BUILD_CL(false, true); else B200_LAUNCH_BUILD_CL(false, false); }
 #undef B200_LAUNCH_BUILD_CL
+#undef B200_LAUNCH_BUILD_CL_MT
       }
     } else
     switch (c->tpa_build) {

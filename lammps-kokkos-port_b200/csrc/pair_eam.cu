@@ -752,7 +752,26 @@ int pair_eam_launch(b200md_ctx *c, bool ev, int pass, const int *tiles, int ntl)
 }
 
 // PairEAM::compute's forward_comm(this): fp of owners -> ghosts (pair_eam.cpp:251, pack :855-876)
+// one rank, one element: fp of the owner and the packed ghost record in one pass
+__global__ void k_fp_xfp_flat(int nghost, int nlocal, const double4 *__restrict__ xq, double *__restrict__ fp,
+                              const int *__restrict__ ghost_src, double4 *__restrict__ xfp) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= nghost) return;
+  const double v = fp[ghost_src[nlocal + g]];
+  const double4 q = xq[nlocal + g];
+  fp[nlocal + g] = v;
+  xfp[nlocal + g] = make_double4(q.x, q.y, q.z, v);
+}
+
 int pair_eam_fp_comm(b200md_ctx *c) {
+  if (c->all_self && c->eam.one) {
+    if (c->nghost > 0) {
+      k_fp_xfp_flat<<<(c->nghost + 255) / 256, 256, 0, c->stream>>>(c->nghost, c->nlocal, c->xq, c->fp, c->ghost_src, c->eam.xfp);
+      c->launches++;
+      CUDA_TRY(cudaGetLastError());
+    }
+    return B200MD_OK;
+  }
   TRY(comm_forward_scalar(c, c->fp));
   if (c->eam.one && c->nghost > 0) {
     k_pack_xfp<<<(c->nghost + 255) / 256, 256, 0, c->stream>>>(c->nghost, c->nlocal, c->xq, c->fp, c->eam.xfp);
@@ -787,7 +806,7 @@ static int pair_eam_compute_half(b200md_ctx *c, bool ev) {
   const int nb_atoms = (c->nlocal + EAM_THREADS - 1) / EAM_THREADS;
   c->ev_valid = false;
   CUDA_TRY(cudaMemsetAsync(c->rho, 0, sizeof(double) * nall, c->stream));
-  for (int d = 0; d < 3; d++) CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax, 0, sizeof(double) * nall, c->stream));
+  CUDA_TRY(cudaMemset2DAsync(c->f, sizeof(double) * (size_t)c->nmax, 0, sizeof(double) * nall, 3, c->stream));
   double e_embed = 0, out7[7] = {0, 0, 0, 0, 0, 0, 0};
   if (nblocks) {
     if (ev) TRY(ensure_partials(c, nblocks > nb_atoms ? nblocks : nb_atoms));

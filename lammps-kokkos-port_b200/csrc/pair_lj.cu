@@ -299,9 +299,8 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag) {
   const int ntiles = list_tiles(c);
   const int nblocks = (ntiles + PAIR_THREADS / 32 - 1) / (PAIR_THREADS / 32);
   const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON;
-  if (half)  // Verlet::force_clear over owned + ghost (src/verlet.cpp:376-421)
-    for (int d = 0; d < 3; d++)
-      CUDA_TRY(cudaMemsetAsync(c->f + d * (size_t)c->nmax, 0, sizeof(double) * (c->nlocal + c->nghost), c->stream));
+  if (half && c->nlocal + c->nghost > 0)  // Verlet::force_clear over owned + ghost (src/verlet.cpp:376-421): 3 rows, one launch
+    CUDA_TRY(cudaMemset2DAsync(c->f, sizeof(double) * (size_t)c->nmax, 0, sizeof(double) * (c->nlocal + c->nghost), 3, c->stream));
   c->ev_valid = false;
   if (nblocks == 0) {
     if (ev) { c->eng_vdwl = 0; for (int k = 0; k < 6; k++) c->virial[k] = 0; c->ev_valid = true; }

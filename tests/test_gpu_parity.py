@@ -266,3 +266,28 @@ def test_golden_both_list_layouts(pkg, oracle_mod, name, kind, half, cluster):
         for k, key in enumerate(KEYS):
             assert abs(t[key] - row[k]) <= T_TOL * abs(row[k]), (key, t[key], row[k])
     ctx.close()
+
+
+@pytest.mark.parametrize("kind", ["lj", "eam"])
+def test_graph_mode_is_the_same_run(pkg, kind):
+    """option graph: the steps between two list builds replayed as one CUDA graph (a WHILE node whose condition is
+    Neighbor::decide evaluated on the device) must be the SAME run as the host-driven loop: with the full list
+    (newton off, no atomics) positions and velocities are bit-identical, and the rebuilds fall on the same steps
+    (`check no` every 20 for in.lj; `delay 5 every 1 check yes` for in.eam, where the distance test decides)."""
+    B = pkg.b200md
+    res = {}
+    for mode in ("off", "on"):
+        ctx = B.Context(0)
+        ctx.set_option("graph", mode)
+        cfg = pkg.inputs.in_lj(ctx, list_kind=B.LIST_FULL) if kind == "lj" else pkg.inputs.in_eam(ctx, list_kind=B.LIST_FULL)
+        ctx.setup()
+        th = ctx.run(57, cfg["dt"], 25)          # output steps 25, 50 and 57 cut the graph spans
+        th += ctx.run(43, cfg["dt"], 0)
+        a = ctx.get_atoms(("x", "v", "tag"))
+        o = np.argsort(a["tag"])
+        res[mode] = (a["x"][o], a["v"][o], ctx.neigh_stats(), [(t["step"], t["temp"], t["pe"], t["press"]) for t in th])
+        ctx.close()
+    assert np.array_equal(res["on"][0], res["off"][0]) and np.array_equal(res["on"][1], res["off"][1])
+    assert res["on"][2]["nbuilds"] == res["off"][2]["nbuilds"] and res["on"][2]["ndanger"] == res["off"][2]["ndanger"]
+    assert res["on"][3] == res["off"][3]
+    assert res["on"][2]["nbuilds"] == (6 if kind == "lj" else res["off"][2]["nbuilds"])

@@ -27,6 +27,7 @@ def trajectory(pkg, oracle_mod, name, kind, fused):
             del os.environ["B200MD_FUSE_NVE"]
         else:
             os.environ["B200MD_FUSE_NVE"] = old
+    ctx.set_option("graph", "off")           # the launch counts below compare the host-driven loops
     ctx.setup()
     th = ctx.run(60, s["dt"], 25)            # thermo steps at 25, 50, 60 break the fusion; rebuilds fall in between
     th += ctx.run(7, s["dt"], 0)
