@@ -145,6 +145,14 @@ int b200md_get_atoms(b200md_ctx *ctx, double *x_aos, double *v_aos, double *f_ao
  * reference GPU package's per-step `host_x` (src/GPU/pair_lj_cut_gpu.cpp:98-102).  Asynchronous
  * on the context's stream when the host memory is pinned. */
 int b200md_put_atoms(b200md_ctx *ctx, const double *x_aos, const double *v_aos);
+/* Asynchronous download of x and/or f (owned atoms, current local order) into PINNED host arrays: packed on the
+ * context's stream, copied on a separate copy stream, x first.  b200md_wait_download(ctx, 0) returns when x has
+ * arrived, (ctx, 1) when everything has.  A host that re-uploads positions every step (b200md_put_atoms) can do so as
+ * soon as x is there; the f copy then shares the PCIe link's other direction with that upload and overlaps the next
+ * step's kernels — the per-step boundary of the reference's GPU package (host x up, f down,
+ * src/GPU/pair_lj_cut_gpu.cpp:98-130) with the copies double-buffered. */
+int b200md_get_atoms_async(b200md_ctx *ctx, double *x_aos, double *f_aos);
+int b200md_wait_download(b200md_ctx *ctx, int all);
 /* pinned host memory for put/get */
 int b200md_host_alloc(void **ptr, size_t bytes);
 int b200md_host_free(void *ptr);

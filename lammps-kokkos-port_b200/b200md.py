@@ -300,6 +300,14 @@ class Context:
         g = lambda a: _p(a) if a is not None else None
         _chk(self.L.b200md_get_atoms(self.h, g(x), g(v), g(f), None, g(tag), None))
 
+    def get_atoms_async(self, x=None, f=None):
+        """enqueue the download of x / f into pinned arrays (copy stream); wait_download(False) = x is there"""
+        g = lambda a: _p(a) if a is not None else None
+        _chk(self.L.b200md_get_atoms_async(self.h, g(x), g(f)))
+
+    def wait_download(self, everything=True):
+        _chk(self.L.b200md_wait_download(self.h, int(everything)))
+
     def put_atoms(self, x=None, v=None):
         g = lambda a: _p(a) if a is not None else None
         _chk(self.L.b200md_put_atoms(self.h, g(x), g(v)))

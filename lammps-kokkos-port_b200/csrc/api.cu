@@ -90,6 +90,12 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
   if (!c) return B200MD_OK;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  if (c->copy_stream) {
+    cudaStreamSynchronize(c->copy_stream);
+    cudaStreamDestroy(c->copy_stream);
+    cudaEventDestroy(c->ev_packed); cudaEventDestroy(c->ev_dl_x); cudaEventDestroy(c->ev_dl_all);
+  }
+  if (c->dl_stage) cudaFree(c->dl_stage);
   if (c->sg.exec) cudaGraphExecDestroy(c->sg.exec);
   if (c->sg.graph) cudaGraphDestroy(c->sg.graph);
   if (c->sg.d_loop) cudaFree(c->sg.d_loop);
@@ -290,6 +296,58 @@ extern "C" int b200md_host_alloc(void **ptr, size_t bytes) {
 }
 extern "C" int b200md_host_free(void *ptr) {
   CUDA_TRY(cudaFreeHost(ptr));
+  return B200MD_OK;
+}
+
+// Asynchronous download for a host that reads results every step (bench.py e2e): x and f of the owned atoms are packed
+// on the context's stream into a device staging area of their own, then copied on a COPY stream, x first.  The caller
+// waits for x (b200md_wait_download(ctx, 0)), may upload the next step's input at once, and the f copy (D2H) runs
+// while that upload (H2D, the other PCIe direction) and the next step's kernels are in flight.
+__global__ void k_pack_xf(int n, int nmax, const double4 *__restrict__ xq, const double *__restrict__ f,
+                          double *__restrict__ x, double *__restrict__ fo) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const size_t s = (size_t)nmax;
+  if (x) { const double4 q = xq[i]; x[3 * i] = q.x; x[3 * i + 1] = q.y; x[3 * i + 2] = q.z; }
+  if (fo) { fo[3 * i] = f[i]; fo[3 * i + 1] = f[i + s]; fo[3 * i + 2] = f[i + 2 * s]; }
+}
+extern "C" int b200md_get_atoms_async(b200md_ctx *c, double *x, double *f) {
+  NEED(c, "b200md: null context");
+  const int n = c->nlocal;
+  if (n == 0 || (!x && !f)) return B200MD_OK;
+  CUDA_TRY(cudaSetDevice(c->device));
+  if (!c->copy_stream) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&c->ev_dl_x, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&c->ev_dl_all, cudaEventDisableTiming));
+  }
+  const size_t n3 = sizeof(double) * 3 * (size_t)n;
+  if (2 * n3 > c->dl_cap) {
+    CUDA_TRY(cudaStreamSynchronize(c->copy_stream));
+    if (c->dl_stage) CUDA_TRY(cudaFree(c->dl_stage));
+    c->dl_cap = 2 * n3 + n3 / 4 + (1 << 20);
+    CUDA_TRY(cudaMalloc(&c->dl_stage, c->dl_cap));
+  }
+  double *dx = x ? (double *)c->dl_stage : nullptr, *df = f ? (double *)(c->dl_stage + n3) : nullptr;
+  if (c->dl_pending) CUDA_TRY(cudaStreamWaitEvent(c->stream, c->ev_dl_all, 0));   // the staging area is free again
+  k_pack_xf<<<(n + 255) / 256, 256, 0, c->stream>>>(n, c->nmax, c->xq, c->f, dx, df);
+  c->launches++;
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaEventRecord(c->ev_packed, c->stream));
+  CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->ev_packed, 0));
+  if (x) CUDA_TRY(cudaMemcpyAsync(x, dx, n3, cudaMemcpyDeviceToHost, c->copy_stream));
+  CUDA_TRY(cudaEventRecord(c->ev_dl_x, c->copy_stream));
+  if (f) CUDA_TRY(cudaMemcpyAsync(f, df, n3, cudaMemcpyDeviceToHost, c->copy_stream));
+  CUDA_TRY(cudaEventRecord(c->ev_dl_all, c->copy_stream));
+  c->dl_pending = true;
+  return B200MD_OK;
+}
+extern "C" int b200md_wait_download(b200md_ctx *c, int all) {
+  NEED(c, "b200md: null context");
+  if (!c->dl_pending) return B200MD_OK;
+  CUDA_TRY(cudaEventSynchronize(all ? c->ev_dl_all : c->ev_dl_x));
+  if (all) c->dl_pending = false;
   return B200MD_OK;
 }
 

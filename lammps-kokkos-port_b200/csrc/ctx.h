@@ -277,6 +277,11 @@ struct b200md_ctx {
   double *h_result = nullptr;  // pinned [16]
   int *d_flags = nullptr;      // device [8]: 0 rebuild flag, 1 overflow, 2 nonfinite, 3 counter
   int *h_flags = nullptr;      // pinned [8]
+  cudaStream_t copy_stream = nullptr;   // b200md_get_atoms_async: D2H copies next to the next step's upload and kernels
+  cudaEvent_t ev_packed = nullptr, ev_dl_x = nullptr, ev_dl_all = nullptr;
+  char *dl_stage = nullptr;
+  size_t dl_cap = 0;
+  bool dl_pending = false;
   char *stage = nullptr;  // device staging for host<->device atom transfers
   size_t stage_cap = 0;
   // last energies
