@@ -500,7 +500,7 @@ k_eam_rho_cl(int nlocal, int ncl, const double4 *__restrict__ xq, const int *__r
           p -= m;
           p = fmin(p, 1.0);
           if (ONE) {
-            const double4 cf = ld4(P.tabC + (size_t)m * 8);
+            const double4 cf = ld4_if(P.tabC + (size_t)m * 8, hit);
             const double d = hit ? ((cf.x * p + cf.y) * p + cf.z) * p + cf.w : 0.0;
             ri[k] += d;
             if (HALF) g += d;
@@ -621,8 +621,8 @@ k_eam_force_cl(int nlocal, int ncl, int nmax, const double4 *__restrict__ xq, co
           double rhoip, rhojp, scl;
           double4 z;
           if (ONE) {
-            const double4 a = ld4(P.tabC + (size_t)m * 8);
-            z = ld4(P.tabC + (size_t)m * 8 + 4);
+            const double4 a = ld4_if(P.tabC + (size_t)m * 8, hit);
+            z = ld4_if(P.tabC + (size_t)m * 8 + 4, hit);
             rhoip = rhojp = ((3.0 * a.x * p + 2.0 * a.y) * p + a.z) * P.rdr;
             scl = P.scale11;
           } else {

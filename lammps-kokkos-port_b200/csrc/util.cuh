@@ -87,3 +87,13 @@ __device__ __forceinline__ double rsqrt_nr(double x) {
   e = fma(-xh * y, y, 0.5);
   return fma(y, e, y);
 }
+
+// 32-byte table row fetched only by the lanes whose predicate holds (others keep zeros and issue no L1 wavefront):
+// the cluster kernels evaluate masked-out slots branch-free, but must not pay table look-ups for them
+__device__ __forceinline__ double4 ld4_if(const double *p, bool on) {
+  double4 r = make_double4(0.0, 0.0, 0.0, 0.0);
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %5, 0;\n\t@q ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];\n\t}"
+               : "+d"(r.x), "+d"(r.y), "+d"(r.z), "+d"(r.w)
+               : "l"(p), "r"((unsigned)on));
+  return r;
+}
