@@ -262,12 +262,19 @@ def measure(job, ctx, cfg, natoms, steps, warmup, sampler=None):
                 launches=int(tm["launches"]), rebuilds=int(tm["nbuilds"]), phases=phases, clocks=clocks)
 
 
-def roofline_of(kind, lk, m, nloc, ngpus):
+def roofline_of(kind, lk, m, nloc, ngpus, layout=None):
     hbm, which = peaks()
     bk = BYTES_KERNEL[kind][lk]
+    kname = KERNELS[(kind, lk)]
+    if layout and layout["cluster"]:
+        # cluster-pair list: what the kernel's algorithm moves per owned atom and launch is E stored entries
+        # x (4 index + 32 x_j record [+ 24 f_j RED payload on the half list]) + 32 x_i + 24 f_i, E measured from the list
+        e_per_atom = layout["entries"] / max(nloc, 1)
+        bk = e_per_atom * (36 + (24 if lk == "half" else 0)) + 56
+        kname = "k_lj_cl<%s> (cluster-pair list, %.1f entries/atom, %d lanes/cluster)" % (lk, e_per_atom, layout["lanes"])
     pair_ms = m["phases"]["pair"]
     achieved = bk * nloc / (pair_ms / 1e3) / 1e9
-    r = {"bound": "hbm", "kernel": KERNELS[(kind, lk)], "list": lk, "achieved": achieved, "peak": hbm, "peak_source": which,
+    r = {"bound": "hbm", "kernel": kname, "list": lk, "achieved": achieved, "peak": hbm, "peak_source": which,
          "unit": "GB/s", "frac": achieved / hbm, "traffic": None, "kernel_ms": pair_ms, "bytes_per_atom_launch": bk,
          "step_achieved": BYTES_STEP[kind] * (m["value"] / ngpus) / 1e9,
          "step_frac": BYTES_STEP[kind] * (m["value"] / ngpus) / 1e9 / hbm,
@@ -277,7 +284,7 @@ def roofline_of(kind, lk, m, nloc, ngpus):
                  "pipe, see binding_unit / DESIGN.md §3"}
     # DRAM traffic and the binding unit of THIS kernel variant from its `ncu --set full` capture (profiles/), if one is
     # committed for exactly this kernel name
-    tr = os.path.join(ROOT, "profiles", "traffic_%s_%s.json" % ("eam" if kind == "c5" else kind, lk))
+    tr = os.path.join(ROOT, "profiles", "traffic_%s_%s.json" % (kind, lk))
     if os.path.exists(tr):
         t = json.load(open(tr))
         if t.get("kernel_variant") == kernel_variant():
@@ -412,7 +419,7 @@ def main():
     ctx.setup()
     m = measure(job, ctx, cfg, natoms, a.steps, a.warmup, ClockSampler(job.local_rank))
     nloc = ctx.nlocal()[0]
-    roofline = roofline_of(kind, lk_main, m, nloc, ngpus)
+    roofline = roofline_of(kind, lk_main, m, nloc, ngpus, ctx.neigh_layout())
 
     # ---- end to end through the C ABI with HOST buffers (pinned), copies inside the timed region, every step.
     # "offload" (the headline e2e.value): the per-step boundary of the reference's own GPU package — host positions up,
@@ -498,7 +505,7 @@ def main():
                 entry["reference_rebuilds_first_100_steps"] = gold["neighbor_list_builds"]
             m2 = measure(job, ctx, cfg2, n2, a.steps, a.warmup)
             entry.update(value=m2["value"], ms_per_step=m2["ms_per_step"], launches=m2["launches"], rebuilds=m2["rebuilds"],
-                         roofline=roofline_of(k2, lk_sec, m2, ctx.nlocal()[0], ngpus))
+                         roofline=roofline_of(k2, lk_sec, m2, ctx.nlocal()[0], ngpus, ctx.neigh_layout()))
             ctx.close()
             secondary[name] = entry
         if str(parity.get("eam_alloy_4M", "ok")).startswith("MISMATCH"):

@@ -182,6 +182,10 @@ int b200md_forward_comm(b200md_ctx *ctx);
  * Pass neigh_flat=NULL to obtain only numneigh and *total. */
 int b200md_neigh_export(b200md_ctx *ctx, int by_tag, int *numneigh, int *neigh_flat,
                         long long *total);
+/* Storage layout of the current list: *cluster = 1 when 4 consecutive owned atoms share one row of j entries with
+ * 4-bit pair masks (atomic systems, option cluster), 0 for per-atom rows; *entries = stored entries over all rows
+ * (what the force kernel gathers per step); *lanes = lanes that walk one row.  Any pointer may be NULL. */
+int b200md_neigh_layout(b200md_ctx *ctx, int *cluster, long long *entries, int *lanes);
 int b200md_neigh_stats(b200md_ctx *ctx, long long *nbuilds, long long *ndanger,
                        long long *total_neighbors, int *maxneigh_pitch);
 

@@ -355,6 +355,11 @@ class Context:
         _chk(self.L.b200md_neigh_stats(self.h, C.byref(a), C.byref(b), C.byref(t), C.byref(p)))
         return dict(nbuilds=a.value, ndanger=b.value, total=t.value, pitch=p.value)
 
+    def neigh_layout(self):
+        cl, ent, lanes = C.c_int(), C.c_longlong(), C.c_int()
+        _chk(self.L.b200md_neigh_layout(self.h, C.byref(cl), C.byref(ent), C.byref(lanes)))
+        return dict(cluster=bool(cl.value), entries=ent.value, lanes=lanes.value)
+
     def set_lanes_per_atom(self, n):
         _chk(self.L.b200md_set_lanes_per_atom(self.h, int(n)))
 

@@ -556,6 +556,25 @@ extern "C" int b200md_neigh_stats(b200md_ctx *c, long long *nbuilds, long long *
   return B200MD_OK;
 }
 
+// storage layout of the current list: per-atom rows or cluster rows (4 atoms share a row whose entries carry a 4-bit
+// pair mask), the number of stored entries and the lanes that walk a row
+extern "C" int b200md_neigh_layout(b200md_ctx *c, int *cluster, long long *entries, int *lanes) {
+  NEED(c && c->neigh && c->nbuilds > 0, "b200md: no neighbor list built");
+  CUDA_TRY(cudaSetDevice(c->device));
+  if (cluster) *cluster = c->cluster ? 1 : 0;
+  if (lanes) *lanes = c->tpa;
+  if (entries) {
+    const int n = list_units(c);
+    std::vector<int> nn(n);
+    if (n) CUDA_TRY(cudaMemcpyAsync(nn.data(), c->numneigh, sizeof(int) * n, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    long long t = 0;
+    for (int v : nn) t += v;
+    *entries = t;
+  }
+  return B200MD_OK;
+}
+
 extern "C" int b200md_set_lanes_per_atom(b200md_ctx *c, int lanes) {
   NEED(c, "b200md: null context");
   NEED(lanes == 1 || lanes == 2 || lanes == 4 || lanes == 8 || lanes == 16 || lanes == 32,
