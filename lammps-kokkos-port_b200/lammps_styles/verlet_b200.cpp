@@ -13,13 +13,19 @@
 #include "fix.h"
 #include "force.h"
 #include "modify.h"
+#include "neigh_list.h"
+#include "neigh_request.h"
 #include "neighbor.h"
+#include "npair.h"
+#include "npair_b200.h"
 #include "output.h"
 #include "pair.h"
 #include "timer.h"
 #include "update.h"
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 using namespace LAMMPS_NS;
@@ -29,7 +35,7 @@ b200md_ctx *B200Shared::ctx = nullptr;
 /* ---------------------------------------------------------------------- */
 
 VerletB200::VerletB200(LAMMPS *lmp, int narg, char **arg) :
-    Verlet(lmp, narg, arg), ctx(nullptr), host_stale(false), builds_at_setup(0), danger_at_setup(0)
+    Verlet(lmp, narg, arg), ctx(nullptr), host_stale(false), builds_at_setup(0), danger_at_setup(0), ghosts_step(-1)
 {
   // run_style verlet/b200 [keyword value ...]: the runtime options of the device library, the role
   // `package gpu|kokkos <keyword> <value>` plays for the reference's accelerator packages (an unmodified
@@ -201,6 +207,7 @@ void VerletB200::device_setup()
   ev_set(update->ntimestep);
   host_stale = true;
   sync_host();
+  publish_lists();
   publish_peratom();    // clears the styles' global accumulators too (ev_setup): before the tallies
   publish_tallies();
 }
@@ -253,6 +260,69 @@ void VerletB200::publish_tallies()
    (Comm::borders: swap tables + ghost rows, which ev_setup leaves at zero).
 ------------------------------------------------------------------------- */
 
+/* ----------------------------------------------------------------------
+   host ghosts of the current step: Comm::borders on the synced positions, once per step
+------------------------------------------------------------------------- */
+
+void VerletB200::host_borders()
+{
+  if (ghosts_step == update->ntimestep && atom->nghost > 0) return;
+  if (atom->map_style != Atom::MAP_NONE) atom->map_clear();
+  atom->nghost = 0;
+  comm->borders();
+  ghosts_step = update->ntimestep;
+}
+
+/* ----------------------------------------------------------------------
+   NeighList publication (NPair::build, src/neighbor.cpp:2470-2476).  Neighbor::build never runs under this run
+   style, so a host-side consumer of a neighbor list (compute coord/atom, compute rdf, ...) would see nothing.  On
+   output steps every plain bin list of the host — the pair style's own perpetual list included, occasional lists
+   are often copies of it — is filled by NPairFullBinB200 / NPairHalfBinNewtonB200 from the device's list, and the
+   reference's own NPair objects are marked up to date so Neighbor::build_one (src/neighbor.cpp:2528-2572) leaves
+   the lists alone (NeighList::np is that object).  The request flags are protected members of the unmodified
+   NeighRequest: read through pointers to members.
+------------------------------------------------------------------------- */
+
+namespace {
+struct RequestAccess : public NeighRequest {
+  static int NeighRequest::*p_half() { return &RequestAccess::half; }
+  static int NeighRequest::*p_skip() { return &RequestAccess::skip; }
+  static int NeighRequest::*p_halffull() { return &RequestAccess::halffull; }
+};
+}    // namespace
+
+void VerletB200::publish_lists()
+{
+  bool wanted = false;
+  for (int i = 0; i < neighbor->nlist; i++)
+    if (neighbor->lists[i]->requestor != (void *) force->pair) wanted = true;
+  if (!wanted) return;
+  if (comm->nprocs > 1) error->all(FLERR, "Run style verlet/b200: host-side neighbor lists are published on one rank only");
+  host_borders();
+  static NPairFullBinB200 *npfull = nullptr;
+  static NPairHalfBinNewtonB200 *nphalf = nullptr;
+  static LAMMPS *owner = nullptr;
+  if (owner != lmp) { npfull = new NPairFullBinB200(lmp); nphalf = new NPairHalfBinNewtonB200(lmp); owner = lmp; }
+  const bool dbg = getenv("B200_DEBUG_LISTS") != nullptr;
+  for (int pass = 0; pass < 2; pass++)
+    for (int i = 0; i < neighbor->nlist; i++) {
+      NeighList *list = neighbor->lists[i];
+      NeighRequest *rq = neighbor->old_requests[i];    // Neighbor::init hands the requests of this run over to old_requests
+      if ((pass == 1) != (list->copy != 0)) continue;    // parents first, then the lists that alias them
+      if (dbg) { fprintf(stderr, "[lists] step %ld list %d copy %d occasional %d np %p\n", (long) update->ntimestep, i, list->copy, list->occasional, (void *) list->np); fflush(stderr); }
+      if (list->copy) {                                   // NPairCopy (list->np): takes the parent's arrays
+        if (list->np) list->np->build(list);
+      } else {
+        if (rq->*RequestAccess::p_skip() || rq->*RequestAccess::p_halffull() || list->ghost || list->respaouter)
+          error->all(FLERR, "Run style verlet/b200 publishes plain half and full neighbor lists only");
+        if (rq->*RequestAccess::p_half()) nphalf->build(list);
+        else npfull->build(list);
+      }
+      if (list->np) list->np->last_build = update->ntimestep;
+    }
+  if (dbg) { fprintf(stderr, "[lists] done\n"); fflush(stderr); }
+}
+
 void VerletB200::publish_peratom()
 {
   if (!(eflag & ENERGY_ATOM) && !(vflag & (VIRIAL_ATOM | VIRIAL_CENTROID))) return;
@@ -266,10 +336,7 @@ void VerletB200::publish_peratom()
   } else {
     for (int k = 0; k < nlocal; k++) rows[k] = k;    // several ranks: the host arrays are in device order
   }
-  if (force->newton) {
-    if (atom->map_style != Atom::MAP_NONE) atom->map_clear();
-    comm->borders();
-  }
+  if (force->newton) host_borders();
   if (dynamic_cast<B200PairStyle *>(force->pair)->b200_peratom(ctx, eflag, vflag, rows.data(), nlocal)) fail();
   if (force->bond && atom->molecular != Atom::ATOMIC)
     if (dynamic_cast<B200BondStyle *>(force->bond)->b200_peratom_bond(ctx, eflag, vflag, rows.data(), nlocal)) fail();
@@ -401,6 +468,7 @@ void VerletB200::run(int n)
       // the last step of a chunk is evaluated with energy/virial tallies (Integrate::ev_set)
       ev_set(update->ntimestep);
       sync_host();
+      publish_lists();
       publish_peratom();
       publish_tallies();
       timer->stamp();

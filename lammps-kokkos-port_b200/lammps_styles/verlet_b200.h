@@ -44,6 +44,9 @@ class VerletB200 : public Verlet {
   void push_topology();
   void publish_tallies();
   void publish_peratom();
+  void publish_lists();
+  void host_borders();
+  bigint ghosts_step;    // timestep the host ghosts (Comm::borders on the synced positions) belong to
   void sync_host();
 };
 

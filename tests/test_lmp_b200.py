@@ -296,3 +296,54 @@ def test_lmp_b200_without_gpu_fails_loudly():
     if rc == 0:
         pytest.skip("a CUDA device is present")
     assert "no CUDA device" in out
+
+
+IN_LISTS = """
+units           lj
+{newton}
+atom_style      atomic
+lattice         fcc 0.8442
+region          box block 0 8 0 8 0 8
+create_box      1 box
+create_atoms    1 box
+mass            1 1.0
+velocity        all create 1.44 87287 loop geom
+pair_style      lj/cut 2.5
+pair_coeff      1 1 1.0 1.0 2.5
+neighbor        0.3 bin
+neigh_modify    delay 0 every 20 check no
+fix             1 all nve
+compute         c all coord/atom cutoff 1.3
+compute         csum all reduce sum c_c
+compute         cmax all reduce max c_c
+compute         cmin all reduce min c_c
+compute         r all rdf 50
+thermo_style    custom step temp pe press c_csum c_cmax c_cmin c_r[12][2] c_r[23][2] c_r[23][3] c_r[50][3]
+thermo_modify   format float %.15g
+thermo          {thermo}
+run             60
+"""
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("newton,thermo", [("", 10), ("", 7), ("newton off", 10)])
+def test_host_neighbor_lists_are_published(newton, thermo):
+    """NPairFullBinB200 / NPairHalfBinNewtonB200 (lammps_styles/npair_b200.cpp): host-side consumers of a neighbor
+    list under `-sf b200` — compute coord/atom (an occasional FULL list) and compute rdf (an occasional half list, with
+    newton on a copy of the pair style's own) — must print what they print under the unmodified reference executable.
+    thermo 7 puts output steps between the rebuilds (every 20), where the device ghosts and the host ghosts were
+    selected at different times."""
+    have_gpu_binary()
+    if not os.path.exists(LMP_REF):
+        pytest.skip("oracle/_ref/lmp not built")
+    script = IN_LISTS.format(newton=newton, thermo=thermo)
+    rc, out = run_lmp(LMP_B200, script, ("-sf", "b200"))
+    assert rc == 0, out[-3000:]
+    rc2, ref = run_lmp(LMP_REF, script)
+    assert rc2 == 0, ref[-2000:]
+    a, b = thermo_rows(out), thermo_rows(ref)
+    assert a.shape == b.shape and a.shape[1] == 11 and a.shape[0] >= 7
+    np.testing.assert_allclose(a[:, :4], b[:, :4], rtol=1e-8, atol=1e-10)
+    assert np.array_equal(a[:, 4:7], b[:, 4:7])                      # coordination numbers are integers
+    np.testing.assert_allclose(a[:, 7:], b[:, 7:], rtol=1e-10, atol=1e-12)
+    assert b[0, 4] > 0 and b[-1, 10] > 0
