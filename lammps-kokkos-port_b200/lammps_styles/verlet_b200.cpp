@@ -102,8 +102,18 @@ void VerletB200::check_supported()
   if (modify->n_initial_integrate != nintegrate || modify->n_final_integrate != nintegrate ||
       modify->n_post_integrate || modify->n_pre_exchange || modify->n_pre_neighbor ||
       modify->n_post_neighbor || modify->n_pre_force || modify->n_pre_reverse ||
-      modify->n_post_force_any != ndevice_post || modify->n_end_of_step)
+      modify->n_post_force_any != ndevice_post)
     error->all(FLERR, "Run style verlet/b200 does not support fixes that act during the step");
+  // end_of_step fixes that only READ the state (fix ave/time, ave/atom, ave/chunk, ave/histo, ave/correlate, vector,
+  // print) are served: the device loop stops on the steps they are due, the host arrays, tallies and lists are
+  // refreshed, and Modify::end_of_step runs like in Verlet::run (verlet.cpp:349).  One that writes atom data on the
+  // host (fix momentum, ...) would be lost on the device: refused.
+  for (int i = 0; i < modify->nfix; i++)
+    if ((modify->fmask[i] & FixConst::END_OF_STEP) &&
+        !utils::strmatch(modify->fix[i]->style, "^ave/") && !utils::strmatch(modify->fix[i]->style, "^vector$") &&
+        !utils::strmatch(modify->fix[i]->style, "^print$"))
+      error->all(FLERR, "Run style verlet/b200 does not support fix {} (it acts on the host's atoms during the step)",
+                 modify->fix[i]->style);
 }
 
 /* ---------------------------------------------------------------------- */
@@ -447,6 +457,13 @@ void VerletB200::run(int n)
     bigint togo = output->next - update->ntimestep;
     int chunk = n - done;
     if (togo > 0 && togo < (bigint) chunk) chunk = (int) togo;
+    if (modify->n_end_of_step)    // next step an end_of_step fix is due (Modify::end_of_step: ntimestep % nevery == 0)
+      for (int i = 0; i < modify->nfix; i++)
+        if ((modify->fmask[i] & FixConst::END_OF_STEP) && modify->fix[i]->nevery > 0) {
+          const bigint every = modify->fix[i]->nevery;
+          const bigint due = (update->ntimestep / every + 1) * every - update->ntimestep;
+          if (due < (bigint) chunk) chunk = (int) due;
+        }
 
     for (const auto &fix : modify->get_fix_list())
       if (auto dev = dynamic_cast<B200FixStyle *>(fix))
@@ -464,13 +481,27 @@ void VerletB200::run(int n)
     neighbor->ncalls = (bigint) (nb - builds_at_setup);
     neighbor->ndanger = (bigint) (nd - danger_at_setup);
 
-    if (update->ntimestep == output->next) {
+    bool eos = false;
+    if (modify->n_end_of_step)
+      for (int i = 0; i < modify->nfix; i++)
+        if ((modify->fmask[i] & FixConst::END_OF_STEP) && modify->fix[i]->nevery > 0 &&
+            update->ntimestep % modify->fix[i]->nevery == 0)
+          eos = true;
+    const bool out = update->ntimestep == output->next;
+    if (out || eos) {
       // the last step of a chunk is evaluated with energy/virial tallies (Integrate::ev_set)
       ev_set(update->ntimestep);
       sync_host();
       publish_lists();
       publish_peratom();
       publish_tallies();
+    }
+    if (eos) {
+      timer->stamp();
+      modify->end_of_step();
+      timer->stamp(Timer::MODIFY);
+    }
+    if (out) {
       timer->stamp();
       output->write(update->ntimestep);
       timer->stamp(Timer::OUTPUT);

@@ -347,3 +347,25 @@ def test_host_neighbor_lists_are_published(newton, thermo):
     assert np.array_equal(a[:, 4:7], b[:, 4:7])                      # coordination numbers are integers
     np.testing.assert_allclose(a[:, 7:], b[:, 7:], rtol=1e-10, atol=1e-12)
     assert b[0, 4] > 0 and b[-1, 10] > 0
+
+
+@pytest.mark.gpu
+def test_fix_ave_time_is_served():
+    """an end_of_step fix that only reads (fix ave/time over compute coord/atom's sum, the pair energy and the
+    pressure): verlet/b200 stops the device loop on the steps it samples, refreshes the host arrays, tallies and
+    lists, and runs Modify::end_of_step — same averages as the reference executable"""
+    have_gpu_binary()
+    if not os.path.exists(LMP_REF):
+        pytest.skip("oracle/_ref/lmp not built")
+    script = IN_LISTS.format(newton="", thermo=12).replace(
+        "thermo_style    custom step temp pe press c_csum c_cmax c_cmin c_r[12][2] c_r[23][2] c_r[23][3] c_r[50][3]",
+        "fix             av all ave/time 3 4 12 c_csum c_thermo_pe c_thermo_press\n"
+        "thermo_style    custom step temp pe press f_av[1] f_av[2] f_av[3]")
+    rc, out = run_lmp(LMP_B200, script, ("-sf", "b200"))
+    assert rc == 0, out[-3000:]
+    rc2, ref = run_lmp(LMP_REF, script)
+    assert rc2 == 0, ref[-2000:]
+    a, b = thermo_rows(out), thermo_rows(ref)
+    assert a.shape == b.shape and a.shape[1] == 7
+    np.testing.assert_allclose(a, b, rtol=1e-8, atol=1e-9)
+    assert np.abs(b[-1, 4:]).min() > 0
