@@ -358,28 +358,13 @@ def main():
         options.append(("lanes", str(a.lanes)))
     run_info = {"decomposition": "x".join(str(g) for g in B.procgrid(world, [20.0 * xyz[0], 20.0 * xyz[1], 20.0 * xyz[2]]))}
 
-    # ---- list kind.  The scripts run with `newton on` -> half list (f_j, rho_j by FP64 RED + reverse_comm); measured on
-    # B200 (profiles/) the half list wins on one GPU.  On several ranks `--list auto` MEASURES it for in.lj (20 untimed
-    # steps of each kind) and uses half for eam ----
+    # ---- list kind.  The scripts run with `newton on` -> half list (f_j, rho_j by FP64 RED + reverse_comm), which is also
+    # what measures fastest on B200 at every rank count (profiles/r02_summary.md); `--list full` = newton off ----
     lk_main = a.list if a.list != "auto" else "half"
     progress("start: %d rank(s), workload %s" % (world, a.workload))
     ctx = job.open(options)
     run_info["halo"] = ctx.get_option("halo")
     run_info["cpu_affinity"] = job.affinity
-    cfg = job.configure(ctx, kind, xyz, lk_main)
-    ctx.setup()
-    if world > 1 and a.list == "auto" and kind == "lj":
-        trial = {}
-        for k2 in ("full", "half"):
-            progress("list trial " + k2)
-            ctx.neigh_config(**cfg["neigh"], list_kind=B.LIST_HALF_NEWTON if k2 == "half" else B.LIST_FULL)
-            ctx.setup()
-            ctx.run(5, cfg["dt"], 0)
-            job.barrier()
-            ctx.run(20, cfg["dt"], 0)
-            trial[k2] = job.maxr(ctx.timing()["total_ms"]) / 20     # CUDA events on the context's stream, max over ranks
-        lk_main = min(trial, key=trial.get)
-        run_info["list_trial_ms_per_step"] = trial
     ctx.close()
     run_info["neighbor_list"] = "half/bin/atomonly/newton" if lk_main == "half" else "full/bin/atomonly (newton off)"
     lk_sec = a.list if a.list != "auto" else "half"

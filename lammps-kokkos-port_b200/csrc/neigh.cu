@@ -507,6 +507,54 @@ k_build(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ atom
     }
     int own_end = 0;
     if (HALF && role == 2 && active) own_end = cell_start[ibin + 1];
+    if (TPA == 1) {
+      // one lane per atom: no votes, a private counter, and the next candidate in flight while this one is tested
+      if (lo >= hi) continue;
+      double4 qj = ld_xq(&cell_xq[lo]);
+      int j = __ldg(&cell_atoms[lo]);
+      for (int cidx = lo; cidx < hi; cidx++) {
+        const int nx = min(cidx + 1, hi - 1);
+        const double4 qn = ld_xq(&cell_xq[nx]);
+        const int jn = __ldg(&cell_atoms[nx]);
+        const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
+        bool keep = rsq_nofma(dx, dy, dz) <= cutrow[xq_type(qj)];
+        if (keep) {
+          if (HALF) {
+            if (role == 2 && cidx < own_end) {
+              if (j <= i) keep = false;
+              else if (j >= nlocal) {
+                if (qj.z < qi.z) keep = false;
+                else if (qj.z == qi.z) {
+                  if (qj.y < qi.y) keep = false;
+                  else if (qj.y == qi.y && qj.x < qi.x) keep = false;
+                }
+              }
+            }
+          } else if (j == i) keep = false;
+          if (MOL && keep && s1 > s0) {
+            const int tj = M.tag[j];
+            for (int sp = s0; sp < s1; sp++) {
+              if (M.spec_tag[sp] == tj) {
+                const int wh = M.spec_which[sp];
+                const int fl = wh == 1 ? M.flag1 : (wh == 2 ? M.flag2 : M.flag3);
+                if (fl == 0) {
+                  const bool far = (M.hx > 0 && fabs(dx) > M.hx) || (M.hy > 0 && fabs(dy) > M.hy) || (M.hz > 0 && fabs(dz) > M.hz);
+                  if (!far) keep = false;
+                }
+                break;
+              }
+            }
+          }
+          if (keep) {
+            has_ghost |= (j >= nlocal);
+            if (cnt < pitch) out[(cnt / F) * 32 + (cnt % F)] = j;
+            cnt++;
+          }
+        }
+        qj = qn; j = jn;
+      }
+      continue;
+    }
     int cidx = lo + l;
     while (__any_sync(0xffffffffu, cidx < hi)) {
       bool keep = false;
