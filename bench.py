@@ -18,6 +18,8 @@ including the neighbor rebuilds that fall inside the K steps.  One JSON line on 
                            (strong scaling, atom migration at every rebuild); its thermo at steps 0/50/100 is checked
                            against tests/golden/c5_thermo.json (the unmodified reference, 4 M atoms)
   secondary.lj_32k / eam_32k   the 32 000-atom configs C1 / C2 as shipped (latency regime)
+  secondary.chain          config C3: bench/in.chain.scaled at 2 048 000 beads per GPU (parity_check.chain: 32 000 beads against
+                           tests/golden/chain.npz from the unmodified reference)
   cpu_baseline (N=1)       the reference's own CPU implementation on this box's host cores, bounded sample
 """
 import argparse
@@ -392,7 +394,25 @@ def main():
                                   "launches": int(tm["launches"]), "rebuilds": int(tm["nbuilds"]), "list": lk,
                                   "workload": "bench/in.%s as shipped (32 000 atoms)" % wl}
             ctx.close()
-        if any(str(parity[w]).startswith("MISMATCH") for w in ("lj", "eam")):
+        # bench/in.chain (config C3: FENE bonds + lj/cut 1.12, special_bonds fene), 32 000 beads, without its thermostat
+        # (fix langevin draws per rank in local atom order: one-rank only): 10 x `run 10` like the golden run of the
+        # unmodified reference (tests/golden/chain.npz: T, PE, KE, Press, E_vdwl, E_mol), 1e-8 relative
+        progress("parity check chain 32k")
+        gold = np.load(os.path.join(ROOT, "tests", "golden", "chain.npz"))
+        ctx = job.open(options)
+        cfgc = job.P.inputs.in_chain(ctx, None, 1, 1, 1, list_kind=B.LIST_HALF_NEWTON if lk_main == "half" else B.LIST_FULL)
+        ctx.setup()
+        recs = [ctx.thermo()]
+        for _ in range(10):
+            ctx.setup()          # every `run` of the golden script starts with a set-up
+            recs.append(ctx.run(10, cfgc["dt"], 0)[-1])
+        worst = 0.0
+        for t, w in zip(recs, [gold["thermo0"]] + list(gold["thermo_series"])):
+            got = [t["temp"], t["pe"], t["ke"], t["press"], t["pe"] - t["emol"], t["emol"]]
+            worst = max(worst, max(abs(x - y) / abs(y) for x, y in zip(got, w)))
+        parity["chain"] = "ok" if worst <= 1e-8 else "MISMATCH worst relative deviation %.2e" % worst
+        ctx.close()
+        if any(str(parity[w]).startswith("MISMATCH") for w in ("lj", "eam", "chain")):
             if rank == 0:
                 print(json.dumps({"parity_check": parity, "error": "thermo differs from the reference logs"}))
             return 2
@@ -493,6 +513,21 @@ def main():
                          roofline=roofline_of(k2, lk_sec, m2, ctx.nlocal()[0], ngpus, ctx.neigh_layout()))
             ctx.close()
             secondary[name] = entry
+        # config C3 scaled like in.chain.scaled to 2 048 000 beads per GPU; with `fix langevin` as shipped on one rank (the
+        # reference's RanMars stream, sequence-exact), without it on several (the stream is per rank)
+        progress("secondary chain")
+        lang = world == 1
+        ctx = job.open(options)
+        cfgc = job.P.inputs.in_chain(ctx, None, *SCALE.get(ngpus, (4 * ngpus, 4, 4)), list_kind=B.LIST_HALF_NEWTON if lk_sec == "half" else B.LIST_FULL,
+                                     langevin=lang)
+        ctx.setup()
+        nch = cfgc["natoms"]
+        mc = measure(job, ctx, cfgc, nch, a.steps, a.warmup)
+        secondary["chain"] = {"unit": "atom-steps/s", "value": mc["value"], "ms_per_step": mc["ms_per_step"], "launches": mc["launches"],
+                              "rebuilds": mc["rebuilds"], "phases_ms_per_step": mc["phases"], "scaling": "weak", "list": lk_sec,
+                              "workload": "bench/in.chain.scaled, %d beads (FENE + lj/cut 1.12, special_bonds fene), %s"
+                                          % (nch, "fix langevin 1.0 1.0 10.0 904297 as shipped" if lang else "NVE (fix langevin left out on several ranks)")}
+        ctx.close()
         if str(parity.get("eam_alloy_4M", "ok")).startswith("MISMATCH"):
             if rank == 0:
                 print(json.dumps({"parity_check": parity, "error": "eam/alloy 4M thermo differs from the reference"}))
