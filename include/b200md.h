@@ -329,6 +329,22 @@ typedef struct b200md_thermo {
   double emol;                /* bond energy (thermo keyword emol), 0 for atomic systems */
 } b200md_thermo;
 int b200md_thermo_compute(b200md_ctx *ctx, b200md_thermo *out);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under stream capture, tight serving loops, harnesses that forbid it).  The kinetic sums behind
+ * b200md_thermo_compute's temp / ke — out5 = {sum m v.v, sum m vx, sum m vy, sum m vz, sum m} over n atoms — in ONE
+ * launch that allocates nothing: the per-block partial sums go to a static device array inside the library
+ * (164 096 bytes, held by every GPU that loads the library until exit) instead of the context's growable scratch.
+ * All pointers are DEVICE pointers of the CURRENT device, owned by the caller: v_soa_dev = velocities as
+ * [3][stride] (component k of atom i at k*stride + i, stride >= n), type_dev = atom types 1..ntypes (NULL: all
+ * type 1), mass_dev = mass by type [ntypes+1] (Atom::mass), out5_dev = 5 doubles.  The launch goes to `stream`
+ * (cudaStream_t as void*, NULL = default stream) and is not synchronised.  n = 0 only does the once-per-device
+ * set-up (the static array's device address): call that once outside a stream capture.
+ * Limits: n <= B200MD_KE_STATIC_MAX_ATOMS, else B200MD_ERR with a message naming the limit.  The array is shared
+ * by all calls on a device: calls that overlap on the GPU (streams with no ordering between them) race; calls
+ * ordered on one stream, or by events, are safe.  Same input, same n -> same bits on every call. */
+#define B200MD_KE_STATIC_MAX_ATOMS 16777216
+int b200md_ke_sums_static(int n, long long stride, const double *v_soa_dev, const int *type_dev,
+                          const double *mass_dev, double *out5_dev, void *stream);
 
 /* ---- whole loop ---------------------------------------------------------------------- */
 

@@ -198,6 +198,19 @@ def pinned_empty(shape, dtype=np.float64):
     return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
 
 
+KE_STATIC_MAX_ATOMS = 16777216     # B200MD_KE_STATIC_MAX_ATOMS (include/b200md.h)
+
+
+def ke_sums_static(n, stride, v_soa_dev, type_dev, mass_dev, out5_dev, stream=None):
+    """b200md_ke_sums_static: {sum m v.v, sum m vx, sum m vy, sum m vz, sum m} of n atoms into out5_dev, one launch on
+    `stream`, nothing allocated (scratch in a static device array of the library).  Every *_dev argument is a DEVICE
+    address (int) on the current device; type_dev may be None/0.  Not synchronised.  No counterpart in the reference."""
+    L = lib()
+    L.b200md_ke_sums_static.argtypes = [C.c_int, C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    _chk(L.b200md_ke_sums_static(int(n), int(stride), v_soa_dev or None, type_dev or None, mass_dev or None,
+                                 out5_dev or None, stream or None))
+
+
 # ---- unit systems (src/update.cpp:145-200) ---------------------------------------------------
 UNITS = {
     "lj": dict(boltz=1.0, mvv2e=1.0, ftm2v=1.0, nktv2p=1.0, dt=0.005, skin=0.3),
