@@ -429,9 +429,11 @@ def main():
     # ---- end to end through the C ABI with HOST buffers (pinned), copies inside the timed region, every step.
     # "offload" (the headline e2e.value): the per-step boundary of the reference's own GPU package — host positions up,
     # forces down (src/GPU/pair_lj_cut_gpu.cpp:98-130).  The device integrates here, so the new positions come down too:
-    # x up (24 B/atom); x, f down (48 B/atom).  b200md_get_atoms_async copies on a copy stream, x first; the host uploads
-    # the next step's positions as soon as x has arrived, so the f download shares the link with that upload and overlaps
-    # the next step's kernels (host f buffers alternate).  "offload_sync": the same bytes, one copy after the other.
+    # x up (24 B/atom); x, f down (48 B/atom).  b200md_get_atoms_async copies on a copy stream, x first and in pieces; the
+    # host sends every piece of x back up (b200md_put_atoms_range) as soon as it has landed, so upload and download use the
+    # two directions of the link at once, and the f download runs under the next step's kernels (host f buffers
+    # alternate).  "offload_async": whole-array upload after the whole x download (round 2's first version);
+    # "offload_sync": the same bytes, one blocking copy after the other.
     # "full_state": x, v up and x, v, f, tag down (a host that owns the whole state; what round 1 reported as e2e).
     e2e = None
     progress("main workload measured: %.4f ms/step; e2e" % m["ms_per_step"])
@@ -456,7 +458,21 @@ def main():
             ctx.get_atoms_async(hx, hf[it & 1])     # pack, then D2H x, f on the copy stream
             ctx.wait_download(False)                # x is on the host: the next upload may start
 
-        for name, fn, up, down in (("full_state", step_full, 48, 76), ("offload_sync", step_sync, 24, 48), ("offload", step_async, 24, 48)):
+        def step_stream(it):
+            # the same bytes, streamed: every piece of x goes back up as soon as it has come down, so both directions of
+            # the link are busy at once; the f download runs behind the x pieces and under the next step's kernels
+            ctx.run(1, cfg["dt"], 0)
+            ctx.get_atoms_async(hx, hf[it & 1])
+            p = 0
+            while True:
+                first, count = ctx.wait_download_part(p)
+                if count == 0:
+                    break
+                ctx.put_atoms_range(hx, first, count)
+                p += 1
+
+        for name, fn, up, down in (("full_state", step_full, 48, 76), ("offload_sync", step_sync, 24, 48),
+                                   ("offload_async", step_async, 24, 48), ("offload", step_stream, 24, 48)):
             for it in range(3):
                 fn(it)
             ctx.wait_download(True)
@@ -474,8 +490,11 @@ def main():
                               "h2d_bytes_per_step": h2d // a.steps, "d2h_bytes_per_step": d2h // a.steps}
             ctx.get_atoms_into(hx, hv, hf[0], htag)
         e2e = dict(variants["offload"], unit="atom-steps/s",
-                   api="every step: b200md_put_atoms(x) + b200md_run(1) + b200md_get_atoms_async(x, f) + b200md_wait_download(x); "
-                       "pinned host buffers, f download overlaps the next upload and step",
+                   api="every step: b200md_run(1) + b200md_get_atoms_async(x, f) + per piece of x: b200md_wait_download_part + "
+                       "b200md_put_atoms_range; pinned host buffers, upload and download share the link, f download overlaps "
+                       "the next step",
+                   offload_async=dict(variants["offload_async"], api="b200md_put_atoms(x) + b200md_run(1) + b200md_get_atoms_async(x,f) "
+                                      "+ b200md_wait_download(x): whole-array copies, f download overlapped"),
                    offload_sync=dict(variants["offload_sync"], api="b200md_put_atoms(x) + b200md_run(1) + b200md_get_atoms(x,f)"),
                    full_state=dict(variants["full_state"], api="b200md_put_atoms(x,v) + b200md_run(1) + b200md_get_atoms(x,v,f,tag)"))
     ctx.close()

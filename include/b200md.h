@@ -153,6 +153,15 @@ int b200md_put_atoms(b200md_ctx *ctx, const double *x_aos, const double *v_aos);
  * src/GPU/pair_lj_cut_gpu.cpp:98-130) with the copies double-buffered. */
 int b200md_get_atoms_async(b200md_ctx *ctx, double *x_aos, double *f_aos);
 int b200md_wait_download(b200md_ctx *ctx, int all);
+/* The same boundary, streamed: b200md_get_atoms_async sends x in up to B200MD_DL_PARTS pieces of whole atoms.
+ * b200md_wait_download_part(ctx, p, &first, &count) returns when piece p (atoms first .. first+count-1) is on the
+ * host (count = 0 beyond the last piece); b200md_put_atoms_range uploads the positions of that range from the host
+ * array x_aos (row 0 = atom 0) on the context's stream.  Turning piece p around while piece p+1 is still coming
+ * down uses both directions of the link at once (the reference's GPU package overlaps its copies with kernels the
+ * same way, lib/gpu/lal_atom.h add_x_data / lal_answer.cpp copy_answers on their own command queues). */
+#define B200MD_DL_PARTS 8
+int b200md_wait_download_part(b200md_ctx *ctx, int part, int *first, int *count);
+int b200md_put_atoms_range(b200md_ctx *ctx, const double *x_aos, int first, int count);
 /* pinned host memory for put/get */
 int b200md_host_alloc(void **ptr, size_t bytes);
 int b200md_host_free(void *ptr);

@@ -321,6 +321,16 @@ class Context:
     def wait_download(self, everything=True):
         _chk(self.L.b200md_wait_download(self.h, int(everything)))
 
+    def wait_download_part(self, part):
+        """piece `part` of the x download of get_atoms_async is on the host: (first, count), count 0 past the last piece"""
+        first, count = C.c_int(), C.c_int()
+        _chk(self.L.b200md_wait_download_part(self.h, int(part), C.byref(first), C.byref(count)))
+        return first.value, count.value
+
+    def put_atoms_range(self, x, first, count):
+        """upload the positions of the owned atoms [first, first+count) from the host array x (row 0 = atom 0)"""
+        _chk(self.L.b200md_put_atoms_range(self.h, _p(x), int(first), int(count)))
+
     def put_atoms(self, x=None, v=None):
         g = lambda a: _p(a) if a is not None else None
         _chk(self.L.b200md_put_atoms(self.h, g(x), g(v)))

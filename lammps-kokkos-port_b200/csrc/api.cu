@@ -94,6 +94,7 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
     cudaStreamSynchronize(c->copy_stream);
     cudaStreamDestroy(c->copy_stream);
     cudaEventDestroy(c->ev_packed); cudaEventDestroy(c->ev_dl_x); cudaEventDestroy(c->ev_dl_all);
+    for (cudaEvent_t e : c->ev_dl_part) cudaEventDestroy(e);
   }
   if (c->dl_stage) cudaFree(c->dl_stage);
   if (c->sg.exec) cudaGraphExecDestroy(c->sg.exec);
@@ -336,7 +337,20 @@ extern "C" int b200md_get_atoms_async(b200md_ctx *c, double *x, double *f) {
   CUDA_TRY(cudaGetLastError());
   CUDA_TRY(cudaEventRecord(c->ev_packed, c->stream));
   CUDA_TRY(cudaStreamWaitEvent(c->copy_stream, c->ev_packed, 0));
-  if (x) CUDA_TRY(cudaMemcpyAsync(x, dx, n3, cudaMemcpyDeviceToHost, c->copy_stream));
+  // x in B200MD_DL_PARTS pieces of whole atoms, an event behind each: b200md_wait_download_part lets the host turn a
+  // piece around (b200md_put_atoms_range) while the next one is still on the link
+  c->dl_n = n;
+  c->dl_parts = x ? std::min(B200MD_DL_PARTS, std::max(1, n / 65536)) : 0;
+  while ((int)c->ev_dl_part.size() < c->dl_parts) {
+    cudaEvent_t e;
+    CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    c->ev_dl_part.push_back(e);
+  }
+  for (int p = 0; p < c->dl_parts; p++) {
+    const size_t a0 = (size_t)n * p / c->dl_parts, a1 = (size_t)n * (p + 1) / c->dl_parts;
+    CUDA_TRY(cudaMemcpyAsync(x + 3 * a0, dx + 3 * a0, sizeof(double) * 3 * (a1 - a0), cudaMemcpyDeviceToHost, c->copy_stream));
+    CUDA_TRY(cudaEventRecord(c->ev_dl_part[p], c->copy_stream));
+  }
   CUDA_TRY(cudaEventRecord(c->ev_dl_x, c->copy_stream));
   if (f) CUDA_TRY(cudaMemcpyAsync(f, df, n3, cudaMemcpyDeviceToHost, c->copy_stream));
   CUDA_TRY(cudaEventRecord(c->ev_dl_all, c->copy_stream));
@@ -348,6 +362,38 @@ extern "C" int b200md_wait_download(b200md_ctx *c, int all) {
   if (!c->dl_pending) return B200MD_OK;
   CUDA_TRY(cudaEventSynchronize(all ? c->ev_dl_all : c->ev_dl_x));
   if (all) c->dl_pending = false;
+  return B200MD_OK;
+}
+
+extern "C" int b200md_wait_download_part(b200md_ctx *c, int part, int *first, int *count) {
+  NEED(c && first && count, "b200md: null argument");
+  *first = 0; *count = 0;
+  if (!c->dl_pending || part < 0 || part >= c->dl_parts) return B200MD_OK;
+  CUDA_TRY(cudaEventSynchronize(c->ev_dl_part[part]));
+  const size_t a0 = (size_t)c->dl_n * part / c->dl_parts, a1 = (size_t)c->dl_n * (part + 1) / c->dl_parts;
+  *first = (int)a0; *count = (int)(a1 - a0);
+  return B200MD_OK;
+}
+
+// positions of the owned atoms [first, first+count) from the host array x (row 0 = atom 0)
+__global__ void k_put_x_range(int first, int count, const double *__restrict__ x, double4 *__restrict__ xq) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  i += first;
+  double4 q = xq[i]; q.x = x[3 * i]; q.y = x[3 * i + 1]; q.z = x[3 * i + 2]; xq[i] = q;
+}
+extern "C" int b200md_put_atoms_range(b200md_ctx *c, const double *x, int first, int count) {
+  NEED(c && x, "b200md: null argument");
+  NEED(first >= 0 && count >= 0 && first + count <= c->nlocal, "b200md_put_atoms_range: range outside the owned atoms");
+  if (count == 0) return B200MD_OK;
+  CUDA_TRY(cudaSetDevice(c->device));
+  TRY(stage(c, 2 * sizeof(double) * 3 * (size_t)c->nlocal));     // same staging area and size as b200md_put_atoms
+  double *dx = (double *)c->stage;
+  CUDA_TRY(cudaMemcpyAsync(dx + 3 * (size_t)first, x + 3 * (size_t)first, sizeof(double) * 3 * (size_t)count,
+                           cudaMemcpyHostToDevice, c->stream));
+  k_put_x_range<<<(count + 255) / 256, 256, 0, c->stream>>>(first, count, dx, c->xq);
+  c->launches++;
+  CUDA_TRY(cudaGetLastError());
   return B200MD_OK;
 }
 

@@ -282,6 +282,8 @@ struct b200md_ctx {
   char *dl_stage = nullptr;
   size_t dl_cap = 0;
   bool dl_pending = false;
+  std::vector<cudaEvent_t> ev_dl_part;  // x download in pieces (b200md_wait_download_part): one event per piece
+  int dl_parts = 0, dl_n = 0;           // pieces and atoms of the download in flight
   char *stage = nullptr;  // device staging for host<->device atom transfers
   size_t stage_cap = 0;
   // last energies

@@ -291,3 +291,55 @@ def test_graph_mode_is_the_same_run(pkg, kind):
     assert res["on"][2]["nbuilds"] == res["off"][2]["nbuilds"] and res["on"][2]["ndanger"] == res["off"][2]["ndanger"]
     assert res["on"][3] == res["off"][3]
     assert res["on"][2]["nbuilds"] == (6 if kind == "lj" else res["off"][2]["nbuilds"])
+
+
+def test_streamed_offload_boundary_is_the_same_run(pkg):
+    """The e2e boundary of bench.py: a host that takes x and f down and sends x back up every step.  Whole-array
+    blocking copies (put_atoms / get_atoms), the asynchronous download (get_atoms_async / wait_download) and the
+    streamed form (wait_download_part + put_atoms_range piece by piece) must be the SAME run bit for bit on the full
+    list (no atomics), across a rebuild (the local order changes), and the pieces must tile the owned atoms."""
+    B = pkg.b200md
+    res = {}
+    for mode in ("sync", "async", "stream"):
+        ctx = B.Context(0)
+        cfg = pkg.inputs.in_lj(ctx, 2, 2, 2, list_kind=B.LIST_FULL)      # 256 000 atoms: 3 pieces of x
+        ctx.setup()
+        n = ctx.nlocal()[0]
+        hx, hf = B.pinned_empty((n, 3)), B.pinned_empty((n, 3))
+        pieces = []
+        for step in range(25):                                            # rebuild at step 20
+            ctx.run(1, cfg["dt"], 0)
+            if mode == "sync":
+                ctx.get_atoms_into(hx, None, hf, None)
+                ctx.put_atoms(hx, None)
+            elif mode == "async":
+                ctx.get_atoms_async(hx, hf)
+                ctx.wait_download(False)
+                ctx.put_atoms(hx, None)
+                ctx.wait_download(True)
+            else:
+                ctx.get_atoms_async(hx, hf)
+                p, covered = 0, 0
+                while True:
+                    first, count = ctx.wait_download_part(p)
+                    if count == 0:
+                        break
+                    assert first == covered
+                    ctx.put_atoms_range(hx, first, count)
+                    covered += count
+                    p += 1
+                assert covered == n
+                pieces.append(p)
+                ctx.wait_download(True)
+        a = ctx.get_atoms(("x", "v", "f", "tag"))
+        o = np.argsort(a["tag"])
+        res[mode] = (a["x"][o], a["v"][o], a["f"][o], hx.copy(), hf.copy(), ctx.neigh_stats()["nbuilds"])
+        if mode == "stream":
+            assert min(pieces) >= 2, pieces
+            with pytest.raises(B.B200MDError, match="range outside"):
+                ctx.put_atoms_range(hx, n - 10, 11)
+        ctx.close()
+    for mode in ("async", "stream"):
+        for k in range(5):
+            assert np.array_equal(res[mode][k], res["sync"][k]), (mode, k)
+        assert res[mode][5] == res["sync"][5] == 2
