@@ -387,7 +387,8 @@ int b200md_set_lanes_per_atom(b200md_ctx *ctx, int lanes);
  *   overlap      on | off          compute / halo overlap on several ranks
  *   split        0..1              share of the interior tiles evaluated before the boundary tiles
  *   fuse_nve     on | off          final_integrate(n) + initial_integrate(n+1) in one pass (default on)
- *   eam_smem     on | off          one-element EAM tables staged in shared memory (default off)
+ *   eam_smem     on | off | auto   one-element EAM tables staged in shared memory, rows swizzled against bank conflicts
+ *                                  (auto, the default: the force pass only; on: every pass)
  *   phase_timing on | off          per-phase CUDA events in b200md_run (b200md_get_timing)
  *   lanes        1,2,...,32        = b200md_set_lanes_per_atom
  *   build_lanes  1,2,...,32        lanes per atom in the list build

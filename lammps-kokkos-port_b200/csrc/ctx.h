@@ -240,7 +240,8 @@ struct b200md_ctx {
   double split = 0.5;  // share of the interior tiles evaluated before the boundary tiles (half-list overlap)
   bool overlap = true;
   bool fuse_nve = true;   // option fuse_nve: final_integrate(n) + initial_integrate(n+1) in one pass (nve.cu), bit-identical
-  bool eam_smem = false;  // option eam_smem: one-element EAM tables staged in shared memory (measured slower on B200)
+  int eam_smem = -1;      // option eam_smem: one-element EAM tables in shared memory (swizzled rows): -1 auto = the force
+                          // pass only (measured: force 815 -> 756 us, density pass unchanged), 1 every pass, 0 never
   bool phase_timing = false;  // option phase_timing: per-phase CUDA events in b200md_run
   bool trace = false;         // option trace: timestamps of both streams' milestones of every step, printed to stderr after b200md_run
   std::vector<std::pair<std::string, cudaEvent_t>> trace_ev;

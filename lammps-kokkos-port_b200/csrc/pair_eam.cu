@@ -189,20 +189,35 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
 }
 
 // ---- half list: pass 1 without the embedding (every listed pair adds to both atoms) ---------
-template <int TPA, bool ONE>
+// SMEM (one element, table fits): the density rows (32 bytes each) are staged in shared memory, 16-byte chunk k of row m
+// at chunk m*2 + ((k + (m>>2)) & 1): the eight chunks of a 128-byte bank line then belong to (m&3, k ^ parity of m>>2), so
+// a quarter warp reading chunk k of eight unrelated rows spreads over the eight 16-byte bank groups instead of piling onto
+// two of them.  The block walks tiles with a grid stride so that one staging serves many tiles.
+template <int TPA, bool ONE, bool SMEM>
 __global__ void __launch_bounds__(EAM_THREADS, ONE ? EAM_RHO_MINBLOCKS : 4)
 k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh,
                const int *__restrict__ numneigh, int pitch, EamParams P, double *__restrict__ rho,
                const int *__restrict__ tile_list, int ntile_list) {
   constexpr int A = 32 / TPA;
+  extern __shared__ double2 s_rho2[];
+  if (ONE && SMEM) {
+    const double2 *g2 = reinterpret_cast<const double2 *>(P.tabC);
+    const int nq = (P.nr + 1) * 2;
+    for (int q = threadIdx.x; q < nq; q += blockDim.x) {
+      const int m = q >> 1, k = q & 1;
+      s_rho2[m * 2 + ((k + (m >> 2)) & 1)] = g2[m * 4 + k];
+    }
+    __syncthreads();
+  }
   const int lane = threadIdx.x & 31;
   const int sub = lane / TPA, l = lane % TPA;
-  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const bool in_list = !tile_list || w < ntile_list;
-  const int tile = tile_list ? (in_list ? tile_list[w] : 0) : w;
-  const int i = tile * A + sub;
-  const bool active = in_list && i < nlocal;
+  const int wpb = blockDim.x >> 5;
+  const int nwork = tile_list ? ntile_list : (nlocal + A - 1) / A;
   const int nt1 = P.ntypes + 1;
+  for (int w = blockIdx.x * wpb + (threadIdx.x >> 5); w < nwork; w += gridDim.x * wpb) {
+  const int tile = tile_list ? tile_list[w] : w;
+  const int i = tile * A + sub;
+  const bool active = i < nlocal;
   double r_acc = 0;
   if (active) {
     const double4 qi = xq[i];
@@ -224,7 +239,12 @@ k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict
           p -= m;
           p = fmin(p, 1.0);
           if (ONE) {
-            const double4 cf = ld4(P.tabC + (size_t)m * 8);
+            double4 cf;
+            if (SMEM) {
+              const int sw = (m >> 2) & 1;
+              const double2 a = s_rho2[m * 2 + sw], b = s_rho2[m * 2 + (sw ^ 1)];
+              cf = make_double4(a.x, a.y, b.x, b.y);
+            } else cf = ld4(P.tabC + (size_t)m * 8);
             const double d = ((cf.x * p + cf.y) * p + cf.z) * p + cf.w;
             r_acc += d;
             atomicAdd(&rho[j], d);
@@ -248,6 +268,7 @@ k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict
   __syncwarp();
   r_acc = group_sum<TPA>(r_acc);
   if (active && l == 0) atomicAdd(&rho[i], r_acc);
+  }
 }
 
 // embedding for the half-list path (pair_eam.cpp:231-247), one thread per owned atom
@@ -297,24 +318,30 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
             const double *__restrict__ fp, double *__restrict__ f, double *__restrict__ partials,
             const int *__restrict__ tile_list, int ntile_list) {
   constexpr int A = 32 / TPA;
-  extern __shared__ double s_dyn[];
-  const double *tab = P.tabC;
+  // SMEM: the 64-byte rows {density cubic, pair-term cubic} staged in shared memory, 16-byte chunk k of row m at chunk
+  // m*4 + ((k + (m>>1)) & 3) (see k_eam_rho_half: a quarter warp reading chunk k of eight unrelated rows spreads over
+  // the eight 16-byte groups of the banks); the block walks tiles with a grid stride, one staging serves many tiles
+  extern __shared__ double2 s_tab2[];
   if (ONE && SMEM) {
-    const int n8 = (P.nr + 1) * 8;
-    for (int k = threadIdx.x; k < n8; k += blockDim.x) s_dyn[k] = P.tabC[k];
+    const double2 *g2 = reinterpret_cast<const double2 *>(P.tabC);
+    const int nq = (P.nr + 1) * 4;
+    for (int q = threadIdx.x; q < nq; q += blockDim.x) {
+      const int m = q >> 2, k = q & 3;
+      s_tab2[m * 4 + ((k + (m >> 1)) & 3)] = g2[q];
+    }
     __syncthreads();
-    tab = s_dyn;
   }
   const int lane = threadIdx.x & 31;
   const int sub = lane / TPA, l = lane % TPA;
-  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const bool in_list = !tile_list || w < ntile_list;
-  const int tile = tile_list ? (in_list ? tile_list[w] : 0) : w;
-  const int i = tile * A + sub;
-  const bool active = in_list && i < nlocal;
+  const int wpb = blockDim.x >> 5;
+  const int nwork = tile_list ? ntile_list : (nlocal + A - 1) / A;
   const int nt1 = P.ntypes + 1;
-  double fx = 0, fy = 0, fz = 0;
   double ev[7] = {0, 0, 0, 0, 0, 0, 0};
+  for (int w = blockIdx.x * wpb + (threadIdx.x >> 5); w < nwork; w += gridDim.x * wpb) {
+  const int tile = tile_list ? tile_list[w] : w;
+  const int i = tile * A + sub;
+  const bool active = i < nlocal;
+  double fx = 0, fy = 0, fz = 0;
   if (active) {
     const double4 qi = ONE ? xfp[i] : xq[i];
     const int itype = ONE ? 1 : xq_type(qi);
@@ -339,8 +366,17 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
           double rhoip, rhojp, scl, fpj;
           double4 z;
           if (ONE) {
-            const double4 a = ld4(tab + (size_t)m * 8);
-            z = ld4(tab + (size_t)m * 8 + 4);
+            double4 a;
+            if (SMEM) {
+              const int r = m >> 1;
+              const double2 a0 = s_tab2[m * 4 + (r & 3)], a1 = s_tab2[m * 4 + ((r + 1) & 3)];
+              const double2 z0 = s_tab2[m * 4 + ((r + 2) & 3)], z1 = s_tab2[m * 4 + ((r + 3) & 3)];
+              a = make_double4(a0.x, a0.y, a1.x, a1.y);
+              z = make_double4(z0.x, z0.y, z1.x, z1.y);
+            } else {
+              a = ld4(P.tabC + (size_t)m * 8);
+              z = ld4(P.tabC + (size_t)m * 8 + 4);
+            }
             rhoip = rhojp = ((3.0 * a.x * p + 2.0 * a.y) * p + a.z) * P.rdr;
             scl = P.scale11;
             fpj = qj.w;
@@ -386,6 +422,7 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
     if (HALF) { atomicAdd(&f[i], fx); atomicAdd(&f[i + nmax], fy); atomicAdd(&f[i + 2 * (size_t)nmax], fz); }
     else { f[i] = fx; f[i + nmax] = fy; f[i + 2 * (size_t)nmax] = fz; }
   }
+  }
   if (EV) block_reduce_store<7>(ev, partials);
 }
 
@@ -399,8 +436,11 @@ template <int TPA, bool EV, bool ONE, bool SMEM>
 static int launch_pass(b200md_ctx *c, const EamLaunch &L, int pass, const int *tiles, int ntl) {
   const int A = 32 / TPA;
   const int ntiles = tiles ? ntl : (c->nlocal + A - 1) / A;
-  const int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
+  int nblocks = (ntiles + EAM_THREADS / 32 - 1) / (EAM_THREADS / 32);
   if (nblocks == 0) return B200MD_OK;
+  // shared-memory tables: resident blocks only (grid-stride over the tiles), so the table is staged once per block slot
+  // (not on tally steps: the callers reduce one row of partial sums per block of the full grid)
+  if (SMEM && !EV && pass >= 1) nblocks = std::min(nblocks, B200_SMS * (pass == 2 ? EAM_RHO_MINBLOCKS : EAM_FORCE_MINBLOCKS));
   if (pass == 0) {
     auto k = k_eam_rho_fp<TPA, EV, ONE, SMEM>;
     if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem));
@@ -412,10 +452,14 @@ static int launch_pass(b200md_ctx *c, const EamLaunch &L, int pass, const int *t
     k<<<nblocks, EAM_THREADS, SMEM ? L.smem : 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh,
                                                             c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl);
   } else if (pass == 2) {   // half list, density of both atoms of a pair
-    k_eam_rho_half<TPA, ONE><<<nblocks, EAM_THREADS, 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch,
-                                                                   L.P, c->rho, tiles, ntl);
+    auto k = k_eam_rho_half<TPA, ONE, SMEM>;
+    if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(L.smem / 2)));
+    k<<<nblocks, EAM_THREADS, SMEM ? L.smem / 2 : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, L.P, c->rho,
+                                                                tiles, ntl);
   } else {                  // half list, forces
-    k_eam_force<TPA, EV, ONE, false, true><<<nblocks, EAM_THREADS, 0, c->stream>>>(
+    auto k = k_eam_force<TPA, EV, ONE, SMEM, true>;
+    if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem));
+    k<<<nblocks, EAM_THREADS, SMEM ? L.smem : 0, c->stream>>>(
         c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh, c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl);
   }
   c->launches++; c->pair_launches++;
@@ -424,7 +468,9 @@ static int launch_pass(b200md_ctx *c, const EamLaunch &L, int pass, const int *t
 }
 template <int TPA, bool EV>
 static int launch_mode(b200md_ctx *c, const EamLaunch &L, int pass, const int *tiles, int ntl) {
-  if (L.mode == 2) return launch_pass<TPA, EV, true, true>(c, L, pass, tiles, ntl);
+  const bool force_pass = pass == 1 || pass == 3;
+  if (L.mode == 2 && (force_pass || c->eam_smem > 0)) return launch_pass<TPA, EV, true, true>(c, L, pass, tiles, ntl);
+  if (L.mode == 2) return launch_pass<TPA, EV, true, false>(c, L, pass, tiles, ntl);
   if (L.mode == 1) return launch_pass<TPA, EV, true, false>(c, L, pass, tiles, ntl);
   return launch_pass<TPA, EV, false, false>(c, L, pass, tiles, ntl);
 }
@@ -720,10 +766,11 @@ static int eam_prepare(b200md_ctx *c, EamLaunch &L) {
   }
   L.P = pair_eam_params(c);
   L.smem = (size_t)(e.nr + 1) * 8 * sizeof(double);
-  // measured on B200 (2.05 M atoms, Cu_u3): tabC through L1 752 Matom-steps/s, staged in shared
-  // memory 681 (bank conflicts on the random rows + lower occupancy) -> global is the default
+  // measured on B200 (2.05 M atoms, Cu_u3, half list): rows copied as they are into shared memory pile the reads of a
+  // quarter warp onto two 16-byte bank groups (round 1: 681 against 752 Matom-steps/s through L1); with the rows
+  // swizzled the force pass gains 7 % (815 -> 756 us), the density pass nothing (460 -> 462 us).  auto: force pass only.
   L.mode = 0;
-  if (e.one) L.mode = (L.smem <= 64 * 1024 && c->eam_smem) ? 2 : 1;
+  if (e.one) L.mode = (L.smem <= 64 * 1024 && c->eam_smem != 0) ? 2 : 1;
   return B200MD_OK;
 }
 
