@@ -233,7 +233,7 @@ k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict
         const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
         const double rsq = rsq_nofma(dx, dy, dz);
         if (rsq < P.cutforcesq) {
-          double p = sqrt(rsq) * P.rdr + 1.0;
+          double p = (rsq * rsqrt_nr(rsq)) * P.rdr + 1.0;
           int m = (int)p;
           m = min(m, P.nr - 1);
           p -= m;
@@ -357,7 +357,8 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
         const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
         const double rsq = rsq_nofma(dx, dy, dz);
         if (rsq < P.cutforcesq) {
-          const double r = sqrt(rsq);
+          const double recip = rsqrt_nr(rsq);     // 1/r and r = rsq/r to rounding error: no IEEE sqrt / division sequences
+          const double r = rsq * recip;
           double p = r * P.rdr + 1.0;
           int m = (int)p;
           m = min(m, P.nr - 1);
@@ -396,7 +397,6 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
           }
           const double z2p = ((3.0 * z.x * p + 2.0 * z.y) * p + z.z) * P.rdr;
           const double z2 = ((z.x * p + z.y) * p + z.z) * p + z.w;
-          const double recip = 1.0 / r;
           const double phi = z2 * recip;
           const double phip = z2p * recip - phi * recip;
           const double psip = fpi * rhojp + fpj * rhoip + phip;
