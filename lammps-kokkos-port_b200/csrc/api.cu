@@ -672,6 +672,9 @@ extern "C" int b200md_set_option(b200md_ctx *c, const char *key, const char *val
       NEED(opt_bool(value, &b), "Illegal package b200 command: eam_smem must be on, off or auto");
       c->eam_smem = b ? 1 : 0;
     }
+  } else if (k == "eam_mask") {
+    NEED(opt_bool(value, &b), "Illegal package b200 command: eam_mask must be on or off");
+    c->eam_mask = b;
   } else if (k == "cluster") {
     if (!strcmp(value, "auto")) c->use_cluster = -1;
     else {
@@ -712,6 +715,7 @@ extern "C" int b200md_get_option(b200md_ctx *c, const char *key, char *value, in
   else if (k == "split") v = std::to_string(c->split);
   else if (k == "fuse_nve") v = c->fuse_nve ? "on" : "off";
   else if (k == "eam_smem") v = c->eam_smem < 0 ? "auto" : (c->eam_smem ? "on" : "off");
+  else if (k == "eam_mask") v = c->eam_mask ? "on" : "off";
   else if (k == "graph") v = c->sg.mode < 0 ? "auto" : (c->sg.mode ? "on" : "off");
   else if (k == "cluster") v = c->use_cluster < 0 ? "auto" : (c->use_cluster ? "on" : "off");
   else if (k == "phase_timing") v = c->phase_timing ? "on" : "off";

@@ -32,6 +32,8 @@ struct EamTables {
   double *tabC = nullptr;   // [nr+1][8]           one-element runs: {rhoA row, z2rV row}
   double4 *xfp = nullptr;   // [nmax]              one-element runs: {x,y,z,fp} gather record
   int xfp_cap = 0;
+  unsigned *pmask = nullptr; // [tiles][4][32] half list: bit `it` of a lane's 128 = its it-th list entry is inside the force cutoff this step
+  size_t pmask_cap = 0;     //              (written by the density pass, walked by the force pass)
   bool one = false;
   double scale11 = 1.0;
   int *type2frho = nullptr; // [ntypes+1]
@@ -240,6 +242,7 @@ struct b200md_ctx {
   double split = 0.5;  // share of the interior tiles evaluated before the boundary tiles (half-list overlap)
   bool overlap = true;
   bool fuse_nve = true;   // option fuse_nve: final_integrate(n) + initial_integrate(n+1) in one pass (nve.cu), bit-identical
+  bool eam_mask = true;   // option eam_mask: the force pass walks only the pairs the density pass found inside the cutoff
   int eam_smem = -1;      // option eam_smem: one-element EAM tables in shared memory (swizzled rows): -1 auto = the force
                           // pass only (measured: force 815 -> 756 us, density pass unchanged), 1 every pass, 0 never
   bool phase_timing = false;  // option phase_timing: per-phase CUDA events in b200md_run

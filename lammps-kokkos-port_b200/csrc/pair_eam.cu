@@ -46,7 +46,7 @@
 
 void pair_eam_free(b200md_ctx *c) {
   EamTables &e = c->eam;
-  void *p[] = {e.frho, e.rhoA, e.z2rV, e.tabC, e.type2frho, e.type2rhor, e.type2z2r, e.scale, e.xfp};
+  void *p[] = {e.frho, e.rhoA, e.z2rV, e.tabC, e.type2frho, e.type2rhor, e.type2z2r, e.scale, e.xfp, e.pmask};
   for (void *q : p) if (q) cudaFree(q);
   e = EamTables();
 }
@@ -193,11 +193,13 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
 // at chunk m*2 + ((k + (m>>2)) & 1): the eight chunks of a 128-byte bank line then belong to (m&3, k ^ parity of m>>2), so
 // a quarter warp reading chunk k of eight unrelated rows spreads over the eight 16-byte bank groups instead of piling onto
 // two of them.  The block walks tiles with a grid stride so that one staging serves many tiles.
-template <int TPA, bool ONE, bool SMEM>
+// MASK: every lane records which of its list entries were inside the force cutoff (bit `it` of a 128-bit mask per
+// lane); positions do not change before the force pass of the same step, which then walks the set bits only.
+template <int TPA, bool ONE, bool SMEM, bool MASK>
 __global__ void __launch_bounds__(EAM_THREADS, ONE ? EAM_RHO_MINBLOCKS : 4)
 k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh,
                const int *__restrict__ numneigh, int pitch, EamParams P, double *__restrict__ rho,
-               const int *__restrict__ tile_list, int ntile_list) {
+               const int *__restrict__ tile_list, int ntile_list, unsigned *__restrict__ pmask) {
   constexpr int A = 32 / TPA;
   extern __shared__ double2 s_rho2[];
   if (ONE && SMEM) {
@@ -219,20 +221,25 @@ k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict
   const int i = tile * A + sub;
   const bool active = i < nlocal;
   double r_acc = 0;
+  unsigned mk = 0;          // MASK: the current 32 entries of this lane; words go to pmask[tile][word][lane] as they fill
+  int nit = 0;
   if (active) {
     const double4 qi = xq[i];
     const int itype = ONE ? 1 : xq_type(qi);
     const int n = numneigh[i];
     const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
     const int niter = (n + TPA - 1) / TPA;
+    nit = niter;
 #pragma unroll kRhoUnroll
     for (int it = 0; it < niter; it++) {
+      if (MASK && it && !(it & 31)) { pmask[((size_t)tile * 4 + (it >> 5) - 1) * 32 + lane] = mk; mk = 0; }
       if (it * TPA + l < n) {
         const int j = __ldg(nb + it * 32);
         const double4 qj = ld_xq(&xq[j]);
         const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
         const double rsq = rsq_nofma(dx, dy, dz);
         if (rsq < P.cutforcesq) {
+          if (MASK) mk |= 1u << (it & 31);
           double p = (rsq * rsqrt_nr(rsq)) * P.rdr + 1.0;
           int m = (int)p;
           m = min(m, P.nr - 1);
@@ -268,6 +275,10 @@ k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict
   __syncwarp();
   r_acc = group_sum<TPA>(r_acc);
   if (active && l == 0) atomicAdd(&rho[i], r_acc);
+  if (MASK) {   // the word in progress, zeros behind it (words already flushed: those below (nit-1)/32)
+    const int w0 = nit ? (nit - 1) >> 5 : 0;
+    for (int wd = w0; wd < 4; wd++) pmask[((size_t)tile * 4 + wd) * 32 + lane] = wd == w0 ? mk : 0u;
+  }
   }
 }
 
@@ -311,12 +322,15 @@ __global__ void k_pack_xfp(int nghost, int nlocal, const double4 *__restrict__ x
 }
 
 // ---- pass 3: forces -------------------------------------------------------------------------
-template <int TPA, bool EV, bool ONE, bool SMEM, bool HALF>
+// MASK (half list): walk only the entries k_eam_rho_half<…,MASK> marked as inside the cutoff this step — no gather, no
+// distance test and no idle lane-iterations for the ~40 % of a skin-1.0 list that lie beyond it; the next entry and its
+// record are fetched while the current pair is evaluated.
+template <int TPA, bool EV, bool ONE, bool SMEM, bool HALF, bool MASK>
 __global__ void __launch_bounds__(EAM_THREADS, EAM_FORCE_MINBLOCKS)
 k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 *__restrict__ xfp,
             const int *__restrict__ neigh, const int *__restrict__ numneigh, int pitch, EamParams P,
             const double *__restrict__ fp, double *__restrict__ f, double *__restrict__ partials,
-            const int *__restrict__ tile_list, int ntile_list) {
+            const int *__restrict__ tile_list, int ntile_list, const unsigned *__restrict__ pmask) {
   constexpr int A = 32 / TPA;
   // SMEM: the 64-byte rows {density cubic, pair-term cubic} staged in shared memory, 16-byte chunk k of row m at chunk
   // m*4 + ((k + (m>>1)) & 3) (see k_eam_rho_half: a quarter warp reading chunk k of eight unrelated rows spreads over
@@ -349,14 +363,10 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
     const int n = numneigh[i];
     const int *nb = neigh + (size_t)tile * pitch * A + sub * TPA + l;
     const int niter = (n + TPA - 1) / TPA;
-#pragma unroll kForceUnroll
-    for (int it = 0; it < niter; it++) {
-      if (it * TPA + l < n) {
-        const int j = __ldg(nb + it * 32);
-        const double4 qj = ld_xq(ONE ? &xfp[j] : &xq[j]);
+    auto pair = [&](const int j, const double4 qj) {
         const double dx = qi.x - qj.x, dy = qi.y - qj.y, dz = qi.z - qj.z;
         const double rsq = rsq_nofma(dx, dy, dz);
-        if (rsq < P.cutforcesq) {
+        if (MASK || rsq < P.cutforcesq) {
           const double recip = rsqrt_nr(rsq);     // 1/r and r = rsq/r to rounding error: no IEEE sqrt / division sequences
           const double r = rsq * recip;
           double p = r * P.rdr + 1.0;
@@ -413,6 +423,32 @@ k_eam_force(int nlocal, int nmax, const double4 *__restrict__ xq, const double4 
             ev[4] += dx * dy * fpair; ev[5] += dx * dz * fpair; ev[6] += dy * dz * fpair;
           }
         }
+    };
+    if (MASK) {
+      const unsigned *pm = pmask + (size_t)tile * 128 + lane;
+      unsigned long long m0 = pm[0] | ((unsigned long long)pm[32] << 32), m1 = pm[64] | ((unsigned long long)pm[96] << 32);
+      auto next = [&]() -> int {
+        if (m0) { const int b = __ffsll((long long)m0) - 1; m0 &= m0 - 1; return b; }
+        if (m1) { const int b = __ffsll((long long)m1) - 1; m1 &= m1 - 1; return 64 + b; }
+        return -1;
+      };
+      int it = next();
+      int j = it >= 0 ? __ldg(nb + it * 32) : i;
+      double4 qj = ld_xq(ONE ? &xfp[j] : &xq[j]);
+      while (it >= 0) {
+        const int itn = next();
+        const int jn = itn >= 0 ? __ldg(nb + itn * 32) : i;
+        const double4 qn = ld_xq(ONE ? &xfp[jn] : &xq[jn]);
+        pair(j, qj);
+        it = itn; j = jn; qj = qn;
+      }
+    } else {
+#pragma unroll kForceUnroll
+      for (int it = 0; it < niter; it++) {
+        if (it * TPA + l < n) {
+          const int j = __ldg(nb + it * 32);
+          pair(j, ld_xq(ONE ? &xfp[j] : &xq[j]));
+        }
       }
     }
   }
@@ -430,6 +466,7 @@ struct EamLaunch {
   EamParams P;
   int mode;      // 0 general (multi-type), 1 one element / tables via L1, 2 one element / tables in shared memory
   size_t smem;
+  bool mask;     // half list: density pass records the in-cutoff entries, force pass walks them
 };
 
 template <int TPA, bool EV, bool ONE, bool SMEM>
@@ -447,20 +484,21 @@ static int launch_pass(b200md_ctx *c, const EamLaunch &L, int pass, const int *t
     k<<<nblocks, EAM_THREADS, SMEM ? L.smem : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, L.P, c->rho,
                                                             c->fp, c->eam.xfp, c->partials, tiles, ntl);
   } else if (pass == 1) {
-    auto k = k_eam_force<TPA, EV, ONE, SMEM, false>;
+    auto k = k_eam_force<TPA, EV, ONE, SMEM, false, false>;
     if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem));
     k<<<nblocks, EAM_THREADS, SMEM ? L.smem : 0, c->stream>>>(c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh,
-                                                            c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl);
+                                                            c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl, nullptr);
   } else if (pass == 2) {   // half list, density of both atoms of a pair
-    auto k = k_eam_rho_half<TPA, ONE, SMEM>;
+    auto k = L.mask ? k_eam_rho_half<TPA, ONE, SMEM, true> : k_eam_rho_half<TPA, ONE, SMEM, false>;
     if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(L.smem / 2)));
     k<<<nblocks, EAM_THREADS, SMEM ? L.smem / 2 : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, L.P, c->rho,
-                                                                tiles, ntl);
+                                                                tiles, ntl, c->eam.pmask);
   } else {                  // half list, forces
-    auto k = k_eam_force<TPA, EV, ONE, SMEM, true>;
+    auto k = L.mask ? k_eam_force<TPA, EV, ONE, SMEM, true, true> : k_eam_force<TPA, EV, ONE, SMEM, true, false>;
     if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem));
     k<<<nblocks, EAM_THREADS, SMEM ? L.smem : 0, c->stream>>>(
-        c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh, c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl);
+        c->nlocal, c->nmax, c->xq, c->eam.xfp, c->neigh, c->numneigh, c->pitch, L.P, c->fp, c->f, c->partials, tiles, ntl,
+        c->eam.pmask);
   }
   c->launches++; c->pair_launches++;
   CUDA_TRY(cudaGetLastError());
@@ -765,6 +803,16 @@ static int eam_prepare(b200md_ctx *c, EamLaunch &L) {
     e.xfp_cap = c->nmax;
   }
   L.P = pair_eam_params(c);
+  // in-cutoff masks (half list, per-atom rows): 128 bits per lane, one lane's share of a row must fit
+  L.mask = c->eam_mask && c->list_kind == B200MD_LIST_HALF_NEWTON && !c->cluster && c->pitch / c->tpa <= 128;
+  if (L.mask) {
+    const size_t need = ((size_t)c->nmax / (32 / c->tpa) + 2) * 32;
+    if (need > e.pmask_cap) {
+      if (e.pmask) CUDA_TRY(cudaFree(e.pmask));
+      CUDA_TRY(cudaMalloc(&e.pmask, sizeof(unsigned) * 4 * need));
+      e.pmask_cap = need;
+    }
+  }
   L.smem = (size_t)(e.nr + 1) * 8 * sizeof(double);
   // measured on B200 (2.05 M atoms, Cu_u3, half list): rows copied as they are into shared memory pile the reads of a
   // quarter warp onto two 16-byte bank groups (round 1: 681 against 752 Matom-steps/s through L1); with the rows
