@@ -37,14 +37,20 @@ sys.path.insert(0, ROOT)
 SCALE = {1: (4, 4, 4), 2: (8, 4, 4), 4: (8, 8, 4), 8: (8, 8, 8)}
 # algorithmic bytes: force pass(es) per owned atom per step, and whole step per atom-step.
 # N = full-list length, N_h = N/2.  full list: LJ 28N+52, EAM 64N+104; half list: LJ 52 N_h + 52 (4 index + 24 x_j
-# gathered + 24 f_j RED payload per listed pair), EAM 96 N_h + 104.
+# gathered + 24 f_j RED payload per listed pair), EAM (36 + 60 r) N_h + 136 with r = in-cutoff share (below).
 N_FULL = {"lj": 75.2, "eam": 75.5, "c5": 88.8}
 BYTES_KERNEL = {k: {"full": (28 if k == "lj" else 64) * n + (52 if k == "lj" else 104),
                     "half": (52 if k == "lj" else 96) * n / 2 + (52 if k == "lj" else 104)} for k, n in N_FULL.items()}
+# eam half list with in-cutoff masks: the density pass moves 4 + 24 + 8 (RED) per LISTED pair, the force pass
+# 4 + 24 + 8 + 24 (RED) per pair INSIDE the force cutoff only — share (cutforce / cutneigh)^3 of a list built with skin 1.0 —
+# plus 32 bytes of masks per atom written and read
+IN_CUTOFF = {"eam": (4.95 / 5.95) ** 3, "c5": (5.50679 / 6.50679) ** 3}
+for _k, _r in IN_CUTOFF.items():
+    BYTES_KERNEL[_k]["half"] = (36 + 60 * _r) * N_FULL[_k] / 2 + 104 + 32
 BYTES_STEP = {"lj": 2480.0, "eam": 5510.0, "c5": 6420.0}
 KERNELS = {("lj", "half"): "k_lj<half>", ("lj", "full"): "k_lj<full>",
-           ("eam", "half"): "k_eam_rho_half+k_eam_embed+k_eam_force<half>", ("eam", "full"): "k_eam_rho_fp+k_eam_force",
-           ("c5", "half"): "k_eam_rho_half+k_eam_embed+k_eam_force<half>", ("c5", "full"): "k_eam_rho_fp+k_eam_force"}
+           ("eam", "half"): "k_eam_rho_half<mask>+k_eam_embed+k_eam_force<half,mask>", ("eam", "full"): "k_eam_rho_fp+k_eam_force",
+           ("c5", "half"): "k_eam_rho_half<mask>+k_eam_embed+k_eam_force<half,mask>", ("c5", "full"): "k_eam_rho_fp+k_eam_force"}
 # thermo printed by the reference's own logs (bench/log.6Oct16.{lj,eam}.fixed.icc.1): T, E_pair, TotEng, Press
 LOG = {"lj": {0: (1.44, -6.7733681, -4.6134356, -5.0197073), 100: (0.7574531, -5.7585055, -4.6223613, 0.20726105)},
        "eam": {0: (1600.0, -113280.0, -106662.09, 18703.573), 50: (781.69049, -109873.35, -106640.13, 52273.088),
