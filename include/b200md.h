@@ -389,6 +389,8 @@ int b200md_set_lanes_per_atom(b200md_ctx *ctx, int lanes);
  *   fuse_nve     on | off          final_integrate(n) + initial_integrate(n+1) in one pass (default on)
  *   eam_smem     on | off | auto   one-element EAM tables staged in shared memory, rows swizzled against bank conflicts
  *                                  (auto, the default: the force pass only; on: every pass)
+ *   eam_mask     on | off          half list: the density pass marks the list entries inside the force cutoff, the force
+ *                                  pass walks only those (default on)
  *   phase_timing on | off          per-phase CUDA events in b200md_run (b200md_get_timing)
  *   lanes        1,2,...,32        = b200md_set_lanes_per_atom
  *   build_lanes  1,2,...,32        lanes per atom in the list build
