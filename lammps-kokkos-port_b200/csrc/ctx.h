@@ -318,7 +318,10 @@ void b200md_set_error(const std::string &msg);
   } while (0)
 
 // list units: what a group of `tpa` lanes works on — an atom, or a cluster of 4 atoms (neigh.cu)
-static inline int list_units(const b200md_ctx *c) { return c->cluster ? (c->nlocal + 3) / 4 : c->nlocal; }
+#ifndef CL
+#define CL 4   // atoms per i-cluster of the cluster-pair list (util.cuh)
+#endif
+static inline int list_units(const b200md_ctx *c) { return c->cluster ? (c->nlocal + CL - 1) / CL : c->nlocal; }
 static inline int list_tiles(const b200md_ctx *c) { const int A = 32 / c->tpa; return (list_units(c) + A - 1) / A; }
 
 // ---- kernels' host launchers ----

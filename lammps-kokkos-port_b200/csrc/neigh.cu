@@ -702,7 +702,7 @@ k_build_cluster(int nlocal, int ncl, const double4 *__restrict__ xq, const int *
         if (m) {
           const int d = j - i0;
           if (HALF) {
-            if (j < nlocal) m &= d <= 0 ? 0u : (d >= CL ? 0xfu : (1u << d) - 1u);   // owned j pairs with the atoms before it
+            if (j < nlocal) m &= d <= 0 ? 0u : (d >= CL ? CL_FULL : (1u << d) - 1u);   // owned j pairs with the atoms before it
             else {
 #pragma unroll
               for (int a = 0; a < CL; a++) {
@@ -805,7 +805,7 @@ k_build_cluster_mt(int nlocal, int ncl, const double4 *__restrict__ xq, const in
           if (m) {
             const int d = j - i0;
             if (HALF) {
-              if (j < nlocal) m &= d <= 0 ? 0u : (d >= CL ? 0xfu : (1u << d) - 1u);
+              if (j < nlocal) m &= d <= 0 ? 0u : (d >= CL ? CL_FULL : (1u << d) - 1u);
               else {
 #pragma unroll
                 for (int a = 0; a < CL; a++) {

@@ -62,7 +62,10 @@ __device__ __forceinline__ void block_reduce_store(double (&val)[NV], double *ou
 }
 
 // cluster-pair list (neigh.cu): CL owned atoms share one j-list, entry = j | mask << CL_SHIFT
+#ifndef CL
 #define CL 4
+#endif
+#define CL_FULL ((1u << CL) - 1u)
 #define CL_SHIFT 28
 #define CL_JMASK 0x0fffffff
 
