@@ -482,6 +482,7 @@ extern "C" int b200md_neigh_decide(b200md_ctx *c, int *rebuild) {
 extern "C" int b200md_neigh_build(b200md_ctx *c) {
   NEED(c && c->neigh_configured, "b200md: neighbor not configured");
   CUDA_TRY(cudaSetDevice(c->device));
+  TRY(neigh_choose_layout(c));
   TRY(neigh_pbc(c));
   TRY(comm_exchange(c));
   if (c->lang.on && c->lang.resort_pending) {   // Verlet::run's Atom::sort (verlet.cpp:285): the draws follow the new order
@@ -672,6 +673,17 @@ extern "C" int b200md_set_option(b200md_ctx *c, const char *key, const char *val
       NEED(opt_bool(value, &b), "Illegal package b200 command: eam_smem must be on, off or auto");
       c->eam_smem = b ? 1 : 0;
     }
+  } else if (k == "cell_order") {
+    if (!strcmp(value, "x")) c->cell_by_x = true;
+    else if (!strcmp(value, "index")) c->cell_by_x = false;
+    else { b200md_set_error("Illegal package b200 command: cell_order must be x or index"); return B200MD_ERR; }
+  } else if (k == "bin_scale") {
+    if (!strcmp(value, "auto")) c->bin_scale_user = 0;
+    else {
+      const double v = atof(value);
+      NEED(v >= 0.25 && v <= 4.0, "Illegal package b200 command: bin_scale must be auto or in [0.25,4]");
+      c->bin_scale_user = v;
+    }
   } else if (k == "eam_mask") {
     NEED(opt_bool(value, &b), "Illegal package b200 command: eam_mask must be on or off");
     c->eam_mask = b;
@@ -716,6 +728,8 @@ extern "C" int b200md_get_option(b200md_ctx *c, const char *key, char *value, in
   else if (k == "fuse_nve") v = c->fuse_nve ? "on" : "off";
   else if (k == "eam_smem") v = c->eam_smem < 0 ? "auto" : (c->eam_smem ? "on" : "off");
   else if (k == "eam_mask") v = c->eam_mask ? "on" : "off";
+  else if (k == "bin_scale") v = c->bin_scale_user > 0 ? std::to_string(c->bin_scale_user) : "auto";
+  else if (k == "cell_order") v = c->cell_by_x ? "x" : "index";
   else if (k == "graph") v = c->sg.mode < 0 ? "auto" : (c->sg.mode ? "on" : "off");
   else if (k == "cluster") v = c->use_cluster < 0 ? "auto" : (c->use_cluster ? "on" : "off");
   else if (k == "phase_timing") v = c->phase_timing ? "on" : "off";

@@ -242,6 +242,9 @@ struct b200md_ctx {
   double split = 0.5;  // share of the interior tiles evaluated before the boundary tiles (half-list overlap)
   bool overlap = true;
   bool fuse_nve = true;   // option fuse_nve: final_integrate(n) + initial_integrate(n+1) in one pass (nve.cu), bit-identical
+  bool cell_by_x = true;   // option cell_order: atoms of a bin ordered by x (then index / tag) instead of index / tag
+  double bin_scale = 1.0;  // neighbor bins of bin_scale x cutneighmax/2 in use (neigh_choose_layout)
+  double bin_scale_user = 0; // option bin_scale: > 0 fixes it, 0 = auto
   bool eam_mask = true;   // option eam_mask: the force pass walks only the pairs the density pass found inside the cutoff
   int eam_smem = -1;      // option eam_smem: one-element EAM tables in shared memory (swizzled rows): -1 auto = the force
                           // pass only (measured: force 815 -> 756 us, density pass unchanged), 1 every pass, 0 never
@@ -328,6 +331,7 @@ static inline int list_tiles(const b200md_ctx *c) { const int A = 32 / c->tpa; r
 // neigh.cu
 int neigh_grow_atoms(b200md_ctx *c, int need);   // grow per-atom arrays to >= need
 int neigh_setup_bins(b200md_ctx *c);             // geometry + stencil rows
+int neigh_choose_layout(b200md_ctx *c);          // bin size for the configured pair style / topology (every rebuild)
 int neigh_pbc(b200md_ctx *c);                    // Domain::pbc on owned atoms
 int neigh_sort_owned(b200md_ctx *c);             // bin-order sort of owned atoms
 int neigh_bin_all(b200md_ctx *c);                // cell lists over owned+ghost

@@ -125,8 +125,33 @@ static double bin_distance(const b200md_bin_geometry &g, int i, int j, int k) {
   return delx * delx + dely * dely + delz * delz;
 }
 
+// Bin size and list layout for the system as it is configured now (pair style and topology may arrive after
+// b200md_neigh_config): called at the start of every rebuild, re-derives the bins only when the choice changed.
+// Measured on B200 at 2.05 M atoms: cluster rows want about one 4-atom cluster per bin (1.2 x the
+// reference's cutneighmax/2: the cluster is then roughly cubic, pair 0.436 -> 0.402 ms), per-atom rows of atomic systems
+// thin bin rows (0.6 x: the lists of the 32 atoms of a warp become shifted copies of one another, eam pair 1.13 -> 0.99 ms),
+// short-cutoff molecular systems fewer bins (2 x: in.chain has 5.5 M bins to scan at 1 x).
+int neigh_choose_layout(b200md_ctx *c) {
+  const bool cluster = !c->topo.molecular && (c->use_cluster < 0 ? c->pair_style == B200MD_PAIR_LJ_CUT : c->use_cluster != 0);
+  const double want = c->bin_scale_user > 0 ? c->bin_scale_user : (cluster ? 1.2 : (c->topo.molecular ? 2.0 : 0.6));
+  if (want != c->bin_scale) {
+    c->bin_scale = want;
+    TRY(neigh_setup_bins(c));
+  }
+  return B200MD_OK;
+}
+
 int neigh_setup_bins(b200md_ctx *c) {
-  TRY(b200md_bin_setup(c->boxlo, c->boxhi, c->sublo, c->subhi, c->cutghost, c->cutneighmax, &c->bin));
+  // bins of bin_scale x cutneighmax/2 (1 = the reference's size, NBinStandard::setup_bins).  List membership is decided by
+  // distance, so the bin size is a device-side choice: the stencil rows below are cut by bin_distance < cutneighmax^2
+  // whatever extents the geometry reports.
+  TRY(b200md_bin_setup(c->boxlo, c->boxhi, c->sublo, c->subhi, c->cutghost, c->cutneighmax * c->bin_scale, &c->bin));
+  if (c->bin_scale != 1.0) {   // stencil extents for the real cutoff (NStencil::create_setup, nstencil.cpp:213-247)
+    b200md_bin_geometry &b = c->bin;
+    b.sx = (int)(c->cutneighmax * b.bininvx); if (b.sx * b.binsizex < c->cutneighmax) b.sx++;
+    b.sy = (int)(c->cutneighmax * b.bininvy); if (b.sy * b.binsizey < c->cutneighmax) b.sy++;
+    b.sz = (int)(c->cutneighmax * b.bininvz); if (b.sz * b.binsizez < c->cutneighmax) b.sz++;
+  }
   const b200md_bin_geometry &g = c->bin;
   long long mb = (long long)g.mbinx * g.mbiny * g.mbinz;
   if (mb + 1 > 2147483647LL) { b200md_set_error("Too many neighbor bins"); return B200MD_ERR; }
@@ -332,8 +357,15 @@ __global__ void k_bin_scatter(const int *__restrict__ atom_bin, int n, const int
 // linked lists (nbin_standard.cpp:252-257: owned ascending, ghosts last).  BYTAG = true (direct halo on several
 // ranks, where arrivals and ghosts are placed through atomic slot counters): owned atoms by tag, then ghosts by
 // (tag, z, y, x) — independent of the order the messages were filled in, and of the decomposition.
-template <bool BYTAG>
+// BYX (option cell_order x): ascending x first.  Atoms that follow each other in memory then follow each other along
+// the bin row, so the lists of the 32 atoms of a warp are shifted copies of one another and their gathers and REDs of
+// the same iteration fall into the same lines (eam, per-atom rows: pair time -5 %).
+template <bool BYTAG, bool BYX>
 __device__ __forceinline__ bool cell_before(int a, int b, int nlocal, const int *__restrict__ tag, const double4 *__restrict__ xq) {
+  if (BYX) {
+    const double xa = xq[a].x, xb = xq[b].x;
+    if (xa != xb) return xa < xb;
+  }
   if (!BYTAG) return a < b;
   const bool ga = a >= nlocal, gb = b >= nlocal;
   if (ga != gb) return gb;
@@ -345,7 +377,7 @@ __device__ __forceinline__ bool cell_before(int a, int b, int nlocal, const int 
   if (qa.y != qb.y) return qa.y < qb.y;
   return qa.x < qb.x;
 }
-template <bool BYTAG>
+template <bool BYTAG, bool BYX>
 __global__ void k_cell_sort(const int *__restrict__ cell_start, int *__restrict__ cell_atoms, int mbins, int nlocal,
                             const int *__restrict__ tag, const double4 *__restrict__ xq) {
   int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -353,7 +385,7 @@ __global__ void k_cell_sort(const int *__restrict__ cell_start, int *__restrict_
   int s = cell_start[b], e = cell_start[b + 1];
   for (int a = s + 1; a < e; a++) {
     int key = cell_atoms[a], k = a - 1;
-    while (k >= s && cell_before<BYTAG>(key, cell_atoms[k], nlocal, tag, xq)) { cell_atoms[k + 1] = cell_atoms[k]; k--; }
+    while (k >= s && cell_before<BYTAG, BYX>(key, cell_atoms[k], nlocal, tag, xq)) { cell_atoms[k + 1] = cell_atoms[k]; k--; }
     cell_atoms[k + 1] = key;
   }
 }
@@ -369,8 +401,14 @@ static int bin_range(b200md_ctx *c, int n, int nown, const int *dead) {
   if (n > 0) k_bin_count<<<(n + 255) / 256, 256, 0, s>>>(c->xq, n, p, c->atom_bin, c->cell_count, c->d_flags, dead, c->mbins);
   TRY(dev_exclusive_scan(c, c->cell_count, c->cell_start, nb + 1));
   if (n > 0) k_bin_scatter<<<(n + 255) / 256, 256, 0, s>>>(c->atom_bin, n, c->cell_start, c->cell_fill, c->cell_atoms);
-  if (c->h26.on) k_cell_sort<true><<<(c->mbins + 255) / 256, 256, 0, s>>>(c->cell_start, c->cell_atoms, c->mbins, nown, c->tag, c->xq);
-  else k_cell_sort<false><<<(c->mbins + 255) / 256, 256, 0, s>>>(c->cell_start, c->cell_atoms, c->mbins, nown, c->tag, c->xq);
+  const int nbk = (c->mbins + 255) / 256;
+  if (c->cell_by_x) {
+    if (c->h26.on) k_cell_sort<true, true><<<nbk, 256, 0, s>>>(c->cell_start, c->cell_atoms, c->mbins, nown, c->tag, c->xq);
+    else k_cell_sort<false, true><<<nbk, 256, 0, s>>>(c->cell_start, c->cell_atoms, c->mbins, nown, c->tag, c->xq);
+  } else {
+    if (c->h26.on) k_cell_sort<true, false><<<nbk, 256, 0, s>>>(c->cell_start, c->cell_atoms, c->mbins, nown, c->tag, c->xq);
+    else k_cell_sort<false, false><<<nbk, 256, 0, s>>>(c->cell_start, c->cell_atoms, c->mbins, nown, c->tag, c->xq);
+  }
   c->launches += 3;
   CUDA_TRY(cudaGetLastError());
   return B200MD_OK;
