@@ -391,6 +391,10 @@ int b200md_set_lanes_per_atom(b200md_ctx *ctx, int lanes);
  *                                  (auto, the default: the force pass only; on: every pass)
  *   eam_mask     on | off          half list: the density pass marks the list entries inside the force cutoff, the force
  *                                  pass walks only those (default on)
+ *   bin_scale    auto | 0.25..4    neighbor bins of bin_scale x cutneighmax/2 (1 = NBinStandard's size; list membership is
+ *                                  decided by distance, so this is a device-side choice).  auto: 1.2 for cluster rows,
+ *                                  0.6 for per-atom rows of atomic systems, 2 for molecular systems
+ *   cell_order   x | index         order of the atoms inside a bin: ascending x (default) or atom index / tag
  *   phase_timing on | off          per-phase CUDA events in b200md_run (b200md_get_timing)
  *   lanes        1,2,...,32        = b200md_set_lanes_per_atom
  *   build_lanes  1,2,...,32        lanes per atom in the list build
