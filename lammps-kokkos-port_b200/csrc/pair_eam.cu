@@ -477,7 +477,11 @@ static int launch_pass(b200md_ctx *c, const EamLaunch &L, int pass, const int *t
   if (nblocks == 0) return B200MD_OK;
   // shared-memory tables: resident blocks only (grid-stride over the tiles), so the table is staged once per block slot
   // (not on tally steps: the callers reduce one row of partial sums per block of the full grid)
-  if (SMEM && !EV && pass >= 1) nblocks = std::min(nblocks, B200_SMS * (pass == 2 ? EAM_RHO_MINBLOCKS : EAM_FORCE_MINBLOCKS));
+  // Under compute/halo overlap (tile lists) the blocks must retire while the kernel runs: the pack kernels of the halo and
+  // the boundary tiles sit on higher-priority streams and can only take the slots of finished blocks (a resident-blocks-only
+  // grid held every SM until the interior pass ended: the fp halo arrived 280 us late) -> eight rounds of blocks there.
+  if (SMEM && !EV && pass >= 1)
+    nblocks = std::min(nblocks, B200_SMS * (pass == 2 ? EAM_RHO_MINBLOCKS : EAM_FORCE_MINBLOCKS) * (tiles ? 8 : 1));
   if (pass == 0) {
     auto k = k_eam_rho_fp<TPA, EV, ONE, SMEM>;
     if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem));

@@ -22,6 +22,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("workload", choices=["lj", "eam", "c5", "chain"])
 ap.add_argument("--steps", type=int, default=25)
 ap.add_argument("--x", type=int, default=0, help="-var x/y/z (default: 4 for lj/eam/chain, 5 for c5)")
+ap.add_argument("--xyz", default="", help="-var x,y,z separately, e.g. 8,4,4 (weak scaling on 2 ranks)")
 ap.add_argument("--list", default="half", choices=["half", "full"])
 ap.add_argument("--lanes", type=int, default=0)
 ap.add_argument("--langevin", action="store_true")
@@ -52,14 +53,15 @@ if a.phases:
     ctx.set_option("phase_timing", "on")
 lk = B.LIST_FULL if a.list == "full" else B.LIST_HALF_NEWTON
 x = a.x or (5 if a.workload == "c5" else 4)
+x, y, z = [int(v) for v in a.xyz.split(",")] if a.xyz else (x, x, x)
 if a.workload == "lj":
-    cfg = P.inputs.in_lj(ctx, x, x, x, list_kind=lk)
+    cfg = P.inputs.in_lj(ctx, x, y, z, list_kind=lk)
 elif a.workload == "eam":
-    cfg = P.inputs.in_eam(ctx, x, x, x, list_kind=lk)
+    cfg = P.inputs.in_eam(ctx, x, y, z, list_kind=lk)
 elif a.workload == "c5":
-    cfg = P.inputs.in_eam(ctx, x, x, x, style="eam/alloy", list_kind=lk)
+    cfg = P.inputs.in_eam(ctx, x, y, z, style="eam/alloy", list_kind=lk)
 else:
-    cfg = P.inputs.in_chain(ctx, None, x, x, x, list_kind=lk, langevin=a.langevin)
+    cfg = P.inputs.in_chain(ctx, None, x, y, z, list_kind=lk, langevin=a.langevin)
 ctx.setup()
 t0 = ctx.thermo()
 th = ctx.run(a.steps, cfg["dt"], 0)[-1]
