@@ -343,3 +343,66 @@ def test_streamed_offload_boundary_is_the_same_run(pkg):
         for k in range(5):
             assert np.array_equal(res[mode][k], res["sync"][k]), (mode, k)
         assert res[mode][5] == res["sync"][5] == 2
+
+
+@pytest.mark.parametrize("order", ["x", "index"])
+@pytest.mark.parametrize("scale", ["0.5", "0.8", "1.0", "1.7", "3.0"])
+@pytest.mark.parametrize("half", [True, False])
+@pytest.mark.parametrize("name,kind", CASES)
+def test_lists_do_not_depend_on_the_bins(pkg, oracle_mod, name, kind, half, scale, order):
+    """options bin_scale / cell_order: the device picks its own bin size and in-bin order.  Membership is
+    decided by distance and the half rule, so for every bin size — smaller and larger than the reference's
+    cutneighmax/2, i.e. more and fewer stencil rows than NStencil builds — and either order the per-atom lists must
+    stay the reference's exact sets, and forces / thermo over 30 steps (two or more rebuilds) the golden ones."""
+    B = pkg.b200md
+    g = np.load(os.path.join(Cm.GOLDEN, name + ".npz"))
+    ctx, s = make_ctx(pkg, oracle_mod, g, kind, B.LIST_HALF_NEWTON if half else B.LIST_FULL, 2)
+    ctx.set_option("bin_scale", scale)
+    ctx.set_option("cell_order", order)
+    assert float(ctx.get_option("bin_scale")) == float(scale) and ctx.get_option("cell_order") == order
+    ctx.setup()
+    a = ctx.get_atoms()
+    nn, flat = ctx.neigh_export(by_tag=True)
+    if half:
+        want = np.sort(g["half_lo"].astype(np.int64) * (1 << 32) + g["half_hi"].astype(np.int64))
+        assert np.array_equal(Cm.pairs_from_lists(a["tag"], nn, flat), want)
+    else:
+        want = np.sort(g["full_i"].astype(np.int64) * (1 << 32) + g["full_j"].astype(np.int64))
+        assert np.array_equal(Cm.full_sets(a["tag"], nn, flat), want)
+    o = np.argsort(a["tag"])
+    assert np.abs(a["f"][o] - g["f"]).max() <= F_TOL * np.abs(g["f"]).max()
+    for row in g["thermo_series"][:3]:
+        ctx.setup()
+        t = ctx.run(10, s["dt"], 0)[-1]
+        for k, key in enumerate(KEYS):
+            assert abs(t[key] - row[k]) <= T_TOL * abs(row[k]), (key, t[key], row[k])
+    ctx.close()
+
+
+@pytest.mark.parametrize("name,kind", [c for c in CASES if c[1] != "lj"])
+def test_eam_masks_and_shared_tables_change_nothing(pkg, oracle_mod, name, kind):
+    """options eam_mask / eam_smem: the force pass walking only the pairs the density pass found inside the cutoff, and
+    the one-element tables read from (swizzled) shared memory, are the same arithmetic on the same pairs — forces equal
+    to rounding (the RED order differs), thermo over 30 steps equal to the golden run in every combination."""
+    B = pkg.b200md
+    g = np.load(os.path.join(Cm.GOLDEN, name + ".npz"))
+    ref = None
+    for mask in ("on", "off"):
+        for smem in ("auto", "on", "off"):
+            ctx, s = make_ctx(pkg, oracle_mod, g, kind, B.LIST_HALF_NEWTON, 1)
+            ctx.set_option("eam_mask", mask)
+            ctx.set_option("eam_smem", smem)
+            assert ctx.get_option("eam_mask") == mask and ctx.get_option("eam_smem") == smem
+            ctx.setup()
+            a = ctx.get_atoms(("f", "tag"))
+            f = a["f"][np.argsort(a["tag"])]
+            assert np.abs(f - g["f"]).max() <= F_TOL * np.abs(g["f"]).max()
+            if ref is None:
+                ref = f
+            assert np.abs(f - ref).max() <= 1e-13 * np.abs(ref).max()
+            for row in g["thermo_series"][:3]:
+                ctx.setup()
+                t = ctx.run(10, s["dt"], 0)[-1]
+                for k, key in enumerate(KEYS):
+                    assert abs(t[key] - row[k]) <= T_TOL * abs(row[k]), (mask, smem, key, t[key], row[k])
+            ctx.close()
