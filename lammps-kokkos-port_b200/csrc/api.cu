@@ -1233,8 +1233,13 @@ extern "C" int b200md_run(b200md_ctx *c, int nsteps, double dt, int thermo_every
     }
     // Modify::post_force (fix langevin) fused with FixNVE::final_integrate when the thermostat is on
     T.begin(4);
-    if (LG.on) TRY(langevin_post_force(c, true, dtf));
-    else if (c->fuse_nve && !out_step && i + 1 < nsteps) {
+    if (LG.on) {
+      // the thermostat's step counter (ramp, re-sort) moves at the top of the loop: nothing sits between this step's
+      // final_integrate and the next step's initial_integrate on non-output steps
+      const bool next = c->fuse_nve && !out_step && i + 1 < nsteps;
+      TRY(langevin_post_force(c, true, dtf, next, dtv, next && decide_will_check(c) && c->nbuilds > 0));
+      initial_done = next;
+    } else if (c->fuse_nve && !out_step && i + 1 < nsteps) {
       // the distance check belongs to the NEXT step's initial_integrate; ago only moves in decide / build
       TRY(nve_final_initial(c, dtv, dtf, decide_will_check(c) && c->nbuilds > 0));
       initial_done = true;

@@ -374,7 +374,8 @@ int bond_compute(b200md_ctx *c, int eflag, int vflag);
 int langevin_config(b200md_ctx *c, double t_start, double t_stop, double t_period, int seed, const double *ratio, double dt);
 int langevin_set_dt(b200md_ctx *c, double dt);
 int langevin_rank_from_host_order(b200md_ctx *c);
-int langevin_post_force(b200md_ctx *c, bool with_final, double dtf);
+int langevin_post_force(b200md_ctx *c, bool with_final, double dtf, bool with_next = false, double dtv = 0.0,
+                        bool check_dist = false);
 int langevin_resort(b200md_ctx *c);
 int langevin_test_stream(b200md_ctx *c, int seed, int n, int fills, double *out);
 void langevin_free(b200md_ctx *c);

@@ -109,19 +109,25 @@ k_ranmars_fill(uint32_t *__restrict__ chunk_state, const uint32_t *__restrict__ 
 }
 
 // f += gamma1 v + gamma2 (u - 0.5)  [+ FixNVE::final_integrate when FINAL]
-template <bool FINAL>
-__global__ void k_langevin(int n, int nmax, const double4 *__restrict__ xq, double *__restrict__ v,
+// NEXT (with FINAL): FixNVE::initial_integrate of the following step in the same pass, like k_nve_final_initial (nve.cu):
+// both half-kicks use the same thermostatted force, every rounding stays where the separate kernels have it, and the
+// rebuild-distance check of the next step rides along (CHECK).  Only between steps with nothing in between.
+template <bool FINAL, bool NEXT, bool CHECK>
+__global__ void k_langevin(int n, int nmax, double4 *__restrict__ xq, double *__restrict__ v,
                            double *__restrict__ f, const int *__restrict__ tag, const int *__restrict__ rank_by_tag,
                            const uint32_t *__restrict__ rnd, const double *__restrict__ gfac /* [ntypes+1][2] */,
-                           const double *__restrict__ mass, double tsqrt, double dtf) {
+                           const double *__restrict__ mass, double tsqrt, double dtf, double dtv,
+                           const double *__restrict__ xhold, double triggersq, int *__restrict__ flags) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const int type = xq_type(xq[i]);
+  double4 q = xq[i];
+  const int type = xq_type(q);
   const double gamma1 = gfac[2 * type], gamma2 = __dmul_rn(gfac[2 * type + 1], tsqrt);
   const size_t r = (size_t)rank_by_tag[tag[i]] * 3;
   const size_t s = (size_t)nmax;
   double dtfm = 0.0;
   if (FINAL) dtfm = dtf / mass[type];
+  double xn[3] = {q.x, q.y, q.z};
 #pragma unroll
   for (int d = 0; d < 3; d++) {
     const double u = (double)rnd[r + d] * (1.0 / 16777216.0);
@@ -130,7 +136,23 @@ __global__ void k_langevin(int n, int nmax, const double4 *__restrict__ xq, doub
     const double fdrag = __dmul_rn(gamma1, vv);
     const double fn = __dadd_rn(f[i + d * s], __dadd_rn(fdrag, fran));
     f[i + d * s] = fn;
-    if (FINAL) v[i + d * s] = __dadd_rn(vv, __dmul_rn(dtfm, fn));
+    if (FINAL) {
+      const double kick = __dmul_rn(dtfm, fn);
+      double vn = __dadd_rn(vv, kick);
+      if (NEXT) {
+        vn = __dadd_rn(vn, kick);
+        xn[d] = __dadd_rn(xn[d], __dmul_rn(dtv, vn));
+      }
+      v[i + d * s] = vn;
+    }
+  }
+  if (NEXT) {
+    q.x = xn[0]; q.y = xn[1]; q.z = xn[2];
+    xq[i] = q;
+    if (CHECK) {
+      const double dx = q.x - xhold[i], dy = q.y - xhold[i + s], dz = q.z - xhold[i + 2 * s];
+      if (rsq_nofma(dx, dy, dz) > triggersq) flags[0] = 1;
+    }
   }
 }
 
@@ -381,8 +403,8 @@ int langevin_set_dt(b200md_ctx *c, double dt) {
 }
 
 // Modify::post_force -> FixLangevin::post_force at timestep L.now; with_final also does
-// FixNVE::final_integrate in the same pass
-int langevin_post_force(b200md_ctx *c, bool with_final, double dtf) {
+// FixNVE::final_integrate in the same pass; with_next (needs with_final) the next step's initial_integrate, too
+int langevin_post_force(b200md_ctx *c, bool with_final, double dtf, bool with_next, double dtv, bool check_dist) {
   Langevin &L = c->lang;
   const int n = c->nlocal;
   if (n != L.nrank) {
@@ -397,10 +419,13 @@ int langevin_post_force(b200md_ctx *c, bool with_final, double dtf) {
   TRY(ranmars_fill(c, 3 * n));
   if (n == 0) return B200MD_OK;
   const int nb = (n + 255) / 256;
-  if (with_final)
-    k_langevin<true><<<nb, 256, 0, c->stream>>>(n, c->nmax, c->xq, c->v, c->f, c->tag, L.rank_by_tag, L.rnd, L.gfac, c->mass, tsqrt, dtf);
-  else
-    k_langevin<false><<<nb, 256, 0, c->stream>>>(n, c->nmax, c->xq, c->v, c->f, c->tag, L.rank_by_tag, L.rnd, L.gfac, c->mass, tsqrt, dtf);
+#define B200_LANGEVIN(F, N, C)                                                                                              \
+  k_langevin<F, N, C><<<nb, 256, 0, c->stream>>>(n, c->nmax, c->xq, c->v, c->f, c->tag, L.rank_by_tag, L.rnd, L.gfac, c->mass, \
+                                                 tsqrt, dtf, dtv, c->xhold, c->triggersq, c->d_flags)
+  if (with_final && with_next) { if (check_dist) B200_LANGEVIN(true, true, true); else B200_LANGEVIN(true, true, false); }
+  else if (with_final) B200_LANGEVIN(true, false, false);
+  else B200_LANGEVIN(false, false, false);
+#undef B200_LANGEVIN
   CUDA_TRY(cudaGetLastError());
   c->launches++;
   return B200MD_OK;
