@@ -395,6 +395,9 @@ int b200md_set_lanes_per_atom(b200md_ctx *ctx, int lanes);
  *                                  decided by distance, so this is a device-side choice).  auto: 1.2 for cluster rows,
  *                                  0.6 for per-atom rows of atomic systems, 2 for molecular systems
  *   cell_order   x | index         order of the atoms inside a bin: ascending x (default) or atom index / tag
+ *   self_border  direct | staged   one rank: all ghost images of a rebuild in one pass (26 directions), or the
+ *                                  reference's three stages (default direct; staged is used when a side needs
+ *                                  more than one ghost layer)
  *   phase_timing on | off          per-phase CUDA events in b200md_run (b200md_get_timing)
  *   lanes        1,2,...,32        = b200md_set_lanes_per_atom
  *   build_lanes  1,2,...,32        lanes per atom in the list build

@@ -19,7 +19,7 @@ LIB_PATH = os.environ.get("B200MD_LIB", os.path.join(_HERE, "libb200md.so"))
 LIST_FULL, LIST_HALF_NEWTON = 0, 1
 PERATOM_PAIR, PERATOM_BOND = 1, 2
 MAXSWAP = 64
-OPTION_KEYS = ("halo", "overlap", "split", "fuse_nve", "eam_smem", "eam_mask", "bin_scale", "cell_order", "phase_timing", "lanes", "build_lanes", "graph", "cluster", "trace")
+OPTION_KEYS = ("halo", "overlap", "split", "fuse_nve", "eam_smem", "eam_mask", "bin_scale", "cell_order", "self_border", "phase_timing", "lanes", "build_lanes", "graph", "cluster", "trace")
 
 
 class B200MDError(RuntimeError):

@@ -97,6 +97,7 @@ extern "C" int b200md_destroy(b200md_ctx *c) {
     for (cudaEvent_t e : c->ev_dl_part) cudaEventDestroy(e);
   }
   if (c->dl_stage) cudaFree(c->dl_stage);
+  if (c->s26_cnt) { cudaFree(c->s26_cnt); cudaFreeHost(c->s26_hcnt); }
   if (c->sg.exec) cudaGraphExecDestroy(c->sg.exec);
   if (c->sg.graph) cudaGraphDestroy(c->sg.graph);
   if (c->sg.d_loop) cudaFree(c->sg.d_loop);
@@ -673,6 +674,10 @@ extern "C" int b200md_set_option(b200md_ctx *c, const char *key, const char *val
       NEED(opt_bool(value, &b), "Illegal package b200 command: eam_smem must be on, off or auto");
       c->eam_smem = b ? 1 : 0;
     }
+  } else if (k == "self_border") {
+    if (!strcmp(value, "direct")) c->self26 = true;
+    else if (!strcmp(value, "staged")) c->self26 = false;
+    else { b200md_set_error("Illegal package b200 command: self_border must be direct or staged"); return B200MD_ERR; }
   } else if (k == "cell_order") {
     if (!strcmp(value, "x")) c->cell_by_x = true;
     else if (!strcmp(value, "index")) c->cell_by_x = false;
@@ -730,6 +735,7 @@ extern "C" int b200md_get_option(b200md_ctx *c, const char *key, char *value, in
   else if (k == "eam_mask") v = c->eam_mask ? "on" : "off";
   else if (k == "bin_scale") v = c->bin_scale_user > 0 ? std::to_string(c->bin_scale_user) : "auto";
   else if (k == "cell_order") v = c->cell_by_x ? "x" : "index";
+  else if (k == "self_border") v = c->self26 ? "direct" : "staged";
   else if (k == "graph") v = c->sg.mode < 0 ? "auto" : (c->sg.mode ? "on" : "off");
   else if (k == "cluster") v = c->use_cluster < 0 ? "auto" : (c->use_cluster ? "on" : "off");
   else if (k == "phase_timing") v = c->phase_timing ? "on" : "off";

@@ -490,8 +490,200 @@ static int grow_sendlist(Swap &s, int nsend) {
   return B200MD_OK;
 }
 
+// ---------------------------------------------------------------------------------------
+// One rank, one ghost layer per side: all borders in one pass ("self26").  Every swap partner is this rank, so the
+// staged ghost set is the product set over the dimensions of the per-dimension send slabs (halo26.cu's argument): an
+// owned atom has an image in direction (dx,dy,dz) != 0 iff for every non-zero component it lies in that dimension's
+// slab.  Three kernels and ONE host sync per rebuild instead of the staged 9 selection kernels + 6 copies + 3 syncs:
+// count per (direction, tile), scan per direction, fill.  Ghost order: direction-major, ascending owner index inside a
+// direction (deterministic).  Image position = x + pbc*prd, one addition per crossed dimension (AtomVec::pack_border).
+// ---------------------------------------------------------------------------------------
+#define S26_T 256
+#define S26_ITEMS 4
+#define S26_TILE (S26_T * S26_ITEMS)
+struct S26Geom {
+  double lhi[3], rlo[3];     // left swap: x <= lhi; right swap: x >= rlo (first swap of a dimension: one-sided)
+  double llo[3], rhi[3];
+  int useL[3], useR[3];
+  int pbcL[3], pbcR[3];      // periodic shift multiple applied by that swap in its own dimension
+};
+__device__ __forceinline__ unsigned s26_dirs(const double4 q, const S26Geom &G) {
+  bool L[3], R[3];
+  const double x[3] = {q.x, q.y, q.z};
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    L[k] = G.useL[k] && x[k] >= G.llo[k] && x[k] <= G.lhi[k];
+    R[k] = G.useR[k] && x[k] >= G.rlo[k] && x[k] <= G.rhi[k];
+  }
+  unsigned m = 0;
+#pragma unroll
+  for (int d = 0; d < 27; d++) {
+    if (d == 13) continue;
+    const int c0 = d % 3 - 1, c1 = (d / 3) % 3 - 1, c2 = d / 9 - 1;
+    const bool ok = (c0 == 0 || (c0 < 0 ? L[0] : R[0])) && (c1 == 0 || (c1 < 0 ? L[1] : R[1])) && (c2 == 0 || (c2 < 0 ? L[2] : R[2]));
+    m |= (ok ? 1u : 0u) << d;
+  }
+  return m;
+}
+__global__ void __launch_bounds__(S26_T) k_s26_count(const double4 *__restrict__ xq, int n, S26Geom G, int *__restrict__ tile_cnt,
+                                                     int ntiles) {
+  __shared__ int s_cnt[27];
+  if (threadIdx.x < 27) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const int base = blockIdx.x * S26_TILE;
+#pragma unroll
+  for (int it = 0; it < S26_ITEMS; it++) {
+    const int i = base + it * S26_T + threadIdx.x;
+    unsigned m = i < n ? s26_dirs(xq[i], G) : 0u;
+    if (__any_sync(0xffffffffu, m != 0)) {
+      for (int d = 0; d < 27; d++) {
+        const unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
+        if (b && (threadIdx.x & 31) == 0) atomicAdd(&s_cnt[d], __popc(b));
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 27) tile_cnt[threadIdx.x * ntiles + blockIdx.x] = s_cnt[threadIdx.x];
+}
+// one block per direction: exclusive scan of its tile counts in place, total to totals[d]
+__global__ void __launch_bounds__(S26_T) k_s26_offsets(int *tile_cnt, int ntiles, int *totals) {
+  __shared__ int s_warp[33];
+  int *t = tile_cnt + blockIdx.x * ntiles;
+  int carry = 0;
+  for (int base = 0; base < ntiles; base += S26_T) {
+    const int i = base + threadIdx.x;
+    const int v = i < ntiles ? t[i] : 0;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+      int w = lane < S26_T / 32 ? s_warp[lane] : 0, winc = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += y; }
+      s_warp[lane] = winc - w;
+      if (lane == 31) s_warp[32] = winc;
+    }
+    __syncthreads();
+    if (i < ntiles) t[i] = carry + s_warp[wid] + inc - v;
+    carry += s_warp[32];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) totals[blockIdx.x] = carry;
+}
+struct S26Base { int v[27]; };
+__global__ void __launch_bounds__(S26_T) k_s26_fill(double4 *__restrict__ xq, int *__restrict__ tag, int n, S26Geom G,
+                                                    const int *__restrict__ tile_off, int ntiles, S26Base first,
+                                                    int *__restrict__ ghost_src, int *__restrict__ ghost_pbc, double prdx,
+                                                    double prdy, double prdz) {
+  // per direction, per (item, warp): how many images come before -> ascending owner index inside the tile
+  __shared__ int s_cnt[27][S26_ITEMS * (S26_T / 32)];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int base = blockIdx.x * S26_TILE;
+  unsigned m[S26_ITEMS];
+  for (int k = threadIdx.x; k < 27 * S26_ITEMS * (S26_T / 32); k += S26_T) (&s_cnt[0][0])[k] = 0;
+  __syncthreads();
+  bool any_tile = false;
+#pragma unroll
+  for (int it = 0; it < S26_ITEMS; it++) {
+    const int i = base + it * S26_T + threadIdx.x;
+    m[it] = i < n ? s26_dirs(xq[i], G) : 0u;
+    if (__any_sync(0xffffffffu, m[it] != 0)) {
+      any_tile = true;
+      for (int d = 0; d < 27; d++) {
+        const unsigned b = __ballot_sync(0xffffffffu, (m[it] >> d) & 1u);
+        if (b && lane == 0) s_cnt[d][it * (S26_T / 32) + wid] = __popc(b);
+      }
+    }
+  }
+  if (!__syncthreads_or(any_tile)) return;
+  if (threadIdx.x < 27) {   // exclusive scan over the (item, warp) slots of one direction
+    int run = 0;
+    for (int k = 0; k < S26_ITEMS * (S26_T / 32); k++) { const int v = s_cnt[threadIdx.x][k]; s_cnt[threadIdx.x][k] = run; run += v; }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int it = 0; it < S26_ITEMS; it++) {
+    if (!__any_sync(0xffffffffu, m[it] != 0)) continue;
+    const int i = base + it * S26_T + threadIdx.x;
+    const double4 q = i < n ? xq[i] : make_double4(0, 0, 0, 0);
+    for (int d = 0; d < 27; d++) {
+      const unsigned b = __ballot_sync(0xffffffffu, (m[it] >> d) & 1u);
+      if (!((m[it] >> d) & 1u)) continue;
+      const int slot = first.v[d] + tile_off[d * ntiles + blockIdx.x] + s_cnt[d][it * (S26_T / 32) + wid] + __popc(b & ((1u << lane) - 1u));
+      const int c0 = d % 3 - 1, c1 = (d / 3) % 3 - 1, c2 = d / 9 - 1;
+      const int px = c0 < 0 ? G.pbcL[0] : (c0 > 0 ? G.pbcR[0] : 0);
+      const int py = c1 < 0 ? G.pbcL[1] : (c1 > 0 ? G.pbcR[1] : 0);
+      const int pz = c2 < 0 ? G.pbcL[2] : (c2 > 0 ? G.pbcR[2] : 0);
+      double4 g = q;
+      g.x = shift_n(q.x, px, prdx); g.y = shift_n(q.y, py, prdy); g.z = shift_n(q.z, pz, prdz);
+      xq[slot] = g;
+      tag[slot] = tag[i];
+      ghost_src[slot] = i;
+      ghost_pbc[slot] = pbc_code_add(PBC_ZERO, px, py, pz);
+    }
+  }
+}
+
+static bool self26_usable(const b200md_ctx *c) {
+  if (c->nranks != 1 || !c->self26) return false;
+  for (int d = 0; d < 3; d++) if (c->sched.maxneed[d] > 1) return false;
+  for (auto &s : c->swaps) if (s.sendproc != c->rank || s.recvproc != c->rank) return false;
+  return true;
+}
+
+static int comm_borders_self26(b200md_ctx *c) {
+  cudaStream_t st = c->stream;
+  const int n = c->nlocal;
+  c->nghost = 0;
+  c->all_self = true;
+  c->direct.ready = false;
+  for (auto &s : c->swaps) { s.sendnum = 0; s.recvnum = 0; s.firstrecv = n; }
+  S26Geom G;
+  int iswap = 0;
+  for (int dim = 0; dim < 3; dim++) {
+    G.useL[dim] = G.useR[dim] = 0; G.pbcL[dim] = G.pbcR[dim] = 0;
+    G.llo[dim] = G.rlo[dim] = 0; G.lhi[dim] = G.rhi[dim] = 0;
+    if (c->sched.maxneed[dim] == 1) {
+      const Swap &a = c->swaps[iswap], &b = c->swaps[iswap + 1];
+      G.useL[dim] = a.sendflag ? 1 : 0; G.llo[dim] = a.slablo; G.lhi[dim] = a.slabhi; G.pbcL[dim] = a.pbc[dim];
+      G.useR[dim] = b.sendflag ? 1 : 0; G.rlo[dim] = b.slablo; G.rhi[dim] = b.slabhi; G.pbcR[dim] = b.pbc[dim];
+      iswap += 2;
+    }
+  }
+  if (n == 0) return B200MD_OK;
+  const int ntiles = (n + S26_TILE - 1) / S26_TILE;
+  if (27 * ntiles + 64 > c->scan_cap) {
+    if (c->scan_block) CUDA_TRY(cudaFree(c->scan_block));
+    c->scan_cap = 27 * ntiles + 1024;
+    CUDA_TRY(cudaMalloc(&c->scan_block, sizeof(int) * c->scan_cap));
+  }
+  if (!c->s26_cnt) {
+    CUDA_TRY(cudaMalloc(&c->s26_cnt, 32 * sizeof(int)));
+    CUDA_TRY(cudaMallocHost(&c->s26_hcnt, 32 * sizeof(int)));
+  }
+  k_s26_count<<<ntiles, S26_T, 0, st>>>(c->xq, n, G, c->scan_block, ntiles);
+  k_s26_offsets<<<27, S26_T, 0, st>>>(c->scan_block, ntiles, c->s26_cnt);
+  CUDA_TRY(cudaMemcpyAsync(c->s26_hcnt, c->s26_cnt, 27 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  S26Base first;
+  int tot = 0;
+  for (int d = 0; d < 27; d++) { first.v[d] = n + tot; tot += (d == 13) ? 0 : c->s26_hcnt[d]; }
+  if (n + tot + 1 > c->nmax) TRY(neigh_grow_atoms(c, n + tot + 1));
+  if (tot)
+    k_s26_fill<<<ntiles, S26_T, 0, st>>>(c->xq, c->tag, n, G, c->scan_block, ntiles, first, c->ghost_src, c->ghost_pbc, c->prd[0],
+                                         c->prd[1], c->prd[2]);
+  c->launches += 3;
+  CUDA_TRY(cudaGetLastError());
+  c->nghost = tot;
+  return B200MD_OK;
+}
+
 int comm_borders(b200md_ctx *c) {
   if (c->h26.on) return h26_borders(c);
+  if (self26_usable(c)) return comm_borders_self26(c);
   cudaStream_t st = c->stream;
   c->nghost = 0;
   c->all_self = true;

@@ -263,6 +263,8 @@ struct b200md_ctx {
   StepGraph sg;
   int halo_mode = 2;              // option halo: 0 staged, 1 owner (staged borders that track owners), 2 direct (halo26.cu)
   bool all_self = true;           // every swap partner is this rank -> flattened forward path
+  bool self26 = true;             // option self_border: one rank, one ghost layer: all borders in one pass (comm.cu)
+  int *s26_cnt = nullptr, *s26_hcnt = nullptr;   // its per-direction totals (device / pinned host)
   double *sendbuf = nullptr, *recvbuf = nullptr;
   size_t sendcap = 0, recvcap = 0;
   // pair
