@@ -406,3 +406,39 @@ def test_eam_masks_and_shared_tables_change_nothing(pkg, oracle_mod, name, kind)
                 for k, key in enumerate(KEYS):
                     assert abs(t[key] - row[k]) <= T_TOL * abs(row[k]), (mask, smem, key, t[key], row[k])
             ctx.close()
+
+
+@pytest.mark.parametrize("mode", ["direct", "staged"])
+@pytest.mark.parametrize("half", [True, False])
+@pytest.mark.parametrize("name,kind", CASES)
+def test_one_rank_border_modes(pkg, oracle_mod, name, kind, half, mode):
+    """option self_border: the one-pass 26-direction ghost images (default) and the reference's three stages
+    (CommBrick::borders, comm_brick.cpp:771-979) must produce the same ghost SET — same number of ghosts, same multiset
+    of (tag, position) — and with it the reference's exact lists, forces and thermo."""
+    B = pkg.b200md
+    g = np.load(os.path.join(Cm.GOLDEN, name + ".npz"))
+    res = {}
+    for m in (mode, "staged"):
+        ctx, s = make_ctx(pkg, oracle_mod, g, kind, B.LIST_HALF_NEWTON if half else B.LIST_FULL, 2)
+        ctx.set_option("self_border", m)
+        assert ctx.get_option("self_border") == m
+        ctx.setup()
+        gh = ctx.get_ghosts()
+        key = np.lexsort((gh["x"][:, 2], gh["x"][:, 1], gh["x"][:, 0], gh["tag"]))
+        a = ctx.get_atoms()
+        nn, flat = ctx.neigh_export(by_tag=True)
+        sets = Cm.pairs_from_lists(a["tag"], nn, flat) if half else Cm.full_sets(a["tag"], nn, flat)
+        th = []
+        for row in g["thermo_series"][:2]:
+            ctx.setup()
+            th.append(ctx.run(10, s["dt"], 0)[-1])
+        res[m] = (gh["tag"][key], gh["x"][key], sets, a["f"][np.argsort(a["tag"])], th)
+        ctx.close()
+    want = (np.sort(g["half_lo"].astype(np.int64) * (1 << 32) + g["half_hi"].astype(np.int64)) if half
+            else np.sort(g["full_i"].astype(np.int64) * (1 << 32) + g["full_j"].astype(np.int64)))
+    assert np.array_equal(res[mode][2], want)
+    assert np.array_equal(res[mode][0], res["staged"][0]) and np.array_equal(res[mode][1], res["staged"][1])
+    assert np.abs(res[mode][3] - g["f"]).max() <= F_TOL * np.abs(g["f"]).max()
+    for t, row in zip(res[mode][4], g["thermo_series"][:2]):
+        for k, key_ in enumerate(KEYS):
+            assert abs(t[key_] - row[k]) <= T_TOL * abs(row[k]), (key_, t[key_], row[k])
