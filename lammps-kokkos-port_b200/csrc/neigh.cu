@@ -484,7 +484,9 @@ int neigh_save_xhold(b200md_ctx *c) {
 // ---------------------------------------------------------------------------------------
 // neighbor list build
 // ---------------------------------------------------------------------------------------
+#ifndef BUILD_THREADS
 #define BUILD_THREADS 128
+#endif
 #define MAX_ROWS 128
 #define MAX_TYPES_SMEM 8
 

@@ -37,6 +37,12 @@
 #ifndef EAM_RHO_MINBLOCKS
 #define EAM_RHO_MINBLOCKS 8
 #endif
+// block size of the half-list density pass (it shares nothing between warps unless its table is staged): 2048 threads per
+// SM as blocks of EAM_RHO_THREADS
+#ifndef EAM_RHO_THREADS
+#define EAM_RHO_THREADS 256
+#endif
+#define EAM_RHO_HALF_MINBLOCKS ((EAM_RHO_MINBLOCKS * 256 / EAM_RHO_THREADS) > 32 ? 32 : (EAM_RHO_MINBLOCKS * 256 / EAM_RHO_THREADS))
 #ifndef EAM_FORCE_UNROLL
 #define EAM_FORCE_UNROLL 2
 #endif
@@ -196,7 +202,7 @@ k_eam_rho_fp(int nlocal, const double4 *__restrict__ xq, const int *__restrict__
 // MASK: every lane records which of its list entries were inside the force cutoff (bit `it` of a 128-bit mask per
 // lane); positions do not change before the force pass of the same step, which then walks the set bits only.
 template <int TPA, bool ONE, bool SMEM, bool MASK>
-__global__ void __launch_bounds__(EAM_THREADS, ONE ? EAM_RHO_MINBLOCKS : 4)
+__global__ void __launch_bounds__(EAM_RHO_THREADS, ONE ? EAM_RHO_HALF_MINBLOCKS : (1024 / EAM_RHO_THREADS))
 k_eam_rho_half(int nlocal, const double4 *__restrict__ xq, const int *__restrict__ neigh,
                const int *__restrict__ numneigh, int pitch, EamParams P, double *__restrict__ rho,
                const int *__restrict__ tile_list, int ntile_list, unsigned *__restrict__ pmask) {
@@ -495,7 +501,8 @@ static int launch_pass(b200md_ctx *c, const EamLaunch &L, int pass, const int *t
   } else if (pass == 2) {   // half list, density of both atoms of a pair
     auto k = L.mask ? k_eam_rho_half<TPA, ONE, SMEM, true> : k_eam_rho_half<TPA, ONE, SMEM, false>;
     if (SMEM) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(L.smem / 2)));
-    k<<<nblocks, EAM_THREADS, SMEM ? L.smem / 2 : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, L.P, c->rho,
+    if (!SMEM) nblocks = (ntiles + EAM_RHO_THREADS / 32 - 1) / (EAM_RHO_THREADS / 32);   // this pass writes no per-block partial sums
+    k<<<nblocks, EAM_RHO_THREADS, SMEM ? L.smem / 2 : 0, c->stream>>>(c->nlocal, c->xq, c->neigh, c->numneigh, c->pitch, L.P, c->rho,
                                                                 tiles, ntl, c->eam.pmask);
   } else {                  // half list, forces
     auto k = L.mask ? k_eam_force<TPA, EV, ONE, SMEM, true, true> : k_eam_force<TPA, EV, ONE, SMEM, true, false>;

@@ -132,11 +132,18 @@ static void launch_lj(b200md_ctx *c, int nblocks, bool ev, const LJOne &one, con
 // its 4-bit mask names, and (half list) returns the summed f_j with ONE RED triple.  Against the per-atom
 // list this cuts the gathers and REDs per atom ~2.2x (the L1 data pipe is what binds these kernels) at
 // the price of distance tests on masked-out slots (FP64 pipe was at 26 %).
+// 512 threads per SM (117 registers) as blocks of LJ_CL_THREADS: measured at 2.05 M atoms, pair time 0.406 ms with 2 blocks
+// of 256 threads, 0.390 with 4 x 128, 0.372 with 8 x 64, 0.364 with 16 x 32.  The warps of a block share nothing (the
+// one-type constants are kernel arguments), but a block's registers stay allocated until its slowest warp has walked its
+// clusters' lists: one warp per block returns every slot as soon as its own work ends.
+#ifndef LJ_CL_THREADS
+#define LJ_CL_THREADS 32
+#endif
 #ifndef LJ_CL_MINBLOCKS
-#define LJ_CL_MINBLOCKS 2
+#define LJ_CL_MINBLOCKS (512 / LJ_CL_THREADS)
 #endif
 template <int L, bool EV, bool HALF, bool ONETYPE>
-__global__ void __launch_bounds__(PAIR_THREADS, EV ? 2 : LJ_CL_MINBLOCKS)
+__global__ void __launch_bounds__(LJ_CL_THREADS, LJ_CL_MINBLOCKS)
 k_lj_cl(int nlocal, int ncl, int nmax, const double4 *__restrict__ xq, const int *__restrict__ neigh,
         const int *__restrict__ numneigh, int pitch, LJOne one, const double *__restrict__ ljtab, int ntypes,
         double *__restrict__ f, double *__restrict__ partials, const int *__restrict__ tile_list, int ntile_list) {
@@ -246,10 +253,10 @@ template <int L, bool EV, bool HALF>
 static void launch_lj_cl2(b200md_ctx *c, int nblocks, const LJOne &one, const int *tiles, int ntl) {
   const int ncl = list_units(c);
   if (c->ntypes == 1)
-    k_lj_cl<L, EV, HALF, true><<<nblocks, PAIR_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->nmax, c->xq, c->neigh, c->numneigh,
+    k_lj_cl<L, EV, HALF, true><<<nblocks, LJ_CL_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->nmax, c->xq, c->neigh, c->numneigh,
                                                                       c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials, tiles, ntl);
   else
-    k_lj_cl<L, EV, HALF, false><<<nblocks, PAIR_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->nmax, c->xq, c->neigh, c->numneigh,
+    k_lj_cl<L, EV, HALF, false><<<nblocks, LJ_CL_THREADS, 0, c->stream>>>(c->nlocal, ncl, c->nmax, c->xq, c->neigh, c->numneigh,
                                                                        c->pitch, one, c->ljtab, c->ntypes, c->f, c->partials, tiles, ntl);
 }
 template <int L>
@@ -262,7 +269,8 @@ static void launch_lj_cl(b200md_ctx *c, int nblocks, bool ev, const LJOne &one, 
 // one launch over all tiles (tiles == nullptr) or over a tile list (interior / boundary split)
 int pair_lj_launch(b200md_ctx *c, bool ev, const int *tiles, int ntl) {
   const int ntiles = tiles ? ntl : list_tiles(c);
-  const int nblocks = (ntiles + PAIR_THREADS / 32 - 1) / (PAIR_THREADS / 32);
+  const int tpb = (c->cluster ? LJ_CL_THREADS : PAIR_THREADS) / 32;   // tiles (warps) per block
+  const int nblocks = (ntiles + tpb - 1) / tpb;
   if (nblocks == 0) return B200MD_OK;
   LJOne one = {0, 0, 0, 0, 0, 0};
   if (c->ntypes == 1) {
@@ -297,7 +305,8 @@ int pair_lj_compute(b200md_ctx *c, int eflag, int vflag) {
   if (c->ntypes > LJ_MAX_TYPES_SMEM) { b200md_set_error("b200md: lj/cut supports at most 8 atom types"); return B200MD_ERR; }
   const bool ev = eflag || vflag;
   const int ntiles = list_tiles(c);
-  const int nblocks = (ntiles + PAIR_THREADS / 32 - 1) / (PAIR_THREADS / 32);
+  const int tpb = (c->cluster ? LJ_CL_THREADS : PAIR_THREADS) / 32;
+  const int nblocks = (ntiles + tpb - 1) / tpb;
   const bool half = c->list_kind == B200MD_LIST_HALF_NEWTON;
   if (half && c->nlocal + c->nghost > 0)  // Verlet::force_clear over owned + ghost (src/verlet.cpp:376-421): 3 rows, one launch
     CUDA_TRY(cudaMemset2DAsync(c->f, sizeof(double) * (size_t)c->nmax, 0, sizeof(double) * (c->nlocal + c->nghost), 3, c->stream));
