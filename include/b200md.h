@@ -399,6 +399,7 @@ int b200md_set_lanes_per_atom(b200md_ctx *ctx, int lanes);
  *                                  reference's three stages (default direct; staged is used when a side needs
  *                                  more than one ghost layer)
  *   phase_timing on | off          per-phase CUDA events in b200md_run (b200md_get_timing)
+ *   trace        on | off          timestamps of both streams' milestones of an overlapped step on stderr (development)
  *   lanes        1,2,...,32        = b200md_set_lanes_per_atom
  *   build_lanes  1,2,...,32        lanes per atom in the list build
  *   cluster      on | off | auto   cluster-pair neighbor list for atomic systems: 4 consecutive atoms of the bin-sorted

@@ -41,3 +41,18 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cpp", ".h", ".cuh")):
                 src = open(os.path.join(dp, f)).read()
                 assert "md_oracle" not in src and "from oracle" not in src and "import oracle" not in src, f
+
+
+def test_every_option_is_documented(pkg):
+    """the runtime options are the library's whole tuning surface (no environment variables): every keyword the Python
+    mirror knows must be in the header's keyword table and in INTEGRATION.md's option table, and the other way round"""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "b200md.h")).read()
+    integ = open(os.path.join(root, "INTEGRATION.md")).read()
+    table = header[header.index("Keywords (value as text)"):header.index("int b200md_set_option")]
+    in_header = set(re.findall(r"^ \*   (\w+) ", table, re.M))
+    in_integ = set(re.findall(r"^\| `(\w+)` \|", integ[integ.index("## 7. Runtime options"):], re.M))
+    keys = set(pkg.b200md.OPTION_KEYS)
+    assert keys == in_header, (keys - in_header, in_header - keys)
+    assert keys == in_integ, (keys - in_integ, in_integ - keys)
