@@ -133,3 +133,68 @@ def test_eam_tables_shapes(pkg, oracle_mod):
     # interpolate(): derivative rows are the value cubic's coefficients over delta (pair_eam.cpp:792-796)
     assert np.allclose(sp[1:, 2], sp[1:, 5] * tb["rdr"], rtol=1e-15)
     assert np.allclose(sp[1:, 0], 3 * sp[1:, 3] * tb["rdr"], rtol=1e-15)
+
+
+@pytest.mark.parametrize("periodic", [(1, 1, 1), (1, 0, 1)])
+def test_one_rank_product_set_is_the_staged_ghost_set(pkg, periodic):
+    """csrc/comm.cu comm_borders_self26: on one rank the ghosts of CommBrick::borders (comm_brick.cpp:771-979, three
+    stages, each forwarding the ghosts of the stages before it) are the product set over the dimensions of the
+    per-dimension send slabs — an owned atom has an image in direction (dx,dy,dz) != 0 iff it lies in the slab of
+    every non-zero component — with the same positions bit for bit (one addition of pbc*prd per crossed dimension,
+    AtomVec::pack_border).  Both restated in numpy on the library's own swap schedule."""
+    B = pkg.b200md
+    rng = np.random.default_rng(7)
+    boxlo, boxhi = [0.0, -3.0, 1.0], [21.0, 17.5, 24.0]
+    prd = np.array(boxhi) - np.array(boxlo)
+    cut = 5.95
+    n = 4000
+    x = np.array(boxlo) + rng.random((n, 3)) * prd
+    tag = np.arange(1, n + 1)
+    s = B.comm_schedule(boxlo, boxhi, list(periodic), [1, 1, 1], [0, 0, 0], cut)
+    assert max(s.maxneed) <= 1
+    # staged
+    X, T = x.copy(), tag.copy()
+    iswap = 0
+    for dim in range(3):
+        nlast = 0
+        for ineed in range(2 * s.maxneed[dim]):
+            if ineed % 2 == 0:
+                nfirst, nlast = nlast, len(T)
+            sel = (np.nonzero((X[nfirst:nlast, dim] >= s.slablo[iswap]) & (X[nfirst:nlast, dim] <= s.slabhi[iswap]))[0] + nfirst
+                   if s.sendflag[iswap] else np.empty(0, np.int64))
+            buf = X[sel].copy()
+            for d in range(3):
+                if s.pbc[iswap][d]:
+                    buf[:, d] = buf[:, d] + s.pbc[iswap][d] * prd[d]
+            X = np.concatenate([X, buf]); T = np.concatenate([T, T[sel]])
+            iswap += 1
+    staged = sorted(zip(T[n:].tolist(), map(tuple, X[n:].tolist())))
+    # product set
+    L, R, pL, pR = [None] * 3, [None] * 3, [0] * 3, [0] * 3
+    iswap = 0
+    for dim in range(3):
+        L[dim] = np.zeros(n, bool); R[dim] = np.zeros(n, bool)
+        if s.maxneed[dim] == 1:
+            if s.sendflag[iswap]:
+                L[dim] = (x[:, dim] >= s.slablo[iswap]) & (x[:, dim] <= s.slabhi[iswap]); pL[dim] = s.pbc[iswap][dim]
+            if s.sendflag[iswap + 1]:
+                R[dim] = (x[:, dim] >= s.slablo[iswap + 1]) & (x[:, dim] <= s.slabhi[iswap + 1]); pR[dim] = s.pbc[iswap + 1][dim]
+            iswap += 2
+    prod = []
+    for dz in (-1, 0, 1):
+        for dy in (-1, 0, 1):
+            for dx in (-1, 0, 1):
+                comp = (dx, dy, dz)
+                if comp == (0, 0, 0):
+                    continue
+                ok = np.ones(n, bool)
+                for k in range(3):
+                    if comp[k] < 0: ok &= L[k]
+                    elif comp[k] > 0: ok &= R[k]
+                img = x[ok].copy()
+                for k in range(3):
+                    p = pL[k] if comp[k] < 0 else (pR[k] if comp[k] > 0 else 0)
+                    if p:
+                        img[:, k] = img[:, k] + p * prd[k]
+                prod += list(zip(tag[ok].tolist(), map(tuple, img.tolist())))
+    assert len(staged) > 0 and sorted(prod) == staged
