@@ -22,7 +22,7 @@ void pair_eam_free(b200md_ctx *c);
 static thread_local std::string g_error;
 void b200md_set_error(const std::string &msg) { g_error = msg; }
 extern "C" const char *b200md_last_error(void) { return g_error.c_str(); }
-extern "C" const char *b200md_version(void) { return "b200md 0.1 (sm_100a)"; }
+extern "C" const char *b200md_version(void) { return "b200md 0.2 (sm_100a)"; }
 
 #define NEED(cond, msg) do { if (!(cond)) { b200md_set_error(msg); return B200MD_ERR; } } while (0)
 
